@@ -1,0 +1,133 @@
+/* ipoke_inn.h -- C ABI of the B200-native flat-INN hot path (libipoke_inn.so).
+ *
+ * Drop-in boundary underneath the reference's nn.Module interface
+ * (reference: models/modules/INN/INN.py:19-88 SupervisedTransformer, :250-296
+ * UnsupervisedTransformer3; models/modules/INN/flow_blocks.py:10-66 ConditionalFlow,
+ * :432-465 UnconditionalFlow2).  The reference has no FFI of its own for this path:
+ * every entry point below replaces a span of eager PyTorch ops, cited per function.
+ *
+ * Conventions
+ *   - plain C types only; every pointer is a DEVICE pointer unless the name ends in
+ *     _host or the comment says "host array";
+ *   - tensors are fp32, row-major, contiguous: x/z [B,C], cond [B,E], logdet [B];
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*),
+ *     allocates nothing on the device and never synchronises the host;
+ *   - return value: 0 = ok, < 0 = IPOKE_INN_E_*, > 0 = a cudaError_t value;
+ *     ipoke_inn_last_error_string() decodes both.  Nothing throws or aborts.
+ *   - a plan is immutable after creation and may be shared by streams of one device.
+ */
+#ifndef IPOKE_INN_H_
+#define IPOKE_INN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IPOKE_INN_VERSION 100 /* major*100 + minor */
+
+enum {
+  IPOKE_INN_OK = 0,
+  IPOKE_INN_E_INVALID = -1,     /* bad argument (null pointer, B <= 0, bad block range ...) */
+  IPOKE_INN_E_UNSUPPORTED = -2, /* shape outside what the kernels cover (odd C, E > 0 unconditional ...) */
+  IPOKE_INN_E_NO_DEVICE = -3,   /* no sm_100 device / driver entry point missing */
+  IPOKE_INN_E_INTERNAL = -4
+};
+
+enum { IPOKE_INN_PREC_FP32_SPLIT = 0, /* bf16 hi+lo operands, 3 MMAs per k-step: <= 1e-4 vs fp32 */
+       IPOKE_INN_PREC_BF16 = 1 };     /* single bf16 pass: stated looser bound */
+
+/* Architecture of one flow stack.  conditional=1: ConditionalFlow (flow_blocks.py:10-35: blocks
+ * alternate 'cond'/'normal' couplings, InvLeakyRelu(alpha) after ActNorm); conditional=0:
+ * UnconditionalFlow2 (flow_blocks.py:432-446, no activation, E must be 0).
+ * Subnetworks: BasicFullyConnectedNet (modules.py:165-191) with `depth` hidden HxH layers. */
+typedef struct ipoke_inn_desc {
+  int32_t C;           /* flow_in_channels (even)                                  INN.py:26  */
+  int32_t E;           /* flow_embedding_channels (conditioning width), 0 if none  INN.py:31  */
+  int32_t H;           /* hidden width (mid_channels)                              INN.py:27  */
+  int32_t depth;       /* flow_hidden_depth                                        INN.py:28  */
+  int32_t n_flows;     /* number of flow blocks                                    INN.py:29  */
+  int32_t conditional; /* 1 = ConditionalFlow, 0 = UnconditionalFlow2                         */
+  int32_t precision;   /* IPOKE_INN_PREC_*                                                    */
+  float alpha;         /* InvLeakyRelu slope (0.9)                       flow_blocks.py:373   */
+  float mlp_slope;     /* nn.LeakyReLU slope inside the subnetworks (0.01)   modules.py:174   */
+} ipoke_inn_desc;
+
+typedef struct ipoke_inn_plan ipoke_inn_plan; /* opaque, host side */
+
+int ipoke_inn_version(void);
+const char* ipoke_inn_last_error_string(int code);
+
+/* Build the launch plan (tile shapes, packed-weight layout) for one architecture on `device`. */
+int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan** out);
+void ipoke_inn_plan_destroy(ipoke_inn_plan* plan);
+
+/* Bytes of the packed parameter buffer / of the scratch workspace for batch B.
+ * mode 0 = forward/reverse only, 1 = also keeps what ipoke_inn_backward needs. */
+size_t ipoke_inn_packed_bytes(const ipoke_inn_plan* plan);
+size_t ipoke_inn_workspace_bytes(const ipoke_inn_plan* plan, int B, int mode);
+/* Number of nn.Linear layers the plan expects, = n_flows * 2 * 2 * (depth + 2). */
+int ipoke_inn_num_linears(const ipoke_inn_plan* plan);
+
+/* Repack module parameters into the kernel layout (bf16 hi/lo, s|t stacked, K padded, transposed copies
+ * for dgrad), gather ActNorm loc/scale, pre-compute sum(log|scale|) and the int32 gather maps of every
+ * Shuffle.  Replaces nothing in the reference (its weights are used in place by cuBLAS addmm); call once
+ * after construction / load_state_dict and after every optimizer step.
+ *   linear_w / linear_b : host arrays [num_linears] of device pointers, ordered
+ *                         (block, half-step i, net s|t, layer)  -- sub_layers[k].coupling.{s,t}[i].main[2*l]
+ *   an_loc / an_scale   : host arrays [n_flows] of device pointers to ActNorm.loc / .scale (C floats each)
+ *   perm_fwd / perm_bwd : host arrays [n_flows] of device pointers to Shuffle.forward_shuffle_idx /
+ *                         backward_shuffle_idx (int64[C], flow_blocks.py:318-320)                     */
+int ipoke_inn_pack(const ipoke_inn_plan* plan, const float* const* linear_w, const float* const* linear_b,
+                   const float* const* an_loc, const float* const* an_scale, const int64_t* const* perm_fwd,
+                   const int64_t* const* perm_bwd, void* packed, void* stream);
+
+/* Forward (z, logdet) over blocks [block_begin, block_end).  Replaces ConditionalFlow.forward
+ * (flow_blocks.py:37-57) / UnconditionalFlow2.forward (:448-459) including every block's
+ * ActNorm -> InvLeakyRelu -> double coupling -> Shuffle (flow_blocks.py:255-267, 513-523).
+ *   cond         : [B,E] or NULL when E == 0
+ *   block_outs   : nullable [block_end-block_begin, B, C]  = flow.last_outs
+ *   block_logdets: nullable [block_end-block_begin, B]     = flow.last_logdets (cumulative)
+ *   x is never written; z may not alias x.                                                  */
+int ipoke_inn_forward(ipoke_inn_plan* plan, const void* packed, const float* x, const float* cond, float* z,
+                      float* logdet, float* block_outs, float* block_logdets, int B, int block_begin,
+                      int block_end, void* workspace, void* stream);
+
+/* Reverse (sampling) over blocks [block_begin, block_end), last block first.  Replaces
+ * ConditionalFlow.forward(reverse=True) (flow_blocks.py:58-63) / UnconditionalFlow2 (:460-462). */
+int ipoke_inn_reverse(ipoke_inn_plan* plan, const void* packed, const float* z, const float* cond, float* x,
+                      int B, int block_begin, int block_end, void* workspace, void* stream);
+
+/* Same two calls with HOST buffers (pinned or pageable): host->device copies of x/cond, the kernels, and
+ * device->host copies of the results are all enqueued on `stream`; the caller synchronises the stream. */
+int ipoke_inn_forward_host(ipoke_inn_plan* plan, const void* packed, const float* x_host, const float* cond_host,
+                           float* z_host, float* logdet_host, int B, void* workspace, void* stream);
+int ipoke_inn_reverse_host(ipoke_inn_plan* plan, const void* packed, const float* z_host, const float* cond_host,
+                           float* x_host, int B, void* workspace, void* stream);
+
+/* ActNorm data-dependent initialisation (modules.py:255-275), split so that ranks can all-reduce the
+ * moments: stats accumulates per-channel sum / sum of squares of x [B,C] in fp64 into moments[2*C]
+ * (caller zeroes it); finalize writes loc = -mean, scale = 1/(std_unbiased + 1e-6).            */
+int ipoke_inn_actnorm_stats(const float* x, int B, int C, double* moments, void* stream);
+int ipoke_inn_actnorm_finalize(const double* moments, double count, int C, float* loc, float* scale, void* stream);
+
+/* FlowLoss (loss.py:17-42, 86-97): out[0] = nll_weight*mean(0.5*sum z^2) - logdet_weight*mean(logdet),
+ * out[1] = mean nll, out[2] = -mean logdet; also the gradients the backward pass starts from:
+ * dz = nll_weight * z / B, dlogdet = -logdet_weight / B (either may be NULL).                 */
+int ipoke_inn_flow_loss(const float* z, const float* logdet, int B, int C, float nll_weight, float logdet_weight,
+                        float* out3, float* dz, float* dlogdet, void* stream);
+
+/* Number of kernels the last forward / reverse call on this plan launched (for bench accounting). */
+int ipoke_inn_last_launch_count(const ipoke_inn_plan* plan);
+
+/* Test/diagnostic aid: byte offsets of the scratch buffers inside the workspace for batch B and the padded
+ * dimensions, out[20] = {S0, S1, U_hi, U_lo, ACT_hi0, ACT_lo0, ACT_hi1, ACT_lo1, logdet, total, ldU, ldACT,
+ * Hp, C2p, Ep, Np, ksplit, Gmax, packed_bytes, num_sms}.                                              */
+int ipoke_inn_debug_layout(const ipoke_inn_plan* plan, int B, long long* out, int n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IPOKE_INN_H_ */

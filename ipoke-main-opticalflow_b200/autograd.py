@@ -1,0 +1,29 @@
+"""torch.autograd glue: one Function per flow call so that ``loss.backward()`` of the caller (Lightning's
+training loop in the reference, models/second_stage_video_fc.py:448-490) reaches the fused backward kernels."""
+import torch
+
+
+def _needs_grad(engine, x, cond):
+    if not torch.is_grad_enabled():
+        return False
+    if x.requires_grad or (cond is not None and cond.requires_grad):
+        return True
+    return any(p.requires_grad for p in engine.flow.parameters())
+
+
+def flow_forward(engine, x, cond):
+    """-> z [B,C], logdet [B], block_outs [n,B,C], block_logdets [n,B]."""
+    if _needs_grad(engine, x, cond):
+        from .backward import FlowFunction
+        return FlowFunction.run(engine, x, cond)
+    with torch.no_grad():
+        return engine.forward(x, cond, want_blocks=True)
+
+
+def flow_reverse(engine, z, cond):
+    if torch.is_grad_enabled() and (z.requires_grad or (cond is not None and cond.requires_grad)):
+        raise NotImplementedError("ipoke_inn_b200: gradients through the reverse (sampling) direction are not "
+                                  "implemented; the reference only samples under torch.no_grad() "
+                                  "(models/second_stage_video_fc.py:359)")
+    with torch.no_grad():
+        return engine.reverse(z, cond)

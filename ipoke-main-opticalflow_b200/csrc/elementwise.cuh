@@ -1,0 +1,241 @@
+// HBM-bound fp32 kernels around the coupling GEMMs: block boundaries (Shuffle gather + ActNorm +
+// InvLeakyRelu and their inverses), parameter packing, ActNorm statistics, FlowLoss.
+#pragma once
+#include "ptx.cuh"
+
+namespace inn {
+
+// ----------------------------------------------------------------------------- boundary
+// out[b,p] = post_p( pre_q( in[b,q] ) ),  q = src[p]
+//   forward, start of block k : src = Shuffle_{k-1} (composed with the half swap of the coupling output),
+//                               post = ActNorm_k then InvLeakyRelu         (flow_blocks.py:257-260, 322-324;
+//                                                                           modules.py:292; flow_blocks.py:380-381)
+//   reverse, start of block k : pre = InvLeakyRelu^-1 then ActNorm_{k+1}^-1 (flow_blocks.py:385-386; modules.py:312),
+//                               src = Shuffle_k^-1                          (flow_blocks.py:326)
+// and writes the bf16 (hi/lo) copy of the half the next subnetwork reads, the conditioning columns of the
+// MLP input buffer, and the ActNorm log-det term.
+struct BoundaryParams {
+  const float* in;  int ld_in;
+  float* out;       int ld_out;        // nullable
+  float* raw_out;   int ld_raw;        // nullable: value after gather+pre, before post
+  float* raw_out2;                      // nullable second copy (same ld)
+  const int* src;                       // nullable = identity
+  const float* pre_loc;  const float* pre_scale;  int pre_leaky;     // pre_scale == nullptr -> no pre
+  const float* post_loc; const float* post_scale; int post_leaky;    // post_scale == nullptr -> no post
+  float alpha;
+  __nv_bfloat16* u_hi; __nv_bfloat16* u_lo; int ld_u;                // nullable
+  int u_begin, u_count, u_pad;          // columns p in [u_begin, u_begin+u_count) -> U col p-u_begin; zero to u_pad
+  const float* cond; int E; int ld_cond; int u_cond_off; int e_pad;  // cond nullable
+  float* logdet; const float* an_logdet; int logdet_init;            // logdet nullable
+  float* block_logdet;                                                // nullable snapshot before the add
+  float* block_logdet2;                                               // nullable second snapshot
+  int B, C;
+};
+
+__global__ void __launch_bounds__(256) inn_boundary_kernel(const BoundaryParams p) {
+  const long long total = static_cast<long long>(p.B) * p.C;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const long long tid0 = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (long long idx = tid0; idx < total; idx += stride) {
+    const int b = static_cast<int>(idx / p.C);
+    const int c = static_cast<int>(idx - static_cast<long long>(b) * p.C);
+    const int q = p.src ? __ldg(p.src + c) : c;
+    float v = __ldg(p.in + static_cast<size_t>(b) * p.ld_in + q);
+    if (p.pre_scale) {
+      if (p.pre_leaky) v = v / (v >= 0.f ? 1.0f : p.alpha);
+      v = v / __ldg(p.pre_scale + q) - __ldg(p.pre_loc + q);
+    }
+    if (p.raw_out) p.raw_out[static_cast<size_t>(b) * p.ld_raw + c] = v;
+    if (p.raw_out2) p.raw_out2[static_cast<size_t>(b) * p.ld_raw + c] = v;
+    if (p.post_scale) {
+      v = __ldg(p.post_scale + c) * (v + __ldg(p.post_loc + c));
+      if (p.post_leaky) v = v * (v >= 0.f ? 1.0f : p.alpha);
+    }
+    if (p.out) p.out[static_cast<size_t>(b) * p.ld_out + c] = v;
+    if (p.u_hi && c >= p.u_begin && c < p.u_begin + p.u_count) {
+      __nv_bfloat16 h, l;
+      split_bf16(v, h, l);
+      const size_t o = static_cast<size_t>(b) * p.ld_u + (c - p.u_begin);
+      p.u_hi[o] = h;
+      if (p.u_lo) p.u_lo[o] = l;
+    }
+    if (c == 0 && p.logdet) {
+      const float cur = p.logdet_init ? 0.f : p.logdet[b];
+      if (p.block_logdet) p.block_logdet[b] = cur;
+      if (p.block_logdet2) p.block_logdet2[b] = cur;
+      p.logdet[b] = p.an_logdet ? cur + __ldg(p.an_logdet) : cur;
+    }
+  }
+  // zero the K padding of the x part of the MLP input buffer
+  if (p.u_hi && p.u_pad > p.u_count) {
+    const int w = p.u_pad - p.u_count;
+    const long long tot = static_cast<long long>(p.B) * w;
+    for (long long idx = tid0; idx < tot; idx += stride) {
+      const int b = static_cast<int>(idx / w);
+      const size_t o = static_cast<size_t>(b) * p.ld_u + p.u_count + static_cast<int>(idx - static_cast<long long>(b) * w);
+      p.u_hi[o] = __float2bfloat16_rn(0.f);
+      if (p.u_lo) p.u_lo[o] = __float2bfloat16_rn(0.f);
+    }
+  }
+  // conditioning columns (written once per pass)
+  if (p.cond && p.u_hi) {
+    const long long tot = static_cast<long long>(p.B) * p.e_pad;
+    for (long long idx = tid0; idx < tot; idx += stride) {
+      const int b = static_cast<int>(idx / p.e_pad);
+      const int e = static_cast<int>(idx - static_cast<long long>(b) * p.e_pad);
+      const float v = e < p.E ? __ldg(p.cond + static_cast<size_t>(b) * p.ld_cond + e) : 0.f;
+      __nv_bfloat16 h, l;
+      split_bf16(v, h, l);
+      const size_t o = static_cast<size_t>(b) * p.ld_u + p.u_cond_off + e;
+      p.u_hi[o] = h;
+      if (p.u_lo) p.u_lo[o] = l;
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------- packing
+struct PackJob {
+  const float* w;      // [N, K] row-major (nn.Linear.weight)
+  const float* b;      // [N]
+  int N, K;
+  int ld_dst;          // elements per packed row
+  long long dst_hi;    // element offsets into the packed buffer viewed as bf16
+  long long dst_lo;    // < 0: not stored
+  int row0;            // first destination row
+  int col_split;       // source columns >= col_split are shifted by col_shift
+  int col_shift;
+  long long dstT_hi;   // transposed copy [K(+shift) rows, ld_dstT] for dgrad; < 0: none
+  long long dstT_lo;
+  int ld_dstT;
+  long long bias_off;  // float offset into the packed buffer viewed as fp32
+};
+
+__global__ void __launch_bounds__(256) inn_pack_linear_kernel(const PackJob* __restrict__ jobs, void* packed) {
+  const PackJob j = jobs[blockIdx.y];
+  __nv_bfloat16* pk = reinterpret_cast<__nv_bfloat16*>(packed);
+  float* pf = reinterpret_cast<float*>(packed);
+  const long long total = static_cast<long long>(j.N) * j.K;
+  for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int n = static_cast<int>(idx / j.K);
+    const int k = static_cast<int>(idx - static_cast<long long>(n) * j.K);
+    const int kd = k < j.col_split ? k : k + j.col_shift;
+    __nv_bfloat16 h, l;
+    split_bf16(__ldg(j.w + idx), h, l);
+    const long long o = static_cast<long long>(j.row0 + n) * j.ld_dst + kd;
+    pk[j.dst_hi + o] = h;
+    if (j.dst_lo >= 0) pk[j.dst_lo + o] = l;
+    if (j.dstT_hi >= 0) {
+      const long long ot = static_cast<long long>(kd) * j.ld_dstT + j.row0 + n;
+      pk[j.dstT_hi + ot] = h;
+      if (j.dstT_lo >= 0) pk[j.dstT_lo + ot] = l;
+    }
+  }
+  if (blockIdx.x == 0)
+    for (int n = threadIdx.x; n < j.N; n += blockDim.x) pf[j.bias_off + j.row0 + n] = __ldg(j.b + n);
+}
+
+struct PackBlockJob {
+  const float* loc; const float* scale;       // [C]
+  const long long* perm_fwd; const long long* perm_bwd;   // int64 [C]
+  long long loc_off, scale_off, an_logdet_off;            // float offsets
+  long long map_fwd_off, map_rev_off;                     // int32 offsets
+};
+
+// One CTA per flow block: copy loc/scale, sum log|scale| (modules.py:298-299), build the int32 gather maps
+//   map_fwd[p] = (perm_fwd[p] + C/2) % C     (coupling output is stored [xa' | xb'], logical order is [xb' | xa'])
+//   map_rev[p] = perm_bwd[(p + C/2) % C]
+__global__ void __launch_bounds__(256) inn_pack_block_kernel(const PackBlockJob* __restrict__ jobs, void* packed, int C) {
+  const PackBlockJob j = jobs[blockIdx.x];
+  float* pf = reinterpret_cast<float*>(packed);
+  int* pi = reinterpret_cast<int*>(packed);
+  __shared__ float red[256];
+  float acc = 0.f;
+  const int half = C / 2;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float s = __ldg(j.scale + c);
+    pf[j.loc_off + c] = __ldg(j.loc + c);
+    pf[j.scale_off + c] = s;
+    acc += logf(fabsf(s));
+    pi[j.map_fwd_off + c] = static_cast<int>((j.perm_fwd[c] + half) % C);
+    pi[j.map_rev_off + c] = static_cast<int>(j.perm_bwd[(c + half) % C]);
+  }
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) pf[j.an_logdet_off] = red[0];
+}
+
+// ----------------------------------------------------------------------------- ActNorm init
+__global__ void __launch_bounds__(256) inn_actnorm_stats_kernel(const float* __restrict__ x, int B, int C,
+                                                                double* __restrict__ moments) {
+  // each thread owns one channel of a row slab: coalesced across channels
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const int rows_per = (B + gridDim.y - 1) / gridDim.y;
+  const int r0 = blockIdx.y * rows_per;
+  const int r1 = min(B, r0 + rows_per);
+  double s = 0.0, ss = 0.0;
+  for (int r = r0; r < r1; ++r) {
+    const double v = static_cast<double>(__ldg(x + static_cast<size_t>(r) * C + c));
+    s += v;
+    ss += v * v;
+  }
+  if (r1 > r0) {
+    atomicAdd(moments + c, s);
+    atomicAdd(moments + C + c, ss);
+  }
+}
+
+__global__ void inn_actnorm_finalize_kernel(const double* __restrict__ moments, double count, int C,
+                                            float* __restrict__ loc, float* __restrict__ scale) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const double mean = moments[c] / count;
+  double var = (moments[C + c] - count * mean * mean) / (count - 1.0);     // unbiased, torch.std default
+  var = var > 0.0 ? var : 0.0;
+  loc[c] = static_cast<float>(-mean);
+  scale[c] = static_cast<float>(1.0 / (sqrt(var) + 1e-6));
+}
+
+// ----------------------------------------------------------------------------- FlowLoss
+// single CTA: B*C is small next to the GEMMs; deterministic tree reduction
+__global__ void __launch_bounds__(1024) inn_flow_loss_kernel(const float* __restrict__ z, const float* __restrict__ logdet,
+                                                             int B, int C, float nll_w, float ld_w, float* out3,
+                                                             float* dz, float* dlogdet) {
+  __shared__ double r_nll[1024];
+  __shared__ double r_ld[1024];
+  double a = 0.0, l = 0.0;
+  const long long total = static_cast<long long>(B) * C;
+  const float inv_b = 1.0f / static_cast<float>(B);
+  for (long long i = threadIdx.x; i < total; i += blockDim.x) {
+    const float v = z[i];
+    a += 0.5 * static_cast<double>(v) * v;
+    if (dz) dz[i] = nll_w * v * inv_b;
+  }
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    l += logdet[b];
+    if (dlogdet) dlogdet[b] = -ld_w * inv_b;
+  }
+  r_nll[threadIdx.x] = a;
+  r_ld[threadIdx.x] = l;
+  __syncthreads();
+  for (int s = 512; s > 0; s >>= 1) {
+    if (threadIdx.x < s) {
+      r_nll[threadIdx.x] += r_nll[threadIdx.x + s];
+      r_ld[threadIdx.x] += r_ld[threadIdx.x + s];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const double nll = r_nll[0] / B, nld = -r_ld[0] / B;
+    out3[0] = static_cast<float>(nll_w * nll + ld_w * nld);
+    out3[1] = static_cast<float>(nll);
+    out3[2] = static_cast<float>(nld);
+  }
+}
+
+}  // namespace inn

@@ -1,0 +1,248 @@
+"""Host-side driver of one flow stack: owns the C-ABI plan, the packed parameter buffer and the scratch
+workspaces, mirrors the ActNorm ``initialized`` flags on the host (no per-call ``.item()`` sync as in the
+reference, modules.py:288) and exposes forward / reverse / backward on 2-D fp32 CUDA tensors."""
+import ctypes
+
+import torch
+
+from . import _capi
+
+
+def _ptr_array(tensors):
+    arr = (ctypes.c_void_p * len(tensors))()
+    for i, t in enumerate(tensors):
+        arr[i] = t.data_ptr()
+    return arr
+
+
+class FlowEngine:
+    def __init__(self, flow, conditional, C, E, H, depth, n_flows, alpha, precision="fp32"):
+        if precision not in _capi.PRECISIONS:
+            raise ValueError(f"precision must be one of {list(_capi.PRECISIONS)}")
+        if C % 2 != 0:
+            raise NotImplementedError("ipoke_inn_b200 covers even flow_in_channels only (all reference configs)")
+        self.flow = flow                      # not registered as a sub-module: FlowEngine is a plain object
+        self.desc = _capi.InnDesc(C=C, E=E, H=H, depth=depth, n_flows=n_flows, conditional=int(conditional),
+                                  precision=_capi.PRECISIONS[precision], alpha=float(alpha), mlp_slope=0.01)
+        self.precision = precision
+        self.C, self.E, self.n_flows = C, E, n_flows
+        self._plan = None
+        self._device = None
+        self._packed = None
+        self._packed_sig = None
+        self._ws = {}
+        self._init_epoch = None               # sum of ActNorm._state_epoch when `initialized` was last read
+        self.assume_frozen = False            # skip the per-call parameter-version check (inference loops)
+        self.sync_actnorm_init = True         # all-reduce ActNorm init moments when torch.distributed is up
+        self.launches = 0
+
+    # ------------------------------------------------------------------ plumbing
+    def invalidate(self):
+        """Force a repack before the next call (after out-of-band ``param.data`` edits)."""
+        self._packed_sig = None
+        self._init_epoch = None
+
+    def release(self):
+        if self._plan is not None:
+            _capi.lib().ipoke_inn_plan_destroy(self._plan)
+        self._plan, self._packed, self._packed_sig, self._ws, self._device = None, None, None, {}, None
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:
+            pass
+
+    def _tensors(self):
+        blocks = self.flow.sub_layers
+        lin_w, lin_b = [], []
+        for blk in blocks:
+            for i in range(2):
+                for nets in (blk.coupling.s, blk.coupling.t):
+                    for lin in nets[i].linears():
+                        lin_w.append(lin.weight)
+                        lin_b.append(lin.bias)
+        loc = [b.norm_layer.loc for b in blocks]
+        scale = [b.norm_layer.scale for b in blocks]
+        pf = [b.shuffle.forward_shuffle_idx for b in blocks]
+        pb = [b.shuffle.backward_shuffle_idx for b in blocks]
+        return lin_w, lin_b, loc, scale, pf, pb
+
+    def _ensure(self, device):
+        L = _capi.lib()
+        if device.type != "cuda":
+            raise RuntimeError("ipoke_inn_b200 runs on CUDA (sm_100a) only: move the module and its inputs to a "
+                               "B200 device; there is no CPU fallback")
+        if self._plan is None or self._device != device:
+            self.release()
+            plan = ctypes.c_void_p()
+            idx = device.index if device.index is not None else torch.cuda.current_device()
+            _capi.check(L.ipoke_inn_plan_create(ctypes.byref(self.desc), idx, ctypes.byref(plan)), "plan_create")
+            self._plan = plan
+            self._device = device
+            self._packed = torch.empty(L.ipoke_inn_packed_bytes(plan), dtype=torch.uint8, device=device)
+            self._packed_sig = None
+        return L
+
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self._device).cuda_stream)
+
+    def _workspace(self, B):
+        ws = self._ws.get(B)
+        if ws is None:
+            if len(self._ws) >= 4:
+                self._ws.pop(next(iter(self._ws)))
+            n = _capi.lib().ipoke_inn_workspace_bytes(self._plan, B, 1)
+            ws = torch.empty(n, dtype=torch.uint8, device=self._device)
+            self._ws[B] = ws
+        return ws
+
+    def _signature(self, tensors):
+        lin_w, lin_b, loc, scale, pf, pb = tensors
+        v = 0
+        for group in (lin_w, lin_b, loc, scale, pf, pb):
+            for t in group:
+                v += t._version
+        return (v, lin_w[0].data_ptr(), lin_w[-1].data_ptr(), loc[0].data_ptr())
+
+    def pack(self, force=False):
+        """Repack parameters into the kernel layout if they changed since the last pack."""
+        if self.assume_frozen and self._packed_sig is not None and not force:
+            return
+        tensors = self._tensors()
+        sig = self._signature(tensors)
+        if not force and sig == self._packed_sig:
+            return
+        lin_w, lin_b, loc, scale, pf, pb = tensors
+        for t in lin_w + lin_b + loc + scale:
+            if t.dtype != torch.float32 or not t.is_contiguous() or t.device != self._device:
+                raise RuntimeError("ipoke_inn_b200: parameters must be contiguous fp32 CUDA tensors on one device")
+        for t in pf + pb:
+            if t.dtype != torch.int64 or t.device != self._device:
+                raise RuntimeError("ipoke_inn_b200: shuffle indices must be int64 tensors on the module's device")
+        L = _capi.lib()
+        _capi.check(L.ipoke_inn_pack(self._plan, _ptr_array(lin_w), _ptr_array(lin_b), _ptr_array(loc),
+                                     _ptr_array(scale), _ptr_array(pf), _ptr_array(pb),
+                                     ctypes.c_void_p(self._packed.data_ptr()), self._stream()), "pack")
+        self._packed_sig = sig
+
+    # ------------------------------------------------------------------ inputs
+    def _prep(self, x, cond):
+        if x.dtype != torch.float32:
+            raise TypeError("ipoke_inn_b200 computes in fp32 I/O; got input dtype %s" % x.dtype)
+        B = x.shape[0]
+        x2 = x.reshape(B, -1)
+        if x2.shape[1] != self.C:
+            raise RuntimeError(f"expected {self.C} channels, got input of shape {tuple(x.shape)}")
+        x2 = x2.contiguous()
+        c2 = None
+        if self.E > 0:
+            if cond is None:
+                raise RuntimeError("conditional flow needs a conditioning tensor")
+            if cond.dtype != torch.float32 or cond.device != x.device:
+                raise TypeError("conditioning must be an fp32 tensor on the input's device")
+            c2 = cond.reshape(B, -1)
+            if c2.shape[1] != self.E:
+                raise RuntimeError(f"expected {self.E} conditioning channels, got {tuple(cond.shape)}")
+            c2 = c2.contiguous()
+        return B, x2, c2
+
+    # ------------------------------------------------------------------ ActNorm data init
+    def _maybe_actnorm_init(self, x2, c2):
+        norms = [b.norm_layer for b in self.flow.sub_layers]
+        epoch = sum(n._state_epoch for n in norms)
+        if self._init_epoch == epoch:
+            return
+        flags = torch.stack([n.initialized for n in norms]).cpu()      # one host sync, first call only
+        if bool((flags == 0).any()):
+            self._actnorm_init(x2, c2, flags)
+        self._init_epoch = epoch
+
+    def _actnorm_init(self, x2, c2, flags):
+        """Reference modules.py:255-275 + :288-290: every uninitialised ActNorm takes loc=-mean, scale=1/(std+1e-6)
+        from its own input, block after block.  Moments are all-reduced across ranks when torch.distributed is
+        initialised so that all replicas start identical."""
+        L = _capi.lib()
+        B = x2.shape[0]
+        cur = x2
+        dist = torch.distributed if (self.sync_actnorm_init and torch.distributed.is_available()
+                                     and torch.distributed.is_initialized()) else None
+        with torch.no_grad():
+            for k, blk in enumerate(self.flow.sub_layers):
+                if int(flags[k]) == 0:
+                    mom = torch.zeros(2 * self.C + 1, dtype=torch.float64, device=self._device)
+                    mom[-1] = B
+                    _capi.check(L.ipoke_inn_actnorm_stats(cur.data_ptr(), B, self.C, mom.data_ptr(), self._stream()))
+                    if dist is not None:
+                        dist.all_reduce(mom)
+                    count = float(mom[-1].item())
+                    nl = blk.norm_layer
+                    _capi.check(L.ipoke_inn_actnorm_finalize(mom.data_ptr(), count, self.C, nl.loc.data_ptr(),
+                                                             nl.scale.data_ptr(), self._stream()))
+                    nl.initialized.fill_(1)
+                    self._packed_sig = None
+                self.pack()
+                nxt = torch.empty_like(cur)
+                ld = torch.empty(B, dtype=torch.float32, device=self._device)
+                self._forward_raw(cur, c2, nxt, ld, None, None, k, k + 1)
+                cur = nxt
+        self._packed_sig = None
+
+    # ------------------------------------------------------------------ calls
+    def _forward_raw(self, x2, c2, z, ld, outs, lds, kb, ke):
+        L = _capi.lib()
+        B = x2.shape[0]
+        ws = self._workspace(B)
+        _capi.check(L.ipoke_inn_forward(self._plan, self._packed.data_ptr(), x2.data_ptr(),
+                                        c2.data_ptr() if c2 is not None else None, z.data_ptr(), ld.data_ptr(),
+                                        outs.data_ptr() if outs is not None else None,
+                                        lds.data_ptr() if lds is not None else None, B, kb, ke, ws.data_ptr(),
+                                        self._stream()), "forward")
+        self.launches = L.ipoke_inn_last_launch_count(self._plan)
+
+    def forward(self, x, cond, want_blocks=False):
+        """-> z [B,C], logdet [B] (+ block_outs [n,B,C], block_logdets [n,B])"""
+        B, x2, c2 = self._prep(x, cond)
+        self._ensure(x2.device)
+        self._maybe_actnorm_init(x2, c2)
+        self.pack()
+        z = torch.empty(B, self.C, dtype=torch.float32, device=self._device)
+        ld = torch.empty(B, dtype=torch.float32, device=self._device)
+        outs = lds = None
+        if want_blocks:
+            outs = torch.empty(self.n_flows, B, self.C, dtype=torch.float32, device=self._device)
+            lds = torch.empty(self.n_flows, B, dtype=torch.float32, device=self._device)
+        self._forward_raw(x2, c2, z, ld, outs, lds, 0, self.n_flows)
+        return z, ld, outs, lds
+
+    def reverse(self, z, cond):
+        B, z2, c2 = self._prep(z, cond)
+        L = self._ensure(z2.device)
+        self.pack()
+        x = torch.empty(B, self.C, dtype=torch.float32, device=self._device)
+        ws = self._workspace(B)
+        _capi.check(L.ipoke_inn_reverse(self._plan, self._packed.data_ptr(), z2.data_ptr(),
+                                        c2.data_ptr() if c2 is not None else None, x.data_ptr(), B, 0, self.n_flows,
+                                        ws.data_ptr(), self._stream()), "reverse")
+        self.launches = L.ipoke_inn_last_launch_count(self._plan)
+        return x
+
+    # host-buffer entry points (pinned CPU tensors in, pinned CPU tensors out; stream-ordered, caller syncs)
+    def forward_host(self, x_host, cond_host, z_host, logdet_host):
+        L = _capi.lib()
+        B = x_host.shape[0]
+        ws = self._workspace(B)
+        _capi.check(L.ipoke_inn_forward_host(self._plan, self._packed.data_ptr(), x_host.data_ptr(),
+                                             cond_host.data_ptr() if cond_host is not None else None,
+                                             z_host.data_ptr(), logdet_host.data_ptr(), B, ws.data_ptr(),
+                                             self._stream()), "forward_host")
+        self.launches = L.ipoke_inn_last_launch_count(self._plan)
+
+    def reverse_host(self, z_host, cond_host, x_host):
+        L = _capi.lib()
+        B = z_host.shape[0]
+        ws = self._workspace(B)
+        _capi.check(L.ipoke_inn_reverse_host(self._plan, self._packed.data_ptr(), z_host.data_ptr(),
+                                             cond_host.data_ptr() if cond_host is not None else None,
+                                             x_host.data_ptr(), B, ws.data_ptr(), self._stream()), "reverse_host")
+        self.launches = L.ipoke_inn_last_launch_count(self._plan)

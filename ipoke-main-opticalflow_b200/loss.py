@@ -1,0 +1,62 @@
+"""FlowLoss with the reference's interface (models/modules/INN/loss.py:8-42, nll :86-97), computed by
+``ipoke_inn_flow_loss`` (one reduction kernel that also emits dz / dlogdet for the backward pass)."""
+import torch
+import torch.nn as nn
+
+from . import _capi
+
+
+def _loss_kernel(z2, logdet, nll_w, ld_w, want_grads):
+    B, C = z2.shape
+    out3 = torch.empty(3, dtype=torch.float32, device=z2.device)
+    dz = torch.empty_like(z2) if want_grads else None
+    dld = torch.empty_like(logdet) if want_grads else None
+    stream = torch.cuda.current_stream(z2.device).cuda_stream
+    _capi.check(_capi.lib().ipoke_inn_flow_loss(z2.data_ptr(), logdet.data_ptr(), B, C, float(nll_w), float(ld_w),
+                                                out3.data_ptr(), dz.data_ptr() if want_grads else None,
+                                                dld.data_ptr() if want_grads else None, stream), "flow_loss")
+    return out3, dz, dld
+
+
+class _FlowLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z2, logdet, nll_w, ld_w):
+        out3, dz, dld = _loss_kernel(z2, logdet, nll_w, ld_w, True)
+        ctx.save_for_backward(dz, dld)
+        return out3
+
+    @staticmethod
+    def backward(ctx, g):
+        dz, dld = ctx.saved_tensors
+        return dz * g[0], dld * g[0], None, None      # only out3[0] (the loss) is differentiated
+
+
+class FlowLoss(nn.Module):
+    def __init__(self, spatial_mean=False, logdet_weight=1., nll_weight=1., radial=False):
+        super().__init__()
+        if spatial_mean or radial:
+            raise NotImplementedError("spatial_mean / radial are off in every flat-INN config "
+                                      "(reference models/second_stage_video_fc.py:150)")
+        self.spatial_mean = spatial_mean
+        self.logdet_weight = logdet_weight
+        self.nll_weight = nll_weight
+        self.radial = radial
+
+    def forward(self, sample, logdet):
+        assert len(logdet.shape) == 1
+        if sample.device.type != "cuda":
+            raise RuntimeError("ipoke_inn_b200.FlowLoss runs on CUDA only")
+        B = sample.shape[0]
+        z2 = sample.reshape(B, -1).contiguous()
+        ld = logdet.contiguous()
+        if torch.is_grad_enabled() and (z2.requires_grad or ld.requires_grad):
+            out3 = _FlowLossFn.apply(z2, ld, self.nll_weight, self.logdet_weight)
+        else:
+            out3, _, _ = _loss_kernel(z2, ld, self.nll_weight, self.logdet_weight, False)
+        loss = out3[0]
+        # reference draws a fresh N(0,1) sample for a logged reference NLL (loss.py:27,32) -- same RNG use
+        ref_sample = torch.randn_like(sample)
+        ref3, _, _ = _loss_kernel(ref_sample.reshape(B, -1), torch.zeros_like(ld), 1.0, 0.0, False)
+        log = {"flow_loss": loss.detach(), "reference_nll_loss": ref3[1], "nlogdet_loss": out3[2].detach(),
+               "nll_loss": out3[1].detach(), "logdet_w": self.logdet_weight, "nll_w": self.nll_weight}
+        return loss, log

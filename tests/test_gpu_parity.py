@@ -1,0 +1,190 @@
+"""GPU parity tests (run on the B200 box): CUDA path through the module API / C ABI vs
+(1) the committed live-reference fixtures, (2) the numpy oracle on seeded inputs at BASELINE sizes,
+(3) size-independent properties (forward->reverse round trip, batch-slice independence).
+
+Tolerances (max-abs error relative to the tensor's max-abs, and rel-L2):
+  precision="fp32" (split-bf16, 3 MMAs): <= 1e-4   -- the north star's fp32 bound
+  precision="bf16" (single pass)       : <= 2e-3 z / reverse, <= 5e-4 logdet   (random-init weights)
+"""
+import numpy as np
+import pytest
+import torch
+
+import ipoke_inn_b200 as P
+from oracle import inn_oracle as O
+from conftest import GOLDEN_CASES, load_golden, max_rel, rel_l2
+from test_host_logic import CFG, build
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"fp32": dict(z=1e-4, ld=1e-4), "bf16": dict(z=2e-3, ld=5e-4)}
+
+
+def _dev():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return torch.device("cuda:0")
+
+
+def _load(name, precision):
+    sd_ref, d = load_golden(name)
+    net = build(name, precision=precision)
+    net.load_state_dict({k: torch.from_numpy(v) for k, v in sd_ref.items()}, strict=True)
+    return net.to(_dev()), sd_ref, d
+
+
+def _call(net, x, cond, **kw):
+    with torch.no_grad():
+        return net(x, cond, **kw) if cond is not None else net(x, **kw)
+
+
+def _inputs(d):
+    dev = _dev()
+    x = torch.from_numpy(d["x"]).to(dev)
+    cond = torch.from_numpy(d["cond"]).to(dev) if "cond" in d else None
+    return x, cond
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_forward_matches_reference_fixture(name, precision):
+    net, sd, d = _load(name, precision)
+    x, cond = _inputs(d)
+    B, C = d["x"].shape
+    z, ld = _call(net, x, cond)
+    assert z.shape == (B, C, 1, 1) and ld.shape == (B,)
+    t = TOL[precision]
+    assert max_rel(z.cpu().numpy().reshape(B, C), d["z"].reshape(B, C)) < t["z"]
+    assert max_rel(ld.cpu().numpy(), d["logdet"]) < t["ld"]
+    outs, lds = _call(net, x, cond, train=True)
+    assert len(outs) == len(lds) == d["last_outs"].shape[0]
+    got = np.stack([o.reshape(B, C).cpu().numpy() for o in outs])
+    assert max_rel(got, d["last_outs"]) < t["z"]
+    assert max_rel(np.stack([l.cpu().numpy() for l in lds]), d["last_logdets"]) < t["ld"]
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_reverse_matches_reference_fixture(name, precision):
+    net, sd, d = _load(name, precision)
+    x, cond = _inputs(d)
+    B, C = d["x"].shape
+    dev = _dev()
+    t = TOL[precision]
+    x_rec = _call(net, torch.from_numpy(d["z"]).to(dev), cond, reverse=True)
+    assert x_rec.shape == (B, C, 1, 1)
+    assert max_rel(x_rec.cpu().numpy().reshape(B, C), d["x_rec"].reshape(B, C)) < t["z"]
+    x_smp = _call(net, torch.from_numpy(d["z_in"]).to(dev), cond, reverse=True)
+    assert max_rel(x_smp.cpu().numpy().reshape(B, C), d["x_smp"].reshape(B, C)) < t["z"]
+    # own round trip: reverse(forward(x)) == x
+    z, _ = _call(net, x, cond)
+    x_back = _call(net, z, cond, reverse=True)
+    assert max_rel(x_back.cpu().numpy().reshape(B, C), d["x"]) < t["z"]
+
+
+@pytest.mark.parametrize("name", ["cfgS_cond", "uncond_small"])
+def test_actnorm_data_init_matches_reference(name):
+    """Fresh module (same seed as the fixture): first forward initialises every ActNorm from its input."""
+    sd_ref, d = load_golden(name)
+    net = build(name).to(_dev())
+    x, cond = _inputs(d)
+    B, C = d["x"].shape
+    z, ld = _call(net, x, cond)
+    sd = net.state_dict()
+    for k, v in sd_ref.items():
+        if "norm_layer" in k:
+            assert max_rel(sd[k].cpu().numpy(), v) < 1e-4, k
+        elif "shuffle" in k:
+            assert np.array_equal(sd[k].cpu().numpy(), v), k          # permutations bit-exact
+    assert max_rel(z.cpu().numpy().reshape(B, C), d["z"].reshape(B, C)) < 2e-4
+    assert max_rel(ld.cpu().numpy(), d["logdet"]) < 2e-4
+    z2, ld2 = _call(net, x, cond)                                      # second call: no re-init
+    assert torch.equal(z, z2) and torch.equal(ld, ld2)
+
+
+FULL = {
+    # BASELINE.json configs restated for the MLP stack
+    "cfgA": ("cond", dict(flow_in_channels=128, flow_mid_channels_factor=12, flow_hidden_depth=3, n_flows=8,
+                          flow_conditioning_option="none", flow_embedding_channels=128)),
+    "cfgB": ("uncond", dict(flow_in_channels=512, flow_mid_channels=1024, flow_hidden_depth=2, n_flows=8)),
+}
+
+
+def _full(name, precision, seed=42):
+    kind, kw = FULL[name]
+    torch.manual_seed(seed)
+    net = P.SupervisedTransformer(dict(kw), precision=precision) if kind == "cond" else \
+        P.UnsupervisedTransformer3(**kw, precision=precision)
+    return net, kind, kw
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("name,B", [("cfgA", 64), ("cfgA", 300), ("cfgB", 256), ("cfgB", 1)])
+def test_full_size_against_oracle(name, B, precision):
+    """BASELINE-size stacks, random-init weights under seed 42, ActNorm initialised from the first batch by the
+    oracle; the CUDA path must reproduce the oracle's z / logdet / reverse on the same weights."""
+    net, kind, kw = _full(name, precision)
+    C, E = kw["flow_in_channels"], kw.get("flow_embedding_channels", 0)
+    g = torch.Generator().manual_seed(1234)
+    x = torch.randn(max(B, 32), C, generator=g)
+    cond = torch.randn(max(B, 32), E, 1, 1, generator=g) if kind == "cond" else None
+    sd = O.state_dict_to_numpy(net.state_dict())
+    c2 = None if cond is None else cond.numpy().reshape(cond.shape[0], -1)
+    O.flow_forward_with_actnorm_init(sd, x.numpy(), c2)               # data init on the (>=32-row) first batch
+    net.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()})
+    net = net.to(_dev())
+    xb, cb = x[:B], (None if cond is None else cond[:B])
+    c2b = None if c2 is None else c2[:B]
+    z_ref, ld_ref = O.flow_forward(sd, xb.numpy(), c2b)
+    z, ld = _call(net, xb.to(_dev()), None if cb is None else cb.to(_dev()))
+    t = TOL[precision]
+    assert max_rel(z.cpu().numpy().reshape(B, C), z_ref) < t["z"]
+    assert max_rel(ld.cpu().numpy(), ld_ref) < t["ld"] or np.max(np.abs(ld.cpu().numpy() - ld_ref)) < 1e-3
+    x_ref = O.flow_reverse(sd, z_ref, c2b)
+    x_rec = _call(net, torch.from_numpy(z_ref).to(_dev()), None if cb is None else cb.to(_dev()), reverse=True)
+    assert max_rel(x_rec.cpu().numpy().reshape(B, C), x_ref) < t["z"]
+
+
+@pytest.mark.parametrize("name,B", [("cfgA", 4096 + 77), ("cfgB", 2048)])
+def test_large_batch_properties(name, B):
+    """Sizes the oracle does not run in seconds: round trip and batch-slice independence (rows are independent,
+    so any 128-row slice computed alone must equal the same rows of the big batch bit for bit)."""
+    net, kind, kw = _full(name, "fp32")
+    C, E = kw["flow_in_channels"], kw.get("flow_embedding_channels", 0)
+    net = net.to(_dev())
+    g = torch.Generator(device="cuda").manual_seed(99)
+    x = torch.randn(B, C, device=_dev(), generator=g)
+    cond = torch.randn(B, E, 1, 1, device=_dev(), generator=g) if kind == "cond" else None
+    z, ld = _call(net, x, cond)                                        # also runs the ActNorm init
+    assert torch.isfinite(z).all() and torch.isfinite(ld).all()
+    x_back = _call(net, z, cond, reverse=True)
+    assert float((x_back.reshape(B, C) - x).abs().max()) < 1e-3 * float(x.abs().max())
+    lo, hi = 1000, 1128
+    zs, lds = _call(net, x[lo:hi].contiguous(), None if cond is None else cond[lo:hi].contiguous())
+    assert float((zs - z[lo:hi]).abs().max()) < 1e-5 * float(z.abs().max())
+    assert float((lds - ld[lo:hi]).abs().max()) < 1e-4 * float(ld.abs().max())
+
+
+def test_flow_loss_kernel_matches_oracle():
+    dev = _dev()
+    g = torch.Generator().manual_seed(5)
+    z = torch.randn(37, 24, 1, 1, generator=g)
+    ld = torch.randn(37, generator=g)
+    loss, log = P.FlowLoss()(z.to(dev), ld.to(dev))
+    ref, nll_ref, nld_ref = O.flow_loss(z.numpy().astype(np.float64), ld.numpy().astype(np.float64))
+    assert abs(float(loss) - ref) < 1e-5 * abs(ref)
+    assert abs(float(log["nll_loss"]) - nll_ref) < 1e-5 * abs(nll_ref)
+    assert abs(float(log["nlogdet_loss"]) - nld_ref) < 1e-5 * max(abs(nld_ref), 1e-3)
+    assert 0.3 * 24 < float(log["reference_nll_loss"]) < 0.7 * 24
+
+
+def test_inputs_are_not_mutated_and_shapes_follow_reference():
+    net, sd, d = _load("cfgS_cond", "fp32")
+    x, cond = _inputs(d)
+    x0, c0 = x.clone(), cond.clone()
+    z, ld = _call(net, x, cond)
+    z4, _ = _call(net, x[:, :, None, None], cond)                      # 4-D input accepted (flow_blocks.py:50-51)
+    assert torch.equal(z, z4)
+    assert torch.equal(x, x0) and torch.equal(cond, c0)
+    u, sdu, du = _load("uncond_small", "fp32")
+    xs = u.sample((5, 16, 1, 1), device=_dev())
+    assert xs.shape == (5, 16)                                         # INN.py:272-276 squeezes
