@@ -1,0 +1,395 @@
+#!/usr/bin/env python
+"""bench.py -- INN samples/s (forward+logdet then reverse sampling) on N B200s, one process per GPU.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                  [--config cfgB|cfgA|cfgS] [--batch B] [--precision bf16|fp32] [--no-sweep]
+
+A "step" = one forward (z, logdet) + one reverse pass over a batch of B synthetic latents per GPU
+(weights: reference default init under seed 42, ActNorm data-initialised on the first batch).
+Default workload = BASELINE.json configs[1]: cfg B (INN_FCAE.yaml: unconditional C=512 H=1024 depth=2
+n_flows=8), batch 256 per GPU.  Prints ONE JSON line on rank 0 (contract in the task statement).
+`--impl reference` times the CPU port of the reference path (oracle/, numpy + OpenBLAS on all host cores).
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CONFIGS = {
+    # name: (kind, ctor kwargs, default batch per GPU, source)
+    "cfgB": ("uncond", dict(flow_in_channels=512, flow_mid_channels=1024, flow_hidden_depth=2, n_flows=8), 256,
+             "INN_FCAE.yaml (config/INN_FCAE.yaml:40-42, z_dim config/BigGanAE.yaml:49): UnsupervisedTransformer3"),
+    "cfgA": ("cond", dict(flow_in_channels=128, flow_mid_channels_factor=12, flow_hidden_depth=3, n_flows=8,
+                          flow_conditioning_option="none", flow_embedding_channels=128), 4096,
+             "FullyConnected/second_stage.yaml:55-59: SupervisedTransformer"),
+    "cfgS": ("cond", dict(flow_in_channels=8, flow_mid_channels_factor=8, flow_hidden_depth=2, n_flows=8,
+                          flow_conditioning_option="none", flow_embedding_channels=16), 256,
+             "INN_test.yaml:17 (smoke)"),
+}
+METRIC = "INN samples/sec (fwd+logdet, reverse sampling)"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], bf16=d["bf16_tflops"], bf16_sus=d.get("bf16_tflops_sustained", d["bf16_tflops"]),
+                    src="MEASURED_PEAKS.json")
+    return dict(hbm=6650.0, bf16=1590.0, bf16_sus=1400.0, src="fallback (B200_PROFILING.md)")
+
+
+def macs_per_sample(kind, kw):
+    C = kw["flow_in_channels"]
+    d, n = kw["flow_hidden_depth"], kw["n_flows"]
+    if kind == "cond":
+        H, E = kw["flow_mid_channels_factor"] * C, kw["flow_embedding_channels"]
+        tot = 0
+        for k in range(n):
+            din = E if k % 2 == 0 else C // 2 + E
+            tot += 4 * (din * H + d * H * H + H * (C // 2))
+        return tot
+    H = kw["flow_mid_channels"]
+    return n * 4 * ((C // 2) * H + d * H * H + H * (C // 2))
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        rows = [r for (t, r) in self.rows if t0 - 0.05 <= t <= t1 + 0.15] or [r for (_, r) in self.rows]
+        for r in rows:
+            f = [x.strip() for x in r.split(",")]
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except Exception:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- CPU arm (oracle port)
+def cpu_port_run(cfg_name, B, steps, warmup, budget_s=20.0):
+    """Times the numpy port of the reference path (oracle/inn_oracle.py) on the host cores.  One step =
+    forward + reverse on a sample of the workload; the sample batch is bounded so a run stays short."""
+    import numpy as np
+    import torch
+    from oracle import inn_oracle as O
+    import ipoke_inn_b200 as P
+    kind, kw, _, _ = CONFIGS[cfg_name]
+    torch.manual_seed(42)
+    net = P.SupervisedTransformer(dict(kw)) if kind == "cond" else P.UnsupervisedTransformer3(**kw)
+    sd = O.state_dict_to_numpy(net.state_dict())
+    C, E = kw["flow_in_channels"], kw.get("flow_embedding_channels", 0)
+    rng = np.random.default_rng(1234)
+    x = rng.standard_normal((B, C), dtype=np.float32)
+    cond = rng.standard_normal((B, E), dtype=np.float32) if kind == "cond" else None
+    zin = rng.standard_normal((B, C), dtype=np.float32)
+    O.flow_forward_with_actnorm_init(sd, x, cond)
+    t_first = time.perf_counter()
+    O.flow_forward(sd, x, cond)
+    O.flow_reverse(sd, zin, cond)
+    t_first = time.perf_counter() - t_first
+    steps = max(1, min(steps, int(budget_s / max(t_first, 1e-6))))
+    for _ in range(min(warmup, 1)):
+        O.flow_forward(sd, x, cond)
+        O.flow_reverse(sd, zin, cond)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        O.flow_forward(sd, x, cond)
+        O.flow_reverse(sd, zin, cond)
+    dt = time.perf_counter() - t0
+    return {"value": B * steps / dt, "unit": "samples/s", "cores": os.cpu_count(), "kind": "port",
+            "sample": f"{steps} step(s) of forward+reverse on batch {B} ({cfg_name}, numpy fp32 + OpenBLAS, "
+                      f"all host threads)", "ms_per_step": 1e3 * dt / steps, "steps": steps}
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def gpu_run(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import ipoke_inn_b200 as P
+    from ipoke_inn_b200 import _capi
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    kind, kw, defB, src = CONFIGS[args.config]
+    B = args.batch or defB
+    C, E = kw["flow_in_channels"], kw.get("flow_embedding_channels", 0)
+    pk = peaks()
+
+    def make(precision):
+        torch.manual_seed(42)
+        net = P.SupervisedTransformer(dict(kw), precision=precision) if kind == "cond" else \
+            P.UnsupervisedTransformer3(**kw, precision=precision)
+        return net.to(dev).eval()
+
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    x = torch.randn(B, C, device=dev, generator=g)
+    cond = torch.randn(B, E, 1, 1, device=dev, generator=g) if kind == "cond" else None
+    zin = torch.randn(B, C, 1, 1, device=dev, generator=g)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
+
+    def call(net, inp, reverse=False):
+        with torch.no_grad():
+            if kind == "cond":
+                return net(inp, cond, reverse=reverse)
+            return net(inp, reverse=reverse)
+
+    def timed(net, steps, warmup, step_fn):
+        for _ in range(warmup):
+            step_fn()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        t0 = time.time()
+        for s in range(steps):
+            flush.fill_(s & 0xFF)                                       # L2 flush between timed iterations
+            evs[s][0].record()
+            step_fn()
+            evs[s][1].record()
+        torch.cuda.synchronize()
+        t1 = time.time()
+        ms = sum(a.elapsed_time(b) for a, b in evs)
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+            dist.barrier()
+        return ms, t0, t1
+
+    net = make(args.precision)
+    call(net, x)                                                        # ActNorm data init + pack
+    eng = net.flow.engine
+    eng.assume_frozen = True
+
+    def step_dev():
+        call(net, x)
+        call(net, zin, reverse=True)
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms, t0, t1 = timed(net, args.steps, args.warmup, step_dev)
+    clocks = sampler.stop(t0, t1) if sampler else None
+    call(net, x)
+    launches = eng.launches
+    call(net, zin, reverse=True)
+    launches += eng.launches
+    value = world * B * args.steps / (ms * 1e-3)
+
+    # ---- e2e: host (pinned) buffers through the C-ABI host entry points, copies inside the timed region
+    xh = x.cpu().pin_memory()
+    zinh = zin.reshape(B, C).cpu().pin_memory()
+    ch = cond.reshape(B, E).cpu().pin_memory() if cond is not None else None
+    zh = torch.empty(B, C).pin_memory()
+    ldh = torch.empty(B).pin_memory()
+    xoh = torch.empty(B, C).pin_memory()
+
+    def step_host():
+        eng.forward_host(xh, ch, zh, ldh)
+        eng.reverse_host(zinh, ch, xoh)
+        torch.cuda.current_stream().synchronize()                       # results are on the host
+
+    ms_e2e, _, _ = timed(net, args.steps, args.warmup, step_host)
+    e2e_value = world * B * args.steps / (ms_e2e * 1e-3)
+    h2d = 2 * B * C * 4 + (2 * B * E * 4 if cond is not None else 0)
+    d2h = 2 * B * C * 4 + B * 4
+
+    out = None
+    if rank == 0:
+        # ---- roofline of the dominant kernel (hidden-layer GEMM), CUDA events around each launch
+        L = _capi.lib()
+        L.ipoke_inn_profile_enable(eng._plan, 1)
+        tot = np.zeros(3)
+        cnt = np.zeros(3, dtype=np.int64)
+        ms3 = (ctypes.c_double * 3)()
+        n3 = (ctypes.c_int * 3)()
+        for s in range(args.steps):
+            flush.fill_(s & 0xFF)
+            for rev in (False, True):
+                call(net, zin if rev else x, reverse=rev)
+                L.ipoke_inn_profile_read(eng._plan, ms3, n3)
+                tot += np.array(list(ms3))
+                cnt += np.array(list(n3))
+        L.ipoke_inn_profile_enable(eng._plan, 0)
+        H = kw["flow_mid_channels"] if kind == "uncond" else kw["flow_mid_channels_factor"] * C
+        d = kw["flow_hidden_depth"]
+        P_w = macs_per_sample(kind, kw)
+        tail_macs = kw["n_flows"] * 4 * H * (C // 2)
+        hidden_flops_per_step = 2 * 2.0 * (P_w - tail_macs) * B             # fwd + rev
+        wbytes = 2 if args.precision == "bf16" else 4
+        hidden_launches = int(cnt[1] // args.steps)
+        # algorithmic bytes of the hidden GEMMs per step: weights once + activations in/out (bf16) per launch
+        hidden_bytes_per_step = 2.0 * ((P_w - tail_macs) * wbytes) + hidden_launches * (2.0 * B * 2 * H * wbytes)
+        t_hidden = tot[1] / args.steps * 1e-3
+        tf = hidden_flops_per_step / t_hidden / 1e12 * (3 if args.precision == "fp32" else 1)
+        gbs = hidden_bytes_per_step / t_hidden / 1e9
+        tensor_bound = (hidden_flops_per_step / (pk["bf16"] * 1e12)) > (hidden_bytes_per_step / (pk["hbm"] * 1e9))
+        roofline = {
+            "kernel": "inn_gemm_kernel<EPI_HIDDEN> (hidden Linear + bias + LeakyReLU)",
+            "bound": "tensor" if tensor_bound else "hbm",
+            "achieved": tf if tensor_bound else gbs,
+            "peak": pk["bf16"] if tensor_bound else pk["hbm"],
+            "unit": "TFLOP/s" if tensor_bound else "GB/s",
+            "frac": (tf / pk["bf16"]) if tensor_bound else (gbs / pk["hbm"]),
+            "traffic": None,
+            "peak_source": pk["src"] + " (burst)",
+            "launches_per_step": hidden_launches,
+            "avg_launch_us": 1e3 * tot[1] / max(cnt[1], 1),
+            "share_of_step": float(tot[1] / max(tot.sum(), 1e-9)),
+            "tflops_bf16_equiv": tf, "gbs": gbs,
+            "per_kind_ms_per_step": {"boundary": tot[0] / args.steps, "hidden": tot[1] / args.steps,
+                                     "tail": tot[2] / args.steps},
+            "note": "per-launch CUDA events in a separate pass right after the timed region (same inputs, L2 "
+                    "flushed each step); fp32-split mode counts 3 MMAs per algorithmic MAC in tflops_bf16_equiv",
+        }
+        cpu = cpu_port_run(args.config, min(B, 256), 3, 1, budget_s=15.0)
+        out = {
+            "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "bf16x2-split(fp32 parity)",
+            "data": "synthetic",
+            "config": {"workload": f"{args.config}: {src}; {B} latents per GPU per step, forward+logdet then reverse",
+                       "batch_per_gpu": B, "global_batch": B * world, "C": C, "E": E, "H": H, "depth": d,
+                       "n_flows": kw["n_flows"], "precision": args.precision, "parallelism": f"dp{world}",
+                       "l2": "256 MiB buffer written between timed iterations (L2 flush); weights "
+                             f"{P_w * wbytes / 1e6:.0f} MB"},
+            "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e / args.steps,
+                    "path": "ipoke_inn_forward_host / ipoke_inn_reverse_host (pinned host buffers)"},
+            "gpu_launches": launches * args.steps,
+            "launches_per_step": launches,
+            "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "flops_per_sample_fwd_rev": 4 * P_w,
+            "tflops_algorithmic": value * 4 * P_w / 1e12,
+            "frac_of_bf16_peak": value * 4 * P_w / 1e12 / (pk["bf16"] * world),
+        }
+    # ---- optional sweep (rank 0, N=1): the other precision at this size + large-batch regime
+    if rank == 0 and world == 1 and not args.no_sweep:
+        sweep = []
+        del net
+        torch.cuda.empty_cache()
+        cases = [(args.config, B, "fp32" if args.precision == "bf16" else "bf16")]
+        cases += [("cfgB", 4096, "bf16"), ("cfgB", 32768, "bf16"), ("cfgA", 4096, "bf16"), ("cfgA", 32768, "bf16"),
+                  ("cfgA", 32768, "fp32")]
+        for cname, cb, prec in cases:
+            try:
+                k2, kw2, _, _ = CONFIGS[cname]
+                torch.manual_seed(42)
+                n2 = (P.SupervisedTransformer(dict(kw2), precision=prec) if k2 == "cond" else
+                      P.UnsupervisedTransformer3(**kw2, precision=prec)).to(dev).eval()
+                C2, E2 = kw2["flow_in_channels"], kw2.get("flow_embedding_channels", 0)
+                xs = torch.randn(cb, C2, device=dev, generator=g)
+                cs = torch.randn(cb, E2, 1, 1, device=dev, generator=g) if k2 == "cond" else None
+                with torch.no_grad():
+                    f = (lambda inp, r: n2(inp, cs, reverse=r)) if k2 == "cond" else (lambda inp, r: n2(inp, reverse=r))
+                    z0, _ = f(xs, False)
+                    n2.flow.engine.assume_frozen = True
+                    for _ in range(3):
+                        f(xs, False); f(z0, True)
+                    torch.cuda.synchronize()
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    reps = 5
+                    e0.record()
+                    for _ in range(reps):
+                        f(xs, False); f(z0, True)
+                    e1.record()
+                    torch.cuda.synchronize()
+                    xr = f(z0, True)
+                    rt = float((xr.reshape(cb, C2) - xs).abs().max())
+                t = e0.elapsed_time(e1) / reps * 1e-3
+                pw2 = macs_per_sample(k2, kw2)
+                sweep.append({"config": cname, "batch": cb, "precision": prec, "samples_per_s": cb / t,
+                              "ms_per_step": t * 1e3, "tflops_algorithmic": cb * 4 * pw2 / t / 1e12,
+                              "frac_of_bf16_peak": cb * 4 * pw2 / t / 1e12 / pk["bf16"], "round_trip_max_abs": rt})
+                del n2, xs, cs, z0
+                torch.cuda.empty_cache()
+            except Exception as e:      # the sweep is informational; never lose the headline line
+                sweep.append({"config": cname, "batch": cb, "precision": prec, "error": str(e)[:200]})
+        out["sweep"] = sweep
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="cfgB", choices=list(CONFIGS))
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-sweep", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+
+    if args.impl == "reference":
+        if int(os.environ.get("RANK", 0)) != 0:
+            return
+        kind, kw, defB, src = CONFIGS[args.config]
+        B = args.batch or defB
+        cpu = cpu_port_run(args.config, min(B, 256), args.steps, args.warmup, budget_s=60.0)
+        line = {"impl": "reference", "metric": METRIC, "value": cpu["value"], "unit": "samples/s",
+                "n_gpus": args.gpus, "steps": cpu["steps"], "warmup": 1, "ms_per_step": cpu["ms_per_step"],
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic",
+                "config": {"workload": f"{args.config}: {src}; CPU port of the reference path (oracle/inn_oracle.py), "
+                                       f"batch {min(B, 256)} per step, forward+logdet then reverse"},
+                "cpu_baseline": {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "e2e": {"value": cpu["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return
+
+    out = gpu_run(args)
+    if out is not None:
+        print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

@@ -122,6 +122,12 @@ int ipoke_inn_flow_loss(const float* z, const float* logdet, int B, int C, float
 /* Number of kernels the last forward / reverse call on this plan launched (for bench accounting). */
 int ipoke_inn_last_launch_count(const ipoke_inn_plan* plan);
 
+/* Per-launch timing for the roofline report: while enabled, every kernel of a forward/reverse call is
+ * bracketed by CUDA events on the launching stream; read() waits for the last call and returns the summed
+ * milliseconds and launch counts of {boundary kernels, hidden-layer GEMMs, tail GEMMs} of that call.     */
+int ipoke_inn_profile_enable(ipoke_inn_plan* plan, int on);
+int ipoke_inn_profile_read(ipoke_inn_plan* plan, double* ms3, int* launches3);
+
 /* Test/diagnostic aid: byte offsets of the scratch buffers inside the workspace for batch B and the padded
  * dimensions, out[20] = {S0, S1, U_hi, U_lo, ACT_hi0, ACT_lo0, ACT_hi1, ACT_lo1, logdet, total, ldU, ldACT,
  * Hp, C2p, Ep, Np, ksplit, Gmax, packed_bytes, num_sms}.                                              */

@@ -102,6 +102,10 @@ struct ipoke_inn_plan {
   std::mutex mu;
   std::vector<std::unique_ptr<Program>> programs;
   int last_launches = 0;
+  // optional per-launch CUDA-event timing (bench roofline): events of the last profiled run
+  bool profile = false;
+  std::vector<cudaEvent_t> prof_ev;
+  std::vector<int> prof_kind;   // 0 boundary, 1 hidden GEMM, 2 tail GEMM
 };
 
 namespace {
@@ -480,7 +484,25 @@ cudaError_t launch_gemm(const ipoke_inn_plan* P, const GemmOp& g, cudaStream_t s
 int run_program(ipoke_inn_plan* P, Program* prog, const float* in, const float* cond, float* out, float* logdet_out,
                 float* block_outs, float* block_lds, cudaStream_t st) {
   const long long BC = (long long)prog->key.B * P->d.C;
+  size_t op_i = 0;
+  if (P->profile) {
+    while (P->prof_ev.size() < 2 * prog->ops.size()) {
+      cudaEvent_t ev;
+      cudaError_t e = cudaEventCreate(&ev);
+      if (e != cudaSuccess) return (int)e;
+      P->prof_ev.push_back(ev);
+    }
+    P->prof_kind.assign(prog->ops.size(), 0);
+  }
+  struct ProfScope {
+    ipoke_inn_plan* P; size_t i; cudaStream_t st;
+    ProfScope(ipoke_inn_plan* P_, size_t i_, cudaStream_t st_, int kind) : P(P_), i(i_), st(st_) {
+      if (P->profile) { P->prof_kind[i] = kind; cudaEventRecord(P->prof_ev[2 * i], st); }
+    }
+    ~ProfScope() { if (P->profile) cudaEventRecord(P->prof_ev[2 * i + 1], st); }
+  };
   for (Op& o : prog->ops) {
+    ProfScope scope(P, op_i++, st, o.kind == 0 ? 0 : (prog->gemms[o.gemm].mode == EPI_HIDDEN ? 1 : 2));
     if (o.kind == 0) {
       BoundaryParams b = o.b;
       if (o.user_in) b.in = in;
@@ -794,6 +816,32 @@ int ipoke_inn_flow_loss(const float* z, const float* logdet, int B, int C, float
 }
 
 int ipoke_inn_last_launch_count(const ipoke_inn_plan* plan) { return plan ? plan->last_launches : 0; }
+
+int ipoke_inn_profile_enable(ipoke_inn_plan* P, int on) {
+  if (!P) return IPOKE_INN_E_INVALID;
+  std::lock_guard<std::mutex> lock(P->mu);
+  P->profile = on != 0;
+  P->prof_kind.clear();
+  return 0;
+}
+
+int ipoke_inn_profile_read(ipoke_inn_plan* P, double* ms3, int* launches3) {
+  if (!P || !ms3 || !launches3) return IPOKE_INN_E_INVALID;
+  std::lock_guard<std::mutex> lock(P->mu);
+  for (int k = 0; k < 3; ++k) { ms3[k] = 0.0; launches3[k] = 0; }
+  const size_t n = P->prof_kind.size();
+  if (n == 0) return 0;
+  cudaError_t e = cudaEventSynchronize(P->prof_ev[2 * n - 1]);
+  if (e != cudaSuccess) return (int)e;
+  for (size_t i = 0; i < n; ++i) {
+    float ms = 0.f;
+    e = cudaEventElapsedTime(&ms, P->prof_ev[2 * i], P->prof_ev[2 * i + 1]);
+    if (e != cudaSuccess) return (int)e;
+    ms3[P->prof_kind[i]] += ms;
+    launches3[P->prof_kind[i]] += 1;
+  }
+  return 0;
+}
 
 int ipoke_inn_debug_layout(const ipoke_inn_plan* P, int B, long long* out, int n) {
   if (!P || !out || n < 20 || B <= 0) return IPOKE_INN_E_INVALID;
