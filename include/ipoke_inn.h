@@ -122,6 +122,11 @@ int ipoke_inn_flow_loss(const float* z, const float* logdet, int B, int C, float
 /* Number of kernels the last forward / reverse call on this plan launched (for bench accounting). */
 int ipoke_inn_last_launch_count(const ipoke_inn_plan* plan);
 
+/* Launch options: "graph" (default 1: replay a call as one CUDA graph when the caller's pointers repeat),
+ * "pdl" (default 1: programmatic dependent launch between the GEMM kernels).  Environment overrides at plan
+ * creation: IPOKE_INN_GRAPH=0/1, IPOKE_INN_PDL=0/1.                                                     */
+int ipoke_inn_set_option(ipoke_inn_plan* plan, const char* name, int value);
+
 /* Per-launch timing for the roofline report: while enabled, every kernel of a forward/reverse call is
  * bracketed by CUDA events on the launching stream; read() waits for the last call and returns the summed
  * milliseconds and launch counts of {boundary kernels, hidden-layer GEMMs, tail GEMMs} of that call.     */

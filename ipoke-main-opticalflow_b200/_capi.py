@@ -16,7 +16,7 @@ SYMBOLS = [
     "ipoke_inn_forward", "ipoke_inn_reverse", "ipoke_inn_forward_host", "ipoke_inn_reverse_host",
     "ipoke_inn_actnorm_stats", "ipoke_inn_actnorm_finalize", "ipoke_inn_flow_loss",
     "ipoke_inn_last_launch_count", "ipoke_inn_debug_layout",
-    "ipoke_inn_profile_enable", "ipoke_inn_profile_read",
+    "ipoke_inn_profile_enable", "ipoke_inn_profile_read", "ipoke_inn_set_option",
 ]
 
 
@@ -73,6 +73,8 @@ def lib():
     L.ipoke_inn_last_launch_count.argtypes = [vp]
     L.ipoke_inn_debug_layout.restype = i32
     L.ipoke_inn_debug_layout.argtypes = [vp, i32, vp, i32]
+    L.ipoke_inn_set_option.restype = i32
+    L.ipoke_inn_set_option.argtypes = [vp, ctypes.c_char_p, i32]
     L.ipoke_inn_profile_enable.restype = i32
     L.ipoke_inn_profile_enable.argtypes = [vp, i32]
     L.ipoke_inn_profile_read.restype = i32

@@ -33,6 +33,8 @@ struct BoundaryParams {
 };
 
 __global__ void __launch_bounds__(256) inn_boundary_kernel(const BoundaryParams p) {
+  grid_dep_launch();      // PDL: the next GEMM may start its prologue / weight prefetch
+  grid_dep_wait();        // previous kernel's state is complete and visible
   const long long total = static_cast<long long>(p.B) * p.C;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   const long long tid0 = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;

@@ -1,0 +1,186 @@
+// Epilogue warps (4..7) of inn_gemm_kernel -- textually included inside the kernel body.
+// One thread owns one accumulator row (TMEM lane); 128 threads cover the 128-row tile.
+    // ============================ epilogue ================================
+    const int q = warp - 4;                       // TMEM lane quarter (== warp % 4)
+    const int tid_e = threadIdx.x - 128;          // 0..127
+    const int r_loc = q * 32 + lane;              // row inside the tile
+    int it = 0;
+    int slab_ctr = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int m_tile = tile / p.num_n_tiles;
+      const int n_tile = tile - m_tile * p.num_n_tiles;
+      const int acc = (nacc == 2) ? (it & 1) : 0;
+      const uint32_t acc_phase = ((nacc == 2) ? (it >> 1) : it) & 1;
+      const int row = m_tile * BM + r_loc;
+      const bool row_ok = row < p.M;
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * acc_cols;
+
+      if (kMode == EPI_HIDDEN) {
+        // ---- bias slice -> smem while the MMAs of this tile run
+        float* bias_s = epi_f32 + (it & 1) * BN;
+        for (int c = tid_e; c < BN; c += EPI_THREADS) bias_s[c] = __ldg(p.bias + n_tile * BN + c);
+        named_bar_sync(1, EPI_THREADS);
+        mbar_wait(&tfull_bar[acc], acc_phase, 4);
+        tc_fence_after();
+        if (p.slab_bufs > 0) {
+          // ---- 64-column slabs: TMEM -> regs -> swizzled smem -> TMA store
+          const int n_slabs = BN >> 6;
+          for (int s = 0; s < n_slabs; ++s, ++slab_ctr) {
+            const int buf = (p.slab_bufs == 2) ? (slab_ctr & 1) : 0;
+            if (tid_e == 0) {
+              if (p.slab_bufs == 2) bulk_wait_read<1>();
+              else bulk_wait_read<0>();
+            }
+            named_bar_sync(1, EPI_THREADS);                      // slab buffer `buf` is free again
+            float v[64];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) tmem_ld16(t_row + s * 64 + c * 16, v + c * 16);
+            tmem_ld_wait();
+            if (s == n_slabs - 1) {                              // accumulator fully read: hand TMEM back
+              tc_fence_before();
+              mbar_arrive(&tempty_bar[acc]);
+            }
+            const float* bs = bias_s + s * 64;
+            uint8_t* slab_hi = epi_smem + (buf * kSplit) * SLAB_BYTES + r_loc * 128;
+            uint8_t* slab_lo = slab_hi + SLAB_BYTES;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              uint32_t hi[4], lo[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                float a = v[j * 8 + 2 * e] + bs[j * 8 + 2 * e];
+                float b = v[j * 8 + 2 * e + 1] + bs[j * 8 + 2 * e + 1];
+                a = a >= 0.f ? a : a * p.slope;
+                b = b >= 0.f ? b : b * p.slope;
+                __nv_bfloat16 h0, l0, h1, l1;
+                split_bf16(a, h0, l0);
+                split_bf16(b, h1, l1);
+                hi[e] = pack_bf16x2(h0, h1);
+                lo[e] = pack_bf16x2(l0, l1);
+              }
+              const int chunk = (j ^ (r_loc & 7)) << 4;          // 128-B swizzle: 16-B chunk index XOR (row % 8)
+              *reinterpret_cast<uint4*>(slab_hi + chunk) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+              if (kSplit == 2) *reinterpret_cast<uint4*>(slab_lo + chunk) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            }
+            fence_proxy_async();                                 // generic-proxy smem writes -> visible to TMA
+            named_bar_sync(1, EPI_THREADS);
+            if (tid_e == 0) {
+              const int col = n_tile * BN + s * 64;
+              tma_store_2d(&tmO0, epi_smem + (buf * kSplit) * SLAB_BYTES, col, m_tile * BM);
+              if (kSplit == 2) tma_store_2d(&tmO1, epi_smem + (buf * kSplit + 1) * SLAB_BYTES, col, m_tile * BM);
+              bulk_commit();
+            }
+          }
+        } else {
+          // ---- narrow tiles (BN < 64, small batches): direct 32-B global stores per thread
+          for (int c0 = 0; c0 < BN; c0 += 16) {
+            float v[16];
+            tmem_ld16(t_row + c0, v);
+            tmem_ld_wait();
+            const int col = n_tile * BN + c0;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              v[j] += bias_s[c0 + j];
+              v[j] = v[j] >= 0.f ? v[j] : v[j] * p.slope;
+            }
+            if (row_ok) {
+              uint32_t hi[8], lo[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                __nv_bfloat16 h0, l0, h1, l1;
+                split_bf16(v[2 * j], h0, l0);
+                split_bf16(v[2 * j + 1], h1, l1);
+                hi[j] = pack_bf16x2(h0, h1);
+                lo[j] = pack_bf16x2(l0, l1);
+              }
+              uint4* o = reinterpret_cast<uint4*>(p.out_hi + static_cast<size_t>(row) * p.ld_out + col);
+              o[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+              o[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+              if (kSplit == 2) {
+                uint4* ol = reinterpret_cast<uint4*>(p.out_lo + static_cast<size_t>(row) * p.ld_out + col);
+                ol[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                ol[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+              }
+            }
+          }
+          tc_fence_before();
+          mbar_arrive(&tempty_bar[acc]);
+        }
+      } else {
+        // ---- coupling tail: stage the kept half of this tile and both biases in smem (coalesced), overlapping
+        //      the MMAs; then one row per thread out of smem; then coalesced write-back.
+        float* keep_s = epi_f32;                                  // [128][BN + 1]
+        float* bias_s = epi_f32 + BM * (BN + 1);
+        float* bias_t = bias_s + BN;
+        const int ldk = BN + 1;
+        const int col_base = n_tile * BN;
+        for (int idx = tid_e; idx < BM * BN; idx += EPI_THREADS) {
+          const int r = idx >> p.bn_log2;
+          const int c = idx & (BN - 1);
+          const int grow = m_tile * BM + r;
+          const int gcol = col_base + c;
+          float kv = 0.f;
+          if (grow < p.M && gcol < p.n_valid) kv = p.state[static_cast<size_t>(grow) * p.ld_state + p.keep_off + gcol];
+          keep_s[r * ldk + c] = kv;
+        }
+        for (int c = tid_e; c < BN; c += EPI_THREADS) {
+          bias_s[c] = __ldg(p.bias + col_base + c);
+          bias_t[c] = __ldg(p.bias2 + col_base + c);
+        }
+        named_bar_sync(1, EPI_THREADS);
+        mbar_wait(&tfull_bar[acc], acc_phase, 4);
+        tc_fence_after();
+        float ld_sum = 0.f;
+        float* my_keep = keep_s + r_loc * ldk;
+        for (int c0 = 0; c0 < BN; c0 += 16) {
+          float vs[16], vt[16];
+          tmem_ld16(t_row + c0, vs);
+          tmem_ld16(t_row + BN + c0, vt);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int c = c0 + j;
+            const float s = tanhf(vs[j] + bias_s[c]);
+            const float t = vt[j] + bias_t[c];
+            const float keep = my_keep[c];
+            float nw;
+            if (kMode == EPI_TAIL_FWD) {
+              nw = keep * expf(s) + t;
+              if (col_base + c < p.n_valid) ld_sum += s;
+            } else {
+              nw = (keep - t) * expf(-s);
+            }
+            my_keep[c] = nw;
+            if (p.s_save != nullptr && row_ok && col_base + c < p.n_valid) {
+              p.s_save[static_cast<size_t>(row) * p.ld_save + col_base + c] = s;
+              p.keep_save[static_cast<size_t>(row) * p.ld_save + col_base + c] = keep;
+            }
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&tempty_bar[acc]);
+        if (kMode == EPI_TAIL_FWD && row_ok) {
+          if (p.logdet_atomic) atomicAdd(p.logdet + row, ld_sum);
+          else p.logdet[row] += ld_sum;
+        }
+        named_bar_sync(1, EPI_THREADS);
+        for (int idx = tid_e; idx < BM * BN; idx += EPI_THREADS) {
+          const int r = idx >> p.bn_log2;
+          const int c = idx & (BN - 1);
+          const int grow = m_tile * BM + r;
+          const int gcol = col_base + c;
+          if (grow < p.M && gcol < p.n_valid) {
+            const float nw = keep_s[r * ldk + c];
+            p.state[static_cast<size_t>(grow) * p.ld_state + p.keep_off + gcol] = nw;
+            if (p.u_hi != nullptr) {
+              __nv_bfloat16 h, l;
+              split_bf16(nw, h, l);
+              p.u_hi[static_cast<size_t>(grow) * p.ld_u + gcol] = h;
+              if (kSplit == 2) p.u_lo[static_cast<size_t>(grow) * p.ld_u + gcol] = l;
+            }
+          }
+        }
+        named_bar_sync(1, EPI_THREADS);                           // keep_s is reused by the next tile
+      }
+    }
+    if (kMode == EPI_HIDDEN && p.slab_bufs > 0 && tid_e == 0) bulk_wait<0>();   // stores landed before exit

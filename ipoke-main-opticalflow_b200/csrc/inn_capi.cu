@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <mutex>
@@ -54,9 +55,9 @@ struct Block {
 };
 
 struct GemmOp {
-  CUtensorMap tmA[2], tmW[2];
+  CUtensorMap tmA[2], tmW[2], tmO[2];
   GemmParams p;
-  int mode, grid, smem;
+  int mode, grid, smem, cluster;
 };
 struct Op {
   int kind;  // 0 boundary, 1 gemm
@@ -73,11 +74,22 @@ struct ProgramKey {
            want_blocks == o.want_blocks;
   }
 };
+struct GraphEntry {
+  const void* ptrs[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  cudaGraphExec_t exec = nullptr;
+  unsigned long long last_use = 0;
+};
 struct Program {
   ProgramKey key;
   std::vector<Op> ops;
   std::vector<GemmOp> gemms;
   int launches = 0;
+  std::vector<GraphEntry> graphs;     // instantiated CUDA graphs keyed by the caller's pointers
+  int graph_misses = 0, graph_hits = 0;
+  ~Program() {
+    for (auto& g : graphs)
+      if (g.exec) cudaGraphExecDestroy(g.exec);
+  }
 };
 
 struct WsLayout {
@@ -102,6 +114,12 @@ struct ipoke_inn_plan {
   std::mutex mu;
   std::vector<std::unique_ptr<Program>> programs;
   int last_launches = 0;
+  // launch options: 1 = replay the program as a CUDA graph (captured on an internal stream), PDL attribute on GEMMs
+  int use_graph = 1, use_pdl = 1, use_mcast = 0;
+  int w_prefetch = 1;
+  int latency_smem_cap_kb = 0;   // > 0: cap smem of one-wave launches so two kernels can be co-resident under PDL
+  cudaStream_t cap_stream = nullptr;
+  unsigned long long tick = 0;
   // optional per-launch CUDA-event timing (bench roofline): events of the last profiled run
   bool profile = false;
   std::vector<cudaEvent_t> prof_ev;
@@ -186,24 +204,52 @@ int make_map(const ipoke_inn_plan* P, CUtensorMap* m, const void* base, long lon
   return r == CUDA_SUCCESS ? 0 : IPOKE_INN_E_INTERNAL;
 }
 
-int stages_for(int ksplit, int mode, int bn) {
+struct TileCfg { int bn = 0, stages = 0, slab_bufs = 0, mc = 1; };
+
+// smem plan for one tile width: pipeline stages + epilogue staging must fit in 227 KB
+TileCfg tile_cfg(int ksplit, int mode, int bn) {
+  TileCfg t;
+  t.bn = bn;
+  const int avail = kMaxDynSmem - 1024 - SMEM_BARRIER_BYTES;
   const int sb = gemm_stage_bytes(ksplit, mode, bn);
-  return std::min(MAX_STAGES, (kMaxDynSmem - 1024 - SMEM_BARRIER_BYTES) / sb);
+  auto stages_with = [&](int slabs) {
+    const int epi = (gemm_epi_bytes(ksplit, mode, bn, slabs) + 15) & ~15;
+    return std::min(MAX_STAGES, (avail - epi) / sb);
+  };
+  if (mode == EPI_HIDDEN && bn >= 64) {
+    const int s2 = stages_with(2), s1 = stages_with(1);
+    if (s2 >= 4 || s2 == s1) { t.slab_bufs = 2; t.stages = s2; }
+    else { t.slab_bufs = 1; t.stages = s1; }
+  } else {
+    t.slab_bufs = 0;
+    t.stages = stages_with(0);
+  }
+  return t;
 }
 
 // Largest UMMA N that divides `rows_per_group`, keeps >= 2 pipeline stages and still yields about one CTA
 // per SM; otherwise the smallest (most tiles) -- small batches are latency/weight-streaming bound.
-int pick_bn(const ipoke_inn_plan* P, int mode, int rows_per_group, int tiles_other) {
+TileCfg pick_bn(const ipoke_inn_plan* P, int mode, int rows_per_group, int tiles_other) {
   static const int cand[5] = {256, 128, 64, 32, 16};
-  int best = 0;
+  TileCfg best;
   for (int i = 0; i < 5; ++i) {
     const int bn = cand[i];
     if (rows_per_group % bn != 0) continue;
-    if (stages_for(P->ksplit, mode, bn) < 2) continue;
-    best = bn;
-    if ((long long)tiles_other * (rows_per_group / bn) >= (long long)(P->num_sms * 4) / 5) return bn;
+    const TileCfg t = tile_cfg(P->ksplit, mode, bn);
+    if (t.stages < 2) continue;
+    best = t;
+    if ((long long)tiles_other * (rows_per_group / bn) >= (long long)(P->num_sms * 4) / 5) return t;
   }
   return best;
+}
+
+// Latency mode (one wave of tiles): CTAs of consecutive n-tiles share their A tile -> cluster + TMA multicast.
+int pick_mc(const ipoke_inn_plan* P, int tiles, int n_tiles, int tiles_per_group) {
+  if (!P->use_mcast || tiles > P->num_sms) return 1;
+  static const int cand[3] = {8, 4, 2};
+  for (int i = 0; i < 3; ++i)
+    if (n_tiles % cand[i] == 0 && tiles_per_group % cand[i] == 0) return cand[i];
+  return 1;
 }
 
 struct Builder {
@@ -259,26 +305,49 @@ struct Builder {
     prog->launches++;
     return g;
   }
-  void finish_gemm(GemmOp& g) {
+  void finish_gemm(GemmOp& g, const TileCfg& t) {
     g.p.M = B;
     g.p.num_m_tiles = m_tiles;
-    g.p.stages = std::min(stages_for(P->ksplit, g.mode, g.p.BN), std::max(2, g.p.num_k_blocks));
-    g.smem = gemm_smem_bytes(P->ksplit, g.mode, g.p.BN, g.p.stages);
-    g.grid = std::min(g.p.num_m_tiles * g.p.num_n_tiles, P->num_sms);
+    g.p.BN = t.bn;
+    g.p.bn_log2 = 0;
+    while ((1 << g.p.bn_log2) < t.bn) g.p.bn_log2++;
+    g.p.stages = std::min(t.stages, std::max(2, g.p.num_k_blocks));
+    g.p.slab_bufs = t.slab_bufs;
+    g.p.mcast = t.mc;
+    g.p.w_prefetch = P->w_prefetch;
+    const int tiles = g.p.num_m_tiles * g.p.num_n_tiles;
+    if (tiles <= P->num_sms && P->latency_smem_cap_kb > 0) {
+      // optional: keep the footprint small so the next kernel's CTA (PDL) can be co-resident
+      while (g.p.stages > 2 &&
+             gemm_smem_bytes(P->ksplit, g.mode, t.bn, g.p.stages, t.slab_bufs) > P->latency_smem_cap_kb * 1024)
+        g.p.stages--;
+    }
+    const int acc_cols = gemm_nsub(g.mode) * t.bn;
+    g.p.nacc = (2 * acc_cols <= 512) ? 2 : 1;
+    int cols = 32;
+    while (cols < g.p.nacc * acc_cols) cols <<= 1;
+    g.p.tmem_cols = cols;
+    g.p.epi_off = g.p.stages * gemm_stage_bytes(P->ksplit, g.mode, t.bn);
+    g.smem = gemm_smem_bytes(P->ksplit, g.mode, t.bn, g.p.stages, t.slab_bufs);
+    g.grid = t.mc > 1 ? tiles : std::min(tiles, P->num_sms);
+    g.cluster = t.mc;
     if (P->ksplit == 1) {
       g.tmA[1] = g.tmA[0];
       g.tmW[1] = g.tmW[0];
+      g.tmO[1] = g.tmO[0];
     }
   }
 
   // hidden layers of one chain; returns the ACT buffer index holding the last hidden activation
   int chain(const Chain& c) {
     const int rows = c.G * P->Hp;
-    const int bn = pick_bn(P, EPI_HIDDEN, P->Hp, m_tiles * c.G);
+    TileCfg tc = pick_bn(P, EPI_HIDDEN, P->Hp, m_tiles * c.G);
+    const int bn = tc.bn;
+    tc.mc = pick_mc(P, m_tiles * (rows / bn), rows / bn, P->Hp / bn);
+    const int a_box = BM / tc.mc;
     for (size_t l = 0; l < c.L.size(); ++l) {
       const LayerW& L = c.L[l];
       GemmOp& g = add_gemm(EPI_HIDDEN);
-      g.p.BN = bn;
       g.p.num_n_tiles = rows / bn;
       g.p.tiles_per_group = P->Hp / bn;
       g.p.num_k_blocks = L.Kp / BK;
@@ -291,14 +360,16 @@ struct Builder {
       for (int sp = 0; sp < P->ksplit; ++sp) {
         if (l == 0) {
           const long long base = (sp == 0 ? wl.U_hi : wl.U_lo) + 2ll * c.a_col_off;
-          err |= make_map(P, &g.tmA[sp], ws + base, c.Kin_p, B, 2ll * P->ldU, BM);
+          err |= make_map(P, &g.tmA[sp], ws + base, c.Kin_p, B, 2ll * P->ldU, a_box);
         } else {
           const long long base = sp == 0 ? wl.ACT_hi[(l - 1) & 1] : wl.ACT_lo[(l - 1) & 1];
-          err |= make_map(P, &g.tmA[sp], ws + base, rows, B, 2ll * P->ldACT, BM);
+          err |= make_map(P, &g.tmA[sp], ws + base, rows, B, 2ll * P->ldACT, a_box);
         }
         err |= make_map(P, &g.tmW[sp], packed + (sp == 0 ? L.hi : L.lo), L.Kp, L.rows, 2ll * L.Kp, bn);
+        // output slabs (TMA store): same 64 x 128 box as the next layer's A loads
+        err |= make_map(P, &g.tmO[sp], ws + (sp == 0 ? wl.ACT_hi[l & 1] : wl.ACT_lo[l & 1]), rows, B, 2ll * P->ldACT, BM);
       }
-      finish_gemm(g);
+      finish_gemm(g, tc);
     }
     return (int)(c.L.size() - 1) & 1;
   }
@@ -306,9 +377,10 @@ struct Builder {
   void tail(const Block& blk, int i, int act_buf, int G, int state_buf, bool reverse, bool write_u) {
     const Tail& t = blk.tails[i];
     GemmOp& g = add_gemm(reverse ? EPI_TAIL_REV : EPI_TAIL_FWD);
-    const int bn = pick_bn(P, g.mode, P->Np, m_tiles);
-    g.p.BN = bn;
+    TileCfg tc = pick_bn(P, g.mode, P->Np, m_tiles);
+    const int bn = tc.bn;
     g.p.num_n_tiles = P->Np / bn;
+    tc.mc = pick_mc(P, m_tiles * (P->Np / bn), P->Np / bn, P->Np / bn);
     g.p.tiles_per_group = 1 << 30;
     g.p.num_k_blocks = P->Hp / BK;
     g.p.a_group_stride = 0;
@@ -331,10 +403,11 @@ struct Builder {
     }
     for (int sp = 0; sp < P->ksplit; ++sp) {
       const long long base = sp == 0 ? wl.ACT_hi[act_buf] : wl.ACT_lo[act_buf];
-      err |= make_map(P, &g.tmA[sp], ws + base, G * P->Hp, B, 2ll * P->ldACT, BM);
+      err |= make_map(P, &g.tmA[sp], ws + base, G * P->Hp, B, 2ll * P->ldACT, BM / tc.mc);
       err |= make_map(P, &g.tmW[sp], packed + (sp == 0 ? t.w.hi : t.w.lo), t.w.Kp, t.w.rows, 2ll * t.w.Kp, bn);
+      g.tmO[sp] = g.tmA[sp];      // unused by the tail epilogue
     }
-    finish_gemm(g);
+    finish_gemm(g, tc);
   }
 
   void coupling(const Block& blk, int state_buf, bool reverse) {
@@ -461,28 +534,51 @@ Program* get_program(ipoke_inn_plan* P, const ProgramKey& key, int* err) {
 }
 
 template <int kSplit, int kMode>
-cudaError_t launch_gemm_t(const GemmOp& g, cudaStream_t st) {
-  inn_gemm_kernel<kSplit, kMode><<<g.grid, GEMM_THREADS, g.smem, st>>>(g.tmA[0], g.tmA[1], g.tmW[0], g.tmW[1], g.p);
-  return cudaGetLastError();
+cudaError_t launch_gemm_t(const GemmOp& g, cudaStream_t st, int pdl) {
+  cudaLaunchConfig_t cfg;
+  std::memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)g.grid);
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = (size_t)g.smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (g.cluster > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = (unsigned)g.cluster;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  return cudaLaunchKernelEx(&cfg, inn_gemm_kernel<kSplit, kMode>, g.tmA[0], g.tmA[1], g.tmW[0], g.tmW[1], g.tmO[0],
+                            g.tmO[1], g.p);
 }
 
 cudaError_t launch_gemm(const ipoke_inn_plan* P, const GemmOp& g, cudaStream_t st) {
+  const int pdl = P->use_pdl;
   if (P->ksplit == 2) {
     switch (g.mode) {
-      case EPI_HIDDEN: return launch_gemm_t<2, EPI_HIDDEN>(g, st);
-      case EPI_TAIL_FWD: return launch_gemm_t<2, EPI_TAIL_FWD>(g, st);
-      default: return launch_gemm_t<2, EPI_TAIL_REV>(g, st);
+      case EPI_HIDDEN: return launch_gemm_t<2, EPI_HIDDEN>(g, st, pdl);
+      case EPI_TAIL_FWD: return launch_gemm_t<2, EPI_TAIL_FWD>(g, st, pdl);
+      default: return launch_gemm_t<2, EPI_TAIL_REV>(g, st, pdl);
     }
   }
   switch (g.mode) {
-    case EPI_HIDDEN: return launch_gemm_t<1, EPI_HIDDEN>(g, st);
-    case EPI_TAIL_FWD: return launch_gemm_t<1, EPI_TAIL_FWD>(g, st);
-    default: return launch_gemm_t<1, EPI_TAIL_REV>(g, st);
+    case EPI_HIDDEN: return launch_gemm_t<1, EPI_HIDDEN>(g, st, pdl);
+    case EPI_TAIL_FWD: return launch_gemm_t<1, EPI_TAIL_FWD>(g, st, pdl);
+    default: return launch_gemm_t<1, EPI_TAIL_REV>(g, st, pdl);
   }
 }
 
-int run_program(ipoke_inn_plan* P, Program* prog, const float* in, const float* cond, float* out, float* logdet_out,
-                float* block_outs, float* block_lds, cudaStream_t st) {
+int issue_program(ipoke_inn_plan* P, Program* prog, const float* in, const float* cond, float* out, float* logdet_out,
+                  float* block_outs, float* block_lds, cudaStream_t st) {
   const long long BC = (long long)prog->key.B * P->d.C;
   size_t op_i = 0;
   if (P->profile) {
@@ -522,8 +618,17 @@ int run_program(ipoke_inn_plan* P, Program* prog, const float* in, const float* 
           b.raw_out = out;
         }
       }
-      inn_boundary_kernel<<<o.b_grid, 256, 0, st>>>(b);
-      cudaError_t e = cudaGetLastError();
+      cudaLaunchConfig_t cfg;
+      std::memset(&cfg, 0, sizeof(cfg));
+      cfg.gridDim = dim3((unsigned)o.b_grid);
+      cfg.blockDim = dim3(256);
+      cfg.stream = st;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[0].val.programmaticStreamSerializationAllowed = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = P->use_pdl ? 1 : 0;
+      cudaError_t e = cudaLaunchKernelEx(&cfg, inn_boundary_kernel, b);
       if (e != cudaSuccess) return (int)e;
     } else {
       cudaError_t e = launch_gemm(P, prog->gemms[o.gemm], st);
@@ -532,6 +637,62 @@ int run_program(ipoke_inn_plan* P, Program* prog, const float* in, const float* 
   }
   P->last_launches = prog->launches;
   return 0;
+}
+
+// Replay as a CUDA graph when the caller's pointers repeat (steady-state loops); plain launches otherwise.
+int run_program(ipoke_inn_plan* P, Program* prog, const float* in, const float* cond, float* out, float* logdet_out,
+                float* block_outs, float* block_lds, cudaStream_t st) {
+  if (!P->use_graph || P->profile || prog->graph_misses > 8 + 4 * prog->graph_hits)
+    return issue_program(P, prog, in, cond, out, logdet_out, block_outs, block_lds, st);
+  const void* ptrs[6] = {in, cond, out, logdet_out, block_outs, block_lds};
+  ++P->tick;
+  for (auto& g : prog->graphs) {
+    if (std::memcmp(g.ptrs, ptrs, sizeof(ptrs)) == 0) {
+      g.last_use = P->tick;
+      ++prog->graph_hits;
+      cudaError_t e = cudaGraphLaunch(g.exec, st);
+      P->last_launches = prog->launches;
+      return e == cudaSuccess ? 0 : (int)e;
+    }
+  }
+  ++prog->graph_misses;
+  if (!P->cap_stream) {
+    cudaError_t e = cudaStreamCreateWithFlags(&P->cap_stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) return (int)e;
+  }
+  cudaError_t e = cudaStreamBeginCapture(P->cap_stream, cudaStreamCaptureModeThreadLocal);
+  if (e != cudaSuccess) return (int)e;
+  int rc = issue_program(P, prog, in, cond, out, logdet_out, block_outs, block_lds, P->cap_stream);
+  cudaGraph_t graph = nullptr;
+  e = cudaStreamEndCapture(P->cap_stream, &graph);
+  if (rc != 0 || e != cudaSuccess || graph == nullptr) {
+    if (graph) cudaGraphDestroy(graph);
+    cudaGetLastError();
+    P->use_graph = 0;          // capture unsupported here: fall back to plain launches for good
+    return issue_program(P, prog, in, cond, out, logdet_out, block_outs, block_lds, st);
+  }
+  cudaGraphExec_t exec = nullptr;
+  e = cudaGraphInstantiate(&exec, graph, 0);
+  cudaGraphDestroy(graph);
+  if (e != cudaSuccess || exec == nullptr) {
+    cudaGetLastError();
+    P->use_graph = 0;
+    return issue_program(P, prog, in, cond, out, logdet_out, block_outs, block_lds, st);
+  }
+  if (prog->graphs.size() >= 4) {                       // evict the least recently used
+    size_t lru = 0;
+    for (size_t i = 1; i < prog->graphs.size(); ++i)
+      if (prog->graphs[i].last_use < prog->graphs[lru].last_use) lru = i;
+    cudaGraphExecDestroy(prog->graphs[lru].exec);
+    prog->graphs.erase(prog->graphs.begin() + lru);
+  }
+  GraphEntry ge;
+  std::memcpy(ge.ptrs, ptrs, sizeof(ptrs));
+  ge.exec = exec;
+  ge.last_use = P->tick;
+  prog->graphs.push_back(ge);
+  e = cudaGraphLaunch(exec, st);
+  return e == cudaSuccess ? 0 : (int)e;
 }
 
 int check_common(const ipoke_inn_plan* P, const void* packed, const void* a, const void* b, int B, int kb, int ke,
@@ -572,6 +733,11 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (!P) return IPOKE_INN_E_INTERNAL;
   P->d = d;
   P->device = device;
+  if (const char* e = std::getenv("IPOKE_INN_GRAPH")) P->use_graph = std::atoi(e) != 0;
+  if (const char* e = std::getenv("IPOKE_INN_PDL")) P->use_pdl = std::atoi(e) != 0;
+  if (const char* e = std::getenv("IPOKE_INN_MCAST")) P->use_mcast = std::atoi(e) != 0;
+  if (const char* e = std::getenv("IPOKE_INN_WPREFETCH")) P->w_prefetch = std::atoi(e) != 0;
+  if (const char* e = std::getenv("IPOKE_INN_STAGECAP_KB")) P->latency_smem_cap_kb = std::atoi(e);
   P->ksplit = d.precision == IPOKE_INN_PREC_FP32_SPLIT ? 2 : 1;
   P->C2 = d.C / 2;
   P->C2p = (int)round_up(P->C2, BK);
@@ -816,6 +982,16 @@ int ipoke_inn_flow_loss(const float* z, const float* logdet, int B, int C, float
 }
 
 int ipoke_inn_last_launch_count(const ipoke_inn_plan* plan) { return plan ? plan->last_launches : 0; }
+
+int ipoke_inn_set_option(ipoke_inn_plan* P, const char* name, int value) {
+  if (!P || !name) return IPOKE_INN_E_INVALID;
+  std::lock_guard<std::mutex> lock(P->mu);
+  if (std::strcmp(name, "graph") == 0) P->use_graph = value != 0;
+  else if (std::strcmp(name, "pdl") == 0) { P->use_pdl = value != 0; P->programs.clear(); }
+  else if (std::strcmp(name, "mcast") == 0) { P->use_mcast = value != 0; P->programs.clear(); }
+  else return IPOKE_INN_E_INVALID;
+  return 0;
+}
 
 int ipoke_inn_profile_enable(ipoke_inn_plan* P, int on) {
   if (!P) return IPOKE_INN_E_INVALID;
