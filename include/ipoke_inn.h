@@ -100,6 +100,35 @@ int ipoke_inn_forward(ipoke_inn_plan* plan, const void* packed, const float* x, 
 int ipoke_inn_reverse(ipoke_inn_plan* plan, const void* packed, const float* z, const float* cond, float* x,
                       int B, int block_begin, int block_end, void* workspace, void* stream);
 
+/* ---- training: forward that keeps what the backward pass needs, and the fused backward -----------------
+ * The reference has no backward code of its own: gradients are torch.autograd over the ops of
+ * flow_blocks.py:125-143, 255-267, modules.py:190-191, 292-301.  These two calls replace
+ * that autograd graph: `saved` (ipoke_inn_saved_bytes(plan, B) bytes, caller-owned) receives every hidden
+ * activation (bf16, as the GEMMs wrote them), the MLP inputs, and per half-step the tanh output s and the
+ * pre-update kept half; block_outs ([n_flows, B, C], = flow.last_outs) is required because block k's
+ * ActNorm backward reads its input from block_outs[k-1].                                                */
+size_t ipoke_inn_saved_bytes(const ipoke_inn_plan* plan, int B);
+int ipoke_inn_forward_train(ipoke_inn_plan* plan, const void* packed, const float* x, const float* cond, float* z,
+                            float* logdet, float* block_outs, float* block_logdets, int B, void* workspace,
+                            void* saved, void* stream);
+
+/* Gradients of  sum(dz * z) + sum(dlogdet * logdet)  over blocks [block_begin, block_end), last block first.
+ *   dz          : [B,C] gradient w.r.t. the output of block block_end-1 (the flow output z when block_end == n_flows)
+ *   dlogdet     : [B]
+ *   dx          : nullable [B,C], gradient w.r.t. the input of block block_begin (feed it as dz of the next call
+ *                 when the backward pass is issued in block chunks to overlap the gradient all-reduce)
+ *   dcond       : nullable [B,E]; zeroed when block_end == n_flows, accumulated otherwise
+ *   grad_w/grad_b      : host arrays [num_linears] of device pointers, same order as ipoke_inn_pack; each
+ *                        tensor has the nn.Linear's own shape ([out,in] / [out]) and is OVERWRITTEN
+ *   grad_loc/grad_scale: host arrays [n_flows] of device pointers to C floats each (ActNorm, incl. the
+ *                        d log|scale| term of the log-det), overwritten
+ * Only the entries of blocks in the range are touched.                                                   */
+int ipoke_inn_backward(ipoke_inn_plan* plan, const void* packed, const float* x, const float* cond,
+                       const float* block_outs, const void* saved, const float* dz, const float* dlogdet, float* dx,
+                       float* dcond, float* const* grad_w, float* const* grad_b, float* const* grad_loc,
+                       float* const* grad_scale, int B, int block_begin, int block_end, void* workspace,
+                       void* stream);
+
 /* Same two calls with HOST buffers (pinned or pageable): host->device copies of x/cond, the kernels, and
  * device->host copies of the results are all enqueued on `stream`; the caller synchronises the stream. */
 int ipoke_inn_forward_host(ipoke_inn_plan* plan, const void* packed, const float* x_host, const float* cond_host,
@@ -132,6 +161,8 @@ int ipoke_inn_set_option(ipoke_inn_plan* plan, const char* name, int value);
  * milliseconds and launch counts of {boundary kernels, hidden-layer GEMMs, tail GEMMs} of that call.     */
 int ipoke_inn_profile_enable(ipoke_inn_plan* plan, int on);
 int ipoke_inn_profile_read(ipoke_inn_plan* plan, double* ms3, int* launches3);
+/* n kinds: 0 elementwise, 1 hidden GEMM, 2 tail GEMM, 3 dgrad GEMM, 4 wgrad GEMM (3, 4: backward calls). */
+int ipoke_inn_profile_read_n(ipoke_inn_plan* plan, double* ms, int* launches, int n);
 
 /* Test/diagnostic aid: byte offsets of the scratch buffers inside the workspace for batch B and the padded
  * dimensions, out[20] = {S0, S1, U_hi, U_lo, ACT_hi0, ACT_lo0, ACT_hi1, ACT_lo1, logdet, total, ldU, ldACT,

@@ -17,6 +17,7 @@ SYMBOLS = [
     "ipoke_inn_actnorm_stats", "ipoke_inn_actnorm_finalize", "ipoke_inn_flow_loss",
     "ipoke_inn_last_launch_count", "ipoke_inn_debug_layout",
     "ipoke_inn_profile_enable", "ipoke_inn_profile_read", "ipoke_inn_set_option",
+    "ipoke_inn_saved_bytes", "ipoke_inn_forward_train", "ipoke_inn_backward", "ipoke_inn_profile_read_n",
 ]
 
 
@@ -79,9 +80,14 @@ def lib():
     L.ipoke_inn_profile_enable.argtypes = [vp, i32]
     L.ipoke_inn_profile_read.restype = i32
     L.ipoke_inn_profile_read.argtypes = [vp, vp, vp]
-    if hasattr(L, "ipoke_inn_backward"):
-        L.ipoke_inn_backward.restype = i32
-        L.ipoke_inn_backward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, vp, vp]
+    L.ipoke_inn_saved_bytes.restype = ctypes.c_size_t
+    L.ipoke_inn_saved_bytes.argtypes = [vp, i32]
+    L.ipoke_inn_forward_train.restype = i32
+    L.ipoke_inn_forward_train.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, i32, vp, vp, vp]
+    L.ipoke_inn_backward.restype = i32
+    L.ipoke_inn_backward.argtypes = [vp] * 14 + [i32, i32, i32, vp, vp]
+    L.ipoke_inn_profile_read_n.restype = i32
+    L.ipoke_inn_profile_read_n.argtypes = [vp, vp, vp, i32]
     _lib = L
     return L
 

@@ -15,7 +15,8 @@ def flow_forward(engine, x, cond):
     """-> z [B,C], logdet [B], block_outs [n,B,C], block_logdets [n,B]."""
     if _needs_grad(engine, x, cond):
         from .backward import FlowFunction
-        return FlowFunction.run(engine, x, cond)
+        params = engine.grad_layout()[3]
+        return FlowFunction.apply(engine, x, cond, *params)
     with torch.no_grad():
         return engine.forward(x, cond, want_blocks=True)
 

@@ -1,9 +1,57 @@
-"""Training path: autograd.Function over the fused forward and backward kernels."""
+"""Training path: one autograd.Function per flow call over the fused forward (with saved state) and the fused
+backward kernels, so that the caller's ``loss.backward()`` (Lightning's loop in the reference,
+models/second_stage_video_fc.py:448-490) reaches ``ipoke_inn_backward``.
+
+Parameter gradients are written by the kernels straight into ONE flat fp32 buffer laid out in
+``flow.parameters()`` order; autograd receives views of it (AccumulateGrad adopts them without a copy when
+``.grad`` is None), and ``engine.last_flat_grad`` / ``engine.grad_layout()`` expose the buffer so that the
+gradient all-reduce of the training step is a few large NCCL calls on contiguous memory (parallel.GradSync).
+"""
 import torch
 
 
-class FlowFunction:
+class FlowFunction(torch.autograd.Function):
     @staticmethod
-    def run(engine, x, cond):
-        raise NotImplementedError("ipoke_inn_b200: the fused backward kernels are not built yet in this round; "
-                                  "run forward/reverse under torch.no_grad()")
+    def forward(ctx, engine, x, cond, *params):
+        z, ld, outs, lds, saved, x2, c2 = engine.forward_train(x, cond)
+        ctx.engine = engine
+        ctx.saved_buf = saved
+        ctx.x_shape = x.shape
+        ctx.cond_shape = None if cond is None else cond.shape
+        ctx.save_for_backward(x2, c2, outs)
+        ctx.mark_non_differentiable(outs, lds)
+        return z, ld, outs, lds
+
+    @staticmethod
+    def backward(ctx, dz, dld, _douts, _dlds):
+        engine = ctx.engine
+        x2, c2, outs = ctx.saved_tensors
+        need_x = ctx.needs_input_grad[1]
+        need_c = c2 is not None and ctx.needs_input_grad[2]
+        flat, views, ptrs = engine.new_grad_buffer()
+        dz = dz.contiguous().float()
+        dld = dld.contiguous().float()
+        hook = engine.grad_ready_hook
+        if hook is None:
+            dx, dcond = engine.backward(x2, c2, outs, ctx.saved_buf, dz, dld, ptrs, want_dx=need_x, want_dcond=need_c)
+        else:
+            # chunked by flow block (last first) so that the hook can start reducing a block's gradients while
+            # the earlier blocks are still being computed
+            n = engine.n_flows
+            chunk = max(1, int(engine.grad_chunk_blocks))
+            dcond = None
+            g = dz
+            ke = n
+            while ke > 0:
+                kb = max(0, ke - chunk)
+                last = kb == 0
+                dx, dcond = engine.backward(x2, c2, outs, ctx.saved_buf, g, dld, ptrs, want_dx=(not last) or need_x,
+                                            want_dcond=need_c, block_begin=kb, block_end=ke, dcond=dcond)
+                hook(engine, flat, kb, ke)
+                g = dx
+                ke = kb
+        engine.last_flat_grad = flat
+        ctx.saved_buf = None
+        gx = dx.view(ctx.x_shape) if (need_x and dx is not None) else None
+        gc = dcond.view(ctx.cond_shape) if (need_c and dcond is not None) else None
+        return (None, gx, gc) + tuple(views)

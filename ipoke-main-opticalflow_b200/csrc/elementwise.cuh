@@ -26,6 +26,7 @@ struct BoundaryParams {
   __nv_bfloat16* u_hi; __nv_bfloat16* u_lo; int ld_u;                // nullable
   int u_begin, u_count, u_pad;          // columns p in [u_begin, u_begin+u_count) -> U col p-u_begin; zero to u_pad
   const float* cond; int E; int ld_cond; int u_cond_off; int e_pad;  // cond nullable
+  __nv_bfloat16* u2_hi; __nv_bfloat16* u2_lo;                         // nullable: second buffer that gets the cond columns
   float* logdet; const float* an_logdet; int logdet_init;            // logdet nullable
   float* block_logdet;                                                // nullable snapshot before the add
   float* block_logdet2;                                               // nullable second snapshot
@@ -77,6 +78,10 @@ __global__ void __launch_bounds__(256) inn_boundary_kernel(const BoundaryParams 
       const size_t o = static_cast<size_t>(b) * p.ld_u + p.u_count + static_cast<int>(idx - static_cast<long long>(b) * w);
       p.u_hi[o] = __float2bfloat16_rn(0.f);
       if (p.u_lo) p.u_lo[o] = __float2bfloat16_rn(0.f);
+      if (p.u2_hi) {
+        p.u2_hi[o] = __float2bfloat16_rn(0.f);
+        if (p.u2_lo) p.u2_lo[o] = __float2bfloat16_rn(0.f);
+      }
     }
   }
   // conditioning columns (written once per pass)
@@ -91,6 +96,150 @@ __global__ void __launch_bounds__(256) inn_boundary_kernel(const BoundaryParams 
       const size_t o = static_cast<size_t>(b) * p.ld_u + p.u_cond_off + e;
       p.u_hi[o] = h;
       if (p.u_lo) p.u_lo[o] = l;
+      if (p.u2_hi) {
+        p.u2_hi[o] = h;
+        if (p.u2_lo) p.u2_lo[o] = l;
+      }
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------- backward (elementwise parts)
+// Gradients are those of sum(dz*z) + sum(dlogdet*logdet); the reference has no backward code of its own
+// (torch.autograd over flow_blocks.py:125-143, 255-267 and modules.py:292-301).
+
+// Start of a backward call: sum_b dlogdet[b] (ActNorm's log|scale| term, modules.py:298-301), zero the
+// conditioning-gradient accumulator and the ActNorm partial-sum scratch.
+__global__ void __launch_bounds__(256) inn_bwd_init_kernel(const float* __restrict__ dlogdet, int B, float* dld_sum,
+                                                           float* zero0, long long n0, float* zero1, long long n1) {
+  grid_dep_launch();
+  grid_dep_wait();
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const long long tid0 = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (zero0) for (long long i = tid0; i < n0; i += stride) zero0[i] = 0.f;
+  if (zero1) for (long long i = tid0; i < n1; i += stride) zero1[i] = 0.f;
+  if (blockIdx.x == 0) {
+    __shared__ double red[256];
+    double a = 0.0;
+    for (int b = threadIdx.x; b < B; b += blockDim.x) a += static_cast<double>(dlogdet[b]);
+    red[threadIdx.x] = a;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+      if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s];
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) *dld_sum = static_cast<float>(red[0]);
+  }
+}
+
+// Backward of one affine half-step  y = keep * exp(s) + t,  logdet += sum_j s_j,  s = tanh(s_pre)
+// (flow_blocks.py:138-142):  dt = g,  ds_pre = (g * keep * exp(s) + dlogdet[b]) * (1 - s^2),  dkeep = g * exp(s).
+// Writes the bf16 (hi/lo) operand [ds_pre | dt] of the tail dgrad / wgrad GEMMs and dkeep in place.
+struct TailBwdParams {
+  float* dstate; int ld_state; int keep_off;      // gradient of the coupling state [B, C]; kept half at keep_off
+  const float* s_save; const float* keep_save; int ld_save;   // [B, C/2] from the training forward
+  const float* dlogdet;                            // [B]
+  __nv_bfloat16* dt_hi; __nv_bfloat16* dt_lo; int ld_dt; int npk;   // [B, 2*npk]: cols [0,npk) = ds_pre, [npk, 2npk) = dt
+  int B, C2;
+};
+
+__global__ void __launch_bounds__(256) inn_tail_bwd_kernel(const TailBwdParams p) {
+  grid_dep_launch();
+  grid_dep_wait();
+  const long long total = static_cast<long long>(p.B) * p.npk;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+    const int b = static_cast<int>(idx / p.npk);
+    const int c = static_cast<int>(idx - static_cast<long long>(b) * p.npk);
+    float ds_pre = 0.f, dt = 0.f;
+    if (c < p.C2) {
+      float* gp = p.dstate + static_cast<size_t>(b) * p.ld_state + p.keep_off + c;
+      const float g = *gp;
+      const float s = p.s_save[static_cast<size_t>(b) * p.ld_save + c];
+      const float keep = p.keep_save[static_cast<size_t>(b) * p.ld_save + c];
+      const float es = expf(s);
+      dt = g;
+      ds_pre = (g * keep * es + __ldg(p.dlogdet + b)) * (1.f - s * s);
+      *gp = g * es;
+    }
+    __nv_bfloat16 h, l;
+    const size_t o = static_cast<size_t>(b) * p.ld_dt + c;
+    split_bf16(ds_pre, h, l);
+    p.dt_hi[o] = h;
+    if (p.dt_lo) p.dt_lo[o] = l;
+    split_bf16(dt, h, l);
+    p.dt_hi[o + p.npk] = h;
+    if (p.dt_lo) p.dt_lo[o + p.npk] = l;
+  }
+}
+
+// Backward of the block boundary: InvLeakyRelu (flow_blocks.py:380-381), ActNorm (modules.py:292-301) and the
+// previous block's Shuffle (flow_blocks.py:322-324) in one pass:
+//   a = scale * (h0 + loc);  da = g * (a >= 0 ? 1 : alpha);  dh0 = da * scale
+//   dloc_c = sum_b da * scale_c;  dscale_c = sum_b da * (h0 + loc_c) + (sum_b dlogdet[b]) / scale_c
+//   dst[b, map[c]] = dh0   (map = previous block's forward gather map; identity for the first block)
+// Channel sums: per-CTA partials -> atomics into scratch -> the last CTA to finish writes the final values.
+struct BoundaryBwdParams {
+  const float* g; int ld_g;              // gradient w.r.t. the block's post-activation state [B, C]
+  const float* h0; int ld_h0;            // the block's input (before ActNorm) saved by the forward pass
+  const float* loc; const float* scale;  // packed copies [C]
+  int leaky; float alpha;
+  float* dst; int ld_dst;                // nullable
+  const int* map;                        // nullable = identity
+  float* acc;                            // scratch [2*C] zeroed at the start of the backward call
+  unsigned int* counter;                 // zeroed likewise
+  const float* dld_sum;
+  float* gloc; float* gscale;            // final [C] each
+  int B, C;
+};
+
+__global__ void __launch_bounds__(256) inn_boundary_bwd_kernel(const BoundaryBwdParams p) {
+  grid_dep_launch();
+  grid_dep_wait();
+  __shared__ float red[2][8][33];
+  __shared__ bool is_last;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
+  const int rows_per = (p.B + gridDim.y - 1) / gridDim.y;
+  const int r0 = blockIdx.y * rows_per;
+  const int r1 = min(p.B, r0 + rows_per);
+  float a_loc = 0.f, a_scale = 0.f;
+  if (c < p.C) {
+    const float sc = __ldg(p.scale + c), lc = __ldg(p.loc + c);
+    const int q = p.map ? __ldg(p.map + c) : c;
+    for (int r = r0 + ty; r < r1; r += 8) {
+      const float xin = __ldg(p.h0 + static_cast<size_t>(r) * p.ld_h0 + c) + lc;
+      float da = __ldg(p.g + static_cast<size_t>(r) * p.ld_g + c);
+      if (p.leaky && sc * xin < 0.f) da *= p.alpha;
+      a_scale += da * xin;
+      const float dh = da * sc;
+      a_loc += dh;
+      if (p.dst) p.dst[static_cast<size_t>(r) * p.ld_dst + q] = dh;
+    }
+  }
+  red[0][ty][tx] = a_loc;
+  red[1][ty][tx] = a_scale;
+  __syncthreads();
+  if (ty == 0 && c < p.C) {
+    float sl = 0.f, ss = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { sl += red[0][k][tx]; ss += red[1][k][tx]; }
+    atomicAdd(p.acc + c, sl);
+    atomicAdd(p.acc + p.C + c, ss);
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int done = atomicAdd(p.counter, 1u);
+    is_last = done == gridDim.x * gridDim.y - 1;
+  }
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    const float dls = *p.dld_sum;
+    for (int i = threadIdx.x; i < p.C; i += blockDim.x) {
+      p.gloc[i] = __ldcg(p.acc + i);
+      p.gscale[i] = __ldcg(p.acc + p.C + i) + dls / __ldg(p.scale + i);
     }
   }
 }
@@ -141,12 +290,13 @@ struct PackBlockJob {
   const float* loc; const float* scale;       // [C]
   const long long* perm_fwd; const long long* perm_bwd;   // int64 [C]
   long long loc_off, scale_off, an_logdet_off;            // float offsets
-  long long map_fwd_off, map_rev_off;                     // int32 offsets
+  long long map_fwd_off, map_rev_off, map_fwd_inv_off;    // int32 offsets
 };
 
 // One CTA per flow block: copy loc/scale, sum log|scale| (modules.py:298-299), build the int32 gather maps
 //   map_fwd[p] = (perm_fwd[p] + C/2) % C     (coupling output is stored [xa' | xb'], logical order is [xb' | xa'])
 //   map_rev[p] = perm_bwd[(p + C/2) % C]
+//   map_fwd_inv[map_fwd[p]] = p            (gradient of the gather: dS[b, q] = g[b, map_fwd_inv[q]])
 __global__ void __launch_bounds__(256) inn_pack_block_kernel(const PackBlockJob* __restrict__ jobs, void* packed, int C) {
   const PackBlockJob j = jobs[blockIdx.x];
   float* pf = reinterpret_cast<float*>(packed);
@@ -161,6 +311,7 @@ __global__ void __launch_bounds__(256) inn_pack_block_kernel(const PackBlockJob*
     acc += logf(fabsf(s));
     pi[j.map_fwd_off + c] = static_cast<int>((j.perm_fwd[c] + half) % C);
     pi[j.map_rev_off + c] = static_cast<int>(j.perm_bwd[(c + half) % C]);
+    pi[j.map_fwd_inv_off + static_cast<int>((j.perm_fwd[c] + half) % C)] = c;   // inverse of map_fwd (backward un-shuffle)
   }
   red[threadIdx.x] = acc;
   __syncthreads();

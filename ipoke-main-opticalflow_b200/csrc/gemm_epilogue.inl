@@ -15,11 +15,17 @@
       const bool row_ok = row < p.M;
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * acc_cols;
 
-      if (kMode == EPI_HIDDEN) {
+      if (kSlabMode) {
         // ---- bias slice -> smem while the MMAs of this tile run
         float* bias_s = epi_f32 + (it & 1) * BN;
-        for (int c = tid_e; c < BN; c += EPI_THREADS) bias_s[c] = __ldg(p.bias + n_tile * BN + c);
-        named_bar_sync(1, EPI_THREADS);
+        const int ocol0 = p.out_col0 + n_tile * BN;              // first output column of this tile
+        if (kMode == EPI_HIDDEN) {
+          for (int c = tid_e; c < BN; c += EPI_THREADS) bias_s[c] = __ldg(p.bias + n_tile * BN + c);
+          named_bar_sync(1, EPI_THREADS);
+        }
+        // EPI_DGRAD: LeakyReLU'(pre) from the sign of the saved activation at the output position (modules.py:174)
+        const __nv_bfloat16* mask_row =
+            (kMode == EPI_DGRAD && row_ok) ? p.mask_act + static_cast<size_t>(row) * p.ld_mask + p.mask_col0 + ocol0 : nullptr;
         mbar_wait(&tfull_bar[acc], acc_phase, 4);
         tc_fence_after();
         if (p.slab_bufs > 0) {
@@ -46,12 +52,22 @@
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               uint32_t hi[4], lo[4];
+              uint4 mk = make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u);   // bf16 ones: mask = 1
+              if (kMode == EPI_DGRAD && mask_row != nullptr)
+                mk = __ldg(reinterpret_cast<const uint4*>(mask_row + s * 64) + j);
+              const uint32_t mw[4] = {mk.x, mk.y, mk.z, mk.w};
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
-                float a = v[j * 8 + 2 * e] + bs[j * 8 + 2 * e];
-                float b = v[j * 8 + 2 * e + 1] + bs[j * 8 + 2 * e + 1];
-                a = a >= 0.f ? a : a * p.slope;
-                b = b >= 0.f ? b : b * p.slope;
+                float a, b;
+                if (kMode == EPI_HIDDEN) {
+                  a = v[j * 8 + 2 * e] + bs[j * 8 + 2 * e];
+                  b = v[j * 8 + 2 * e + 1] + bs[j * 8 + 2 * e + 1];
+                  a = a >= 0.f ? a : a * p.slope;
+                  b = b >= 0.f ? b : b * p.slope;
+                } else {
+                  a = v[j * 8 + 2 * e] * (bf16_bits_positive(mw[e] & 0xFFFFu) ? 1.f : p.slope);
+                  b = v[j * 8 + 2 * e + 1] * (bf16_bits_positive(mw[e] >> 16) ? 1.f : p.slope);
+                }
                 __nv_bfloat16 h0, l0, h1, l1;
                 split_bf16(a, h0, l0);
                 split_bf16(b, h1, l1);
@@ -65,7 +81,7 @@
             fence_proxy_async();                                 // generic-proxy smem writes -> visible to TMA
             named_bar_sync(1, EPI_THREADS);
             if (tid_e == 0) {
-              const int col = n_tile * BN + s * 64;
+              const int col = ocol0 + s * 64;
               tma_store_2d(&tmO0, epi_smem + (buf * kSplit) * SLAB_BYTES, col, m_tile * BM);
               if (kSplit == 2) tma_store_2d(&tmO1, epi_smem + (buf * kSplit + 1) * SLAB_BYTES, col, m_tile * BM);
               bulk_commit();
@@ -77,11 +93,17 @@
             float v[16];
             tmem_ld16(t_row + c0, v);
             tmem_ld_wait();
-            const int col = n_tile * BN + c0;
+            const int col = ocol0 + c0;
+            if (kMode == EPI_HIDDEN) {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              v[j] += bias_s[c0 + j];
-              v[j] = v[j] >= 0.f ? v[j] : v[j] * p.slope;
+              for (int j = 0; j < 16; ++j) {
+                v[j] += bias_s[c0 + j];
+                v[j] = v[j] >= 0.f ? v[j] : v[j] * p.slope;
+              }
+            } else if (mask_row != nullptr) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                v[j] *= bf16_bits_positive(__bfloat16_as_ushort(mask_row[c0 + j])) ? 1.f : p.slope;
             }
             if (row_ok) {
               uint32_t hi[8], lo[8];
@@ -106,6 +128,29 @@
           tc_fence_before();
           mbar_arrive(&tempty_bar[acc]);
         }
+      } else if (kMode == EPI_DU) {
+        // ---- gradient of the MLP input: columns [0, x_cols) add into the state gradient of the conditioner
+        //      half, columns [cond_col0, cond_col0 + E) into the conditioning gradient (flow_blocks.py:137, 224)
+        mbar_wait(&tfull_bar[acc], acc_phase, 4);
+        tc_fence_after();
+        for (int c0 = 0; c0 < BN; c0 += 16) {
+          float v[16];
+          tmem_ld16(t_row + c0, v);
+          tmem_ld_wait();
+          if (row_ok) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int c = n_tile * BN + c0 + j;
+              if (c < p.du_x_cols) {
+                p.du_state[static_cast<size_t>(row) * p.du_ld_state + p.du_state_off + c] += v[j];
+              } else if (c >= p.du_cond_col0 && c < p.du_cond_col0 + p.du_E) {
+                p.du_cond[static_cast<size_t>(row) * p.du_ld_cond + (c - p.du_cond_col0)] += v[j];
+              }
+            }
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&tempty_bar[acc]);
       } else {
         // ---- coupling tail: stage the kept half of this tile and both biases in smem (coalesced), overlapping
         //      the MMAs; then one row per thread out of smem; then coalesced write-back.
@@ -183,4 +228,4 @@
         named_bar_sync(1, EPI_THREADS);                           // keep_s is reused by the next tile
       }
     }
-    if (kMode == EPI_HIDDEN && p.slab_bufs > 0 && tid_e == 0) bulk_wait<0>();   // stores landed before exit
+    if (kSlabMode && p.slab_bufs > 0 && tid_e == 0) bulk_wait<0>();   // stores landed before exit

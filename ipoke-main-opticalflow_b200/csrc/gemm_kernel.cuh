@@ -30,7 +30,7 @@ constexpr int GEMM_THREADS = 256;
 constexpr int EPI_THREADS = 128;
 constexpr int SMEM_BARRIER_BYTES = 256;
 
-enum EpiMode { EPI_HIDDEN = 0, EPI_TAIL_FWD = 1, EPI_TAIL_REV = 2 };
+enum EpiMode { EPI_HIDDEN = 0, EPI_TAIL_FWD = 1, EPI_TAIL_REV = 2, EPI_DGRAD = 3, EPI_DU = 4 };
 
 struct GemmParams {
   int M;                  // valid rows
@@ -70,16 +70,27 @@ struct GemmParams {
   float* s_save;          // training: per half-step tanh output s and the pre-update kept half (nullable)
   float* keep_save;
   int ld_save;
+  // backward (EPI_DGRAD / EPI_DU): dX = dY * W with W read MN-major straight from the forward layout
+  int w_mn;               // 1: the W tile is {64 rows of the contraction index} x {BN columns}, MN-major for the MMA
+  int w_group_rows;       // w_mn: first W row of group g = w_row0[0] + g * w_group_rows
+  int out_col0;           // first output column (EPI_HIDDEN / EPI_DGRAD: out col = out_col0 + n_tile * BN)
+  const __nv_bfloat16* mask_act;   // EPI_DGRAD: saved post-LeakyReLU activation (hi part) at the output position
+  int ld_mask;
+  int mask_col0;
+  // EPI_DU: fp32 accumulation of the MLP-input gradient into the state gradient and the conditioning gradient
+  float* du_state; int du_ld_state; int du_state_off; int du_x_cols;
+  float* du_cond;  int du_ld_cond;  int du_cond_col0; int du_E;
 };
 
-__host__ __device__ constexpr int gemm_nsub(int mode) { return mode == EPI_HIDDEN ? 1 : 2; }
+__host__ __device__ constexpr int gemm_nsub(int mode) { return (mode == EPI_TAIL_FWD || mode == EPI_TAIL_REV) ? 2 : 1; }
 
 __host__ inline int gemm_stage_bytes(int ksplit, int mode, int BN) {
   return gemm_nsub(mode) * ksplit * (A_TILE_BYTES + BN * BK * 2);
 }
 // epilogue smem: [slabs (EPI_HIDDEN with TMA store)] [fp32 area: bias (2 x BN) | tail: keep tile + 2 biases]
 __host__ inline int gemm_epi_bytes(int ksplit, int mode, int BN, int slab_bufs) {
-  if (mode == EPI_HIDDEN) return ksplit * slab_bufs * SLAB_BYTES + 2 * BN * 4;
+  if (mode == EPI_HIDDEN || mode == EPI_DGRAD) return ksplit * slab_bufs * SLAB_BYTES + 2 * BN * 4;
+  if (mode == EPI_DU) return 2 * BN * 4;
   return (BM * (BN + 1) + 2 * BN) * 4;
 }
 __host__ inline int gemm_smem_bytes(int ksplit, int mode, int BN, int stages, int slab_bufs) {
@@ -110,9 +121,11 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
   const uint16_t mc_mask = static_cast<uint16_t>((1u << mc) - 1u);
 
   uint8_t* epi_smem = smem + p.epi_off;
-  const int slab_total = (kMode == EPI_HIDDEN) ? kSplit * p.slab_bufs * SLAB_BYTES : 0;
+  constexpr bool kSlabMode = (kMode == EPI_HIDDEN || kMode == EPI_DGRAD);
+  constexpr bool kTailMode = (kMode == EPI_TAIL_FWD || kMode == EPI_TAIL_REV);
+  const int slab_total = kSlabMode ? kSplit * p.slab_bufs * SLAB_BYTES : 0;
   float* epi_f32 = reinterpret_cast<float*>(epi_smem + slab_total);
-  const int epi_bytes = slab_total + ((kMode == EPI_HIDDEN) ? 2 * BN * 4 : (BM * (BN + 1) + 2 * BN) * 4);
+  const int epi_bytes = slab_total + (kTailMode ? (BM * (BN + 1) + 2 * BN) * 4 : 2 * BN * 4);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(epi_smem + ((epi_bytes + 15) & ~15));
   uint64_t* empty_bar = full_bar + MAX_STAGES;
   uint64_t* tfull_bar = empty_bar + MAX_STAGES;
@@ -126,7 +139,7 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
       tma_prefetch_desc(&tmA1);
       tma_prefetch_desc(&tmW1);
     }
-    if (kMode == EPI_HIDDEN && p.slab_bufs > 0) {
+    if (kSlabMode && p.slab_bufs > 0) {
       tma_prefetch_desc(&tmO0);
       if (kSplit == 2) tma_prefetch_desc(&tmO1);
     }
@@ -202,7 +215,14 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                                &full_bar[stage], a_k, m_tile * BM + cta_rank * a_rows, mc_mask);
               else
                 tma_load_2d(sbase + t * A_TILE_BYTES, sp == 0 ? &tmA0 : &tmA1, &full_bar[stage], a_k, m_tile * BM);
-              if (!w_done)
+              if (p.w_mn) {
+                // contraction index = W row: {64 rows} x {BN columns} as BN/64 MN-major chunks
+                const int w_c = (n_tile - group * p.tiles_per_group) * BN;
+                const int w_rk = p.w_row0[sub] + group * p.w_group_rows + kb * BK;
+                for (int c = 0; c < (BN >> 6); ++c)
+                  tma_load_2d(sbase + NSUB * kSplit * A_TILE_BYTES + t * w_tile_bytes + c * (64 * 128),
+                              sp == 0 ? &tmW0 : &tmW1, &full_bar[stage], w_c + c * 64, w_rk);
+              } else if (!w_done)
                 tma_load_2d(sbase + NSUB * kSplit * A_TILE_BYTES + t * w_tile_bytes, sp == 0 ? &tmW0 : &tmW1,
                             &full_bar[stage], kb * BK, w_r);
             }
@@ -215,7 +235,7 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
     }
   } else if (warp == 1) {
     // ============================ MMA issuer ==============================
-    const uint32_t idesc = umma_idesc_bf16(BM, BN);
+    const uint32_t idesc = umma_idesc_bf16(BM, BN, 0, p.w_mn);
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
@@ -238,20 +258,24 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
             const uint32_t a0 = sbase + (sub * kSplit) * A_TILE_BYTES;
             const uint32_t w0 = sbase + NSUB * kSplit * A_TILE_BYTES + (sub * kSplit) * w_tile_bytes;
             const uint64_t da_hi = umma_desc_k_sw128(a0);
-            const uint64_t dw_hi = umma_desc_k_sw128(w0);
+            const uint32_t w1 = w0 + (kSplit - 1) * w_tile_bytes;
+            const uint64_t dw_hi = p.w_mn ? umma_desc_mn_sw128(w0, 64 * 128) : umma_desc_k_sw128(w0);
             const uint64_t da_lo = umma_desc_k_sw128(a0 + (kSplit - 1) * A_TILE_BYTES);
-            const uint64_t dw_lo = umma_desc_k_sw128(w0 + (kSplit - 1) * w_tile_bytes);
+            const uint64_t dw_lo = p.w_mn ? umma_desc_mn_sw128(w1, 64 * 128) : umma_desc_k_sw128(w1);
+            // per UMMA_K = 16: K-major operands advance 32 B inside the swizzle row, MN-major ones 16 rows x 128 B
+            const uint64_t wstep = p.w_mn ? static_cast<uint64_t>((UMMA_K * 128) >> 4) : static_cast<uint64_t>((UMMA_K * 2) >> 4);
 #pragma unroll
             for (int kk = 0; kk < BK / UMMA_K; ++kk) {
               const uint64_t koff = static_cast<uint64_t>((kk * UMMA_K * 2) >> 4);
+              const uint64_t woff = wstep * kk;
               const uint32_t first = (kb == 0 && kk == 0) ? 0u : 1u;
               if (kSplit == 2) {
                 // small terms first, then the dominant hi*hi product
-                umma_bf16_ss(d_tmem, da_lo + koff, dw_hi + koff, idesc, first);
-                umma_bf16_ss(d_tmem, da_hi + koff, dw_lo + koff, idesc, 1u);
-                umma_bf16_ss(d_tmem, da_hi + koff, dw_hi + koff, idesc, 1u);
+                umma_bf16_ss(d_tmem, da_lo + koff, dw_hi + woff, idesc, first);
+                umma_bf16_ss(d_tmem, da_hi + koff, dw_lo + woff, idesc, 1u);
+                umma_bf16_ss(d_tmem, da_hi + koff, dw_hi + woff, idesc, 1u);
               } else {
-                umma_bf16_ss(d_tmem, da_hi + koff, dw_hi + koff, idesc, first);
+                umma_bf16_ss(d_tmem, da_hi + koff, dw_hi + woff, idesc, first);
               }
             }
           }

@@ -16,6 +16,7 @@
 #include "../../include/ipoke_inn.h"
 #include "elementwise.cuh"
 #include "gemm_kernel.cuh"
+#include "wgrad_kernel.cuh"
 
 using namespace inn;
 
@@ -51,7 +52,7 @@ struct Block {
   Chain chains[2];
   int n_chains = 2;
   Tail tails[2];
-  long long loc = -1, scale = -1, an_ld = -1, map_fwd = -1, map_rev = -1;   // byte offsets
+  long long loc = -1, scale = -1, an_ld = -1, map_fwd = -1, map_rev = -1, map_fwd_inv = -1;   // byte offsets
 };
 
 struct GemmOp {
@@ -59,19 +60,37 @@ struct GemmOp {
   GemmParams p;
   int mode, grid, smem, cluster;
 };
+struct WgradOp {
+  CUtensorMap tmY[2], tmX[2];
+  WgradParams p;
+  int grid, smem;
+  int lin[WG_MAX_GROUPS];   // index of each group's nn.Linear in the caller's gradient pointer arrays
+};
+enum OpKind { OP_BOUNDARY = 0, OP_GEMM = 1, OP_BWD_INIT = 2, OP_TAIL_BWD = 3, OP_BOUNDARY_BWD = 4, OP_WGRAD = 5,
+              OP_ZERO_GRAD = 6 };
 struct Op {
-  int kind;  // 0 boundary, 1 gemm
+  int kind;
   BoundaryParams b;
   int b_grid;
   int gemm;  // index into gemm ops
   // which user pointers this boundary op takes (patched per call)
   int user_in, user_cond, user_out_final, block_index;
+  // backward ops
+  TailBwdParams tb;
+  BoundaryBwdParams bb;
+  int wgrad;          // index into wgrad ops
+  int h0_block;       // OP_BOUNDARY_BWD: the block whose input was saved (0 -> the caller's x, k -> block_outs[k-1])
+  int to_user_dx;     // OP_BOUNDARY_BWD: dst is the caller's dx
+  int du_to_user_dcond;   // OP_GEMM (EPI_DU): du_cond is patched with the conditioning-gradient accumulator
+  int zero_dcond;     // OP_BWD_INIT
+  int lin, lin_rows, lin_cols;   // OP_ZERO_GRAD
 };
 struct ProgramKey {
   const void* packed; void* ws; int B, kb, ke, dir, want_blocks;
+  const void* saved;
   bool operator==(const ProgramKey& o) const {
     return packed == o.packed && ws == o.ws && B == o.B && kb == o.kb && ke == o.ke && dir == o.dir &&
-           want_blocks == o.want_blocks;
+           want_blocks == o.want_blocks && saved == o.saved;
   }
 };
 struct GraphEntry {
@@ -83,6 +102,7 @@ struct Program {
   ProgramKey key;
   std::vector<Op> ops;
   std::vector<GemmOp> gemms;
+  std::vector<WgradOp> wgrads;
   int launches = 0;
   std::vector<GraphEntry> graphs;     // instantiated CUDA graphs keyed by the caller's pointers
   int graph_misses = 0, graph_hits = 0;
@@ -94,6 +114,18 @@ struct Program {
 
 struct WsLayout {
   long long S[2], U_hi, U_lo, ACT_hi[2], ACT_lo[2], logdet, xin, condin, zout, ldout, total;
+  // backward scratch
+  long long dt_hi[2], dt_lo[2], dcond, an_acc, an_cnt, dld_sum;
+};
+// What the training forward keeps for the backward pass (per flow block).
+struct SavedBlock {
+  long long U_hi[2], U_lo[2];                       // MLP input of half-step i (cond blocks: i = 0 only)
+  std::vector<long long> act_hi[2], act_lo[2];      // [chain][layer] post-LeakyReLU activations [B, G*Hp]
+  long long s[2], keep[2];                          // per half-step: tanh output and the kept half before the update
+};
+struct SavedLayout {
+  std::vector<SavedBlock> blk;
+  long long total = 0;
 };
 
 }  // namespace
@@ -102,7 +134,7 @@ struct ipoke_inn_plan {
   ipoke_inn_desc d;
   int device = 0;
   int ksplit = 2;
-  int C2 = 0, C2p = 0, Ep = 0, Hp = 0, Np = 0, ldU = 0, Gmax = 2, ldACT = 0;
+  int C2 = 0, C2p = 0, Ep = 0, Hp = 0, Np = 0, Npk = 0, ldU = 0, Gmax = 2, ldACT = 0;
   std::vector<Block> blocks;
   long long packed_bytes = 0;
   // device-side job tables live inside the packed buffer
@@ -160,8 +192,42 @@ WsLayout ws_layout(const ipoke_inn_plan* P, int B) {
   w.condin = bump(cur, 4ll * B * std::max(1, (int)P->d.E));
   w.zout = bump(cur, 4ll * B * C);
   w.ldout = bump(cur, 4ll * B);
+  for (int i = 0; i < 2; ++i) {
+    w.dt_hi[i] = bump(cur, 2ll * B * 2 * P->Npk);
+    w.dt_lo[i] = bump(cur, 2ll * B * 2 * P->Npk);
+  }
+  w.dcond = bump(cur, 4ll * B * std::max(1, (int)P->d.E));
+  w.an_acc = bump(cur, 4ll * 2 * C * P->d.n_flows);
+  w.an_cnt = bump(cur, 4ll * P->d.n_flows);
+  w.dld_sum = bump(cur, 16);
   w.total = round_up(cur, 1024);
   return w;
+}
+
+SavedLayout saved_layout(const ipoke_inn_plan* P, int B) {
+  SavedLayout L;
+  long long cur = 0;
+  L.blk.resize(P->d.n_flows);
+  for (int k = 0; k < P->d.n_flows; ++k) {
+    const Block& b = P->blocks[k];
+    SavedBlock& sb = L.blk[k];
+    for (int i = 0; i < 2; ++i) {
+      sb.U_hi[i] = sb.U_lo[i] = -1;
+      if (i == 0 || b.mode != MODE_COND) {
+        sb.U_hi[i] = bump(cur, 2ll * B * P->ldU);
+        sb.U_lo[i] = P->ksplit == 2 ? bump(cur, 2ll * B * P->ldU) : -1;
+      }
+      sb.s[i] = bump(cur, 4ll * B * P->C2);
+      sb.keep[i] = bump(cur, 4ll * B * P->C2);
+    }
+    for (int c = 0; c < b.n_chains; ++c)
+      for (int l = 0; l <= P->d.depth; ++l) {
+        sb.act_hi[c].push_back(bump(cur, 2ll * B * b.chains[c].G * P->Hp));
+        sb.act_lo[c].push_back(P->ksplit == 2 ? bump(cur, 2ll * B * b.chains[c].G * P->Hp) : -1);
+      }
+  }
+  L.total = round_up(cur, 1024);
+  return L;
 }
 
 int ensure_device(ipoke_inn_plan* P) {
@@ -187,6 +253,12 @@ int ensure_device(ipoke_inn_plan* P) {
   SET_SMEM((inn_gemm_kernel<2, EPI_TAIL_FWD>))
   SET_SMEM((inn_gemm_kernel<1, EPI_TAIL_REV>))
   SET_SMEM((inn_gemm_kernel<2, EPI_TAIL_REV>))
+  SET_SMEM((inn_gemm_kernel<1, EPI_DGRAD>))
+  SET_SMEM((inn_gemm_kernel<2, EPI_DGRAD>))
+  SET_SMEM((inn_gemm_kernel<1, EPI_DU>))
+  SET_SMEM((inn_gemm_kernel<2, EPI_DU>))
+  SET_SMEM((inn_wgrad_kernel<1>))
+  SET_SMEM((inn_wgrad_kernel<2>))
 #undef SET_SMEM
   P->dev_ready = true;
   return 0;
@@ -216,7 +288,7 @@ TileCfg tile_cfg(int ksplit, int mode, int bn) {
     const int epi = (gemm_epi_bytes(ksplit, mode, bn, slabs) + 15) & ~15;
     return std::min(MAX_STAGES, (avail - epi) / sb);
   };
-  if (mode == EPI_HIDDEN && bn >= 64) {
+  if ((mode == EPI_HIDDEN || mode == EPI_DGRAD) && bn >= 64) {
     const int s2 = stages_with(2), s1 = stages_with(1);
     if (s2 >= 4 || s2 == s1) { t.slab_bufs = 2; t.stages = s2; }
     else { t.slab_bufs = 1; t.stages = s1; }
@@ -260,6 +332,26 @@ struct Builder {
   WsLayout wl;
   int B, m_tiles;
   int err = 0;
+  // training forward / backward: activations live in the caller's `saved` buffer instead of the ping-pong scratch
+  char* saved = nullptr;
+  SavedLayout sl;
+  bool save = false;
+  int cur_block = 0;
+
+  template <typename T>
+  T* sv(long long off) const { return off < 0 ? nullptr : reinterpret_cast<T*>(saved + off); }
+  // MLP input buffer of (block, half-step)
+  char* u_base(int k, int i, int sp) const {
+    if (!save) return ws + (sp == 0 ? wl.U_hi : wl.U_lo);
+    const SavedBlock& sb = sl.blk[k];
+    const int j = sb.U_hi[i] >= 0 ? i : 0;
+    return saved + (sp == 0 ? sb.U_hi[j] : sb.U_lo[j]);
+  }
+  // activation buffer written by layer l of chain c
+  char* act_base(int k, int c, int l, int sp) const {
+    if (!save) return ws + (sp == 0 ? wl.ACT_hi[l & 1] : wl.ACT_lo[l & 1]);
+    return saved + (sp == 0 ? sl.blk[k].act_hi[c][l] : sl.blk[k].act_lo[c][l]);
+  }
 
   template <typename T>
   T* pk(long long off) const { return reinterpret_cast<T*>(const_cast<char*>(packed) + off); }
@@ -283,9 +375,9 @@ struct Builder {
     prog->launches++;
     return o;
   }
-  void set_u(BoundaryParams& b, int u_begin) {
-    b.u_hi = w<__nv_bfloat16>(wl.U_hi);
-    b.u_lo = P->ksplit == 2 ? w<__nv_bfloat16>(wl.U_lo) : nullptr;
+  void set_u(BoundaryParams& b, int u_begin, int k, int i) {
+    b.u_hi = reinterpret_cast<__nv_bfloat16*>(u_base(k, i, 0));
+    b.u_lo = P->ksplit == 2 ? reinterpret_cast<__nv_bfloat16*>(u_base(k, i, 1)) : nullptr;
     b.ld_u = P->ldU;
     b.u_begin = u_begin;
     b.u_count = P->C2;
@@ -339,7 +431,7 @@ struct Builder {
   }
 
   // hidden layers of one chain; returns the ACT buffer index holding the last hidden activation
-  int chain(const Chain& c) {
+  int chain(const Chain& c, int k, int ci, int ui) {
     const int rows = c.G * P->Hp;
     TileCfg tc = pick_bn(P, EPI_HIDDEN, P->Hp, m_tiles * c.G);
     const int bn = tc.bn;
@@ -353,28 +445,28 @@ struct Builder {
       g.p.num_k_blocks = L.Kp / BK;
       g.p.a_group_stride = l == 0 ? 0 : P->Hp;
       g.p.bias = pk<float>(L.bias);
-      g.p.out_hi = w<__nv_bfloat16>(wl.ACT_hi[l & 1]);
-      g.p.out_lo = w<__nv_bfloat16>(wl.ACT_lo[l & 1]);
-      g.p.ld_out = P->ldACT;
+      const long long ld_act = save ? rows : P->ldACT;     // saved activations are stored densely per chain
+      g.p.out_hi = reinterpret_cast<__nv_bfloat16*>(act_base(k, ci, (int)l, 0));
+      g.p.out_lo = P->ksplit == 2 ? reinterpret_cast<__nv_bfloat16*>(act_base(k, ci, (int)l, 1)) : nullptr;
+      g.p.ld_out = (int)ld_act;
       g.p.slope = P->d.mlp_slope;
       for (int sp = 0; sp < P->ksplit; ++sp) {
         if (l == 0) {
-          const long long base = (sp == 0 ? wl.U_hi : wl.U_lo) + 2ll * c.a_col_off;
-          err |= make_map(P, &g.tmA[sp], ws + base, c.Kin_p, B, 2ll * P->ldU, a_box);
+          err |= make_map(P, &g.tmA[sp], u_base(k, ui, sp) + 2ll * c.a_col_off, c.Kin_p, B, 2ll * P->ldU, a_box);
         } else {
-          const long long base = sp == 0 ? wl.ACT_hi[(l - 1) & 1] : wl.ACT_lo[(l - 1) & 1];
-          err |= make_map(P, &g.tmA[sp], ws + base, rows, B, 2ll * P->ldACT, a_box);
+          err |= make_map(P, &g.tmA[sp], act_base(k, ci, (int)l - 1, sp), rows, B, 2ll * ld_act, a_box);
         }
         err |= make_map(P, &g.tmW[sp], packed + (sp == 0 ? L.hi : L.lo), L.Kp, L.rows, 2ll * L.Kp, bn);
         // output slabs (TMA store): same 64 x 128 box as the next layer's A loads
-        err |= make_map(P, &g.tmO[sp], ws + (sp == 0 ? wl.ACT_hi[l & 1] : wl.ACT_lo[l & 1]), rows, B, 2ll * P->ldACT, BM);
+        err |= make_map(P, &g.tmO[sp], act_base(k, ci, (int)l, sp), rows, B, 2ll * ld_act, BM);
       }
       finish_gemm(g, tc);
     }
-    return (int)(c.L.size() - 1) & 1;
+    return (int)(c.L.size() - 1);
   }
 
-  void tail(const Block& blk, int i, int act_buf, int G, int state_buf, bool reverse, bool write_u) {
+  // act_layer: index of the last hidden layer of chain `ci` (its output feeds the tail)
+  void tail(const Block& blk, int k, int i, int ci, int act_layer, int G, int state_buf, bool reverse, bool write_u) {
     const Tail& t = blk.tails[i];
     GemmOp& g = add_gemm(reverse ? EPI_TAIL_REV : EPI_TAIL_FWD);
     TileCfg tc = pick_bn(P, g.mode, P->Np, m_tiles);
@@ -397,30 +489,37 @@ struct Builder {
     g.p.logdet = w<float>(wl.logdet);
     g.p.logdet_atomic = g.p.num_n_tiles > 1;
     if (write_u) {
-      g.p.u_hi = w<__nv_bfloat16>(wl.U_hi);
-      g.p.u_lo = w<__nv_bfloat16>(wl.U_lo);
+      g.p.u_hi = reinterpret_cast<__nv_bfloat16*>(u_base(k, 1, 0));
+      g.p.u_lo = reinterpret_cast<__nv_bfloat16*>(u_base(k, 1, 1));
       g.p.ld_u = P->ldU;
     }
+    if (save && !reverse) {
+      g.p.s_save = sv<float>(sl.blk[k].s[i]);
+      g.p.keep_save = sv<float>(sl.blk[k].keep[i]);
+      g.p.ld_save = P->C2;
+    }
+    const long long ld_act = save ? (long long)G * P->Hp : P->ldACT;
     for (int sp = 0; sp < P->ksplit; ++sp) {
-      const long long base = sp == 0 ? wl.ACT_hi[act_buf] : wl.ACT_lo[act_buf];
-      err |= make_map(P, &g.tmA[sp], ws + base, G * P->Hp, B, 2ll * P->ldACT, BM / tc.mc);
+      err |= make_map(P, &g.tmA[sp], act_base(k, ci, act_layer, sp), G * P->Hp, B, 2ll * ld_act, BM / tc.mc);
       err |= make_map(P, &g.tmW[sp], packed + (sp == 0 ? t.w.hi : t.w.lo), t.w.Kp, t.w.rows, 2ll * t.w.Kp, bn);
       g.tmO[sp] = g.tmA[sp];      // unused by the tail epilogue
     }
     finish_gemm(g, tc);
   }
 
-  void coupling(const Block& blk, int state_buf, bool reverse) {
+  void coupling(const Block& blk, int k, int state_buf, bool reverse) {
     if (blk.mode == MODE_COND) {
-      const int ab = chain(blk.chains[0]);
-      tail(blk, reverse ? 1 : 0, ab, 4, state_buf, reverse, false);
-      tail(blk, reverse ? 0 : 1, ab, 4, state_buf, reverse, false);
+      const int al = chain(blk.chains[0], k, 0, 0);
+      tail(blk, k, reverse ? 1 : 0, 0, al, 4, state_buf, reverse, false);
+      tail(blk, k, reverse ? 0 : 1, 0, al, 4, state_buf, reverse, false);
     } else {
+      // forward: half-step 0 reads U(k,0) (written by the boundary) and writes U(k,1); reverse runs 1 then 0 and,
+      // without `save`, both U views are the same scratch buffer
       const int first = reverse ? 1 : 0;
-      int ab = chain(blk.chains[first]);
-      tail(blk, first, ab, 2, state_buf, reverse, true);
-      ab = chain(blk.chains[1 - first]);
-      tail(blk, 1 - first, ab, 2, state_buf, reverse, false);
+      int al = chain(blk.chains[first], k, first, reverse ? 0 : first);
+      tail(blk, k, first, first, al, 2, state_buf, reverse, true);
+      al = chain(blk.chains[1 - first], k, 1 - first, reverse ? 1 : 1 - first);
+      tail(blk, k, 1 - first, 1 - first, al, 2, state_buf, reverse, false);
     }
   }
 
@@ -445,7 +544,12 @@ struct Builder {
       b.post_loc = pk<float>(blk.loc);
       b.post_scale = pk<float>(blk.scale);
       b.post_leaky = d.conditional;
-      set_u(b, 0);
+      set_u(b, 0, k, 0);
+      if (save && blk.mode != MODE_COND) {       // half-step 1 reads its own saved buffer: same cond columns / padding
+        b.u2_hi = reinterpret_cast<__nv_bfloat16*>(u_base(k, 1, 0));
+        b.u2_lo = P->ksplit == 2 ? reinterpret_cast<__nv_bfloat16*>(u_base(k, 1, 1)) : nullptr;
+      }
+      if (save) o.user_cond = d.E > 0;
       if (d.E > 0) {
         b.E = d.E;
         b.ld_cond = d.E;
@@ -455,7 +559,7 @@ struct Builder {
       b.logdet = w<float>(wl.logdet);
       b.an_logdet = pk<float>(blk.an_ld);
       cur = nxt;
-      coupling(blk, cur, false);
+      coupling(blk, k, cur, false);
     }
     Op& o = add_boundary();
     BoundaryParams& b = o.b;
@@ -485,7 +589,7 @@ struct Builder {
       }
       b.src = pk<int>(blk.map_rev);
       b.out = w<float>(wl.S[nxt]);
-      set_u(b, P->C2);
+      set_u(b, P->C2, k, 0);
       if (d.E > 0) {
         b.E = d.E;
         b.ld_cond = d.E;
@@ -493,7 +597,7 @@ struct Builder {
         b.e_pad = P->Ep;
       }
       cur = nxt;
-      coupling(blk, cur, true);
+      coupling(blk, k, cur, true);
     }
     Op& o = add_boundary();
     BoundaryParams& b = o.b;
@@ -505,12 +609,292 @@ struct Builder {
   }
 };
 
+
+// ------------------------------------------------------------------ backward program
+struct BwdBuilder : Builder {
+  int nl() const { return P->d.depth + 2; }
+  int lin_index(int k, int i, int net, int l) const { return ((k * 2 + i) * 2 + net) * nl() + l; }
+
+  Op& add_op(int kind) {
+    prog->ops.emplace_back();
+    Op& o = prog->ops.back();
+    std::memset(&o, 0, sizeof(Op));
+    o.kind = kind;
+    o.gemm = o.wgrad = -1;
+    o.block_index = o.h0_block = -1;
+    prog->launches++;
+    return o;
+  }
+  int ew_grid(long long total) const { return (int)std::min<long long>((total + 255) / 256, (long long)P->num_sms * 8); }
+  char* d_base(int idx, int sp) const { return ws + (sp == 0 ? wl.ACT_hi[idx] : wl.ACT_lo[idx]); }
+  char* dt_base(int idx, int sp) const { return ws + (sp == 0 ? wl.dt_hi[idx] : wl.dt_lo[idx]); }
+
+  void tail_bwd(int k, int i, int state_buf, int dt_idx) {
+    Op& o = add_op(OP_TAIL_BWD);
+    TailBwdParams& t = o.tb;
+    t.dstate = w<float>(wl.S[state_buf]);
+    t.ld_state = P->d.C;
+    t.keep_off = (i == 0) ? P->C2 : 0;
+    t.s_save = sv<float>(sl.blk[k].s[i]);
+    t.keep_save = sv<float>(sl.blk[k].keep[i]);
+    t.ld_save = P->C2;
+    t.dt_hi = reinterpret_cast<__nv_bfloat16*>(dt_base(dt_idx, 0));
+    t.dt_lo = P->ksplit == 2 ? reinterpret_cast<__nv_bfloat16*>(dt_base(dt_idx, 1)) : nullptr;
+    t.ld_dt = 2 * P->Npk;
+    t.npk = P->Npk;
+    t.B = B;
+    t.C2 = P->C2;
+    o.b_grid = ew_grid((long long)B * P->Npk);
+  }
+
+  TileCfg pick_bn_bwd(int mode, int cols_per_group, int tiles_other) {
+    static const int cand[3] = {256, 128, 64};
+    TileCfg best;
+    for (int c = 0; c < 3; ++c) {
+      const int bn = cand[c];
+      if (cols_per_group % bn != 0) continue;
+      const TileCfg t = tile_cfg(P->ksplit, mode, bn);
+      if (t.stages < 2) continue;
+      best = t;
+      if ((long long)tiles_other * (cols_per_group / bn) >= (long long)(P->num_sms * 4) / 5) return t;
+    }
+    return best;
+  }
+
+  // dX = dY * W (W read MN-major from the forward layout), grouped like the forward chain
+  //   a_sp        : A operand (dY) base per split, [B, a_cols] row stride ld_a (elements)
+  //   groups      : number of independent groups; contraction length per group kcon (multiple of 64)
+  GemmOp& dgrad(int mode, char* const a_sp[2], long long a_cols, long long ld_a, int a_group_stride, const LayerW& W,
+                int w_row0, int w_group_rows, int groups, int kcon, int out_cols_per_group) {
+    GemmOp& g = add_gemm(mode);
+    TileCfg tc = pick_bn_bwd(mode, out_cols_per_group, m_tiles * groups);
+    const int bn = tc.bn;
+    g.p.num_n_tiles = groups * (out_cols_per_group / bn);
+    g.p.tiles_per_group = out_cols_per_group / bn;
+    g.p.num_k_blocks = kcon / BK;
+    g.p.a_group_stride = a_group_stride;
+    g.p.w_mn = 1;
+    g.p.w_row0[0] = w_row0;
+    g.p.w_group_rows = w_group_rows;
+    g.p.slope = P->d.mlp_slope;
+    for (int sp = 0; sp < P->ksplit; ++sp) {
+      err |= make_map(P, &g.tmA[sp], a_sp[sp], a_cols, B, 2ll * ld_a, BM);
+      err |= make_map(P, &g.tmW[sp], packed + (sp == 0 ? W.hi : W.lo), W.Kp, W.rows, 2ll * W.Kp, 64);
+      g.tmO[sp] = g.tmA[sp];
+    }
+    tc.mc = 1;
+    finish_gemm(g, tc);
+    g.p.w_prefetch = 0;
+    return g;
+  }
+  void set_dgrad_out(GemmOp& g, int d_idx, int out_col0, long long out_cols, char* const mask_sp0, long long ld_mask) {
+    g.p.out_hi = reinterpret_cast<__nv_bfloat16*>(d_base(d_idx, 0));
+    g.p.out_lo = P->ksplit == 2 ? reinterpret_cast<__nv_bfloat16*>(d_base(d_idx, 1)) : nullptr;
+    g.p.ld_out = P->ldACT;
+    g.p.out_col0 = out_col0;
+    g.p.mask_act = reinterpret_cast<const __nv_bfloat16*>(mask_sp0);
+    g.p.ld_mask = (int)ld_mask;
+    g.p.mask_col0 = 0;
+    for (int sp = 0; sp < P->ksplit; ++sp)
+      err |= make_map(P, &g.tmO[sp], d_base(d_idx, sp), out_cols, B, 2ll * P->ldACT, BM);
+  }
+
+  // dW_g = dY_g^T X_g, db_g = colsum(dY_g) for the `groups` nets of one layer
+  void wgrad(char* const y_sp[2], long long y_cols, long long ld_y, int dy_col0, int dy_group_stride, int rows_p,
+             int rows_valid, char* const x_sp[2], long long x_cols, long long ld_x, int x_col0, int x_group_stride,
+             int kin_p, int seg0_valid, int seg1_start, int seg1_valid, int ld_gw, int groups, const int* lin) {
+    Op& o = add_op(OP_WGRAD);
+    prog->wgrads.emplace_back();
+    o.wgrad = (int)prog->wgrads.size() - 1;
+    WgradOp& wgo = prog->wgrads.back();
+    std::memset(&wgo, 0, sizeof(WgradOp));
+    WgradParams& q = wgo.p;
+    q.B = B;
+    q.num_kb = (B + 63) / 64;
+    q.G = groups;
+    q.m_tiles = (rows_p + BM - 1) / BM;
+    int bn = kin_p >= 128 ? 128 : 64;
+    if (P->ksplit == 2 && kin_p >= 128) bn = 128;
+    q.BN = bn;
+    q.n_tiles = (kin_p + bn - 1) / bn;
+    const int tiles = groups * q.m_tiles * q.n_tiles;
+    int ks = 1;
+    if (tiles * 2 <= P->num_sms && q.num_kb >= 8) {
+      ks = std::min(P->num_sms / tiles, q.num_kb / 4);
+      ks = std::max(ks, 1);
+      const int per = (q.num_kb + ks - 1) / ks;
+      ks = (q.num_kb + per - 1) / per;                  // no empty slice
+    }
+    q.kslices = ks;
+    const int avail = kMaxDynSmem - 1024 - SMEM_BARRIER_BYTES - WG_ONES_BYTES - ((wgrad_epi_bytes(bn) + 15) & ~15);
+    q.stages = std::max(2, std::min(MAX_STAGES, avail / wgrad_stage_bytes(P->ksplit, bn)));
+    q.stages = std::min(q.stages, std::max(2, (q.num_kb + ks - 1) / ks));
+    const int acc_cols = bn + 16;
+    q.nacc = (2 * acc_cols <= 512) ? 2 : 1;
+    int cols = 32;
+    while (cols < q.nacc * acc_cols) cols <<= 1;
+    q.tmem_cols = cols;
+    q.dy_col0 = dy_col0;
+    q.dy_group_stride = dy_group_stride;
+    q.x_col0 = x_col0;
+    q.x_group_stride = x_group_stride;
+    q.rows_valid = rows_valid;
+    q.kin_p = kin_p;
+    q.seg0_valid = seg0_valid;
+    q.seg1_start = seg1_start;
+    q.seg1_valid = seg1_valid;
+    q.ld_gw = ld_gw;
+    for (int g = 0; g < groups; ++g) wgo.lin[g] = lin[g];
+    for (int sp = 0; sp < P->ksplit; ++sp) {
+      err |= make_map(P, &wgo.tmY[sp], y_sp[sp], y_cols, B, 2ll * ld_y, 64);
+      err |= make_map(P, &wgo.tmX[sp], x_sp[sp], x_cols, B, 2ll * ld_x, 64);
+    }
+    if (P->ksplit == 1) {
+      wgo.tmY[1] = wgo.tmY[0];
+      wgo.tmX[1] = wgo.tmX[0];
+    }
+    wgo.smem = wgrad_smem_bytes(P->ksplit, bn, q.stages);
+    wgo.grid = std::min(tiles * ks, P->num_sms);
+    if (ks > 1) {
+      // split-batch partial sums are added with atomics: clear the destinations first
+      Op wg_op = prog->ops.back();
+      prog->ops.pop_back();
+      for (int g = 0; g < groups; ++g) {
+        Op& z = add_op(OP_ZERO_GRAD);
+        z.lin = lin[g];
+        z.lin_rows = rows_valid;
+        z.lin_cols = ld_gw;
+      }
+      prog->ops.push_back(wg_op);
+    }
+  }
+
+  // backward of the hidden layers of one chain; `d_idx` holds dpre of the last hidden layer on entry
+  void chain_bwd(const Block& blk, int k, int ci, int ui, const int* nets_i, const int* nets_net, int state_buf,
+                 int du_state_off, int d_idx) {
+    const Chain& c = blk.chains[ci];
+    const int G = c.G;
+    const long long rows = (long long)G * P->Hp;
+    const int depth = P->d.depth;
+    int lin[WG_MAX_GROUPS];
+    for (int l = depth; l >= 0; --l) {
+      char* y_sp[2] = {d_base(d_idx, 0), d_base(d_idx, 1)};
+      for (int g = 0; g < G; ++g) lin[g] = lin_index(k, nets_i[g], nets_net[g], l);
+      if (l > 0) {
+        char* x_sp[2] = {act_base(k, ci, l - 1, 0), act_base(k, ci, l - 1, 1)};
+        wgrad(y_sp, rows, P->ldACT, 0, P->Hp, P->Hp, P->d.H, x_sp, rows, rows, 0, P->Hp, P->Hp, P->d.H, 1 << 30, 0,
+              P->d.H, G, lin);
+        GemmOp& g = dgrad(EPI_DGRAD, y_sp, rows, P->ldACT, P->Hp, c.L[l], 0, P->Hp, G, P->Hp, P->Hp);
+        set_dgrad_out(g, d_idx ^ 1, 0, rows, act_base(k, ci, l - 1, 0), rows);
+        d_idx ^= 1;
+      } else {
+        char* x_sp[2] = {u_base(k, ui, 0), u_base(k, ui, 1)};
+        const ipoke_inn_desc& d = P->d;
+        int seg0 = 0, seg1s = 1 << 30, seg1v = 0, fan_in = 0;
+        if (blk.mode == MODE_COND) { seg0 = d.E; fan_in = d.E; }
+        else if (blk.mode == MODE_NORMAL) { seg0 = P->C2; seg1s = P->C2p; seg1v = d.E; fan_in = P->C2 + d.E; }
+        else { seg0 = P->C2; fan_in = P->C2; }
+        wgrad(y_sp, rows, P->ldACT, 0, P->Hp, P->Hp, d.H, x_sp, P->ldU, P->ldU, c.a_col_off, 0, c.Kin_p, seg0, seg1s,
+              seg1v, fan_in, G, lin);
+        // dU = sum over the G nets: one GEMM with contraction length G*Hp
+        GemmOp& g = dgrad(EPI_DU, y_sp, rows, P->ldACT, 0, c.L[0], 0, 0, 1, (int)rows, c.Kin_p);
+        g.p.du_state = w<float>(wl.S[state_buf]);
+        g.p.du_ld_state = d.C;
+        g.p.du_state_off = du_state_off;
+        g.p.du_x_cols = blk.mode == MODE_COND ? 0 : P->C2;
+        g.p.du_cond = nullptr;                        // patched per call (caller's dcond or the scratch accumulator)
+        g.p.du_ld_cond = d.E;
+        g.p.du_cond_col0 = blk.mode == MODE_COND ? 0 : P->C2p;
+        g.p.du_E = d.E;
+        prog->ops.back().du_to_user_dcond = d.E > 0;
+      }
+    }
+  }
+
+  // gradient of the last Linear of s_i / t_i: wgrad + dgrad into D[d_idx] at the chain's group columns
+  void tail_grads(const Block& blk, int k, int i, int ci, int G, int dt_idx, int d_idx) {
+    const Tail& t = blk.tails[i];
+    const int depth = P->d.depth;
+    char* y_sp[2] = {dt_base(dt_idx, 0), dt_base(dt_idx, 1)};
+    char* x_sp[2] = {act_base(k, ci, depth, 0), act_base(k, ci, depth, 1)};
+    const long long rows = (long long)G * P->Hp;
+    const int lin[2] = {lin_index(k, i, 0, depth + 1), lin_index(k, i, 1, depth + 1)};
+    wgrad(y_sp, 2ll * P->Npk, 2ll * P->Npk, 0, P->Npk, P->Np, P->C2, x_sp, rows, rows, t.g_s * P->Hp, P->Hp, P->Hp,
+          P->d.H, 1 << 30, 0, P->d.H, 2, lin);
+    GemmOp& g = dgrad(EPI_DGRAD, y_sp, 2ll * P->Npk, 2ll * P->Npk, P->Npk, t.w, 0, P->Np, 2, P->Npk, P->Hp);
+    set_dgrad_out(g, d_idx, t.g_s * P->Hp, rows, act_base(k, ci, depth, 0), rows);
+  }
+
+  void coupling_bwd(const Block& blk, int k, int state_buf) {
+    static const int kI_cond[4] = {0, 0, 1, 1}, kNet[4] = {0, 1, 0, 1};
+    if (blk.mode == MODE_COND) {
+      tail_bwd(k, 1, state_buf, 1);
+      tail_bwd(k, 0, state_buf, 0);
+      tail_grads(blk, k, 1, 0, 4, 1, 0);
+      tail_grads(blk, k, 0, 0, 4, 0, 0);
+      chain_bwd(blk, k, 0, 0, kI_cond, kNet, state_buf, 0, 0);
+    } else {
+      for (int i = 1; i >= 0; --i) {
+        const int ii[2] = {i, i};
+        tail_bwd(k, i, state_buf, 0);
+        tail_grads(blk, k, i, i, 2, 0, 0);
+        chain_bwd(blk, k, i, i, ii, kNet, state_buf, (i == 0) ? 0 : P->C2, 0);
+      }
+    }
+  }
+
+  void build_backward(int kb, int ke) {
+    const ipoke_inn_desc& d = P->d;
+    {
+      Op& o = add_op(OP_BWD_INIT);
+      o.zero_dcond = (d.E > 0 && ke == d.n_flows) ? 1 : 0;
+      o.b_grid = ew_grid(std::max<long long>((long long)B * std::max(1, (int)d.E), 2ll * d.C * d.n_flows));
+    }
+    // un-shuffle the incoming gradient into the physical state layout of block ke-1
+    {
+      Op& o = add_boundary();
+      o.user_in = 1;                                   // patched with dz
+      o.b.src = pk<int>(P->blocks[ke - 1].map_fwd_inv);
+      o.b.out = w<float>(wl.S[0]);
+    }
+    int cur = 0;
+    for (int k = ke - 1; k >= kb; --k) {
+      const Block& blk = P->blocks[k];
+      coupling_bwd(blk, k, cur);
+      Op& o = add_op(OP_BOUNDARY_BWD);
+      BoundaryBwdParams& q = o.bb;
+      q.g = w<float>(wl.S[cur]);
+      q.ld_g = d.C;
+      q.ld_h0 = d.C;
+      q.loc = pk<float>(blk.loc);
+      q.scale = pk<float>(blk.scale);
+      q.leaky = d.conditional;
+      q.alpha = d.alpha;
+      q.ld_dst = d.C;
+      q.acc = w<float>(wl.an_acc) + 2ll * d.C * k;
+      q.counter = w<unsigned int>(wl.an_cnt) + k;
+      q.dld_sum = w<float>(wl.dld_sum);
+      q.B = B;
+      q.C = d.C;
+      o.h0_block = k;
+      o.block_index = k;
+      if (k > kb) {
+        q.dst = w<float>(wl.S[cur ^ 1]);
+        q.map = pk<int>(P->blocks[k - 1].map_fwd);
+        cur ^= 1;
+      } else {
+        o.to_user_dx = 1;
+      }
+    }
+  }
+};
+
 Program* get_program(ipoke_inn_plan* P, const ProgramKey& key, int* err) {
   for (auto& pr : P->programs)
     if (pr->key == key) return pr.get();
   std::unique_ptr<Program> prog(new Program());
   prog->key = key;
-  Builder bld;
+  BwdBuilder bld;
   bld.P = P;
   bld.prog = prog.get();
   bld.packed = static_cast<const char*>(key.packed);
@@ -518,12 +902,19 @@ Program* get_program(ipoke_inn_plan* P, const ProgramKey& key, int* err) {
   bld.wl = ws_layout(P, key.B);
   bld.B = key.B;
   bld.m_tiles = (key.B + BM - 1) / BM;
+  if (key.saved) {
+    bld.saved = static_cast<char*>(const_cast<void*>(key.saved));
+    bld.sl = saved_layout(P, key.B);
+    bld.save = true;
+  }
   // reserve so references stay valid while building
-  const int per_block = 1 + 2 * (P->d.depth + 2);
-  prog->ops.reserve((size_t)(key.ke - key.kb) * per_block + 2);
+  const int per_block = 8 * (P->d.depth + 4) + 8;
+  prog->ops.reserve((size_t)(key.ke - key.kb) * per_block + 8);
   prog->gemms.reserve((size_t)(key.ke - key.kb) * per_block);
+  prog->wgrads.reserve((size_t)(key.ke - key.kb) * per_block);
   if (key.dir == 0) bld.build_forward(key.kb, key.ke, key.want_blocks != 0);
-  else bld.build_reverse(key.kb, key.ke);
+  else if (key.dir == 1) bld.build_reverse(key.kb, key.ke);
+  else bld.build_backward(key.kb, key.ke);
   if (bld.err) {
     *err = IPOKE_INN_E_INTERNAL;
     return nullptr;
@@ -567,14 +958,144 @@ cudaError_t launch_gemm(const ipoke_inn_plan* P, const GemmOp& g, cudaStream_t s
     switch (g.mode) {
       case EPI_HIDDEN: return launch_gemm_t<2, EPI_HIDDEN>(g, st, pdl);
       case EPI_TAIL_FWD: return launch_gemm_t<2, EPI_TAIL_FWD>(g, st, pdl);
-      default: return launch_gemm_t<2, EPI_TAIL_REV>(g, st, pdl);
+      case EPI_TAIL_REV: return launch_gemm_t<2, EPI_TAIL_REV>(g, st, pdl);
+      case EPI_DGRAD: return launch_gemm_t<2, EPI_DGRAD>(g, st, pdl);
+      default: return launch_gemm_t<2, EPI_DU>(g, st, pdl);
     }
   }
   switch (g.mode) {
     case EPI_HIDDEN: return launch_gemm_t<1, EPI_HIDDEN>(g, st, pdl);
     case EPI_TAIL_FWD: return launch_gemm_t<1, EPI_TAIL_FWD>(g, st, pdl);
-    default: return launch_gemm_t<1, EPI_TAIL_REV>(g, st, pdl);
+    case EPI_TAIL_REV: return launch_gemm_t<1, EPI_TAIL_REV>(g, st, pdl);
+    case EPI_DGRAD: return launch_gemm_t<1, EPI_DGRAD>(g, st, pdl);
+    default: return launch_gemm_t<1, EPI_DU>(g, st, pdl);
   }
+}
+
+template <typename... Args>
+cudaError_t launch_ew(void (*kern)(Args...), int grid_x, int grid_y, int pdl, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg;
+  std::memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)grid_x, (unsigned)grid_y);
+  cfg.blockDim = dim3(256);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, args...);
+}
+
+cudaError_t launch_wgrad(const ipoke_inn_plan* P, const WgradOp& wg, const WgradParams& q, cudaStream_t st) {
+  cudaLaunchConfig_t cfg;
+  std::memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)wg.grid);
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = (size_t)wg.smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = P->use_pdl ? 1 : 0;
+  if (P->ksplit == 2) return cudaLaunchKernelEx(&cfg, inn_wgrad_kernel<2>, wg.tmY[0], wg.tmY[1], wg.tmX[0], wg.tmX[1], q);
+  return cudaLaunchKernelEx(&cfg, inn_wgrad_kernel<1>, wg.tmY[0], wg.tmY[1], wg.tmX[0], wg.tmX[1], q);
+}
+
+// caller-owned pointers of one backward call
+struct BwdArgs {
+  const float* x; const float* block_outs; const float* dz; const float* dlogdet;
+  float* dx; float* dcond;
+  float* const* grad_w; float* const* grad_b; float* const* grad_loc; float* const* grad_scale;
+};
+
+int issue_backward(ipoke_inn_plan* P, Program* prog, const BwdArgs& a, cudaStream_t st) {
+  const ipoke_inn_desc& d = P->d;
+  const int B = prog->key.B;
+  const long long BC = (long long)B * d.C;
+  char* ws = static_cast<char*>(prog->key.ws);
+  const WsLayout wl = ws_layout(P, B);
+  float* dcond_acc = d.E > 0 ? (a.dcond ? a.dcond : reinterpret_cast<float*>(ws + wl.dcond)) : nullptr;
+  const int pdl = P->use_pdl;
+  size_t op_i = 0;
+  if (P->profile) {
+    while (P->prof_ev.size() < 2 * prog->ops.size()) {
+      cudaEvent_t ev;
+      cudaError_t e = cudaEventCreate(&ev);
+      if (e != cudaSuccess) return (int)e;
+      P->prof_ev.push_back(ev);
+    }
+    P->prof_kind.assign(prog->ops.size(), 0);
+  }
+  for (Op& o : prog->ops) {
+    int kind = 0;
+    if (o.kind == OP_GEMM) kind = 3;
+    else if (o.kind == OP_WGRAD) kind = 4;
+    if (P->profile) { P->prof_kind[op_i] = kind; cudaEventRecord(P->prof_ev[2 * op_i], st); }
+    cudaError_t e = cudaSuccess;
+    switch (o.kind) {
+      case OP_BWD_INIT: {
+        float* z0 = o.zero_dcond ? dcond_acc : nullptr;
+        const long long n0 = (long long)B * d.E;
+        float* z1 = reinterpret_cast<float*>(ws + wl.an_acc);
+        const long long n1 = (wl.an_cnt + 4ll * d.n_flows - wl.an_acc) / 4;
+        e = launch_ew(inn_bwd_init_kernel, o.b_grid, 1, pdl, st, a.dlogdet, B, reinterpret_cast<float*>(ws + wl.dld_sum),
+                      z0, n0, z1, n1);
+        break;
+      }
+      case OP_BOUNDARY: {
+        BoundaryParams b = o.b;
+        b.in = a.dz;
+        e = launch_ew(inn_boundary_kernel, o.b_grid, 1, pdl, st, (const BoundaryParams)b);
+        break;
+      }
+      case OP_TAIL_BWD: {
+        TailBwdParams t = o.tb;
+        t.dlogdet = a.dlogdet;
+        e = launch_ew(inn_tail_bwd_kernel, o.b_grid, 1, pdl, st, (const TailBwdParams)t);
+        break;
+      }
+      case OP_GEMM: {
+        GemmOp g = prog->gemms[o.gemm];
+        if (o.du_to_user_dcond) g.p.du_cond = dcond_acc;
+        e = launch_gemm(P, g, st);
+        break;
+      }
+      case OP_ZERO_GRAD: {
+        e = cudaMemsetAsync(a.grad_w[o.lin], 0, sizeof(float) * (size_t)o.lin_rows * o.lin_cols, st);
+        if (e == cudaSuccess) e = cudaMemsetAsync(a.grad_b[o.lin], 0, sizeof(float) * (size_t)o.lin_rows, st);
+        break;
+      }
+      case OP_WGRAD: {
+        const WgradOp& wg = prog->wgrads[o.wgrad];
+        WgradParams q = wg.p;
+        for (int g = 0; g < q.G; ++g) {
+          q.gw[g] = a.grad_w[wg.lin[g]];
+          q.gb[g] = a.grad_b[wg.lin[g]];
+        }
+        e = launch_wgrad(P, wg, q, st);
+        break;
+      }
+      case OP_BOUNDARY_BWD: {
+        BoundaryBwdParams q = o.bb;
+        q.h0 = o.h0_block == 0 ? a.x : a.block_outs + (long long)(o.h0_block - 1) * BC;
+        if (o.to_user_dx) { q.dst = a.dx; q.map = nullptr; }
+        q.gloc = a.grad_loc[o.block_index];
+        q.gscale = a.grad_scale[o.block_index];
+        const int gx = (d.C + 31) / 32;
+        int gy = std::max(1, std::min((B + 63) / 64, (2 * P->num_sms + gx - 1) / gx));
+        e = launch_ew(inn_boundary_bwd_kernel, gx, gy, pdl, st, (const BoundaryBwdParams)q);
+        break;
+      }
+      default: return IPOKE_INN_E_INTERNAL;
+    }
+    if (e != cudaSuccess) return (int)e;
+    if (P->profile) cudaEventRecord(P->prof_ev[2 * op_i + 1], st);
+    ++op_i;
+  }
+  P->last_launches = prog->launches;
+  return 0;
 }
 
 int issue_program(ipoke_inn_plan* P, Program* prog, const float* in, const float* cond, float* out, float* logdet_out,
@@ -744,6 +1265,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   P->Ep = d.E > 0 ? (int)round_up(d.E, BK) : 0;
   P->Hp = (int)round_up(d.H, BK);
   P->Np = (int)round_up(P->C2, 16);
+  P->Npk = (int)round_up(P->Np, BK);
   P->ldU = P->C2p + P->Ep;
   P->Gmax = d.conditional ? 4 : 2;
   P->ldACT = P->Gmax * P->Hp;
@@ -774,6 +1296,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
     b.an_ld = bump(cur, 16);
     b.map_fwd = bump(cur, 4ll * d.C);
     b.map_rev = bump(cur, 4ll * d.C);
+    b.map_fwd_inv = bump(cur, 4ll * d.C);
   }
   const int n_lin = d.n_flows * 4 * (d.depth + 2);
   P->jobs_linear = bump(cur, (long long)sizeof(PackJob) * n_lin);
@@ -861,6 +1384,7 @@ int ipoke_inn_pack(const ipoke_inn_plan* cplan, const float* const* linear_w, co
     bj.an_logdet_off = b.an_ld / 4;
     bj.map_fwd_off = b.map_fwd / 4;
     bj.map_rev_off = b.map_rev / 4;
+    bj.map_fwd_inv_off = b.map_fwd_inv / 4;
     bjobs.push_back(bj);
   }
   char* pk = static_cast<char*>(packed);
@@ -890,10 +1414,47 @@ int ipoke_inn_forward(ipoke_inn_plan* P, const void* packed, const float* x, con
   std::lock_guard<std::mutex> lock(P->mu);
   rc = ensure_device(P);
   if (rc) return rc;
-  ProgramKey key{packed, workspace, B, block_begin, block_end, 0, (block_outs || block_logdets) ? 1 : 0};
+  ProgramKey key{packed, workspace, B, block_begin, block_end, 0, (block_outs || block_logdets) ? 1 : 0, nullptr};
   Program* prog = get_program(P, key, &rc);
   if (!prog) return rc;
   return run_program(P, prog, x, cond, z, logdet, block_outs, block_logdets, static_cast<cudaStream_t>(stream));
+}
+
+size_t ipoke_inn_saved_bytes(const ipoke_inn_plan* plan, int B) {
+  if (!plan || B <= 0) return 0;
+  return (size_t)saved_layout(plan, B).total;
+}
+
+int ipoke_inn_forward_train(ipoke_inn_plan* P, const void* packed, const float* x, const float* cond, float* z,
+                            float* logdet, float* block_outs, float* block_logdets, int B, void* workspace,
+                            void* saved, void* stream) {
+  int rc = check_common(P, packed, x, z, B, 0, P ? P->d.n_flows : 0, cond, workspace);
+  if (rc) return rc;
+  if (!logdet || !block_outs || !saved || x == z) return IPOKE_INN_E_INVALID;
+  std::lock_guard<std::mutex> lock(P->mu);
+  rc = ensure_device(P);
+  if (rc) return rc;
+  ProgramKey key{packed, workspace, B, 0, P->d.n_flows, 0, 1, saved};
+  Program* prog = get_program(P, key, &rc);
+  if (!prog) return rc;
+  return run_program(P, prog, x, cond, z, logdet, block_outs, block_logdets, static_cast<cudaStream_t>(stream));
+}
+
+int ipoke_inn_backward(ipoke_inn_plan* P, const void* packed, const float* x, const float* cond,
+                       const float* block_outs, const void* saved, const float* dz, const float* dlogdet, float* dx,
+                       float* dcond, float* const* grad_w, float* const* grad_b, float* const* grad_loc,
+                       float* const* grad_scale, int B, int block_begin, int block_end, void* workspace, void* stream) {
+  int rc = check_common(P, packed, x, dz, B, block_begin, block_end, cond, workspace);
+  if (rc) return rc;
+  if (!block_outs || !saved || !dlogdet || !grad_w || !grad_b || !grad_loc || !grad_scale) return IPOKE_INN_E_INVALID;
+  std::lock_guard<std::mutex> lock(P->mu);
+  rc = ensure_device(P);
+  if (rc) return rc;
+  ProgramKey key{packed, workspace, B, block_begin, block_end, 2, 0, saved};
+  Program* prog = get_program(P, key, &rc);
+  if (!prog) return rc;
+  BwdArgs a{x, block_outs, dz, dlogdet, dx, dcond, grad_w, grad_b, grad_loc, grad_scale};
+  return issue_backward(P, prog, a, static_cast<cudaStream_t>(stream));
 }
 
 int ipoke_inn_reverse(ipoke_inn_plan* P, const void* packed, const float* z, const float* cond, float* x, int B,
@@ -904,7 +1465,7 @@ int ipoke_inn_reverse(ipoke_inn_plan* P, const void* packed, const float* z, con
   std::lock_guard<std::mutex> lock(P->mu);
   rc = ensure_device(P);
   if (rc) return rc;
-  ProgramKey key{packed, workspace, B, block_begin, block_end, 1, 0};
+  ProgramKey key{packed, workspace, B, block_begin, block_end, 1, 0, nullptr};
   Program* prog = get_program(P, key, &rc);
   if (!prog) return rc;
   return run_program(P, prog, z, cond, x, nullptr, nullptr, nullptr, static_cast<cudaStream_t>(stream));
@@ -1013,8 +1574,27 @@ int ipoke_inn_profile_read(ipoke_inn_plan* P, double* ms3, int* launches3) {
     float ms = 0.f;
     e = cudaEventElapsedTime(&ms, P->prof_ev[2 * i], P->prof_ev[2 * i + 1]);
     if (e != cudaSuccess) return (int)e;
+    if (P->prof_kind[i] > 2) continue;           // backward kinds: ipoke_inn_profile_read_n
     ms3[P->prof_kind[i]] += ms;
     launches3[P->prof_kind[i]] += 1;
+  }
+  return 0;
+}
+
+int ipoke_inn_profile_read_n(ipoke_inn_plan* P, double* ms, int* launches, int n) {
+  if (!P || !ms || !launches || n < 1) return IPOKE_INN_E_INVALID;
+  std::lock_guard<std::mutex> lock(P->mu);
+  for (int k = 0; k < n; ++k) { ms[k] = 0.0; launches[k] = 0; }
+  const size_t cnt = P->prof_kind.size();
+  if (cnt == 0) return 0;
+  cudaError_t e = cudaEventSynchronize(P->prof_ev[2 * cnt - 1]);
+  if (e != cudaSuccess) return (int)e;
+  for (size_t i = 0; i < cnt; ++i) {
+    float t = 0.f;
+    e = cudaEventElapsedTime(&t, P->prof_ev[2 * i], P->prof_ev[2 * i + 1]);
+    if (e != cudaSuccess) return (int)e;
+    const int k = P->prof_kind[i];
+    if (k < n) { ms[k] += t; launches[k] += 1; }
   }
   return 0;
 }

@@ -211,6 +211,8 @@ __device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bflo
   hi = __float2bfloat16_rn(v);
   lo = __float2bfloat16_rn(v - __bfloat162float(hi));
 }
+// raw bf16 bits > +0  (sign clear and not zero): LeakyReLU'(pre) selector from a stored activation
+__device__ __forceinline__ bool bf16_bits_positive(uint32_t bits) { return (bits & 0x8000u) == 0u && (bits & 0x7FFFu) != 0u; }
 __device__ __forceinline__ uint32_t pack_bf16x2(__nv_bfloat16 a, __nv_bfloat16 b) {
   return static_cast<uint32_t>(__bfloat16_as_ushort(a)) | (static_cast<uint32_t>(__bfloat16_as_ushort(b)) << 16);
 }

@@ -1,0 +1,289 @@
+// Weight-gradient GEMM of the INN subnetworks on tcgen05 (sm_100a), contraction over the batch.
+//
+//   dW_g[n, k] = sum_b dY_g[b, n] * X_g[b, k]          db_g[n] = sum_b dY_g[b, n]
+//
+// for the G subnetworks of a lockstep chain in one launch.  The reference has no code of its own for this --
+// it is what torch.autograd runs for nn.Linear (models/modules/INN/modules.py:171-188, addmm backward).
+//
+// Both operands are read exactly as the forward / dgrad kernels left them: row-major [B, features] bf16
+// (hi [+ lo]).  The contraction index (batch) is the ROW index of both, i.e. both operands are "MN-major" for
+// the tensor core: a TMA box {64 features, 64 batch rows} with the 128-B swizzle is one canonical MN-major
+// SW128 chunk (8 batch rows x 128 B = one 1024-B swizzle atom, chunks of 64 features LBO apart).
+//   A = dY^T : M = 128 output features (2 chunks), K = 64 batch rows per stage
+//   B = X^T  : N = BN input features (BN/64 chunks)
+// The bias gradient rides on the tensor core too: tiles with n_tile == 0 issue one extra N=16 MMA per k-step
+// against an all-ones B tile, so column BN.. of the accumulator holds sum_b dY[b, n].
+//
+// kSplit = 2 (fp32-parity mode): lo*hi + hi*lo + hi*hi as in the forward kernel.
+// Warp roles as in gemm_kernel.cuh: warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator,
+// warps 4-7 epilogue (TMEM -> regs -> padded smem tile -> coalesced fp32 stores / atomics into the
+// parameter-gradient tensors, which keep the reference's [out, in] layout and true sizes).
+#pragma once
+#include "gemm_kernel.cuh"
+
+namespace inn {
+
+constexpr int WG_CHUNK_BYTES = 64 * 128;          // one {64 features x 64 batch rows} bf16 box
+constexpr int WG_ONES_BYTES = 2 * 1024;           // 16 k-rows x 128 B of bf16 ones (covers any N=16 MN-major read)
+constexpr int WG_MAX_GROUPS = 4;
+
+struct WgradParams {
+  int B;                  // batch rows (contraction length)
+  int num_kb;             // ceil(B / 64)
+  int G;                  // subnetworks in this launch
+  int m_tiles;            // per group: ceil(rows_p / 128)
+  int n_tiles;            // per group: ceil(kin_p / BN)
+  int kslices;            // split of the batch loop across CTAs (atomics when > 1)
+  int BN;                 // 64, 128 or 256
+  int stages;
+  int tmem_cols, nacc;
+  int epi_off;            // byte offset of the epilogue staging tile
+  int dy_col0, dy_group_stride;   // columns of dY: dy_col0 + g * stride + m_tile * 128
+  int x_col0, x_group_stride;     // columns of X
+  int rows_valid;         // true number of output features per group (H or C/2)
+  int kin_p;              // padded input width (columns of X per group)
+  int seg0_valid;         // X columns [0, seg0_valid)                 -> gradient columns [0, seg0_valid)
+  int seg1_start;         // X columns [seg1_start, +seg1_valid)       -> gradient columns [seg0_valid, ...)
+  int seg1_valid;
+  int ld_gw;              // row stride of the gradient tensors (= true fan-in)
+  float* gw[WG_MAX_GROUPS];
+  float* gb[WG_MAX_GROUPS];
+};
+
+__host__ inline int wgrad_stage_bytes(int ksplit, int BN) { return ksplit * (2 + BN / 64) * WG_CHUNK_BYTES; }
+__host__ __device__ inline int wgrad_epi_bytes(int BN) { return BM * (BN + 1) * 4; }
+__host__ inline int wgrad_smem_bytes(int ksplit, int BN, int stages) {
+  return 1024 + stages * wgrad_stage_bytes(ksplit, BN) + WG_ONES_BYTES + ((wgrad_epi_bytes(BN) + 15) & ~15) +
+         SMEM_BARRIER_BYTES;
+}
+
+template <int kSplit>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant__ CUtensorMap tmY1,
+                 const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
+                 const WgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int BN = p.BN;
+  const int n_chunks = BN >> 6;
+  const int stage_bytes = kSplit * (2 + n_chunks) * WG_CHUNK_BYTES;
+  const int stages = p.stages;
+  const int acc_cols = BN + 16;                 // + the bias columns
+  const int nacc = p.nacc;
+
+  uint8_t* ones_smem = smem + stages * stage_bytes;
+  float* epi_tile = reinterpret_cast<float*>(ones_smem + WG_ONES_BYTES);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(epi_tile) + ((wgrad_epi_bytes(BN) + 15) & ~15));
+  uint64_t* empty_bar = full_bar + MAX_STAGES;
+  uint64_t* tfull_bar = empty_bar + MAX_STAGES;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmY0);
+    tma_prefetch_desc(&tmX0);
+    if (kSplit == 2) {
+      tma_prefetch_desc(&tmY1);
+      tma_prefetch_desc(&tmX1);
+    }
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull_bar[a], 1);
+      mbar_init(&tempty_bar[a], EPI_THREADS);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, p.tmem_cols);
+  if (warp == 3) {                               // all-ones B tile for the bias column sums
+    uint32_t* o = reinterpret_cast<uint32_t*>(ones_smem);
+    for (int i = lane; i < WG_ONES_BYTES / 4; i += 32) o[i] = 0x3F803F80u;   // two bf16 1.0
+    fence_proxy_async();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) grid_dep_launch();
+
+  const int tiles_per_group = p.m_tiles * p.n_tiles;
+  const int num_tiles = p.kslices * p.G * tiles_per_group;
+  const int kb_per_slice = (p.num_kb + p.kslices - 1) / p.kslices;
+
+  if (warp == 0) {
+    // ============================ TMA producer ============================
+    grid_dep_wait();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int slice = tile / (p.G * tiles_per_group);
+      int rem = tile - slice * p.G * tiles_per_group;
+      const int g = rem / tiles_per_group;
+      rem -= g * tiles_per_group;
+      const int m_tile = rem / p.n_tiles;
+      const int n_tile = rem - m_tile * p.n_tiles;
+      const int kb0 = slice * kb_per_slice;
+      const int kb1 = min(p.num_kb, kb0 + kb_per_slice);
+      const int y_col = p.dy_col0 + g * p.dy_group_stride + m_tile * BM;
+      const int x_col = p.x_col0 + g * p.x_group_stride + n_tile * BN;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        if (lane == 0) {
+          mbar_wait(&empty_bar[stage], phase ^ 1, 11);
+          mbar_arrive_expect_tx(&full_bar[stage], stage_bytes);
+          uint8_t* sbase = smem + stage * stage_bytes;
+#pragma unroll
+          for (int sp = 0; sp < kSplit; ++sp) {
+            uint8_t* a = sbase + sp * 2 * WG_CHUNK_BYTES;
+            tma_load_2d(a, sp == 0 ? &tmY0 : &tmY1, &full_bar[stage], y_col, kb * 64);
+            tma_load_2d(a + WG_CHUNK_BYTES, sp == 0 ? &tmY0 : &tmY1, &full_bar[stage], y_col + 64, kb * 64);
+            uint8_t* b = sbase + kSplit * 2 * WG_CHUNK_BYTES + sp * n_chunks * WG_CHUNK_BYTES;
+            for (int c = 0; c < n_chunks; ++c)
+              tma_load_2d(b + c * WG_CHUNK_BYTES, sp == 0 ? &tmX0 : &tmX1, &full_bar[stage], x_col + c * 64, kb * 64);
+          }
+        }
+        __syncwarp();
+        if (++stage == stages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ============================ MMA issuer ==============================
+    const uint32_t idesc = umma_idesc_bf16(BM, BN, 1, 1);
+    const uint32_t idesc_b = umma_idesc_bf16(BM, 16, 1, 1);
+    const uint64_t d_ones = umma_desc_mn_sw128(smem_u32(ones_smem), 1024);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int slice = tile / (p.G * tiles_per_group);
+      const int rem = tile - slice * p.G * tiles_per_group;
+      const int n_tile = (rem % tiles_per_group) % p.n_tiles;
+      const bool want_bias = n_tile == 0;
+      const int kb0 = slice * kb_per_slice;
+      const int kb1 = min(p.num_kb, kb0 + kb_per_slice);
+      const int acc = (nacc == 2) ? (it & 1) : 0;
+      const uint32_t acc_phase = ((nacc == 2) ? (it >> 1) : it) & 1;
+      if (lane == 0) {
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1, 12);
+        tc_fence_after();
+      }
+      __syncwarp();
+      const uint32_t d_tmem = tmem_base + acc * acc_cols;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        if (lane == 0) {
+          mbar_wait(&full_bar[stage], phase, 13);
+          tc_fence_after();
+          const uint32_t sbase = smem_u32(smem + stage * stage_bytes);
+          const uint32_t a_hi = sbase;
+          const uint32_t a_lo = sbase + (kSplit - 1) * 2 * WG_CHUNK_BYTES;
+          const uint32_t b_hi = sbase + kSplit * 2 * WG_CHUNK_BYTES;
+          const uint32_t b_lo = b_hi + (kSplit - 1) * n_chunks * WG_CHUNK_BYTES;
+          const uint64_t da_hi = umma_desc_mn_sw128(a_hi, WG_CHUNK_BYTES);
+          const uint64_t da_lo = umma_desc_mn_sw128(a_lo, WG_CHUNK_BYTES);
+          const uint64_t db_hi = umma_desc_mn_sw128(b_hi, WG_CHUNK_BYTES);
+          const uint64_t db_lo = umma_desc_mn_sw128(b_lo, WG_CHUNK_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < 64 / UMMA_K; ++kk) {
+            const uint64_t koff = static_cast<uint64_t>((kk * UMMA_K * 128) >> 4);   // 16 batch rows x 128 B
+            const uint32_t first = (kb == kb0 && kk == 0) ? 0u : 1u;
+            if (kSplit == 2) {
+              umma_bf16_ss(d_tmem, da_lo + koff, db_hi + koff, idesc, first);
+              umma_bf16_ss(d_tmem, da_hi + koff, db_lo + koff, idesc, 1u);
+              umma_bf16_ss(d_tmem, da_hi + koff, db_hi + koff, idesc, 1u);
+              if (want_bias) {
+                umma_bf16_ss(d_tmem + BN, da_lo + koff, d_ones, idesc_b, first);
+                umma_bf16_ss(d_tmem + BN, da_hi + koff, d_ones, idesc_b, 1u);
+              }
+            } else {
+              umma_bf16_ss(d_tmem, da_hi + koff, db_hi + koff, idesc, first);
+              if (want_bias) umma_bf16_ss(d_tmem + BN, da_hi + koff, d_ones, idesc_b, first);
+            }
+          }
+          umma_commit(&empty_bar[stage]);
+          if (kb == kb1 - 1) umma_commit(&tfull_bar[acc]);
+        }
+        __syncwarp();
+        if (++stage == stages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ============================ epilogue ================================
+    grid_dep_wait();
+    const int q = warp - 4;
+    const int tid_e = threadIdx.x - 128;
+    const int r_loc = q * 32 + lane;
+    const int ldt = BN + 1;
+    const bool atomic = p.kslices > 1;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int slice = tile / (p.G * tiles_per_group);
+      int rem = tile - slice * p.G * tiles_per_group;
+      const int g = rem / tiles_per_group;
+      rem -= g * tiles_per_group;
+      const int m_tile = rem / p.n_tiles;
+      const int n_tile = rem - m_tile * p.n_tiles;
+      const int kb0 = slice * kb_per_slice;
+      const int kb1 = min(p.num_kb, kb0 + kb_per_slice);
+      const int acc = (nacc == 2) ? (it & 1) : 0;
+      const uint32_t acc_phase = ((nacc == 2) ? (it >> 1) : it) & 1;
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * acc_cols;
+      if (kb0 >= kb1) continue;                                  // empty slice (never scheduled by the host)
+      mbar_wait(&tfull_bar[acc], acc_phase, 14);
+      tc_fence_after();
+      float* my = epi_tile + r_loc * ldt;
+      for (int c0 = 0; c0 < BN; c0 += 16) {
+        float v[16];
+        tmem_ld16(t_row + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) my[c0 + j] = v[j];
+      }
+      const int row = m_tile * BM + r_loc;                       // output feature inside the group
+      if (n_tile == 0) {
+        float v[16];
+        tmem_ld16(t_row + BN, v);
+        tmem_ld_wait();
+        if (row < p.rows_valid && p.gb[g] != nullptr) {
+          if (atomic) atomicAdd(p.gb[g] + row, v[0]);
+          else p.gb[g][row] = v[0];
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tempty_bar[acc]);
+      named_bar_sync(1, EPI_THREADS);
+      // coalesced write-out: consecutive threads -> consecutive gradient columns of one row
+      float* gw = p.gw[g];
+      const int col_base = n_tile * BN;
+      for (int idx = tid_e; idx < BM * BN; idx += EPI_THREADS) {
+        const int r = idx / BN;
+        const int c = idx - r * BN;
+        const int grow = m_tile * BM + r;
+        const int xcol = col_base + c;
+        int gcol = -1;
+        if (xcol < p.seg0_valid) gcol = xcol;
+        else if (xcol >= p.seg1_start && xcol < p.seg1_start + p.seg1_valid) gcol = xcol - p.seg1_start + p.seg0_valid;
+        if (grow < p.rows_valid && gcol >= 0) {
+          float* dst = gw + static_cast<size_t>(grow) * p.ld_gw + gcol;
+          const float val = epi_tile[r * ldt + c];
+          if (atomic) atomicAdd(dst, val);
+          else *dst = val;
+        }
+      }
+      named_bar_sync(1, EPI_THREADS);                            // staging tile is reused by the next tile
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
+}  // namespace inn

@@ -35,6 +35,11 @@ class FlowEngine:
         self.assume_frozen = False            # skip the per-call parameter-version check (inference loops)
         self.sync_actnorm_init = True         # all-reduce ActNorm init moments when torch.distributed is up
         self.launches = 0
+        self.bwd_launches = 0
+        self.grad_ready_hook = None           # callable(engine, flat_grad, block_begin, block_end): see parallel.GradSync
+        self.grad_chunk_blocks = 2
+        self.last_flat_grad = None
+        self._grad_layout = None
 
     # ------------------------------------------------------------------ plumbing
     def invalidate(self):
@@ -226,6 +231,79 @@ class FlowEngine:
                                         ws.data_ptr(), self._stream()), "reverse")
         self.launches = L.ipoke_inn_last_launch_count(self._plan)
         return x
+
+    # ------------------------------------------------------------------ training (forward with saved state, backward)
+    def forward_train(self, x, cond):
+        """Forward that keeps what the fused backward needs.  -> z, logdet, block_outs [n,B,C], block_logdets [n,B], saved"""
+        B, x2, c2 = self._prep(x, cond)
+        L = self._ensure(x2.device)
+        self._maybe_actnorm_init(x2, c2)
+        self.pack()
+        dev = self._device
+        z = torch.empty(B, self.C, dtype=torch.float32, device=dev)
+        ld = torch.empty(B, dtype=torch.float32, device=dev)
+        outs = torch.empty(self.n_flows, B, self.C, dtype=torch.float32, device=dev)
+        lds = torch.empty(self.n_flows, B, dtype=torch.float32, device=dev)
+        saved = torch.empty(L.ipoke_inn_saved_bytes(self._plan, B), dtype=torch.uint8, device=dev)
+        ws = self._workspace(B)
+        _capi.check(L.ipoke_inn_forward_train(self._plan, self._packed.data_ptr(), x2.data_ptr(),
+                                              c2.data_ptr() if c2 is not None else None, z.data_ptr(), ld.data_ptr(),
+                                              outs.data_ptr(), lds.data_ptr(), B, ws.data_ptr(), saved.data_ptr(),
+                                              self._stream()), "forward_train")
+        self.launches = L.ipoke_inn_last_launch_count(self._plan)
+        return z, ld, outs, lds, saved, x2, c2
+
+    def grad_layout(self):
+        """Flat fp32 gradient buffer layout: every parameter of the flow in ``flow.parameters()`` order (which is
+        block by block), so a block's gradients are one contiguous slice (per-block all-reduce chunks)."""
+        if getattr(self, "_grad_layout", None) is None:
+            offs, cur = {}, 0
+            block_ranges = []
+            for k, blk in enumerate(self.flow.sub_layers):
+                start = cur
+                for p in blk.parameters():
+                    offs[id(p)] = (cur, p.numel(), tuple(p.shape))
+                    cur += p.numel()
+                block_ranges.append((start, cur))
+            params = [p for blk in self.flow.sub_layers for p in blk.parameters()]
+            self._grad_layout = (offs, cur, block_ranges, params)
+        return self._grad_layout
+
+    def new_grad_buffer(self):
+        """-> flat [total] fp32 (fresh storage: gradients handed to autograd must not alias a later call's),
+        the per-parameter views in ``flow.parameters()`` order and the pointer arrays of the C ABI."""
+        offs, total, block_ranges, params = self.grad_layout()
+        flat = torch.empty(total, dtype=torch.float32, device=self._device)
+        base = flat.data_ptr()
+        lin_w, lin_b, loc, scale, _, _ = self._tensors()
+
+        def ptrs(tensors):
+            arr = (ctypes.c_void_p * len(tensors))()
+            for i, t in enumerate(tensors):
+                arr[i] = base + 4 * offs[id(t)][0]
+            return arr
+        views = [flat[offs[id(p)][0]: offs[id(p)][0] + offs[id(p)][1]].view(offs[id(p)][2]) for p in params]
+        return flat, views, (ptrs(lin_w), ptrs(lin_b), ptrs(loc), ptrs(scale))
+
+    def backward(self, x2, c2, outs, saved, dz, dld, grad_ptrs, want_dx=True, want_dcond=True, block_begin=0,
+                 block_end=None, dcond=None):
+        """Fused backward over blocks [block_begin, block_end).  -> dx [B,C] or None, dcond [B,E] or None."""
+        L = _capi.lib()
+        B = x2.shape[0]
+        block_end = self.n_flows if block_end is None else block_end
+        dev = self._device
+        dx = torch.empty(B, self.C, dtype=torch.float32, device=dev) if want_dx else None
+        if self.E > 0 and want_dcond and dcond is None:
+            dcond = torch.empty(B, self.E, dtype=torch.float32, device=dev)
+        gw, gb, gloc, gscale = grad_ptrs
+        ws = self._workspace(B)
+        _capi.check(L.ipoke_inn_backward(self._plan, self._packed.data_ptr(), x2.data_ptr(),
+                                         c2.data_ptr() if c2 is not None else None, outs.data_ptr(), saved.data_ptr(),
+                                         dz.data_ptr(), dld.data_ptr(), dx.data_ptr() if dx is not None else None,
+                                         dcond.data_ptr() if dcond is not None else None, gw, gb, gloc, gscale,
+                                         B, block_begin, block_end, ws.data_ptr(), self._stream()), "backward")
+        self.bwd_launches = L.ipoke_inn_last_launch_count(self._plan)
+        return dx, dcond
 
     # host-buffer entry points (pinned CPU tensors in, pinned CPU tensors out; stream-ordered, caller syncs)
     def forward_host(self, x_host, cond_host, z_host, logdet_host):

@@ -24,6 +24,43 @@ LEAKY_MLP_SLOPE = 0.01   # nn.LeakyReLU() default, models/modules/INN/modules.py
 INV_LEAKY_ALPHA = 0.9    # InvLeakyRelu(alpha=0.9), models/modules/INN/flow_blocks.py:373
 
 
+# ------------------------------------------------- optional emulation of the GPU's bf16 GEMM operands
+# The CUDA path's precision="bf16" variant rounds every GEMM operand (weights, MLP inputs, hidden
+# activations, and in the backward pass the output-gradient operands) to bfloat16 and accumulates in fp32.
+# With ``gemm_rounding("bf16")`` active the oracle rounds at exactly those points, so the bf16 variant can
+# be held to a tight bound against "the same arithmetic on the CPU" (LeakyReLU' is discontinuous: against
+# the exact fp32 reference a bf16 forward flips the mask of units whose pre-activation is ~1e-3 from zero,
+# which moves single-sample gradient contributions by O(1) -- see tests/test_gpu_backward.py).
+def round_bf16(a):
+    """Round-to-nearest-even to bfloat16, returned in the input's dtype."""
+    a = np.asarray(a)
+    u = np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+    r = ((u >> np.uint32(16)) & np.uint32(1)) + np.uint32(0x7FFF)
+    return ((u + r) & np.uint32(0xFFFF0000)).view(np.float32).astype(a.dtype)
+
+
+_ROUND = None
+
+
+class gemm_rounding:
+    """Context manager: ``with gemm_rounding("bf16"): ...`` (None / "none" = exact)."""
+
+    def __init__(self, mode):
+        self.fn = round_bf16 if mode == "bf16" else None
+
+    def __enter__(self):
+        global _ROUND
+        self.prev, _ROUND = _ROUND, self.fn
+
+    def __exit__(self, *exc):
+        global _ROUND
+        _ROUND = self.prev
+
+
+def _R(a):
+    return a if _ROUND is None else _ROUND(a)
+
+
 # --------------------------------------------------------------------------- MLP
 def _linear_indices(sd, prefix):
     """Indices of the nn.Linear entries inside ``<prefix>.main`` (0, 2, 4, ...)."""
@@ -45,7 +82,7 @@ def basic_fc_net(sd, prefix, x, use_tanh):
     for n, i in enumerate(idx):
         w = sd[f"{prefix}.main.{i}.weight"].astype(x.dtype, copy=False)
         b = sd[f"{prefix}.main.{i}.bias"].astype(x.dtype, copy=False)
-        h = h @ w.T + b                                  # nn.Linear: y = x W^T + b
+        h = _R(h) @ _R(w).T + b                          # nn.Linear: y = x W^T + b
         if n + 1 < len(idx):
             h = np.where(h >= 0, h, h * x.dtype.type(LEAKY_MLP_SLOPE))
     if use_tanh:
@@ -261,14 +298,17 @@ def flow_loss(z, logdet, nll_weight=1.0, logdet_weight=1.0):
 # ---------------------------------------------------------------------- backward
 def _fc_forward_cache(sd, prefix, x, use_tanh):
     idx = _linear_indices(sd, prefix)
-    acts = [x]
-    h = x
+    h = _R(x)
+    acts = [h]
     for n, i in enumerate(idx):
         w = sd[f"{prefix}.main.{i}.weight"].astype(x.dtype, copy=False)
         b = sd[f"{prefix}.main.{i}.bias"].astype(x.dtype, copy=False)
-        h = h @ w.T + b
+        h = h @ _R(w).T + b
         if n + 1 < len(idx):
-            h = np.where(h >= 0, h, h * x.dtype.type(LEAKY_MLP_SLOPE))
+            if _KINK_LOG is not None:      # per-sample distance of the closest pre-activation to LeakyReLU's kink
+                rms = np.sqrt(np.mean(h * h)) + 1e-30
+                _KINK_LOG.append(np.min(np.abs(h), axis=1) / rms)
+            h = _R(np.where(h >= 0, h, h * x.dtype.type(LEAKY_MLP_SLOPE)))
             acts.append(h)
     out = np.tanh(h) if use_tanh else h
     return out, acts
@@ -278,16 +318,17 @@ def _fc_backward(sd, prefix, acts, out, dout, use_tanh, grads):
     """Reverse-mode through BasicFullyConnectedNet (autograd over modules.py:190-191)."""
     idx = _linear_indices(sd, prefix)
     dt = dout.dtype
-    g = dout * (1.0 - out * out) if use_tanh else dout
+    g = _R(dout * (1.0 - out * out) if use_tanh else dout)
     for n in reversed(range(len(idx))):
         i = idx[n]
         w = sd[f"{prefix}.main.{i}.weight"].astype(dt, copy=False)
         a = acts[n]
         grads[f"{prefix}.main.{i}.weight"] = grads.get(f"{prefix}.main.{i}.weight", 0) + g.T @ a
         grads[f"{prefix}.main.{i}.bias"] = grads.get(f"{prefix}.main.{i}.bias", 0) + g.sum(axis=0)
-        g = g @ w
+        g = g @ _R(w)
         if n > 0:
-            g = g * np.where(a >= 0, dt.type(1.0), dt.type(LEAKY_MLP_SLOPE))
+            # torch's leaky_relu backward: input > 0 ? grad : grad * slope (a has the sign of the pre-activation)
+            g = _R(g * np.where(a > 0, dt.type(1.0), dt.type(LEAKY_MLP_SLOPE)))
     return g
 
 
@@ -371,6 +412,25 @@ def flow_backward(sd, x, cond, dz, dlogdet, dtype=np.float64):
         grads[f"{p}.norm_layer.loc"] = np.sum(gc * scale[None], axis=0).reshape(1, -1, 1, 1)
         g = gc * scale[None]
     return grads, g, dcond
+
+
+_KINK_LOG = None
+
+
+def kink_distance(sd, x, cond=None):
+    """Per sample: min over every hidden unit of every subnetwork of |pre-activation| / rms(layer).
+
+    LeakyReLU' is discontinuous at 0, so a gradient comparison between two arithmetics is only meaningful for
+    samples whose pre-activations all stay clear of 0 by more than the forward error of the less exact one.
+    Samples of the flow are independent (ActNorm is already initialised), so tests simply drop the others."""
+    global _KINK_LOG
+    _KINK_LOG = []
+    try:
+        x = np.asarray(x, dtype=np.float64)
+        flow_backward(sd, x, cond, np.zeros_like(x), np.zeros(x.shape[0]))
+        return np.min(np.stack(_KINK_LOG, axis=0), axis=0)
+    finally:
+        _KINK_LOG = None
 
 
 # --------------------------------------------------------------------- utilities

@@ -1,0 +1,162 @@
+"""GPU parity of the fused backward kernels (run on the B200 box), through loss.backward() on the module API:
+(1) against gradients torch.autograd produced on the live reference modules (committed fixtures, FlowLoss),
+(2) against the fp64 numpy oracle's hand-derived backward at mid sizes with random output gradients,
+(3) block-chunked backward (the gradient all-reduce overlap path) == single-call backward.
+
+Tolerances: max-abs error relative to the tensor's max-abs, per gradient tensor.
+  precision="fp32" (split-bf16): <= 2e-4 against the exact reference (fixtures / fp64 oracle).
+  precision="bf16"             : <= 2e-2 against the oracle run with the SAME bf16 operand rounding
+      (oracle.gemm_rounding("bf16")).  Against the exact fp32 reference a bf16 forward is not a meaningful
+      per-tensor yardstick for gradients: LeakyReLU' is discontinuous, units whose pre-activation lies within
+      the bf16 GEMM error of zero flip their mask and move single-sample contributions by O(1) (the CPU
+      emulation shows the same 0.2-0.6 per-tensor deviations at the tiny test sizes).  The stated bound of the
+      bf16 variant vs the exact reference is therefore global: rel-L2 over ALL gradients <= 0.1 at these sizes.
+"""
+import numpy as np
+import pytest
+import torch
+
+import ipoke_inn_b200 as P
+from oracle import inn_oracle as O
+from conftest import load_golden, max_rel
+from test_host_logic import CFG, build
+
+pytestmark = pytest.mark.gpu
+
+GTOL = {"fp32": 2e-4, "bf16": 2e-2}
+GLOBAL_L2_BF16 = 0.1
+
+
+def _dev():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return torch.device("cuda:0")
+
+
+def _load(name, precision):
+    sd_ref, d = load_golden(name)
+    net = build(name, precision=precision)
+    net.load_state_dict({k: torch.from_numpy(v) for k, v in sd_ref.items()}, strict=True)
+    return net.to(_dev()), sd_ref, d
+
+
+def _report(errs, tol):
+    bad = sorted(((e, k) for k, e in errs.items() if not (e < tol)), reverse=True)
+    msg = "\n".join(f"  {k}: {e:.3e}" for e, k in bad[:12])
+    assert not bad, f"{len(bad)}/{len(errs)} gradient tensors above {tol:g}:\n{msg}"
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", ["cfgS_cond", "uncond_small"])
+def test_backward_matches_reference_autograd_fixture(name, precision):
+    net, sd_ref, d = _load(name, precision)
+    dev = _dev()
+    x = torch.from_numpy(d["x"]).to(dev).requires_grad_(True)
+    cond = torch.from_numpy(d["cond"]).to(dev).requires_grad_(True) if "cond" in d else None
+    z, ld = net(x, cond) if cond is not None else net(x)
+    loss, log = P.FlowLoss()(z, ld)
+    loss.backward()
+    tol = GTOL[precision]
+    assert abs(float(loss.detach()) - float(d["loss"])) < tol * max(1.0, abs(float(d["loss"])))
+    if precision == "bf16":
+        # global deviation from the exact reference gradients (see module docstring)
+        num = sum(float(((p.grad.cpu().numpy() - d["grad::" + k]) ** 2).sum()) for k, p in net.named_parameters())
+        den = sum(float((d["grad::" + k] ** 2).sum()) for k, p in net.named_parameters())
+        assert np.sqrt(num / den) < GLOBAL_L2_BF16
+        assert max_rel(x.grad.cpu().numpy(), d["dx"]) < 5e-2
+        return
+    errs = {"dx": max_rel(x.grad.cpu().numpy(), d["dx"])}
+    if cond is not None:
+        errs["dcond"] = max_rel(cond.grad.cpu().numpy(), d["dcond"])
+    for k, p in net.named_parameters():
+        assert p.grad is not None, k
+        errs[k] = max_rel(p.grad.cpu().numpy(), d["grad::" + k])
+    _report(errs, tol)
+
+
+KINK_MARGIN = 3e-5     # fp32-split forward error is ~1e-6 of a layer's rms: 30x clearance
+
+
+def _oracle_case(name, B, precision, seed=5):
+    """B samples whose hidden pre-activations all stay clear of LeakyReLU's kink (oracle.kink_distance): the
+    derivative is discontinuous there, and with ~1e6 unit-samples a few would otherwise land within the
+    forward rounding error of 0 and flip their mask relative to the fp64 oracle."""
+    net, sd_ref, d = _load(name, precision)
+    kind, kw = CFG[name]
+    C, E = kw["flow_in_channels"], kw.get("flow_embedding_channels", 0)
+    g = torch.Generator().manual_seed(seed)
+    n = B + B // 2 + 8
+    x = torch.randn(n, C, generator=g)
+    cond = torch.randn(n, E, 1, 1, generator=g) if kind == "cond" else None
+    dist = O.kink_distance(sd_ref, x.numpy(), None if cond is None else cond.numpy().reshape(n, -1))
+    keep = torch.from_numpy(np.nonzero(dist > KINK_MARGIN)[0][:B])
+    assert len(keep) == B, f"only {len(keep)} of {n} candidate samples clear the kink margin"
+    x = x[keep].contiguous()
+    cond = cond[keep].contiguous() if cond is not None else None
+    dz = torch.randn(B, C, generator=g)
+    dld = torch.randn(B, generator=g)
+    return net, sd_ref, x, cond, dz, dld
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("name,B", [("cfgA_mini", 200), ("cfgB_mini", 130), ("cfgS_cond", 700), ("uncond_small", 1)])
+def test_backward_matches_fp64_oracle(name, B, precision):
+    net, sd_ref, x, cond, dz, dld = _oracle_case(name, B, precision)
+    dev = _dev()
+    xg = x.to(dev).requires_grad_(True)
+    cg = cond.to(dev).requires_grad_(True) if cond is not None else None
+    z, ld = net(xg, cg) if cg is not None else net(xg)
+    obj = (z.reshape(B, -1) * dz.to(dev)).sum() + (ld * dld.to(dev)).sum()
+    obj.backward()
+    with O.gemm_rounding("bf16" if precision == "bf16" else None):
+        grads, dx_ref, dcond_ref = O.flow_backward(sd_ref, x.numpy(),
+                                                   None if cond is None else cond.numpy().reshape(B, -1),
+                                                   dz.numpy(), dld.numpy())
+    tol = GTOL[precision]
+    errs = {"dx": max_rel(xg.grad.cpu().numpy(), dx_ref)}
+    if cg is not None:
+        errs["dcond"] = max_rel(cg.grad.cpu().numpy().reshape(B, -1), dcond_ref)
+    for k, p in net.named_parameters():
+        errs[k] = max_rel(p.grad.cpu().numpy(), np.asarray(grads[k]).reshape(p.shape))
+    if precision == "bf16":
+        # two bf16 arithmetics differ by accumulation order: an activation that lands on a bf16 rounding boundary
+        # moves by one ulp and can carry a unit across the kink; a handful of such chains is expected, a tiling
+        # or indexing bug would break most tensors
+        num = sum(float(((p.grad.cpu().numpy().astype(np.float64) - np.asarray(grads[k]).reshape(p.shape)) ** 2).sum())
+                  for k, p in net.named_parameters())
+        den = sum(float((np.asarray(grads[k]) ** 2).sum()) for k, p in net.named_parameters())
+        assert np.sqrt(num / den) < 2e-2, f"global rel-L2 {np.sqrt(num / den):.3e}"
+        n_bad = sum(1 for e in errs.values() if not e < tol)
+        assert n_bad <= max(2, len(errs) // 10), f"{n_bad}/{len(errs)} tensors above {tol}"
+        return
+    _report(errs, tol)
+
+
+def test_chunked_backward_equals_single_call_and_accumulates():
+    name, B = "cfgS_cond", 96
+    net, sd_ref, x, cond, dz, dld = _oracle_case(name, B, "fp32")
+    dev = _dev()
+
+    def run(hook):
+        net.zero_grad(set_to_none=True)
+        net.flow.engine.grad_ready_hook = hook
+        xg = x.to(dev).requires_grad_(True)
+        cg = cond.to(dev).requires_grad_(True)
+        z, ld = net(xg, cg)
+        ((z.reshape(B, -1) * dz.to(dev)).sum() + (ld * dld.to(dev)).sum()).backward()
+        return ([p.grad.clone() for p in net.parameters()], xg.grad.clone(), cg.grad.clone())
+
+    calls = []
+    g0, dx0, dc0 = run(None)
+    g1, dx1, dc1 = run(lambda eng, flat, kb, ke: calls.append((kb, ke)))
+    net.flow.engine.grad_ready_hook = None
+    assert calls == [(6, 8), (4, 6), (2, 4), (0, 2)]
+    assert torch.allclose(dx0, dx1, rtol=0, atol=1e-6 * float(dx0.abs().max()))
+    assert torch.allclose(dc0, dc1, rtol=0, atol=1e-6 * float(dc0.abs().max()))
+    for a, b in zip(g0, g1):
+        assert torch.allclose(a, b, rtol=0, atol=1e-6 * float(a.abs().max()) + 1e-12)
+    # a second backward without zero_grad accumulates (autograd semantics)
+    xg = x.to(dev).requires_grad_(True)
+    z, ld = net(xg, cond.to(dev))
+    ((z.reshape(B, -1) * dz.to(dev)).sum() + (ld * dld.to(dev)).sum()).backward()
+    for a, p in zip(g1, net.parameters()):
+        assert torch.allclose(p.grad, 2 * a, rtol=0, atol=2e-6 * float(a.abs().max()) + 1e-12)
