@@ -61,46 +61,49 @@ def macs_per_sample(kind, kw):
 
 # ----------------------------------------------------------------------------- clocks
 class ClockSampler:
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled DURING the timed region: an NVML polling thread (5 ms period; the
+    timed region of the default workload lasts tens of milliseconds, too short for `nvidia-smi -lms`)."""
+    BAD = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
 
     def __init__(self, gpu_index):
-        self.rows, self.proc = [], None
+        self.rows, self.ok, self._stop = [], False, False
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[gpu_index]) if vis and vis.split(",")[gpu_index].strip().isdigit() else gpu_index
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.ok = True
+            self.t = threading.Thread(target=self._poll, daemon=True)
             self.t.start()
-        except Exception:
-            self.proc = None
+        except Exception as e:  # noqa: BLE001
+            self.err = str(e)[:100]
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append((time.time(), line.strip()))
+    def _poll(self):
+        nv = self.nv
+        while not self._stop:
+            try:
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                try:
+                    reasons = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:  # noqa: BLE001
+                    reasons = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.rows.append((time.time(), float(mhz), int(reasons)))
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(0.005)
 
     def stop(self, t0, t1):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        sm, mx, reasons = [], None, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        rows = [r for (t, r) in self.rows if t0 - 0.05 <= t <= t1 + 0.15] or [r for (_, r) in self.rows]
-        for r in rows:
-            f = [x.strip() for x in r.split(",")]
-            try:
-                sm.append(float(f[0]))
-                mx = float(f[1])
-            except Exception:
-                continue
-            for nm, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
-                "samples": len(sm)}
+        if not self.ok:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable: " + getattr(self, "err", "")]}
+        self._stop = True
+        self.t.join(1.0)
+        rows = [r for r in self.rows if t0 <= r[0] <= t1] or [r for r in self.rows if t0 - 0.05 <= r[0] <= t1 + 0.05]
+        sm = sorted(r[1] for r in rows)
+        reasons = sorted(n for n, bit in self.BAD.items() if any(r[2] & bit for r in rows))
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "reasons": reasons,
+                "samples": len(sm), "source": "NVML polled every 5 ms inside the timed region"}
 
 
 # ----------------------------------------------------------------------------- CPU arm (oracle port)
@@ -153,6 +156,8 @@ def gpu_run(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
     kind, kw, defB, src = CONFIGS[args.config]
     B = args.batch or defB
@@ -349,6 +354,47 @@ def gpu_run(args):
             except Exception as e:      # the sweep is informational; never lose the headline line
                 sweep.append({"config": cname, "batch": cb, "precision": prec, "error": str(e)[:200]})
         out["sweep"] = sweep
+        # ---- training step (forward with saved state + FlowLoss + fused backward), informational
+        train = []
+        for cname, cb, prec in [("cfgB", 256, "bf16"), ("cfgA", 64, "bf16"), ("cfgA", 4096, "bf16"), ("cfgA", 4096, "fp32")]:
+            try:
+                k2, kw2, _, _ = CONFIGS[cname]
+                torch.manual_seed(42)
+                n2 = (P.SupervisedTransformer(dict(kw2), precision=prec) if k2 == "cond" else
+                      P.UnsupervisedTransformer3(**kw2, precision=prec)).to(dev)
+                C2, E2 = kw2["flow_in_channels"], kw2.get("flow_embedding_channels", 0)
+                xs = torch.randn(cb, C2, device=dev, generator=g)
+                cs = torch.randn(cb, E2, 1, 1, device=dev, generator=g) if k2 == "cond" else None
+                lf = P.FlowLoss()
+
+                def tstep():
+                    n2.zero_grad(set_to_none=True)
+                    zz, ll = n2(xs, cs) if cs is not None else n2(xs)
+                    lo, _ = lf(zz, ll)
+                    lo.backward()
+                for _ in range(3):
+                    tstep()
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                reps = 5
+                e0.record()
+                for _ in range(reps):
+                    tstep()
+                e1.record()
+                torch.cuda.synchronize()
+                t = e0.elapsed_time(e1) / reps * 1e-3
+                pw2 = macs_per_sample(k2, kw2)
+                eng2 = n2.flow.engine
+                train.append({"config": cname, "batch": cb, "precision": prec, "ms_per_step": t * 1e3,
+                              "samples_per_s": cb / t, "tflops_algorithmic_6Pw": cb * 6 * pw2 / t / 1e12,
+                              "frac_of_bf16_peak": cb * 6 * pw2 / t / 1e12 / pk["bf16"],
+                              "launches": eng2.launches + eng2.bwd_launches + 1,
+                              "what": "forward(train) + FlowLoss + fused backward (dgrad, wgrad, ActNorm grads), no optimizer"})
+                del n2, xs, cs
+                torch.cuda.empty_cache()
+            except Exception as e:  # noqa: BLE001
+                train.append({"config": cname, "batch": cb, "precision": prec, "error": str(e)[:200]})
+        out["train_step"] = train
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
