@@ -12,13 +12,13 @@ def _needs_grad(engine, x, cond):
 
 
 def flow_forward(engine, x, cond):
-    """-> z [B,C], logdet [B], block_outs [n,B,C], block_logdets [n,B]."""
+    """-> z [B,C], logdet [B], block_outs [n,B,C] | None, block_logdets [n,B] | None."""
     if _needs_grad(engine, x, cond):
         from .backward import FlowFunction
         params = engine.grad_layout()[3]
         return FlowFunction.apply(engine, x, cond, *params)
     with torch.no_grad():
-        return engine.forward(x, cond, want_blocks=True)
+        return engine.forward(x, cond, want_blocks=False)      # per-block lists: lazily, see flow_blocks._FusedFlowMixin
 
 
 def flow_reverse(engine, z, cond):

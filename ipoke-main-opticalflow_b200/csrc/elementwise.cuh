@@ -290,13 +290,14 @@ struct PackBlockJob {
   const float* loc; const float* scale;       // [C]
   const long long* perm_fwd; const long long* perm_bwd;   // int64 [C]
   long long loc_off, scale_off, an_logdet_off;            // float offsets
-  long long map_fwd_off, map_rev_off, map_fwd_inv_off;    // int32 offsets
+  long long map_fwd_off, map_rev_off, map_fwd_inv_off, map_rev_inv_off;    // int32 offsets
 };
 
 // One CTA per flow block: copy loc/scale, sum log|scale| (modules.py:298-299), build the int32 gather maps
 //   map_fwd[p] = (perm_fwd[p] + C/2) % C     (coupling output is stored [xa' | xb'], logical order is [xb' | xa'])
 //   map_rev[p] = perm_bwd[(p + C/2) % C]
-//   map_fwd_inv[map_fwd[p]] = p            (gradient of the gather: dS[b, q] = g[b, map_fwd_inv[q]])
+//   map_fwd_inv[map_fwd[p]] = p            (gradient of the gather: dS[b, q] = g[b, map_fwd_inv[q]]; folded forward scatter)
+//   map_rev_inv[map_rev[p]] = p            (folded reverse scatter)
 __global__ void __launch_bounds__(256) inn_pack_block_kernel(const PackBlockJob* __restrict__ jobs, void* packed, int C) {
   const PackBlockJob j = jobs[blockIdx.x];
   float* pf = reinterpret_cast<float*>(packed);
@@ -312,6 +313,7 @@ __global__ void __launch_bounds__(256) inn_pack_block_kernel(const PackBlockJob*
     pi[j.map_fwd_off + c] = static_cast<int>((j.perm_fwd[c] + half) % C);
     pi[j.map_rev_off + c] = static_cast<int>(j.perm_bwd[(c + half) % C]);
     pi[j.map_fwd_inv_off + static_cast<int>((j.perm_fwd[c] + half) % C)] = c;   // inverse of map_fwd (backward un-shuffle)
+    pi[j.map_rev_inv_off + static_cast<int>(j.perm_bwd[(c + half) % C])] = c;     // inverse of map_rev (folded reverse scatter)
   }
   red[threadIdx.x] = acc;
   __syncthreads();

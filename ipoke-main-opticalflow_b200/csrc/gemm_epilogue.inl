@@ -1,8 +1,10 @@
 // Epilogue warps (4..7) of inn_gemm_kernel -- textually included inside the kernel body.
-// One thread owns one accumulator row (TMEM lane); 128 threads cover the 128-row tile.
+// Two threads own one accumulator row (TMEM lane): warps 4-7 take the even 16/32-column groups, warps 8-11 the
+// odd ones; 256 threads cover the 128-row tile.
     // ============================ epilogue ================================
-    const int q = warp - 4;                       // TMEM lane quarter (== warp % 4)
-    const int tid_e = threadIdx.x - 128;          // 0..127
+    const int q = warp & 3;                       // TMEM lane quarter (== warp % 4, a hardware restriction)
+    const int ch = (warp - 4) >> 2;               // column half handled by this warp
+    const int tid_e = threadIdx.x - 128;          // 0..255
     const int r_loc = q * 32 + lane;              // row inside the tile
     int it = 0;
     int slab_ctr = 0;
@@ -38,23 +40,23 @@
               else bulk_wait_read<0>();
             }
             named_bar_sync(1, EPI_THREADS);                      // slab buffer `buf` is free again
-            float v[64];
+            float v[32];                                         // this thread's half of the 64-column slab row
 #pragma unroll
-            for (int c = 0; c < 4; ++c) tmem_ld16(t_row + s * 64 + c * 16, v + c * 16);
+            for (int c = 0; c < 2; ++c) tmem_ld16(t_row + s * 64 + ch * 32 + c * 16, v + c * 16);
             tmem_ld_wait();
             if (s == n_slabs - 1) {                              // accumulator fully read: hand TMEM back
               tc_fence_before();
               mbar_arrive(&tempty_bar[acc]);
             }
-            const float* bs = bias_s + s * 64;
+            const float* bs = bias_s + s * 64 + ch * 32;
             uint8_t* slab_hi = epi_smem + (buf * kSplit) * SLAB_BYTES + r_loc * 128;
             uint8_t* slab_lo = slab_hi + SLAB_BYTES;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
+            for (int j = 0; j < 4; ++j) {
               uint32_t hi[4], lo[4];
               uint4 mk = make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u);   // bf16 ones: mask = 1
               if (kMode == EPI_DGRAD && mask_row != nullptr)
-                mk = __ldg(reinterpret_cast<const uint4*>(mask_row + s * 64) + j);
+                mk = __ldg(reinterpret_cast<const uint4*>(mask_row + s * 64 + ch * 32) + j);
               const uint32_t mw[4] = {mk.x, mk.y, mk.z, mk.w};
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
@@ -74,7 +76,7 @@
                 hi[e] = pack_bf16x2(h0, h1);
                 lo[e] = pack_bf16x2(l0, l1);
               }
-              const int chunk = (j ^ (r_loc & 7)) << 4;          // 128-B swizzle: 16-B chunk index XOR (row % 8)
+              const int chunk = ((ch * 4 + j) ^ (r_loc & 7)) << 4;   // 128-B swizzle: 16-B chunk index XOR (row % 8)
               *reinterpret_cast<uint4*>(slab_hi + chunk) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
               if (kSplit == 2) *reinterpret_cast<uint4*>(slab_lo + chunk) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
             }
@@ -89,7 +91,7 @@
           }
         } else {
           // ---- narrow tiles (BN < 64, small batches): direct 32-B global stores per thread
-          for (int c0 = 0; c0 < BN; c0 += 16) {
+          for (int c0 = ch * 16; c0 < BN; c0 += 32) {
             float v[16];
             tmem_ld16(t_row + c0, v);
             tmem_ld_wait();
@@ -133,7 +135,7 @@
         //      half, columns [cond_col0, cond_col0 + E) into the conditioning gradient (flow_blocks.py:137, 224)
         mbar_wait(&tfull_bar[acc], acc_phase, 4);
         tc_fence_after();
-        for (int c0 = 0; c0 < BN; c0 += 16) {
+        for (int c0 = ch * 16; c0 < BN; c0 += 32) {
           float v[16];
           tmem_ld16(t_row + c0, v);
           tmem_ld_wait();
@@ -177,7 +179,7 @@
         tc_fence_after();
         float ld_sum = 0.f;
         float* my_keep = keep_s + r_loc * ldk;
-        for (int c0 = 0; c0 < BN; c0 += 16) {
+        for (int c0 = ch * 16; c0 < BN; c0 += 32) {
           float vs[16], vt[16];
           tmem_ld16(t_row + c0, vs);
           tmem_ld16(t_row + BN + c0, vt);
@@ -185,15 +187,17 @@
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             const int c = c0 + j;
-            const float s = tanhf(vs[j] + bias_s[c]);
+            // bf16 mode: tanh / exp from ex2.approx (abs error ~2e-7, far below the bf16 GEMM error);
+            // fp32-parity mode keeps libm-accurate tanhf / expf
+            const float s = kSplit == 2 ? tanhf(vs[j] + bias_s[c]) : fast_tanh(vs[j] + bias_s[c]);
             const float t = vt[j] + bias_t[c];
             const float keep = my_keep[c];
             float nw;
             if (kMode == EPI_TAIL_FWD) {
-              nw = keep * expf(s) + t;
+              nw = keep * (kSplit == 2 ? expf(s) : __expf(s)) + t;
               if (col_base + c < p.n_valid) ld_sum += s;
             } else {
-              nw = (keep - t) * expf(-s);
+              nw = (keep - t) * (kSplit == 2 ? expf(-s) : __expf(-s));
             }
             my_keep[c] = nw;
             if (p.s_save != nullptr && row_ok && col_base + c < p.n_valid) {
@@ -205,8 +209,8 @@
         tc_fence_before();
         mbar_arrive(&tempty_bar[acc]);
         if (kMode == EPI_TAIL_FWD && row_ok) {
-          if (p.logdet_atomic) atomicAdd(p.logdet + row, ld_sum);
-          else p.logdet[row] += ld_sum;
+          if (p.ld_extra != nullptr && n_tile == 0 && ch == 0) ld_sum += __ldg(p.ld_extra);
+          atomicAdd(p.logdet + row, ld_sum);       // two column halves (and possibly several n-tiles) per row
         }
         named_bar_sync(1, EPI_THREADS);
         for (int idx = tid_e; idx < BM * BN; idx += EPI_THREADS) {
@@ -216,12 +220,34 @@
           const int gcol = col_base + c;
           if (grow < p.M && gcol < p.n_valid) {
             const float nw = keep_s[r * ldk + c];
-            p.state[static_cast<size_t>(grow) * p.ld_state + p.keep_off + gcol] = nw;
             if (p.u_hi != nullptr) {
               __nv_bfloat16 h, l;
               split_bf16(nw, h, l);
               p.u_hi[static_cast<size_t>(grow) * p.ld_u + gcol] = h;
               if (kSplit == 2) p.u_lo[static_cast<size_t>(grow) * p.ld_u + gcol] = l;
+            }
+            if (p.f_out == nullptr) {
+              p.state[static_cast<size_t>(grow) * p.ld_state + p.keep_off + gcol] = nw;
+            } else {
+              // folded boundary: this element's place (and normalisation) in the next block's state
+              const int src = p.keep_off + gcol;
+              const int dst = p.f_dst != nullptr ? __ldg(p.f_dst + src) : src;
+              float v = nw;
+              if (p.f_mode == 1) {
+                v = __ldg(p.f_scale + dst) * (v + __ldg(p.f_loc + dst));
+                if (p.f_leaky) v = v * (v >= 0.f ? 1.0f : p.f_alpha);
+              } else if (p.f_mode == 2) {
+                if (p.f_leaky) v = v / (v >= 0.f ? 1.0f : p.f_alpha);
+                v = v / __ldg(p.f_scale + src) - __ldg(p.f_loc + src);
+              }
+              p.f_out[static_cast<size_t>(grow) * p.f_ld + dst] = v;
+              const int ucol = dst - p.f_u_begin;
+              if (p.f_u_hi != nullptr && ucol >= 0 && ucol < p.n_valid) {
+                __nv_bfloat16 h, l;
+                split_bf16(v, h, l);
+                p.f_u_hi[static_cast<size_t>(grow) * p.ld_u + ucol] = h;
+                if (kSplit == 2) p.f_u_lo[static_cast<size_t>(grow) * p.ld_u + ucol] = l;
+              }
             }
           }
         }

@@ -12,8 +12,8 @@
 // kSplit = 2 is the fp32-parity mode: activations and weights are carried as bf16 hi + bf16 lo and each
 // k-step issues lo*hi + hi*lo + hi*hi (3 MMAs, fp32 accumulate), dropping only the lo*lo term (~2^-16 rel).
 //
-// Warp roles (256 threads): warp 0 TMA producer, warp 1 MMA issuer (one lane), warp 2 TMEM allocator,
-// warps 4-7 epilogue (TMEM lane quarter = warp % 4). Rings: smem full/empty (TMA <-> MMA), TMEM full/empty
+// Warp roles (384 threads): warp 0 TMA producer, warp 1 MMA issuer (one lane), warp 2 TMEM allocator,
+// warps 4-11 epilogue (TMEM lane quarter = warp % 4, column half = (warp - 4) / 4). Rings: smem full/empty (TMA <-> MMA), TMEM full/empty
 // (MMA <-> epilogue, double-buffered when the accumulators fit twice in the allocated columns).
 #pragma once
 #include "ptx.cuh"
@@ -26,8 +26,10 @@ constexpr int UMMA_K = 16;
 constexpr int A_TILE_BYTES = BM * BK * 2;
 constexpr int SLAB_BYTES = BM * 128;    // one 128 x 64 bf16 output slab (TMA store box)
 constexpr int MAX_STAGES = 8;
-constexpr int GEMM_THREADS = 256;
-constexpr int EPI_THREADS = 128;
+constexpr int GEMM_THREADS = 384;       // warps 0-3: TMA / MMA / TMEM alloc / idle; warps 4-11: epilogue
+constexpr int EPI_THREADS = 256;        // two warps per TMEM lane quarter, each takes half of the columns
+constexpr int WG_THREADS = 256;         // wgrad kernel (wgrad_kernel.cuh) keeps one epilogue warp per quarter
+constexpr int WG_EPI_THREADS = 128;
 constexpr int SMEM_BARRIER_BYTES = 256;
 
 enum EpiMode { EPI_HIDDEN = 0, EPI_TAIL_FWD = 1, EPI_TAIL_REV = 2, EPI_DGRAD = 3, EPI_DU = 4 };
@@ -70,6 +72,21 @@ struct GemmParams {
   float* s_save;          // training: per half-step tanh output s and the pre-update kept half (nullable)
   float* keep_save;
   int ld_save;
+  // Folded block boundary (inference programs): the updated half goes straight into the NEXT block's layout --
+  // Shuffle scatter + ActNorm (+ InvLeakyRelu) of the next block in forward, their inverses in reverse
+  // (flow_blocks.py:255-274, 322-326, 380-387; modules.py:292-316) -- so no boundary kernel runs between blocks.
+  float* f_out;           // nullable = not folded; [M, f_ld] next state (or the caller's output)
+  int f_ld;
+  const int* f_dst;       // [C] destination column of physical source column (keep_off + c)
+  const float* f_loc;     // f_mode 1: indexed by destination column; f_mode 2: by source column
+  const float* f_scale;
+  int f_mode;             // 0: scatter only, 1: v = scale*(v+loc) [, *alpha if < 0], 2: [v /= alpha if < 0,] v = v/scale - loc
+  int f_leaky;
+  float f_alpha;
+  __nv_bfloat16* f_u_hi;  // next half-step's MLP input: destination columns [f_u_begin, f_u_begin + n_valid)
+  __nv_bfloat16* f_u_lo;
+  int f_u_begin;
+  const float* ld_extra;  // nullable: scalar added once per row (the next block's ActNorm log-det)
   // backward (EPI_DGRAD / EPI_DU): dX = dY * W with W read MN-major straight from the forward layout
   int w_mn;               // 1: the W tile is {64 rows of the contraction index} x {BN columns}, MN-major for the MMA
   int w_group_rows;       // w_mn: first W row of group g = w_row0[0] + g * w_group_rows

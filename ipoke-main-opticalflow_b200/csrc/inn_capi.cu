@@ -52,7 +52,7 @@ struct Block {
   Chain chains[2];
   int n_chains = 2;
   Tail tails[2];
-  long long loc = -1, scale = -1, an_ld = -1, map_fwd = -1, map_rev = -1, map_fwd_inv = -1;   // byte offsets
+  long long loc = -1, scale = -1, an_ld = -1, map_fwd = -1, map_rev = -1, map_fwd_inv = -1, map_rev_inv = -1;   // byte offsets
 };
 
 struct GemmOp {
@@ -75,6 +75,7 @@ struct Op {
   int gemm;  // index into gemm ops
   // which user pointers this boundary op takes (patched per call)
   int user_in, user_cond, user_out_final, block_index;
+  int user_logdet;    // folded programs: the log-det accumulates in the caller's buffer (boundary and tail ops)
   // backward ops
   TailBwdParams tb;
   BoundaryBwdParams bb;
@@ -113,7 +114,7 @@ struct Program {
 };
 
 struct WsLayout {
-  long long S[2], U_hi, U_lo, ACT_hi[2], ACT_lo[2], logdet, xin, condin, zout, ldout, total;
+  long long S[2], U_hi, U_lo, U2_hi, U2_lo, ACT_hi[2], ACT_lo[2], logdet, xin, condin, zout, ldout, total;
   // backward scratch
   long long dt_hi[2], dt_lo[2], dcond, an_acc, an_cnt, dld_sum;
 };
@@ -148,6 +149,7 @@ struct ipoke_inn_plan {
   int last_launches = 0;
   // launch options: 1 = replay the program as a CUDA graph (captured on an internal stream), PDL attribute on GEMMs
   int use_graph = 1, use_pdl = 1, use_mcast = 0;
+  int use_fold = 1;              // inference programs: block boundaries folded into the coupling tails
   int w_prefetch = 1;
   int latency_smem_cap_kb = 0;   // > 0: cap smem of one-wave launches so two kernels can be co-resident under PDL
   cudaStream_t cap_stream = nullptr;
@@ -200,6 +202,8 @@ WsLayout ws_layout(const ipoke_inn_plan* P, int B) {
   w.an_acc = bump(cur, 4ll * 2 * C * P->d.n_flows);
   w.an_cnt = bump(cur, 4ll * P->d.n_flows);
   w.dld_sum = bump(cur, 16);
+  w.U2_hi = bump(cur, 2ll * B * P->ldU);       // second MLP-input buffer (folded programs alternate per block)
+  w.U2_lo = bump(cur, 2ll * B * P->ldU);
   w.total = round_up(cur, 1024);
   return w;
 }
@@ -301,12 +305,12 @@ TileCfg tile_cfg(int ksplit, int mode, int bn) {
 
 // Largest UMMA N that divides `rows_per_group`, keeps >= 2 pipeline stages and still yields about one CTA
 // per SM; otherwise the smallest (most tiles) -- small batches are latency/weight-streaming bound.
-TileCfg pick_bn(const ipoke_inn_plan* P, int mode, int rows_per_group, int tiles_other) {
+TileCfg pick_bn(const ipoke_inn_plan* P, int mode, int rows_per_group, int tiles_other, int bn_max = 256) {
   static const int cand[5] = {256, 128, 64, 32, 16};
   TileCfg best;
   for (int i = 0; i < 5; ++i) {
     const int bn = cand[i];
-    if (rows_per_group % bn != 0) continue;
+    if (bn > bn_max || rows_per_group % bn != 0) continue;
     const TileCfg t = tile_cfg(P->ksplit, mode, bn);
     if (t.stages < 2) continue;
     best = t;
@@ -337,12 +341,18 @@ struct Builder {
   SavedLayout sl;
   bool save = false;
   int cur_block = 0;
+  // inference programs: Shuffle / ActNorm / InvLeakyRelu between blocks run inside the tail epilogues
+  bool fold = false;
+  int f_kb = 0, f_ke = 0;
 
   template <typename T>
   T* sv(long long off) const { return off < 0 ? nullptr : reinterpret_cast<T*>(saved + off); }
   // MLP input buffer of (block, half-step)
   char* u_base(int k, int i, int sp) const {
-    if (!save) return ws + (sp == 0 ? wl.U_hi : wl.U_lo);
+    if (!save) {
+      if (fold && (k & 1)) return ws + (sp == 0 ? wl.U2_hi : wl.U2_lo);
+      return ws + (sp == 0 ? wl.U_hi : wl.U_lo);
+    }
     const SavedBlock& sb = sl.blk[k];
     const int j = sb.U_hi[i] >= 0 ? i : 0;
     return saved + (sp == 0 ? sb.U_hi[j] : sb.U_lo[j]);
@@ -466,10 +476,14 @@ struct Builder {
   }
 
   // act_layer: index of the last hidden layer of chain `ci` (its output feeds the tail)
-  void tail(const Block& blk, int k, int i, int ci, int act_layer, int G, int state_buf, bool reverse, bool write_u) {
+  void tail(const Block& blk, int k, int i, int ci, int act_layer, int G, int state_buf, bool reverse, bool write_u,
+            bool last_in_block) {
     const Tail& t = blk.tails[i];
     GemmOp& g = add_gemm(reverse ? EPI_TAIL_REV : EPI_TAIL_FWD);
-    TileCfg tc = pick_bn(P, g.mode, P->Np, m_tiles);
+    Op& op = prog->ops.back();
+    // two accumulators (s, t) per stage: cap the tile at 128 columns so TMEM still double-buffers and the
+    // (transcendental-heavy) epilogue of tile i overlaps the MMAs of tile i+1
+    TileCfg tc = pick_bn(P, g.mode, P->Np, m_tiles, 128);
     const int bn = tc.bn;
     g.p.num_n_tiles = P->Np / bn;
     tc.mc = pick_mc(P, m_tiles * (P->Np / bn), P->Np / bn, P->Np / bn);
@@ -493,6 +507,38 @@ struct Builder {
       g.p.u_lo = reinterpret_cast<__nv_bfloat16*>(u_base(k, 1, 1));
       g.p.ld_u = P->ldU;
     }
+    if (fold) {
+      const ipoke_inn_desc& d = P->d;
+      const int nk = reverse ? k - 1 : k + 1;                      // the block that consumes this one's output
+      const bool has_next = reverse ? nk >= f_kb : nk < f_ke;
+      g.p.f_ld = d.C;
+      g.p.f_alpha = d.alpha;
+      g.p.f_leaky = d.conditional;
+      g.p.ld_u = P->ldU;
+      if (has_next) {
+        g.p.f_out = w<float>(wl.S[state_buf ^ 1]);
+        g.p.f_u_hi = reinterpret_cast<__nv_bfloat16*>(u_base(nk, 0, 0));
+        g.p.f_u_lo = reinterpret_cast<__nv_bfloat16*>(u_base(nk, 0, 1));
+        g.p.f_u_begin = reverse ? P->C2 : 0;
+      } else {
+        op.user_out_final = 1;                                     // f_out = the caller's output
+      }
+      if (!reverse) {
+        g.p.f_dst = pk<int>(blk.map_fwd_inv);
+        g.p.f_mode = has_next ? 1 : 0;
+        if (has_next) {
+          g.p.f_loc = pk<float>(P->blocks[nk].loc);
+          g.p.f_scale = pk<float>(P->blocks[nk].scale);
+          if (last_in_block) g.p.ld_extra = pk<float>(P->blocks[nk].an_ld);
+        }
+        op.user_logdet = 1;
+      } else {
+        g.p.f_dst = has_next ? pk<int>(P->blocks[nk].map_rev_inv) : nullptr;   // nullptr = identity
+        g.p.f_mode = 2;
+        g.p.f_loc = pk<float>(blk.loc);
+        g.p.f_scale = pk<float>(blk.scale);
+      }
+    }
     if (save && !reverse) {
       g.p.s_save = sv<float>(sl.blk[k].s[i]);
       g.p.keep_save = sv<float>(sl.blk[k].keep[i]);
@@ -510,24 +556,32 @@ struct Builder {
   void coupling(const Block& blk, int k, int state_buf, bool reverse) {
     if (blk.mode == MODE_COND) {
       const int al = chain(blk.chains[0], k, 0, 0);
-      tail(blk, k, reverse ? 1 : 0, 0, al, 4, state_buf, reverse, false);
-      tail(blk, k, reverse ? 0 : 1, 0, al, 4, state_buf, reverse, false);
+      tail(blk, k, reverse ? 1 : 0, 0, al, 4, state_buf, reverse, false, false);
+      tail(blk, k, reverse ? 0 : 1, 0, al, 4, state_buf, reverse, false, true);
     } else {
       // forward: half-step 0 reads U(k,0) (written by the boundary) and writes U(k,1); reverse runs 1 then 0 and,
       // without `save`, both U views are the same scratch buffer
       const int first = reverse ? 1 : 0;
       int al = chain(blk.chains[first], k, first, reverse ? 0 : first);
-      tail(blk, k, first, first, al, 2, state_buf, reverse, true);
+      tail(blk, k, first, first, al, 2, state_buf, reverse, true, false);
       al = chain(blk.chains[1 - first], k, 1 - first, reverse ? 1 : 1 - first);
-      tail(blk, k, 1 - first, 1 - first, al, 2, state_buf, reverse, false);
+      tail(blk, k, 1 - first, 1 - first, al, 2, state_buf, reverse, false, true);
     }
   }
 
   void build_forward(int kb, int ke, bool want_blocks) {
     const ipoke_inn_desc& d = P->d;
     int cur = 0;
+    fold = P->use_fold && !save && !want_blocks;
+    f_kb = kb;
+    f_ke = ke;
     for (int k = kb; k < ke; ++k) {
       const Block& blk = P->blocks[k];
+      if (fold && k > kb) {            // the previous block's tails already wrote this block's state and MLP input
+        cur ^= 1;
+        coupling(blk, k, cur, false);
+        continue;
+      }
       Op& o = add_boundary();
       BoundaryParams& b = o.b;
       const int nxt = (k == kb) ? 0 : (cur ^ 1);
@@ -549,6 +603,11 @@ struct Builder {
         b.u2_hi = reinterpret_cast<__nv_bfloat16*>(u_base(k, 1, 0));
         b.u2_lo = P->ksplit == 2 ? reinterpret_cast<__nv_bfloat16*>(u_base(k, 1, 1)) : nullptr;
       }
+      if (fold) {                                // both alternating MLP-input buffers get the cond columns / padding
+        b.u2_hi = reinterpret_cast<__nv_bfloat16*>(u_base(k + 1, 0, 0));
+        b.u2_lo = P->ksplit == 2 ? reinterpret_cast<__nv_bfloat16*>(u_base(k + 1, 0, 1)) : nullptr;
+        o.user_logdet = 1;
+      }
       if (save) o.user_cond = d.E > 0;
       if (d.E > 0) {
         b.E = d.E;
@@ -561,6 +620,7 @@ struct Builder {
       cur = nxt;
       coupling(blk, k, cur, false);
     }
+    if (fold) return;
     Op& o = add_boundary();
     BoundaryParams& b = o.b;
     b.in = w<float>(wl.S[cur]);
@@ -573,8 +633,16 @@ struct Builder {
   void build_reverse(int kb, int ke) {
     const ipoke_inn_desc& d = P->d;
     int cur = 0;
+    fold = P->use_fold && !save;
+    f_kb = kb;
+    f_ke = ke;
     for (int k = ke - 1; k >= kb; --k) {
       const Block& blk = P->blocks[k];
+      if (fold && k < ke - 1) {
+        cur ^= 1;
+        coupling(blk, k, cur, true);
+        continue;
+      }
       Op& o = add_boundary();
       BoundaryParams& b = o.b;
       const int nxt = (k == ke - 1) ? 0 : (cur ^ 1);
@@ -590,6 +658,10 @@ struct Builder {
       b.src = pk<int>(blk.map_rev);
       b.out = w<float>(wl.S[nxt]);
       set_u(b, P->C2, k, 0);
+      if (fold) {
+        b.u2_hi = reinterpret_cast<__nv_bfloat16*>(u_base(k + 1, 0, 0));
+        b.u2_lo = P->ksplit == 2 ? reinterpret_cast<__nv_bfloat16*>(u_base(k + 1, 0, 1)) : nullptr;
+      }
       if (d.E > 0) {
         b.E = d.E;
         b.ld_cond = d.E;
@@ -599,6 +671,7 @@ struct Builder {
       cur = nxt;
       coupling(blk, k, cur, true);
     }
+    if (fold) return;
     Op& o = add_boundary();
     BoundaryParams& b = o.b;
     b.in = w<float>(wl.S[cur]);
@@ -925,7 +998,7 @@ Program* get_program(ipoke_inn_plan* P, const ProgramKey& key, int* err) {
 }
 
 template <int kSplit, int kMode>
-cudaError_t launch_gemm_t(const GemmOp& g, cudaStream_t st, int pdl) {
+cudaError_t launch_gemm_t(const GemmOp& g, const GemmParams& gp, cudaStream_t st, int pdl) {
   cudaLaunchConfig_t cfg;
   std::memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3((unsigned)g.grid);
@@ -949,26 +1022,26 @@ cudaError_t launch_gemm_t(const GemmOp& g, cudaStream_t st, int pdl) {
   cfg.attrs = attr;
   cfg.numAttrs = na;
   return cudaLaunchKernelEx(&cfg, inn_gemm_kernel<kSplit, kMode>, g.tmA[0], g.tmA[1], g.tmW[0], g.tmW[1], g.tmO[0],
-                            g.tmO[1], g.p);
+                            g.tmO[1], gp);
 }
 
-cudaError_t launch_gemm(const ipoke_inn_plan* P, const GemmOp& g, cudaStream_t st) {
+cudaError_t launch_gemm(const ipoke_inn_plan* P, const GemmOp& g, const GemmParams& gp, cudaStream_t st) {
   const int pdl = P->use_pdl;
   if (P->ksplit == 2) {
     switch (g.mode) {
-      case EPI_HIDDEN: return launch_gemm_t<2, EPI_HIDDEN>(g, st, pdl);
-      case EPI_TAIL_FWD: return launch_gemm_t<2, EPI_TAIL_FWD>(g, st, pdl);
-      case EPI_TAIL_REV: return launch_gemm_t<2, EPI_TAIL_REV>(g, st, pdl);
-      case EPI_DGRAD: return launch_gemm_t<2, EPI_DGRAD>(g, st, pdl);
-      default: return launch_gemm_t<2, EPI_DU>(g, st, pdl);
+      case EPI_HIDDEN: return launch_gemm_t<2, EPI_HIDDEN>(g, gp, st, pdl);
+      case EPI_TAIL_FWD: return launch_gemm_t<2, EPI_TAIL_FWD>(g, gp, st, pdl);
+      case EPI_TAIL_REV: return launch_gemm_t<2, EPI_TAIL_REV>(g, gp, st, pdl);
+      case EPI_DGRAD: return launch_gemm_t<2, EPI_DGRAD>(g, gp, st, pdl);
+      default: return launch_gemm_t<2, EPI_DU>(g, gp, st, pdl);
     }
   }
   switch (g.mode) {
-    case EPI_HIDDEN: return launch_gemm_t<1, EPI_HIDDEN>(g, st, pdl);
-    case EPI_TAIL_FWD: return launch_gemm_t<1, EPI_TAIL_FWD>(g, st, pdl);
-    case EPI_TAIL_REV: return launch_gemm_t<1, EPI_TAIL_REV>(g, st, pdl);
-    case EPI_DGRAD: return launch_gemm_t<1, EPI_DGRAD>(g, st, pdl);
-    default: return launch_gemm_t<1, EPI_DU>(g, st, pdl);
+    case EPI_HIDDEN: return launch_gemm_t<1, EPI_HIDDEN>(g, gp, st, pdl);
+    case EPI_TAIL_FWD: return launch_gemm_t<1, EPI_TAIL_FWD>(g, gp, st, pdl);
+    case EPI_TAIL_REV: return launch_gemm_t<1, EPI_TAIL_REV>(g, gp, st, pdl);
+    case EPI_DGRAD: return launch_gemm_t<1, EPI_DGRAD>(g, gp, st, pdl);
+    default: return launch_gemm_t<1, EPI_DU>(g, gp, st, pdl);
   }
 }
 
@@ -991,7 +1064,7 @@ cudaError_t launch_wgrad(const ipoke_inn_plan* P, const WgradOp& wg, const Wgrad
   cudaLaunchConfig_t cfg;
   std::memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3((unsigned)wg.grid);
-  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.blockDim = dim3(WG_THREADS);
   cfg.dynamicSmemBytes = (size_t)wg.smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -1059,7 +1132,7 @@ int issue_backward(ipoke_inn_plan* P, Program* prog, const BwdArgs& a, cudaStrea
       case OP_GEMM: {
         GemmOp g = prog->gemms[o.gemm];
         if (o.du_to_user_dcond) g.p.du_cond = dcond_acc;
-        e = launch_gemm(P, g, st);
+        e = launch_gemm(P, g, g.p, st);
         break;
       }
       case OP_ZERO_GRAD: {
@@ -1124,6 +1197,7 @@ int issue_program(ipoke_inn_plan* P, Program* prog, const float* in, const float
       BoundaryParams b = o.b;
       if (o.user_in) b.in = in;
       if (o.user_cond) b.cond = cond;
+      if (o.user_logdet) b.logdet = logdet_out;
       if (o.block_index >= 0) {
         if (block_outs) b.raw_out = block_outs + o.block_index * BC;
         if (block_lds) b.block_logdet = block_lds + (long long)o.block_index * prog->key.B;
@@ -1152,7 +1226,11 @@ int issue_program(ipoke_inn_plan* P, Program* prog, const float* in, const float
       cudaError_t e = cudaLaunchKernelEx(&cfg, inn_boundary_kernel, b);
       if (e != cudaSuccess) return (int)e;
     } else {
-      cudaError_t e = launch_gemm(P, prog->gemms[o.gemm], st);
+      const GemmOp& g = prog->gemms[o.gemm];
+      GemmParams gp = g.p;
+      if (o.user_logdet) gp.logdet = logdet_out;
+      if (o.user_out_final) gp.f_out = out;
+      cudaError_t e = launch_gemm(P, g, gp, st);
       if (e != cudaSuccess) return (int)e;
     }
   }
@@ -1257,6 +1335,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_GRAPH")) P->use_graph = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_PDL")) P->use_pdl = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_MCAST")) P->use_mcast = std::atoi(e) != 0;
+  if (const char* e = std::getenv("IPOKE_INN_FOLD")) P->use_fold = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_WPREFETCH")) P->w_prefetch = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_STAGECAP_KB")) P->latency_smem_cap_kb = std::atoi(e);
   P->ksplit = d.precision == IPOKE_INN_PREC_FP32_SPLIT ? 2 : 1;
@@ -1297,6 +1376,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
     b.map_fwd = bump(cur, 4ll * d.C);
     b.map_rev = bump(cur, 4ll * d.C);
     b.map_fwd_inv = bump(cur, 4ll * d.C);
+    b.map_rev_inv = bump(cur, 4ll * d.C);
   }
   const int n_lin = d.n_flows * 4 * (d.depth + 2);
   P->jobs_linear = bump(cur, (long long)sizeof(PackJob) * n_lin);
@@ -1385,6 +1465,7 @@ int ipoke_inn_pack(const ipoke_inn_plan* cplan, const float* const* linear_w, co
     bj.map_fwd_off = b.map_fwd / 4;
     bj.map_rev_off = b.map_rev / 4;
     bj.map_fwd_inv_off = b.map_fwd_inv / 4;
+    bj.map_rev_inv_off = b.map_rev_inv / 4;
     bjobs.push_back(bj);
   }
   char* pk = static_cast<char*>(packed);
@@ -1550,6 +1631,7 @@ int ipoke_inn_set_option(ipoke_inn_plan* P, const char* name, int value) {
   if (std::strcmp(name, "graph") == 0) P->use_graph = value != 0;
   else if (std::strcmp(name, "pdl") == 0) { P->use_pdl = value != 0; P->programs.clear(); }
   else if (std::strcmp(name, "mcast") == 0) { P->use_mcast = value != 0; P->programs.clear(); }
+  else if (std::strcmp(name, "fold") == 0) { P->use_fold = value != 0; P->programs.clear(); }
   else return IPOKE_INN_E_INVALID;
   return 0;
 }

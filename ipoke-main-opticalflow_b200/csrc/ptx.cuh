@@ -206,6 +206,13 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, int a_mn_ma
          (static_cast<uint32_t>(M >> 4) << 24);
 }
 
+// tanh from one ex2.approx and one fast divide: 1 - 2 / (exp(2x) + 1). Saturates correctly (exp -> inf gives 1,
+// exp -> 0 gives -1); absolute error ~2e-7.
+__device__ __forceinline__ float fast_tanh(float x) {
+  const float e = __expf(2.0f * x);
+  return 1.0f - __fdividef(2.0f, e + 1.0f);
+}
+
 // ------------------------------------------------------------------ bf16 split
 __device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bfloat16& lo) {
   hi = __float2bfloat16_rn(v);

@@ -58,7 +58,7 @@ __host__ inline int wgrad_smem_bytes(int ksplit, int BN, int stages) {
 }
 
 template <int kSplit>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(WG_THREADS, 1)
 inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant__ CUtensorMap tmY1,
                  const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
                  const WgradParams p) {
@@ -96,7 +96,7 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull_bar[a], 1);
-      mbar_init(&tempty_bar[a], EPI_THREADS);
+      mbar_init(&tempty_bar[a], WG_EPI_THREADS);
     }
     fence_mbar_init();
   }
@@ -255,11 +255,11 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
       }
       tc_fence_before();
       mbar_arrive(&tempty_bar[acc]);
-      named_bar_sync(1, EPI_THREADS);
+      named_bar_sync(1, WG_EPI_THREADS);
       // coalesced write-out: consecutive threads -> consecutive gradient columns of one row
       float* gw = p.gw[g];
       const int col_base = n_tile * BN;
-      for (int idx = tid_e; idx < BM * BN; idx += EPI_THREADS) {
+      for (int idx = tid_e; idx < BM * BN; idx += WG_EPI_THREADS) {
         const int r = idx / BN;
         const int c = idx - r * BN;
         const int grow = m_tile * BM + r;
@@ -274,7 +274,7 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
           else *dst = val;
         }
       }
-      named_bar_sync(1, EPI_THREADS);                            // staging tile is reused by the next tile
+      named_bar_sync(1, WG_EPI_THREADS);                            // staging tile is reused by the next tile
     }
   }
 

@@ -125,6 +125,54 @@ class _FusedFlowMixin:
         old.release()
         return self
 
+    # ``last_outs`` / ``last_logdets`` (reference flow_blocks.py:48-57) are only read by the wrappers' ``train=True``
+    # return (INN.py:80-81, 284-285).  Under no_grad the fused forward therefore skips the per-block outputs (so
+    # the block boundaries stay folded into the coupling tails) and the lists are materialised on first access
+    # by one extra pass over the same input tensors (which are kept alive, not copied, until the next call).
+    def _reset_last(self):
+        self._last_outs, self._last_logdets, self._last_lazy = [], [], None
+
+    def _fill_last(self, outs, lds):
+        four_d = not bool(self._engine.desc.conditional)            # unconditional blocks return 4-D (reference :606)
+        self._last_outs = [o.unsqueeze(-1).unsqueeze(-1) for o in outs.unbind(0)] if four_d else list(outs.unbind(0))
+        self._last_logdets = list(lds.unbind(0))
+        self._last_lazy = None
+
+    def _materialise_last(self):
+        if getattr(self, "_last_lazy", None) is not None:
+            x, cond = self._last_lazy
+            with torch.no_grad():
+                _, _, outs, lds = self._engine.forward(x, cond, want_blocks=True)
+            self._fill_last(outs, lds)
+
+    @property
+    def last_outs(self):
+        self._materialise_last()
+        return self._last_outs
+
+    @last_outs.setter
+    def last_outs(self, v):
+        self._last_outs, self._last_lazy = v, None
+
+    @property
+    def last_logdets(self):
+        self._materialise_last()
+        return self._last_logdets
+
+    @last_logdets.setter
+    def last_logdets(self, v):
+        self._last_logdets, self._last_lazy = v, None
+
+    def _forward_fused(self, x, cond):
+        from .autograd import flow_forward
+        self._reset_last()
+        z, logdet, outs, lds = flow_forward(self._engine, x, cond)
+        if outs is not None:
+            self._fill_last(outs, lds)
+        else:
+            self._last_lazy = (x, cond)
+        return z.unsqueeze(-1).unsqueeze(-1), logdet                # reference :57
+
     def _apply(self, fn, *args, **kwargs):      # .to() / .cuda() / .float(): parameters move, repack
         out = super()._apply(fn, *args, **kwargs)
         self._engine.invalidate()
@@ -154,20 +202,15 @@ class ConditionalFlow(_FusedFlowMixin, nn.Module):
             self.sub_layers.append(ConditionalFlatDoubleCouplingFlowBlock(
                 self.in_channels, self.cond_channels, self.mid_channels, self.num_blocks,
                 activation=activation, mode=mode))
-        self.last_outs, self.last_logdets = [], []
+        self._reset_last()
         alpha = 0.9 if activation == "lrelu" else 1.0              # 'none' -> identity (IgnoreLeakyRelu)
         self._make_engine(True, embedding_dim, alpha, precision or DEFAULT_PRECISION)
 
     def forward(self, x, embedding, reverse=False):
         assert len(embedding.shape) == 4                            # reference flow_blocks.py:127
-        self.last_outs, self.last_logdets = [], []
         if not reverse:
-            from .autograd import flow_forward
-            z, logdet, outs, lds = flow_forward(self._engine, x, embedding)
-            if outs is not None:
-                self.last_outs = list(outs.unbind(0))               # [B,C] each, reference :55
-                self.last_logdets = list(lds.unbind(0))
-            return z.unsqueeze(-1).unsqueeze(-1), logdet            # reference :57
+            return self._forward_fused(x, embedding)                # fills last_outs ([B,C] each, reference :55)
+        self._reset_last()
         from .autograd import flow_reverse
         return flow_reverse(self._engine, x, embedding).unsqueeze(-1).unsqueeze(-1)   # reference :153
 
@@ -188,19 +231,14 @@ class UnconditionalFlow2(_FusedFlowMixin, nn.Module):
         for flow in range(self.n_flows):
             self.sub_layers.append(UnconditionalFlatDoubleCouplingFlowBlock2(
                 self.in_channels, self.mid_channels, self.num_blocks, data_init))
-        self.last_outs, self.last_logdets = [], []
+        self._reset_last()
         self._make_engine(False, 0, 1.0, precision or DEFAULT_PRECISION)
 
     def forward(self, x, reverse=False):
         assert len(x.shape) == 4                                    # reference flow_blocks.py:592
-        self.last_outs, self.last_logdets = [], []
         if not reverse:
-            from .autograd import flow_forward
-            z, logdet, outs, lds = flow_forward(self._engine, x, None)
-            if outs is not None:
-                self.last_outs = [o.unsqueeze(-1).unsqueeze(-1) for o in outs.unbind(0)]   # 4-D, reference :606
-                self.last_logdets = list(lds.unbind(0))
-            return z.unsqueeze(-1).unsqueeze(-1), logdet
+            return self._forward_fused(x, None)                     # last_outs are 4-D here, reference :606
+        self._reset_last()
         from .autograd import flow_reverse
         return flow_reverse(self._engine, x, None).unsqueeze(-1).unsqueeze(-1)
 
