@@ -159,20 +159,59 @@
         float* keep_s = epi_f32;                                  // [128][BN + 1]
         float* bias_s = epi_f32 + BM * (BN + 1);
         float* bias_t = bias_s + BN;
+        float* col_scale = bias_t + BN;                           // folded boundary: per-column constants of this tile
+        float* col_loc = col_scale + BN;
+        int* col_dst = reinterpret_cast<int*>(col_loc + BN);
         const int ldk = BN + 1;
         const int col_base = n_tile * BN;
-        for (int idx = tid_e; idx < BM * BN; idx += EPI_THREADS) {
-          const int r = idx >> p.bn_log2;
-          const int c = idx & (BN - 1);
-          const int grow = m_tile * BM + r;
-          const int gcol = col_base + c;
-          float kv = 0.f;
-          if (grow < p.M && gcol < p.n_valid) kv = p.state[static_cast<size_t>(grow) * p.ld_state + p.keep_off + gcol];
-          keep_s[r * ldk + c] = kv;
+        const int bn4_log2 = p.bn_log2 - 2;                       // float4 groups per tile row
+        const int groups = BM << bn4_log2;                        // multiple of EPI_THREADS (BN >= 16)
+        // 8 independent 16-byte loads in flight per thread (a scalar loop here is latency-bound: ncu r01)
+        for (int g0 = tid_e; g0 < groups; g0 += 8 * EPI_THREADS) {
+          float4 kv[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int idx = g0 + u * EPI_THREADS;
+            kv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (idx < groups) {
+              const int r = idx >> bn4_log2;
+              const int gcol = col_base + ((idx & ((1 << bn4_log2) - 1)) << 2);
+              const int grow = m_tile * BM + r;
+              if (grow < p.M && gcol < p.n_valid) {
+                const float* src = p.state + static_cast<size_t>(grow) * p.ld_state + p.keep_off + gcol;
+                if (p.vec4) {
+                  kv[u] = *reinterpret_cast<const float4*>(src);
+                } else {
+                  kv[u].x = src[0];
+                  if (gcol + 1 < p.n_valid) kv[u].y = src[1];
+                  if (gcol + 2 < p.n_valid) kv[u].z = src[2];
+                  if (gcol + 3 < p.n_valid) kv[u].w = src[3];
+                }
+              }
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int idx = g0 + u * EPI_THREADS;
+            if (idx < groups) {
+              float* d = keep_s + (idx >> bn4_log2) * ldk + ((idx & ((1 << bn4_log2) - 1)) << 2);
+              d[0] = kv[u].x; d[1] = kv[u].y; d[2] = kv[u].z; d[3] = kv[u].w;
+            }
+          }
         }
         for (int c = tid_e; c < BN; c += EPI_THREADS) {
           bias_s[c] = __ldg(p.bias + col_base + c);
           bias_t[c] = __ldg(p.bias2 + col_base + c);
+          if (p.f_out != nullptr && col_base + c < p.n_valid) {
+            const int src = p.keep_off + col_base + c;
+            const int dst = p.f_dst != nullptr ? __ldg(p.f_dst + src) : src;
+            col_dst[c] = dst;
+            if (p.f_mode != 0) {
+              const int pi = p.f_mode == 1 ? dst : src;           // forward: next block's ActNorm; reverse: this block's
+              col_scale[c] = __ldg(p.f_scale + pi);
+              col_loc[c] = __ldg(p.f_loc + pi);
+            }
+          }
         }
         named_bar_sync(1, EPI_THREADS);
         mbar_wait(&tfull_bar[acc], acc_phase, 4);
@@ -213,40 +252,59 @@
           atomicAdd(p.logdet + row, ld_sum);       // two column halves (and possibly several n-tiles) per row
         }
         named_bar_sync(1, EPI_THREADS);
-        for (int idx = tid_e; idx < BM * BN; idx += EPI_THREADS) {
-          const int r = idx >> p.bn_log2;
-          const int c = idx & (BN - 1);
+        for (int idx = tid_e; idx < groups; idx += EPI_THREADS) {
+          const int r = idx >> bn4_log2;
+          const int c = (idx & ((1 << bn4_log2) - 1)) << 2;
           const int grow = m_tile * BM + r;
           const int gcol = col_base + c;
           if (grow < p.M && gcol < p.n_valid) {
-            const float nw = keep_s[r * ldk + c];
+            const float* ks = keep_s + r * ldk + c;
+            const float nw[4] = {ks[0], ks[1], ks[2], ks[3]};
+            const int nv = p.n_valid - gcol < 4 ? p.n_valid - gcol : 4;
             if (p.u_hi != nullptr) {
-              __nv_bfloat16 h, l;
-              split_bf16(nw, h, l);
-              p.u_hi[static_cast<size_t>(grow) * p.ld_u + gcol] = h;
-              if (kSplit == 2) p.u_lo[static_cast<size_t>(grow) * p.ld_u + gcol] = l;
+              __nv_bfloat16 h[4], l[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) split_bf16(nw[e], h[e], l[e]);
+              __nv_bfloat16* uh = p.u_hi + static_cast<size_t>(grow) * p.ld_u + gcol;
+              if (p.vec4) {
+                *reinterpret_cast<uint2*>(uh) = make_uint2(pack_bf16x2(h[0], h[1]), pack_bf16x2(h[2], h[3]));
+                if (kSplit == 2)
+                  *reinterpret_cast<uint2*>(p.u_lo + static_cast<size_t>(grow) * p.ld_u + gcol) =
+                      make_uint2(pack_bf16x2(l[0], l[1]), pack_bf16x2(l[2], l[3]));
+              } else {
+                for (int e = 0; e < nv; ++e) {
+                  uh[e] = h[e];
+                  if (kSplit == 2) p.u_lo[static_cast<size_t>(grow) * p.ld_u + gcol + e] = l[e];
+                }
+              }
             }
             if (p.f_out == nullptr) {
-              p.state[static_cast<size_t>(grow) * p.ld_state + p.keep_off + gcol] = nw;
+              float* d = p.state + static_cast<size_t>(grow) * p.ld_state + p.keep_off + gcol;
+              if (p.vec4) *reinterpret_cast<float4*>(d) = make_float4(nw[0], nw[1], nw[2], nw[3]);
+              else for (int e = 0; e < nv; ++e) d[e] = nw[e];
             } else {
-              // folded boundary: this element's place (and normalisation) in the next block's state
-              const int src = p.keep_off + gcol;
-              const int dst = p.f_dst != nullptr ? __ldg(p.f_dst + src) : src;
-              float v = nw;
-              if (p.f_mode == 1) {
-                v = __ldg(p.f_scale + dst) * (v + __ldg(p.f_loc + dst));
-                if (p.f_leaky) v = v * (v >= 0.f ? 1.0f : p.f_alpha);
-              } else if (p.f_mode == 2) {
-                if (p.f_leaky) v = v / (v >= 0.f ? 1.0f : p.f_alpha);
-                v = v / __ldg(p.f_scale + src) - __ldg(p.f_loc + src);
-              }
-              p.f_out[static_cast<size_t>(grow) * p.f_ld + dst] = v;
-              const int ucol = dst - p.f_u_begin;
-              if (p.f_u_hi != nullptr && ucol >= 0 && ucol < p.n_valid) {
-                __nv_bfloat16 h, l;
-                split_bf16(v, h, l);
-                p.f_u_hi[static_cast<size_t>(grow) * p.ld_u + ucol] = h;
-                if (kSplit == 2) p.f_u_lo[static_cast<size_t>(grow) * p.ld_u + ucol] = l;
+              // folded boundary: each element's place (and normalisation) in the next block's state
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                if (e < nv) {
+                  const int dst = col_dst[c + e];
+                  float v = nw[e];
+                  if (p.f_mode == 1) {
+                    v = col_scale[c + e] * (v + col_loc[c + e]);
+                    if (p.f_leaky) v = v * (v >= 0.f ? 1.0f : p.f_alpha);
+                  } else if (p.f_mode == 2) {
+                    if (p.f_leaky) v = v / (v >= 0.f ? 1.0f : p.f_alpha);
+                    v = v / col_scale[c + e] - col_loc[c + e];
+                  }
+                  p.f_out[static_cast<size_t>(grow) * p.f_ld + dst] = v;
+                  const int ucol = dst - p.f_u_begin;
+                  if (p.f_u_hi != nullptr && ucol >= 0 && ucol < p.n_valid) {
+                    __nv_bfloat16 h, l;
+                    split_bf16(v, h, l);
+                    p.f_u_hi[static_cast<size_t>(grow) * p.ld_u + ucol] = h;
+                    if (kSplit == 2) p.f_u_lo[static_cast<size_t>(grow) * p.ld_u + ucol] = l;
+                  }
+                }
               }
             }
           }

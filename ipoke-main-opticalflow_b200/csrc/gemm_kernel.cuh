@@ -64,6 +64,7 @@ struct GemmParams {
   int ld_state;
   int keep_off;
   int n_valid;            // true C/2
+  int vec4;               // C/2, keep_off and the row strides are multiples of 4: 16-byte state / 8-byte bf16 accesses
   float* logdet;          // [M], forward only
   int logdet_atomic;      // >1 n-tile per row -> atomicAdd
   __nv_bfloat16* u_hi;    // next half-step's MLP input (bf16 copy of the new half), nullable
@@ -104,11 +105,12 @@ __host__ __device__ constexpr int gemm_nsub(int mode) { return (mode == EPI_TAIL
 __host__ inline int gemm_stage_bytes(int ksplit, int mode, int BN) {
   return gemm_nsub(mode) * ksplit * (A_TILE_BYTES + BN * BK * 2);
 }
-// epilogue smem: [slabs (EPI_HIDDEN with TMA store)] [fp32 area: bias (2 x BN) | tail: keep tile + 2 biases]
+// epilogue smem: [slabs (EPI_HIDDEN with TMA store)] [fp32 area: bias (2 x BN) | tail: keep tile + 2 biases +
+// 3 per-column arrays of the folded boundary]
 __host__ inline int gemm_epi_bytes(int ksplit, int mode, int BN, int slab_bufs) {
   if (mode == EPI_HIDDEN || mode == EPI_DGRAD) return ksplit * slab_bufs * SLAB_BYTES + 2 * BN * 4;
   if (mode == EPI_DU) return 2 * BN * 4;
-  return (BM * (BN + 1) + 2 * BN) * 4;
+  return (BM * (BN + 1) + 5 * BN) * 4;
 }
 __host__ inline int gemm_smem_bytes(int ksplit, int mode, int BN, int stages, int slab_bufs) {
   return 1024 + stages * gemm_stage_bytes(ksplit, mode, BN) + ((gemm_epi_bytes(ksplit, mode, BN, slab_bufs) + 15) & ~15) +
@@ -142,7 +144,7 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
   constexpr bool kTailMode = (kMode == EPI_TAIL_FWD || kMode == EPI_TAIL_REV);
   const int slab_total = kSlabMode ? kSplit * p.slab_bufs * SLAB_BYTES : 0;
   float* epi_f32 = reinterpret_cast<float*>(epi_smem + slab_total);
-  const int epi_bytes = slab_total + (kTailMode ? (BM * (BN + 1) + 2 * BN) * 4 : 2 * BN * 4);
+  const int epi_bytes = slab_total + (kTailMode ? (BM * (BN + 1) + 5 * BN) * 4 : 2 * BN * 4);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(epi_smem + ((epi_bytes + 15) & ~15));
   uint64_t* empty_bar = full_bar + MAX_STAGES;
   uint64_t* tfull_bar = empty_bar + MAX_STAGES;

@@ -500,6 +500,7 @@ struct Builder {
     g.p.ld_state = P->d.C;
     g.p.keep_off = (i == 0) ? P->C2 : 0;
     g.p.n_valid = P->C2;
+    g.p.vec4 = (P->C2 % 4 == 0 && P->d.C % 4 == 0 && P->ldU % 4 == 0) ? 1 : 0;
     g.p.logdet = w<float>(wl.logdet);
     g.p.logdet_atomic = g.p.num_n_tiles > 1;
     if (write_u) {
