@@ -218,31 +218,50 @@
         tc_fence_after();
         float ld_sum = 0.f;
         float* my_keep = keep_s + r_loc * ldk;
+        const bool sv = p.s_save != nullptr && row_ok;            // training forward keeps s and the old kept half
         for (int c0 = ch * 16; c0 < BN; c0 += 32) {
           float vs[16], vt[16];
           tmem_ld16(t_row + c0, vs);
           tmem_ld16(t_row + BN + c0, vt);
           tmem_ld_wait();
+          if (sv) {
+            float* ks = p.keep_save + static_cast<size_t>(row) * p.ld_save + col_base + c0;
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const int c = c0 + j;
-            // bf16 mode: tanh / exp from ex2.approx (abs error ~2e-7, far below the bf16 GEMM error);
-            // fp32-parity mode keeps libm-accurate tanhf / expf
-            const float s = kSplit == 2 ? tanhf(vs[j] + bias_s[c]) : fast_tanh(vs[j] + bias_s[c]);
-            const float t = vt[j] + bias_t[c];
-            const float keep = my_keep[c];
-            float nw;
-            if (kMode == EPI_TAIL_FWD) {
-              nw = keep * (kSplit == 2 ? expf(s) : __expf(s)) + t;
-              if (col_base + c < p.n_valid) ld_sum += s;
-            } else {
-              nw = (keep - t) * (kSplit == 2 ? expf(-s) : __expf(-s));
+            for (int j = 0; j < 16; ++j)
+              if (col_base + c0 + j < p.n_valid) ks[j] = my_keep[c0 + j];
+          }
+          // padded columns (>= n_valid) have zero weights and biases: s = tanh(0) = 0 adds nothing to the log-det
+#pragma unroll
+          for (int j4 = 0; j4 < 4; ++j4) {
+            const float4 bs4 = *reinterpret_cast<const float4*>(bias_s + c0 + 4 * j4);
+            const float4 bt4 = *reinterpret_cast<const float4*>(bias_t + c0 + 4 * j4);
+            const float bsv[4] = {bs4.x, bs4.y, bs4.z, bs4.w};
+            const float btv[4] = {bt4.x, bt4.y, bt4.z, bt4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int j = 4 * j4 + e;
+              const int c = c0 + j;
+              // bf16 mode: MUFU tanh / ex2 (abs error <= 5e-4 / 2e-7 relative, below the bf16 GEMM error);
+              // fp32-parity mode keeps libm-accurate tanhf / expf
+              const float s = kSplit == 2 ? tanhf(vs[j] + bsv[e]) : tanh_approx(vs[j] + bsv[e]);
+              const float t = vt[j] + btv[e];
+              const float keep = my_keep[c];
+              float nw;
+              if (kMode == EPI_TAIL_FWD) {
+                nw = keep * (kSplit == 2 ? expf(s) : ex2_approx(s * 1.4426950408889634f)) + t;
+                ld_sum += s;
+              } else {
+                nw = (keep - t) * (kSplit == 2 ? expf(-s) : ex2_approx(s * -1.4426950408889634f));
+              }
+              my_keep[c] = nw;
+              vs[j] = s;
             }
-            my_keep[c] = nw;
-            if (p.s_save != nullptr && row_ok && col_base + c < p.n_valid) {
-              p.s_save[static_cast<size_t>(row) * p.ld_save + col_base + c] = s;
-              p.keep_save[static_cast<size_t>(row) * p.ld_save + col_base + c] = keep;
-            }
+          }
+          if (sv) {
+            float* ss = p.s_save + static_cast<size_t>(row) * p.ld_save + col_base + c0;
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (col_base + c0 + j < p.n_valid) ss[j] = vs[j];
           }
         }
         tc_fence_before();
@@ -252,6 +271,61 @@
           atomicAdd(p.logdet + row, ld_sum);       // two column halves (and possibly several n-tiles) per row
         }
         named_bar_sync(1, EPI_THREADS);
+        if (p.f_out != nullptr) {
+          // ---- folded boundary: lane = column (conflict-free smem reads, per-column constants live in registers),
+          //      each of the 8 warps walks every 8th row; every element goes to its place in the next block's state
+          const int we = warp - 4;
+          float cs[4], cl[4];
+          int cd[4], cu[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int c = lane + 32 * k;
+            cd[k] = -1;
+            cu[k] = -1;
+            cs[k] = 1.f;
+            cl[k] = 0.f;
+            if (c < BN && col_base + c < p.n_valid) {
+              cd[k] = col_dst[c];
+              cs[k] = p.f_mode == 2 ? 1.0f / col_scale[c] : col_scale[c];
+              cl[k] = col_loc[c];
+              const int ucol = cd[k] - p.f_u_begin;
+              if (p.f_u_hi != nullptr && ucol >= 0 && ucol < p.n_valid) cu[k] = ucol;
+            }
+          }
+          const float neg = p.f_leaky ? (p.f_mode == 2 ? 1.0f / p.f_alpha : p.f_alpha) : 1.0f;
+          const int rows_here = p.M - m_tile * BM < BM ? p.M - m_tile * BM : BM;
+          for (int r = we; r < rows_here; r += 8) {
+            const size_t grow = static_cast<size_t>(m_tile * BM + r);
+            float* orow = p.f_out + grow * p.f_ld;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              if (cd[k] >= 0) {
+                const float nw = keep_s[r * ldk + lane + 32 * k];
+                if (p.u_hi != nullptr) {                              // this block's second half-step reads the raw value
+                  __nv_bfloat16 h, l;
+                  split_bf16(nw, h, l);
+                  p.u_hi[grow * p.ld_u + col_base + lane + 32 * k] = h;
+                  if (kSplit == 2) p.u_lo[grow * p.ld_u + col_base + lane + 32 * k] = l;
+                }
+                float v = nw;
+                if (p.f_mode == 1) {
+                  v = cs[k] * (v + cl[k]);
+                  v = v * (v >= 0.f ? 1.0f : neg);
+                } else if (p.f_mode == 2) {
+                  v = v * (v >= 0.f ? 1.0f : neg);
+                  v = v * cs[k] - cl[k];
+                }
+                orow[cd[k]] = v;
+                if (cu[k] >= 0) {
+                  __nv_bfloat16 h, l;
+                  split_bf16(v, h, l);
+                  p.f_u_hi[grow * p.ld_u + cu[k]] = h;
+                  if (kSplit == 2) p.f_u_lo[grow * p.ld_u + cu[k]] = l;
+                }
+              }
+            }
+          }
+        } else
         for (int idx = tid_e; idx < groups; idx += EPI_THREADS) {
           const int r = idx >> bn4_log2;
           const int c = (idx & ((1 << bn4_log2) - 1)) << 2;
@@ -278,35 +352,9 @@
                 }
               }
             }
-            if (p.f_out == nullptr) {
-              float* d = p.state + static_cast<size_t>(grow) * p.ld_state + p.keep_off + gcol;
-              if (p.vec4) *reinterpret_cast<float4*>(d) = make_float4(nw[0], nw[1], nw[2], nw[3]);
-              else for (int e = 0; e < nv; ++e) d[e] = nw[e];
-            } else {
-              // folded boundary: each element's place (and normalisation) in the next block's state
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                if (e < nv) {
-                  const int dst = col_dst[c + e];
-                  float v = nw[e];
-                  if (p.f_mode == 1) {
-                    v = col_scale[c + e] * (v + col_loc[c + e]);
-                    if (p.f_leaky) v = v * (v >= 0.f ? 1.0f : p.f_alpha);
-                  } else if (p.f_mode == 2) {
-                    if (p.f_leaky) v = v / (v >= 0.f ? 1.0f : p.f_alpha);
-                    v = v / col_scale[c + e] - col_loc[c + e];
-                  }
-                  p.f_out[static_cast<size_t>(grow) * p.f_ld + dst] = v;
-                  const int ucol = dst - p.f_u_begin;
-                  if (p.f_u_hi != nullptr && ucol >= 0 && ucol < p.n_valid) {
-                    __nv_bfloat16 h, l;
-                    split_bf16(v, h, l);
-                    p.f_u_hi[static_cast<size_t>(grow) * p.ld_u + ucol] = h;
-                    if (kSplit == 2) p.f_u_lo[static_cast<size_t>(grow) * p.ld_u + ucol] = l;
-                  }
-                }
-              }
-            }
+            float* d = p.state + static_cast<size_t>(grow) * p.ld_state + p.keep_off + gcol;
+            if (p.vec4) *reinterpret_cast<float4*>(d) = make_float4(nw[0], nw[1], nw[2], nw[3]);
+            else for (int e = 0; e < nv; ++e) d[e] = nw[e];
           }
         }
         named_bar_sync(1, EPI_THREADS);                           // keep_s is reused by the next tile

@@ -149,6 +149,7 @@ struct ipoke_inn_plan {
   int last_launches = 0;
   // launch options: 1 = replay the program as a CUDA graph (captured on an internal stream), PDL attribute on GEMMs
   int use_graph = 1, use_pdl = 1, use_mcast = 0;
+  int tail_bn_max = 128;
   int use_fold = 1;              // inference programs: block boundaries folded into the coupling tails
   int w_prefetch = 1;
   int latency_smem_cap_kb = 0;   // > 0: cap smem of one-wave launches so two kernels can be co-resident under PDL
@@ -483,7 +484,7 @@ struct Builder {
     Op& op = prog->ops.back();
     // two accumulators (s, t) per stage: cap the tile at 128 columns so TMEM still double-buffers and the
     // (transcendental-heavy) epilogue of tile i overlaps the MMAs of tile i+1
-    TileCfg tc = pick_bn(P, g.mode, P->Np, m_tiles, 128);
+    TileCfg tc = pick_bn(P, g.mode, P->Np, m_tiles, P->tail_bn_max);
     const int bn = tc.bn;
     g.p.num_n_tiles = P->Np / bn;
     tc.mc = pick_mc(P, m_tiles * (P->Np / bn), P->Np / bn, P->Np / bn);
@@ -1337,6 +1338,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_PDL")) P->use_pdl = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_MCAST")) P->use_mcast = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_FOLD")) P->use_fold = std::atoi(e) != 0;
+  if (const char* e = std::getenv("IPOKE_INN_TAIL_BN")) P->tail_bn_max = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WPREFETCH")) P->w_prefetch = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_STAGECAP_KB")) P->latency_smem_cap_kb = std::atoi(e);
   P->ksplit = d.precision == IPOKE_INN_PREC_FP32_SPLIT ? 2 : 1;
