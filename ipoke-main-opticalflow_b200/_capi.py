@@ -15,7 +15,7 @@ SYMBOLS = [
     "ipoke_inn_packed_bytes", "ipoke_inn_workspace_bytes", "ipoke_inn_num_linears", "ipoke_inn_pack",
     "ipoke_inn_forward", "ipoke_inn_reverse", "ipoke_inn_forward_host", "ipoke_inn_reverse_host",
     "ipoke_inn_actnorm_stats", "ipoke_inn_actnorm_finalize", "ipoke_inn_flow_loss",
-    "ipoke_inn_last_launch_count", "ipoke_inn_debug_layout",
+    "ipoke_inn_last_launch_count", "ipoke_inn_debug_layout", "ipoke_inn_debug_trace",
     "ipoke_inn_profile_enable", "ipoke_inn_profile_read", "ipoke_inn_set_option",
     "ipoke_inn_saved_bytes", "ipoke_inn_forward_train", "ipoke_inn_backward", "ipoke_inn_profile_read_n",
 ]
@@ -74,6 +74,8 @@ def lib():
     L.ipoke_inn_last_launch_count.argtypes = [vp]
     L.ipoke_inn_debug_layout.restype = i32
     L.ipoke_inn_debug_layout.argtypes = [vp, i32, vp, i32]
+    L.ipoke_inn_debug_trace.restype = i32
+    L.ipoke_inn_debug_trace.argtypes = [vp, vp, i32]
     L.ipoke_inn_set_option.restype = i32
     L.ipoke_inn_set_option.argtypes = [vp, ctypes.c_char_p, i32]
     L.ipoke_inn_profile_enable.restype = i32

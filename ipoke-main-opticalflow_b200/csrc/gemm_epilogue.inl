@@ -30,6 +30,7 @@
             (kMode == EPI_DGRAD && row_ok) ? p.mask_act + static_cast<size_t>(row) * p.ld_mask + p.mask_col0 + ocol0 : nullptr;
         mbar_wait(&tfull_bar[acc], acc_phase, 4);
         tc_fence_after();
+        if (tr != nullptr && tid_e == 0) tr[5] = globaltimer_ns();
         if (p.slab_bufs > 0) {
           // ---- 64-column slabs: TMEM -> regs -> swizzled smem -> TMA store
           const int n_slabs = BN >> 6;
@@ -44,6 +45,14 @@
 #pragma unroll
             for (int c = 0; c < 2; ++c) tmem_ld16(t_row + s * 64 + ch * 32 + c * 16, v + c * 16);
             tmem_ld_wait();
+            for (int a = 1; a < kacc; ++a) {                     // K-interleaved partial accumulators
+              float w[32];
+#pragma unroll
+              for (int c = 0; c < 2; ++c) tmem_ld16(t_row + a * BN + s * 64 + ch * 32 + c * 16, w + c * 16);
+              tmem_ld_wait();
+#pragma unroll
+              for (int c = 0; c < 32; ++c) v[c] += w[c];
+            }
             if (s == n_slabs - 1) {                              // accumulator fully read: hand TMEM back
               tc_fence_before();
               mbar_arrive(&tempty_bar[acc]);
@@ -95,6 +104,13 @@
             float v[16];
             tmem_ld16(t_row + c0, v);
             tmem_ld_wait();
+            for (int a = 1; a < kacc; ++a) {
+              float w[16];
+              tmem_ld16(t_row + a * BN + c0, w);
+              tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] += w[j];
+            }
             const int col = ocol0 + c0;
             if (kMode == EPI_HIDDEN) {
 #pragma unroll
@@ -135,6 +151,7 @@
         //      half, columns [cond_col0, cond_col0 + E) into the conditioning gradient (flow_blocks.py:137, 224)
         mbar_wait(&tfull_bar[acc], acc_phase, 4);
         tc_fence_after();
+        if (tr != nullptr && tid_e == 0) tr[5] = globaltimer_ns();
         for (int c0 = ch * 16; c0 < BN; c0 += 32) {
           float v[16];
           tmem_ld16(t_row + c0, v);
@@ -216,14 +233,23 @@
         named_bar_sync(1, EPI_THREADS);
         mbar_wait(&tfull_bar[acc], acc_phase, 4);
         tc_fence_after();
+        if (tr != nullptr && tid_e == 0) tr[5] = globaltimer_ns();
         float ld_sum = 0.f;
         float* my_keep = keep_s + r_loc * ldk;
         const bool sv = p.s_save != nullptr && row_ok;            // training forward keeps s and the old kept half
         for (int c0 = ch * 16; c0 < BN; c0 += 32) {
           float vs[16], vt[16];
           tmem_ld16(t_row + c0, vs);
-          tmem_ld16(t_row + BN + c0, vt);
+          tmem_ld16(t_row + sub_cols + c0, vt);
           tmem_ld_wait();
+          for (int a = 1; a < kacc; ++a) {
+            float ws_[16], wt_[16];
+            tmem_ld16(t_row + a * BN + c0, ws_);
+            tmem_ld16(t_row + sub_cols + a * BN + c0, wt_);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 16; ++j) { vs[j] += ws_[j]; vt[j] += wt_[j]; }
+          }
           if (sv) {
             float* ks = p.keep_save + static_cast<size_t>(row) * p.ld_save + col_base + c0;
 #pragma unroll
@@ -361,3 +387,4 @@
       }
     }
     if (kSlabMode && p.slab_bufs > 0 && tid_e == 0) bulk_wait<0>();   // stores landed before exit
+    if (tr != nullptr && tid_e == 0) tr[6] = globaltimer_ns();

@@ -44,8 +44,14 @@ struct GemmParams {
   int stages;
   int tmem_cols;          // power of two >= nacc * NSUB * BN
   int nacc;               // accumulator stages in TMEM (1 or 2)
+  int kacc;               // K-interleaved accumulators per output tile (1, 2, 4): consecutive MMAs go to different TMEM
+                          // accumulators and the epilogue adds them. An MMA that accumulates into the tile the previous
+                          // one wrote waits ~90 ns for it whatever N is (measured, r01 trace), so a one-wave launch
+                          // (K/16 dependent MMAs per CTA) is bound by that chain unless it is split.
   int epi_off;            // byte offset of the epilogue smem region (1024-aligned) = stages * stage_bytes
   int w_prefetch;         // 1: fetch the first stages' W tiles before griddepcontrol.wait
+  int k_rotate;           // 1: tile (m, n) walks its k-blocks starting at n (mod K/64): CTAs that share an A row
+                          //    block then read different L2 lines at any moment (one-wave launches hot-spot otherwise)
   int mcast;              // cluster size along n (1, 2, 4, 8): A tiles are TMA-multicast to the CTAs sharing an m-tile
   int slab_bufs;          // EPI_HIDDEN: 0 = direct global stores, 1 / 2 = TMA-store slab buffers per (hi|lo)
   int tiles_per_group;    // n-tiles per subnetwork group (hidden layers); >= num_n_tiles otherwise
@@ -88,6 +94,7 @@ struct GemmParams {
   __nv_bfloat16* f_u_lo;
   int f_u_begin;
   const float* ld_extra;  // nullable: scalar added once per row (the next block's ActNorm log-det)
+  unsigned long long* trace;   // nullable debug timeline (ipoke_inn_debug_trace): 16 slots for this launch
   // backward (EPI_DGRAD / EPI_DU): dX = dY * W with W read MN-major straight from the forward layout
   int w_mn;               // 1: the W tile is {64 rows of the contraction index} x {BN columns}, MN-major for the MMA
   int w_group_rows;       // w_mn: first W row of group g = w_row0[0] + g * w_group_rows
@@ -127,13 +134,22 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
 
-  const int warp = threadIdx.x >> 5;
+  // warp index through a shuffle and one-lane roles through elect.sync: the compiler then knows the role code is
+  // warp-uniform and keeps TMA / MMA operands in uniform registers (a plain `lane == 0` branch made it wrap every
+  // UTCHMMA / UTMALDG in an ELECT + R2UR loop, ~90 ns per MMA: r01 trace)
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
   const int BN = p.BN;
+  // debug timeline: first and last CTA only
+  unsigned long long* const tr =
+      (p.trace != nullptr && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) ? p.trace + (blockIdx.x == 0 ? 0 : 8) : nullptr;
+  if (tr != nullptr && threadIdx.x == 0) tr[0] = globaltimer_ns();
   const int w_tile_bytes = BN * BK * 2;
   const int stage_bytes = NSUB * kSplit * (A_TILE_BYTES + w_tile_bytes);
   const int stages = p.stages;
-  const int acc_cols = NSUB * BN;
+  const int kacc = p.kacc;
+  const int sub_cols = kacc * BN;            // TMEM columns of one accumulator set (s or t)
+  const int acc_cols = NSUB * sub_cols;
   const int nacc = p.nacc;
   const int mc = p.mcast;
   const uint32_t cta_rank = mc > 1 ? cluster_ctarank() : 0u;
@@ -180,6 +196,7 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (tr != nullptr && threadIdx.x == 0) tr[1] = globaltimer_ns();
 
   // PDL: let the next kernel start its prologue (and prefetch its weights) now; our own reads of the previous
   // kernel's outputs happen only after grid_dep_wait() in the roles below.
@@ -194,33 +211,36 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
     const int a_rows = BM / mc;                               // rows of the A box this CTA loads (and multicasts)
     // weights do not depend on the previous kernel: arm the first stages and fetch their W tiles before the wait
     int pre = 0;
-    if (lane == 0 && p.w_prefetch && static_cast<int>(blockIdx.x) < num_tiles) {
+    if (p.w_prefetch && static_cast<int>(blockIdx.x) < num_tiles) {
       const int n_tile0 = blockIdx.x % p.num_n_tiles;
       pre = p.num_k_blocks < stages ? p.num_k_blocks : stages;
-      for (int kb = 0; kb < pre; ++kb) {
-        mbar_arrive_expect_tx(&full_bar[kb], stage_bytes);
-        uint8_t* sbase = smem + kb * stage_bytes;
+      for (int ki = 0; ki < pre; ++ki) {
+        const int kb = p.k_rotate ? (ki + n_tile0) % p.num_k_blocks : ki;
+        mbar_arrive_expect_tx_el(&full_bar[ki], stage_bytes);
+        uint8_t* sbase = smem + ki * stage_bytes;
 #pragma unroll
         for (int sub = 0; sub < NSUB; ++sub)
 #pragma unroll
           for (int sp = 0; sp < kSplit; ++sp)
-            tma_load_2d(sbase + NSUB * kSplit * A_TILE_BYTES + (sub * kSplit + sp) * w_tile_bytes,
-                        sp == 0 ? &tmW0 : &tmW1, &full_bar[kb], kb * BK, p.w_row0[sub] + n_tile0 * BN);
+            tma_load_2d_el(sbase + NSUB * kSplit * A_TILE_BYTES + (sub * kSplit + sp) * w_tile_bytes,
+                        sp == 0 ? &tmW0 : &tmW1, &full_bar[ki], kb * BK, p.w_row0[sub] + n_tile0 * BN);
       }
     }
     grid_dep_wait();
+    if (tr != nullptr && lane == 0) tr[2] = globaltimer_ns();
     bool first_tile = true;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m_tile = tile / p.num_n_tiles;
       const int n_tile = tile - m_tile * p.num_n_tiles;
       const int group = n_tile / p.tiles_per_group;
-      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-        if (lane == 0) {
+      for (int ki = 0; ki < p.num_k_blocks; ++ki) {
+        const int kb = p.k_rotate ? (ki + n_tile) % p.num_k_blocks : ki;
+        {
           uint8_t* sbase = smem + stage * stage_bytes;
-          const bool w_done = first_tile && kb < pre;
+          const bool w_done = first_tile && ki < pre;
           if (!w_done) {
             mbar_wait(&empty_bar[stage], phase ^ 1, 1);
-            mbar_arrive_expect_tx(&full_bar[stage], stage_bytes);
+            mbar_arrive_expect_tx_el(&full_bar[stage], stage_bytes);
           }
 #pragma unroll
           for (int sub = 0; sub < NSUB; ++sub) {
@@ -230,24 +250,23 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
             for (int sp = 0; sp < kSplit; ++sp) {
               const int t = sub * kSplit + sp;
               if (mc > 1)
-                tma_load_2d_mc(sbase + t * A_TILE_BYTES + cta_rank * a_rows * 128, sp == 0 ? &tmA0 : &tmA1,
+                tma_load_2d_mc_el(sbase + t * A_TILE_BYTES + cta_rank * a_rows * 128, sp == 0 ? &tmA0 : &tmA1,
                                &full_bar[stage], a_k, m_tile * BM + cta_rank * a_rows, mc_mask);
               else
-                tma_load_2d(sbase + t * A_TILE_BYTES, sp == 0 ? &tmA0 : &tmA1, &full_bar[stage], a_k, m_tile * BM);
+                tma_load_2d_el(sbase + t * A_TILE_BYTES, sp == 0 ? &tmA0 : &tmA1, &full_bar[stage], a_k, m_tile * BM);
               if (p.w_mn) {
                 // contraction index = W row: {64 rows} x {BN columns} as BN/64 MN-major chunks
                 const int w_c = (n_tile - group * p.tiles_per_group) * BN;
                 const int w_rk = p.w_row0[sub] + group * p.w_group_rows + kb * BK;
                 for (int c = 0; c < (BN >> 6); ++c)
-                  tma_load_2d(sbase + NSUB * kSplit * A_TILE_BYTES + t * w_tile_bytes + c * (64 * 128),
+                  tma_load_2d_el(sbase + NSUB * kSplit * A_TILE_BYTES + t * w_tile_bytes + c * (64 * 128),
                               sp == 0 ? &tmW0 : &tmW1, &full_bar[stage], w_c + c * 64, w_rk);
               } else if (!w_done)
-                tma_load_2d(sbase + NSUB * kSplit * A_TILE_BYTES + t * w_tile_bytes, sp == 0 ? &tmW0 : &tmW1,
+                tma_load_2d_el(sbase + NSUB * kSplit * A_TILE_BYTES + t * w_tile_bytes, sp == 0 ? &tmW0 : &tmW1,
                             &full_bar[stage], kb * BK, w_r);
             }
           }
         }
-        __syncwarp();
         if (++stage == stages) { stage = 0; phase ^= 1; }
       }
       first_tile = false;
@@ -261,19 +280,17 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int acc = (nacc == 2) ? (it & 1) : 0;
       const uint32_t acc_phase = ((nacc == 2) ? (it >> 1) : it) & 1;
-      if (lane == 0) {
-        mbar_wait(&tempty_bar[acc], acc_phase ^ 1, 2);
-        tc_fence_after();
-      }
-      __syncwarp();
+      mbar_wait(&tempty_bar[acc], acc_phase ^ 1, 2);
+      tc_fence_after();
       for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-        if (lane == 0) {
+        {
           mbar_wait(&full_bar[stage], phase, 3);
           tc_fence_after();
+          if (tr != nullptr && lane == 0 && it == 0 && kb == 0) tr[3] = globaltimer_ns();
           const uint32_t sbase = smem_u32(smem + stage * stage_bytes);
 #pragma unroll
           for (int sub = 0; sub < NSUB; ++sub) {
-            const uint32_t d_tmem = tmem_base + acc * acc_cols + sub * BN;
+            const uint32_t d_base = tmem_base + acc * acc_cols + sub * sub_cols;
             const uint32_t a0 = sbase + (sub * kSplit) * A_TILE_BYTES;
             const uint32_t w0 = sbase + NSUB * kSplit * A_TILE_BYTES + (sub * kSplit) * w_tile_bytes;
             const uint64_t da_hi = umma_desc_k_sw128(a0);
@@ -287,22 +304,24 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
             for (int kk = 0; kk < BK / UMMA_K; ++kk) {
               const uint64_t koff = static_cast<uint64_t>((kk * UMMA_K * 2) >> 4);
               const uint64_t woff = wstep * kk;
-              const uint32_t first = (kb == 0 && kk == 0) ? 0u : 1u;
+              // round-robin over the kacc accumulators; the first MMA into each one overwrites
+              const int mi = (kb * (BK / UMMA_K) + kk) * (kSplit == 2 ? 3 : 1);
               if (kSplit == 2) {
-                // small terms first, then the dominant hi*hi product
-                umma_bf16_ss(d_tmem, da_lo + koff, dw_hi + woff, idesc, first);
-                umma_bf16_ss(d_tmem, da_hi + koff, dw_lo + woff, idesc, 1u);
-                umma_bf16_ss(d_tmem, da_hi + koff, dw_hi + woff, idesc, 1u);
+                umma_bf16_ss_el(d_base + ((mi) & (kacc - 1)) * BN, da_lo + koff, dw_hi + woff, idesc, mi >= kacc ? 1u : 0u);
+                umma_bf16_ss_el(d_base + ((mi + 1) & (kacc - 1)) * BN, da_hi + koff, dw_lo + woff, idesc, mi + 1 >= kacc ? 1u : 0u);
+                umma_bf16_ss_el(d_base + ((mi + 2) & (kacc - 1)) * BN, da_hi + koff, dw_hi + woff, idesc, mi + 2 >= kacc ? 1u : 0u);
               } else {
-                umma_bf16_ss(d_tmem, da_hi + koff, dw_hi + woff, idesc, first);
+                umma_bf16_ss_el(d_base + (mi & (kacc - 1)) * BN, da_hi + koff, dw_hi + woff, idesc, mi >= kacc ? 1u : 0u);
               }
             }
           }
-          if (mc > 1) umma_commit_mc(&empty_bar[stage], mc_mask);   // slot is shared: release it in every peer
-          else umma_commit(&empty_bar[stage]);                 // frees the smem slot when the MMAs retire
-          if (kb == p.num_k_blocks - 1) umma_commit(&tfull_bar[acc]);   // accumulators ready
+          if (mc > 1) umma_commit_mc_el(&empty_bar[stage], mc_mask);   // slot is shared: release it in every peer
+          else umma_commit_el(&empty_bar[stage]);                 // frees the smem slot when the MMAs retire
+          if (kb == p.num_k_blocks - 1) {
+            umma_commit_el(&tfull_bar[acc]);   // accumulators ready
+            if (tr != nullptr && lane == 0) tr[4] = globaltimer_ns();
+          }
         }
-        __syncwarp();
         if (++stage == stages) { stage = 0; phase ^= 1; }
       }
     }
@@ -314,6 +333,7 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
   tc_fence_before();
   if (mc > 1) cluster_sync_all();            // no CTA exits while peers may still multicast into it
   else __syncthreads();
+  if (tr != nullptr && threadIdx.x == 0) tr[7] = globaltimer_ns();
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);

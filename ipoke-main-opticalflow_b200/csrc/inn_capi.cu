@@ -150,6 +150,11 @@ struct ipoke_inn_plan {
   // launch options: 1 = replay the program as a CUDA graph (captured on an internal stream), PDL attribute on GEMMs
   int use_graph = 1, use_pdl = 1, use_mcast = 0;
   int tail_bn_max = 128;
+  int k_rotate = 0;
+  int kacc_max = 1;               // K-interleaved accumulators: measured no gain once the MMA issue is uniform
+  int hidden_bn_force = 0;       // debug: fixed tile width of the hidden-layer GEMMs
+  unsigned long long* trace_buf = nullptr;   // ipoke_inn_debug_trace
+  int trace_slots = 0;
   int use_fold = 1;              // inference programs: block boundaries folded into the coupling tails
   int w_prefetch = 1;
   int latency_smem_cap_kb = 0;   // > 0: cap smem of one-wave launches so two kernels can be co-resident under PDL
@@ -325,7 +330,7 @@ int pick_mc(const ipoke_inn_plan* P, int tiles, int n_tiles, int tiles_per_group
   if (!P->use_mcast || tiles > P->num_sms) return 1;
   static const int cand[3] = {8, 4, 2};
   for (int i = 0; i < 3; ++i)
-    if (n_tiles % cand[i] == 0 && tiles_per_group % cand[i] == 0) return cand[i];
+    if (cand[i] <= P->use_mcast && n_tiles % cand[i] == 0 && tiles_per_group % cand[i] == 0) return cand[i];
   return 1;
 }
 
@@ -405,6 +410,8 @@ struct Builder {
     GemmOp& g = prog->gemms.back();
     std::memset(&g, 0, sizeof(GemmOp));
     g.mode = mode;
+    if (P->trace_buf != nullptr && (int)prog->gemms.size() <= P->trace_slots)
+      g.p.trace = P->trace_buf + 16ull * (prog->gemms.size() - 1);
     prog->launches++;
     return g;
   }
@@ -418,6 +425,7 @@ struct Builder {
     g.p.slab_bufs = t.slab_bufs;
     g.p.mcast = t.mc;
     g.p.w_prefetch = P->w_prefetch;
+    g.p.k_rotate = (P->k_rotate && g.p.num_m_tiles * g.p.num_n_tiles <= 2 * P->num_sms && !g.p.w_mn) ? 1 : 0;
     const int tiles = g.p.num_m_tiles * g.p.num_n_tiles;
     if (tiles <= P->num_sms && P->latency_smem_cap_kb > 0) {
       // optional: keep the footprint small so the next kernel's CTA (PDL) can be co-resident
@@ -425,7 +433,14 @@ struct Builder {
              gemm_smem_bytes(P->ksplit, g.mode, t.bn, g.p.stages, t.slab_bufs) > P->latency_smem_cap_kb * 1024)
         g.p.stages--;
     }
-    const int acc_cols = gemm_nsub(g.mode) * t.bn;
+    // one-wave launches: split the dependent MMA chain over up to 4 K-interleaved accumulators
+    int kacc = 1;
+    if (tiles <= P->num_sms && (g.mode == EPI_HIDDEN || g.mode == EPI_TAIL_FWD || g.mode == EPI_TAIL_REV)) {
+      kacc = P->kacc_max;
+      while (kacc > 1 && gemm_nsub(g.mode) * kacc * t.bn > 512) kacc >>= 1;
+    }
+    g.p.kacc = kacc;
+    const int acc_cols = gemm_nsub(g.mode) * kacc * t.bn;
     g.p.nacc = (2 * acc_cols <= 512) ? 2 : 1;
     int cols = 32;
     while (cols < g.p.nacc * acc_cols) cols <<= 1;
@@ -445,6 +460,7 @@ struct Builder {
   int chain(const Chain& c, int k, int ci, int ui) {
     const int rows = c.G * P->Hp;
     TileCfg tc = pick_bn(P, EPI_HIDDEN, P->Hp, m_tiles * c.G);
+    if (P->hidden_bn_force > 0 && P->Hp % P->hidden_bn_force == 0) tc = tile_cfg(P->ksplit, EPI_HIDDEN, P->hidden_bn_force);
     const int bn = tc.bn;
     tc.mc = pick_mc(P, m_tiles * (rows / bn), rows / bn, P->Hp / bn);
     const int a_box = BM / tc.mc;
@@ -1336,9 +1352,12 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   P->device = device;
   if (const char* e = std::getenv("IPOKE_INN_GRAPH")) P->use_graph = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_PDL")) P->use_pdl = std::atoi(e) != 0;
-  if (const char* e = std::getenv("IPOKE_INN_MCAST")) P->use_mcast = std::atoi(e) != 0;
+  if (const char* e = std::getenv("IPOKE_INN_MCAST")) P->use_mcast = std::atoi(e) == 1 ? 8 : std::atoi(e);   // max cluster size (1 = 8)
   if (const char* e = std::getenv("IPOKE_INN_FOLD")) P->use_fold = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_TAIL_BN")) P->tail_bn_max = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_HIDDEN_BN")) P->hidden_bn_force = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_KROT")) P->k_rotate = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_KACC")) P->kacc_max = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WPREFETCH")) P->w_prefetch = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_STAGECAP_KB")) P->latency_smem_cap_kb = std::atoi(e);
   P->ksplit = d.precision == IPOKE_INN_PREC_FP32_SPLIT ? 2 : 1;
@@ -1633,7 +1652,7 @@ int ipoke_inn_set_option(ipoke_inn_plan* P, const char* name, int value) {
   std::lock_guard<std::mutex> lock(P->mu);
   if (std::strcmp(name, "graph") == 0) P->use_graph = value != 0;
   else if (std::strcmp(name, "pdl") == 0) { P->use_pdl = value != 0; P->programs.clear(); }
-  else if (std::strcmp(name, "mcast") == 0) { P->use_mcast = value != 0; P->programs.clear(); }
+  else if (std::strcmp(name, "mcast") == 0) { P->use_mcast = value == 1 ? 8 : value; P->programs.clear(); }
   else if (std::strcmp(name, "fold") == 0) { P->use_fold = value != 0; P->programs.clear(); }
   else return IPOKE_INN_E_INVALID;
   return 0;
@@ -1681,6 +1700,15 @@ int ipoke_inn_profile_read_n(ipoke_inn_plan* P, double* ms, int* launches, int n
     const int k = P->prof_kind[i];
     if (k < n) { ms[k] += t; launches[k] += 1; }
   }
+  return 0;
+}
+
+int ipoke_inn_debug_trace(ipoke_inn_plan* P, void* dev_buf, int n_slots) {
+  if (!P) return IPOKE_INN_E_INVALID;
+  std::lock_guard<std::mutex> lock(P->mu);
+  P->trace_buf = static_cast<unsigned long long*>(dev_buf);
+  P->trace_slots = dev_buf ? n_slots : 0;
+  P->programs.clear();
   return 0;
 }
 
