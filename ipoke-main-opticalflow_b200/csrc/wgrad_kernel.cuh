@@ -64,7 +64,7 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
                  const WgradParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform role index (see gemm_kernel.cuh)
   const int lane = threadIdx.x & 31;
   const int BN = p.BN;
   const int n_chunks = BN >> 6;
@@ -133,21 +133,20 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
       const int y_col = p.dy_col0 + g * p.dy_group_stride + m_tile * BM;
       const int x_col = p.x_col0 + g * p.x_group_stride + n_tile * BN;
       for (int kb = kb0; kb < kb1; ++kb) {
-        if (lane == 0) {
+        {
           mbar_wait(&empty_bar[stage], phase ^ 1, 11);
-          mbar_arrive_expect_tx(&full_bar[stage], stage_bytes);
+          mbar_arrive_expect_tx_el(&full_bar[stage], stage_bytes);
           uint8_t* sbase = smem + stage * stage_bytes;
 #pragma unroll
           for (int sp = 0; sp < kSplit; ++sp) {
             uint8_t* a = sbase + sp * 2 * WG_CHUNK_BYTES;
-            tma_load_2d(a, sp == 0 ? &tmY0 : &tmY1, &full_bar[stage], y_col, kb * 64);
-            tma_load_2d(a + WG_CHUNK_BYTES, sp == 0 ? &tmY0 : &tmY1, &full_bar[stage], y_col + 64, kb * 64);
+            tma_load_2d_el(a, sp == 0 ? &tmY0 : &tmY1, &full_bar[stage], y_col, kb * 64);
+            tma_load_2d_el(a + WG_CHUNK_BYTES, sp == 0 ? &tmY0 : &tmY1, &full_bar[stage], y_col + 64, kb * 64);
             uint8_t* b = sbase + kSplit * 2 * WG_CHUNK_BYTES + sp * n_chunks * WG_CHUNK_BYTES;
             for (int c = 0; c < n_chunks; ++c)
-              tma_load_2d(b + c * WG_CHUNK_BYTES, sp == 0 ? &tmX0 : &tmX1, &full_bar[stage], x_col + c * 64, kb * 64);
+              tma_load_2d_el(b + c * WG_CHUNK_BYTES, sp == 0 ? &tmX0 : &tmX1, &full_bar[stage], x_col + c * 64, kb * 64);
           }
         }
-        __syncwarp();
         if (++stage == stages) { stage = 0; phase ^= 1; }
       }
     }
@@ -168,14 +167,11 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
       const int kb1 = min(p.num_kb, kb0 + kb_per_slice);
       const int acc = (nacc == 2) ? (it & 1) : 0;
       const uint32_t acc_phase = ((nacc == 2) ? (it >> 1) : it) & 1;
-      if (lane == 0) {
-        mbar_wait(&tempty_bar[acc], acc_phase ^ 1, 12);
-        tc_fence_after();
-      }
-      __syncwarp();
+      mbar_wait(&tempty_bar[acc], acc_phase ^ 1, 12);
+      tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * acc_cols;
       for (int kb = kb0; kb < kb1; ++kb) {
-        if (lane == 0) {
+        {
           mbar_wait(&full_bar[stage], phase, 13);
           tc_fence_after();
           const uint32_t sbase = smem_u32(smem + stage * stage_bytes);
@@ -192,22 +188,21 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
             const uint64_t koff = static_cast<uint64_t>((kk * UMMA_K * 128) >> 4);   // 16 batch rows x 128 B
             const uint32_t first = (kb == kb0 && kk == 0) ? 0u : 1u;
             if (kSplit == 2) {
-              umma_bf16_ss(d_tmem, da_lo + koff, db_hi + koff, idesc, first);
-              umma_bf16_ss(d_tmem, da_hi + koff, db_lo + koff, idesc, 1u);
-              umma_bf16_ss(d_tmem, da_hi + koff, db_hi + koff, idesc, 1u);
+              umma_bf16_ss_el(d_tmem, da_lo + koff, db_hi + koff, idesc, first);
+              umma_bf16_ss_el(d_tmem, da_hi + koff, db_lo + koff, idesc, 1u);
+              umma_bf16_ss_el(d_tmem, da_hi + koff, db_hi + koff, idesc, 1u);
               if (want_bias) {
-                umma_bf16_ss(d_tmem + BN, da_lo + koff, d_ones, idesc_b, first);
-                umma_bf16_ss(d_tmem + BN, da_hi + koff, d_ones, idesc_b, 1u);
+                umma_bf16_ss_el(d_tmem + BN, da_lo + koff, d_ones, idesc_b, first);
+                umma_bf16_ss_el(d_tmem + BN, da_hi + koff, d_ones, idesc_b, 1u);
               }
             } else {
-              umma_bf16_ss(d_tmem, da_hi + koff, db_hi + koff, idesc, first);
-              if (want_bias) umma_bf16_ss(d_tmem + BN, da_hi + koff, d_ones, idesc_b, first);
+              umma_bf16_ss_el(d_tmem, da_hi + koff, db_hi + koff, idesc, first);
+              if (want_bias) umma_bf16_ss_el(d_tmem + BN, da_hi + koff, d_ones, idesc_b, first);
             }
           }
-          umma_commit(&empty_bar[stage]);
-          if (kb == kb1 - 1) umma_commit(&tfull_bar[acc]);
+          umma_commit_el(&empty_bar[stage]);
+          if (kb == kb1 - 1) umma_commit_el(&tfull_bar[acc]);
         }
-        __syncwarp();
         if (++stage == stages) { stage = 0; phase ^= 1; }
       }
     }
