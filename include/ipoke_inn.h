@@ -169,10 +169,10 @@ int ipoke_inn_profile_read_n(ipoke_inn_plan* plan, double* ms, int* launches, in
  * Hp, C2p, Ep, Np, ksplit, Gmax, packed_bytes, num_sms}.                                              */
 int ipoke_inn_debug_layout(const ipoke_inn_plan* plan, int B, long long* out, int n);
 
-/* Debug: per-launch device timeline. `dev_buf` (device memory, n_slots * 16 * 8 bytes, zeroed by the caller) gets,
- * for GEMM launch i of every program built afterwards, 8 %globaltimer stamps (ns) of its first CTA at
- * [16*i .. 16*i+7] and of its last CTA at [16*i+8 ..]: kernel entry, prologue done, producer past the grid
- * dependency, first operands landed, last MMA issued, accumulator ready (epilogue), epilogue stores issued, exit.
+/* Debug: per-launch device timeline. `dev_buf` (device memory, n_slots * 32 * 8 bytes, zeroed by the caller) gets,
+ * for GEMM launch i of every program built afterwards, up to 16 %globaltimer stamps (ns) of its first CTA at
+ * [32*i .. 32*i+15] and of its last CTA at [32*i+16 ..]: kernel entry, prologue done, producer past the grid
+ * dependency, first operands landed, last MMA issued, accumulator ready (epilogue), epilogue stores issued, exit; 8.. = tail-epilogue phases.
  * dev_buf = NULL switches tracing off.  Not for production use (extra global stores in every role).      */
 int ipoke_inn_debug_trace(ipoke_inn_plan* plan, void* dev_buf, int n_slots);
 

@@ -183,6 +183,176 @@
         const int col_base = n_tile * BN;
         const int bn4_log2 = p.bn_log2 - 2;                       // float4 groups per tile row
         const int groups = BM << bn4_log2;                        // multiple of EPI_THREADS (BN >= 16)
+        if (p.direct) {
+          // ---- one-wave launches (small batches): no smem transposition, no second pass. Each thread owns a row and
+          //      its 16-column groups: kept values straight from global into registers (whole 64-byte runs, the first
+          //      group prefetched before the accumulator wait), math, then stores / folded scatter from registers.
+          for (int c = tid_e; c < BN; c += EPI_THREADS) {
+            bias_s[c] = __ldg(p.bias + col_base + c);
+            bias_t[c] = __ldg(p.bias2 + col_base + c);
+            if (p.f_out != nullptr && col_base + c < p.n_valid) {
+              const int src = p.keep_off + col_base + c;
+              const int dst = p.f_dst != nullptr ? __ldg(p.f_dst + src) : src;
+              col_dst[c] = dst;
+              col_scale[c] = 1.f;
+              col_loc[c] = 0.f;
+              if (p.f_mode != 0) {
+                const int pi = p.f_mode == 1 ? dst : src;
+                const float sc = __ldg(p.f_scale + pi);
+                col_scale[c] = p.f_mode == 2 ? 1.0f / sc : sc;
+                col_loc[c] = __ldg(p.f_loc + pi);
+              }
+            }
+          }
+          float* krow = p.state + static_cast<size_t>(row_ok ? row : 0) * p.ld_state + p.keep_off + col_base;
+          float kp[16];
+          auto load_keep = [&](int c0) {
+#pragma unroll
+            for (int j4 = 0; j4 < 4; ++j4) {
+              const int c = c0 + 4 * j4;
+              float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (row_ok && col_base + c < p.n_valid) {
+                if (p.vec4) {
+                  v = *reinterpret_cast<const float4*>(krow + c);
+                } else {
+                  v.x = krow[c];
+                  if (col_base + c + 1 < p.n_valid) v.y = krow[c + 1];
+                  if (col_base + c + 2 < p.n_valid) v.z = krow[c + 2];
+                  if (col_base + c + 3 < p.n_valid) v.w = krow[c + 3];
+                }
+              }
+              kp[4 * j4] = v.x; kp[4 * j4 + 1] = v.y; kp[4 * j4 + 2] = v.z; kp[4 * j4 + 3] = v.w;
+            }
+          };
+          if (ch * 16 < BN) load_keep(ch * 16);
+          named_bar_sync(1, EPI_THREADS);                           // biases / column constants are in smem
+          mbar_wait(&tfull_bar[acc], acc_phase, 4);
+          tc_fence_after();
+          if (tr != nullptr && tid_e == 0) tr[5] = globaltimer_ns();
+          float ld_sum = 0.f;
+          const float neg = p.f_leaky ? (p.f_mode == 2 ? 1.0f / p.f_alpha : p.f_alpha) : 1.0f;
+          const bool sv = p.s_save != nullptr && row_ok;
+          for (int c0 = ch * 16; c0 < BN; c0 += 32) {
+            float vs[16], vt[16];
+            tmem_ld16(t_row + c0, vs);
+            tmem_ld16(t_row + sub_cols + c0, vt);
+            tmem_ld_wait();
+            for (int a = 1; a < kacc; ++a) {
+              float ws_[16], wt_[16];
+              tmem_ld16(t_row + a * BN + c0, ws_);
+              tmem_ld16(t_row + sub_cols + a * BN + c0, wt_);
+              tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 16; ++j) { vs[j] += ws_[j]; vt[j] += wt_[j]; }
+            }
+            if (c0 + 32 >= BN) {                                    // last group: hand the accumulator back early
+              tc_fence_before();
+              mbar_arrive(&tempty_bar[acc]);
+            }
+            const int gcol = col_base + c0;
+            const int nv = p.n_valid - gcol < 16 ? p.n_valid - gcol : 16;   // <= 0 for padded groups
+            if (sv) {
+              float* ks = p.keep_save + static_cast<size_t>(row) * p.ld_save + gcol;
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (j < nv) ks[j] = kp[j];
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float s = kSplit == 2 ? tanhf(vs[j] + bias_s[c0 + j]) : tanh_approx(vs[j] + bias_s[c0 + j]);
+              const float t = vt[j] + bias_t[c0 + j];
+              if (kMode == EPI_TAIL_FWD) {
+                kp[j] = kp[j] * (kSplit == 2 ? expf(s) : ex2_approx(s * 1.4426950408889634f)) + t;
+                ld_sum += s;                                        // padded columns: zero weights and biases -> s = 0
+              } else {
+                kp[j] = (kp[j] - t) * (kSplit == 2 ? expf(-s) : ex2_approx(s * -1.4426950408889634f));
+              }
+              vs[j] = s;
+            }
+            if (row_ok && nv > 0) {
+              if (sv) {
+                float* ss = p.s_save + static_cast<size_t>(row) * p.ld_save + gcol;
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                  if (j < nv) ss[j] = vs[j];
+              }
+              if (p.u_hi != nullptr) {                              // bf16 copy for this block's second half-step
+                __nv_bfloat16* uh = p.u_hi + static_cast<size_t>(row) * p.ld_u + gcol;
+                __nv_bfloat16* ul = kSplit == 2 ? p.u_lo + static_cast<size_t>(row) * p.ld_u + gcol : nullptr;
+#pragma unroll
+                for (int j4 = 0; j4 < 4; ++j4) {
+                  __nv_bfloat16 h[4], l[4];
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) split_bf16(kp[4 * j4 + e], h[e], l[e]);
+                  if (p.vec4) {
+                    if (4 * j4 < nv) {
+                      *reinterpret_cast<uint2*>(uh + 4 * j4) = make_uint2(pack_bf16x2(h[0], h[1]), pack_bf16x2(h[2], h[3]));
+                      if (kSplit == 2)
+                        *reinterpret_cast<uint2*>(ul + 4 * j4) = make_uint2(pack_bf16x2(l[0], l[1]), pack_bf16x2(l[2], l[3]));
+                    }
+                  } else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                      if (4 * j4 + e < nv) {
+                        uh[4 * j4 + e] = h[e];
+                        if (kSplit == 2) ul[4 * j4 + e] = l[e];
+                      }
+                  }
+                }
+              }
+              if (p.f_out == nullptr) {
+#pragma unroll
+                for (int j4 = 0; j4 < 4; ++j4) {
+                  if (p.vec4) {
+                    if (4 * j4 < nv)
+                      *reinterpret_cast<float4*>(krow + c0 + 4 * j4) =
+                          make_float4(kp[4 * j4], kp[4 * j4 + 1], kp[4 * j4 + 2], kp[4 * j4 + 3]);
+                  } else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                      if (4 * j4 + e < nv) krow[c0 + 4 * j4 + e] = kp[4 * j4 + e];
+                  }
+                }
+              } else {
+                float* orow = p.f_out + static_cast<size_t>(row) * p.f_ld;
+                const size_t uoff = static_cast<size_t>(row) * p.ld_u;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                  if (j < nv) {
+                    const int dst = col_dst[c0 + j];
+                    float v = kp[j];
+                    if (p.f_mode == 1) {
+                      v = col_scale[c0 + j] * (v + col_loc[c0 + j]);
+                      v = v * (v >= 0.f ? 1.0f : neg);
+                    } else if (p.f_mode == 2) {
+                      v = v * (v >= 0.f ? 1.0f : neg);
+                      v = v * col_scale[c0 + j] - col_loc[c0 + j];
+                    }
+                    orow[dst] = v;
+                    const int ucol = dst - p.f_u_begin;
+                    if (p.f_u_hi != nullptr && ucol >= 0 && ucol < p.n_valid) {
+                      __nv_bfloat16 h, l;
+                      split_bf16(v, h, l);
+                      p.f_u_hi[uoff + ucol] = h;
+                      if (kSplit == 2) p.f_u_lo[uoff + ucol] = l;
+                    }
+                  }
+                }
+              }
+            }
+            if (c0 + 32 < BN) load_keep(c0 + 32);
+          }
+          if (ch * 16 >= BN) {                                      // warps without a column group still release TMEM
+            tc_fence_before();
+            mbar_arrive(&tempty_bar[acc]);
+          }
+          if (kMode == EPI_TAIL_FWD && row_ok) {
+            if (p.ld_extra != nullptr && n_tile == 0 && ch == 0) ld_sum += __ldg(p.ld_extra);
+            atomicAdd(p.logdet + row, ld_sum);
+          }
+          named_bar_sync(1, EPI_THREADS);                           // smem constants are rewritten by the next tile
+          continue;
+        }
         // 8 independent 16-byte loads in flight per thread (a scalar loop here is latency-bound: ncu r01)
         for (int g0 = tid_e; g0 < groups; g0 += 8 * EPI_THREADS) {
           float4 kv[8];
@@ -230,7 +400,9 @@
             }
           }
         }
+        if (tr != nullptr && tid_e == 0) tr[8] = globaltimer_ns();      // keep tile staged (this thread)
         named_bar_sync(1, EPI_THREADS);
+        if (tr != nullptr && tid_e == 0) tr[9] = globaltimer_ns();
         mbar_wait(&tfull_bar[acc], acc_phase, 4);
         tc_fence_after();
         if (tr != nullptr && tid_e == 0) tr[5] = globaltimer_ns();
@@ -292,25 +464,32 @@
         }
         tc_fence_before();
         mbar_arrive(&tempty_bar[acc]);
+        if (tr != nullptr && tid_e == 0) tr[10] = globaltimer_ns();     // per-row math done
         if (kMode == EPI_TAIL_FWD && row_ok) {
           if (p.ld_extra != nullptr && n_tile == 0 && ch == 0) ld_sum += __ldg(p.ld_extra);
           atomicAdd(p.logdet + row, ld_sum);       // two column halves (and possibly several n-tiles) per row
         }
         named_bar_sync(1, EPI_THREADS);
+        if (tr != nullptr && tid_e == 0) tr[11] = globaltimer_ns();
         if (p.f_out != nullptr) {
-          // ---- folded boundary: lane = column (conflict-free smem reads, per-column constants live in registers),
-          //      each of the 8 warps walks every 8th row; every element goes to its place in the next block's state
+          // ---- folded boundary: lane = column (conflict-free smem reads, per-column constants live in registers;
+          //      BN = 16 packs two rows into one warp pass), the 8 warps walk the rows; every element goes to its
+          //      place in the next block's state
           const int we = warp - 4;
+          const int lpr = BN < 32 ? BN : 32;                        // lanes per row
+          const int rpp = 32 / lpr;                                 // rows per warp pass
+          const int cl0 = lane & (lpr - 1);
+          const int kmax = (BN + 31) >> 5;
           float cs[4], cl[4];
           int cd[4], cu[4];
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            const int c = lane + 32 * k;
+            const int c = cl0 + 32 * k;
             cd[k] = -1;
             cu[k] = -1;
             cs[k] = 1.f;
             cl[k] = 0.f;
-            if (c < BN && col_base + c < p.n_valid) {
+            if (k < kmax && col_base + c < p.n_valid) {
               cd[k] = col_dst[c];
               cs[k] = p.f_mode == 2 ? 1.0f / col_scale[c] : col_scale[c];
               cl[k] = col_loc[c];
@@ -320,33 +499,52 @@
           }
           const float neg = p.f_leaky ? (p.f_mode == 2 ? 1.0f / p.f_alpha : p.f_alpha) : 1.0f;
           const int rows_here = p.M - m_tile * BM < BM ? p.M - m_tile * BM : BM;
-          for (int r = we; r < rows_here; r += 8) {
-            const size_t grow = static_cast<size_t>(m_tile * BM + r);
-            float* orow = p.f_out + grow * p.f_ld;
+          const bool has_u = p.u_hi != nullptr;
+          if (tr != nullptr && tid_e == 0) tr[13] = globaltimer_ns();   // column constants in registers
+          // 4 rows per pass: all smem reads first (they cannot be hoisted over the global stores by the compiler),
+          // then 4 independent chains of math + stores
+          for (int r0 = we * rpp + (lane / lpr); r0 < rows_here; r0 += 32 * rpp) {
+            float nwv[4][4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              if (cd[k] >= 0) {
-                const float nw = keep_s[r * ldk + lane + 32 * k];
-                if (p.u_hi != nullptr) {                              // this block's second half-step reads the raw value
-                  __nv_bfloat16 h, l;
-                  split_bf16(nw, h, l);
-                  p.u_hi[grow * p.ld_u + col_base + lane + 32 * k] = h;
-                  if (kSplit == 2) p.u_lo[grow * p.ld_u + col_base + lane + 32 * k] = l;
-                }
-                float v = nw;
-                if (p.f_mode == 1) {
-                  v = cs[k] * (v + cl[k]);
-                  v = v * (v >= 0.f ? 1.0f : neg);
-                } else if (p.f_mode == 2) {
-                  v = v * (v >= 0.f ? 1.0f : neg);
-                  v = v * cs[k] - cl[k];
-                }
-                orow[cd[k]] = v;
-                if (cu[k] >= 0) {
-                  __nv_bfloat16 h, l;
-                  split_bf16(v, h, l);
-                  p.f_u_hi[grow * p.ld_u + cu[k]] = h;
-                  if (kSplit == 2) p.f_u_lo[grow * p.ld_u + cu[k]] = l;
+            for (int u = 0; u < 4; ++u) {
+              const int r = r0 + u * 8 * rpp;
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                nwv[u][k] = (k < kmax && cd[k] >= 0 && r < rows_here) ? keep_s[r * ldk + cl0 + 32 * k] : 0.f;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int r = r0 + u * 8 * rpp;
+              if (r < rows_here) {
+                const size_t grow = static_cast<size_t>(m_tile * BM + r);
+                float* orow = p.f_out + grow * p.f_ld;
+                const size_t uoff = grow * p.ld_u;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  if (k < kmax && cd[k] >= 0) {
+                    const float nw = nwv[u][k];
+                    if (has_u) {                                      // this block's second half-step reads the raw value
+                      __nv_bfloat16 h, l;
+                      split_bf16(nw, h, l);
+                      p.u_hi[uoff + col_base + cl0 + 32 * k] = h;
+                      if (kSplit == 2) p.u_lo[uoff + col_base + cl0 + 32 * k] = l;
+                    }
+                    float v = nw;
+                    if (p.f_mode == 1) {
+                      v = cs[k] * (v + cl[k]);
+                      v = v * (v >= 0.f ? 1.0f : neg);
+                    } else if (p.f_mode == 2) {
+                      v = v * (v >= 0.f ? 1.0f : neg);
+                      v = v * cs[k] - cl[k];
+                    }
+                    orow[cd[k]] = v;
+                    if (cu[k] >= 0) {
+                      __nv_bfloat16 h, l;
+                      split_bf16(v, h, l);
+                      p.f_u_hi[uoff + cu[k]] = h;
+                      if (kSplit == 2) p.f_u_lo[uoff + cu[k]] = l;
+                    }
+                  }
                 }
               }
             }
@@ -383,6 +581,7 @@
             else for (int e = 0; e < nv; ++e) d[e] = nw[e];
           }
         }
+        if (tr != nullptr && tid_e == 0) tr[12] = globaltimer_ns();     // write-back issued (this thread)
         named_bar_sync(1, EPI_THREADS);                           // keep_s is reused by the next tile
       }
     }

@@ -94,6 +94,8 @@ struct GemmParams {
   __nv_bfloat16* f_u_lo;
   int f_u_begin;
   const float* ld_extra;  // nullable: scalar added once per row (the next block's ActNorm log-det)
+  int direct;                  // tail epilogue without the smem transposition (one-wave launches)
+  int dbg;                     // debug bit mask (IPOKE_INN_DBG), 0 in production
   unsigned long long* trace;   // nullable debug timeline (ipoke_inn_debug_trace): 16 slots for this launch
   // backward (EPI_DGRAD / EPI_DU): dX = dY * W with W read MN-major straight from the forward layout
   int w_mn;               // 1: the W tile is {64 rows of the contraction index} x {BN columns}, MN-major for the MMA
@@ -142,7 +144,7 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
   const int BN = p.BN;
   // debug timeline: first and last CTA only
   unsigned long long* const tr =
-      (p.trace != nullptr && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) ? p.trace + (blockIdx.x == 0 ? 0 : 8) : nullptr;
+      (p.trace != nullptr && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) ? p.trace + (blockIdx.x == 0 ? 0 : 16) : nullptr;
   if (tr != nullptr && threadIdx.x == 0) tr[0] = globaltimer_ns();
   const int w_tile_bytes = BN * BK * 2;
   const int stage_bytes = NSUB * kSplit * (A_TILE_BYTES + w_tile_bytes);

@@ -151,6 +151,8 @@ struct ipoke_inn_plan {
   int use_graph = 1, use_pdl = 1, use_mcast = 0;
   int tail_bn_max = 128;
   int k_rotate = 0;
+  int tail_direct = 1;
+  int dbg = 0;
   int kacc_max = 1;               // K-interleaved accumulators: measured no gain once the MMA issue is uniform
   int hidden_bn_force = 0;       // debug: fixed tile width of the hidden-layer GEMMs
   unsigned long long* trace_buf = nullptr;   // ipoke_inn_debug_trace
@@ -410,8 +412,9 @@ struct Builder {
     GemmOp& g = prog->gemms.back();
     std::memset(&g, 0, sizeof(GemmOp));
     g.mode = mode;
+    g.p.dbg = P->dbg;
     if (P->trace_buf != nullptr && (int)prog->gemms.size() <= P->trace_slots)
-      g.p.trace = P->trace_buf + 16ull * (prog->gemms.size() - 1);
+      g.p.trace = P->trace_buf + 32ull * (prog->gemms.size() - 1);
     prog->launches++;
     return g;
   }
@@ -440,6 +443,7 @@ struct Builder {
       while (kacc > 1 && gemm_nsub(g.mode) * kacc * t.bn > 512) kacc >>= 1;
     }
     g.p.kacc = kacc;
+    g.p.direct = (P->tail_direct && tiles <= P->num_sms) ? 1 : 0;
     const int acc_cols = gemm_nsub(g.mode) * kacc * t.bn;
     g.p.nacc = (2 * acc_cols <= 512) ? 2 : 1;
     int cols = 32;
@@ -1357,6 +1361,8 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_TAIL_BN")) P->tail_bn_max = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_HIDDEN_BN")) P->hidden_bn_force = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_KROT")) P->k_rotate = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_DBG")) P->dbg = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_DIRECT")) P->tail_direct = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_KACC")) P->kacc_max = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WPREFETCH")) P->w_prefetch = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_STAGECAP_KB")) P->latency_smem_cap_kb = std::atoi(e);

@@ -21,13 +21,13 @@ L = _capi.lib()
 with torch.no_grad():
     f(x); eng = net.flow.engine; eng.assume_frozen = True
     n = 256
-    buf = torch.zeros(n * 16, dtype=torch.int64, device=dev)
+    buf = torch.zeros(n * 32, dtype=torch.int64, device=dev)
     _capi.check(L.ipoke_inn_debug_trace(eng._plan, ctypes.c_void_p(buf.data_ptr()), n))
     for _ in range(4): f(x)
     torch.cuda.synchronize()
-    t = buf.cpu().view(n, 2, 8)
+    t = buf.cpu().view(n, 2, 16)
     _capi.check(L.ipoke_inn_debug_trace(eng._plan, None, 0))
-names = ["entry", "prolog", "dep_ok", "1st_full", "lastMMA", "acc_rdy", "epi_done", "exit"]
+names = ["entry", "prolog", "dep_ok", "1st_full", "lastMMA", "acc_rdy", "epi_done", "exit", "staged", "bar1", "math", "bar2", "wb", "cc", "r1", "r8"]
 t0 = int(t[0, 0, 0])
 print("ns relative to the first GEMM's entry; per launch: first CTA | last CTA")
 prev_exit = None
@@ -37,7 +37,7 @@ for i in range(n):
         for c in range(2):
             r = [int(v) - t0 if int(v) else -1 for v in t[i, c]]
             base = r[0]
-            print(f"op{i:3d} cta{'F' if c == 0 else 'L'} entry@{base:8d} " + " ".join(f"{names[k]}+{r[k]-base:5d}" for k in range(1, 8))
+            print(f"op{i:3d} cta{'F' if c == 0 else 'L'} entry@{base:8d} " + " ".join(f"{names[k]}+{r[k]-base:5d}" for k in range(1, 16) if r[k] >= 0)
                   + (f" | gap_from_prev_exit {base - prev_exit:5d}" if (prev_exit is not None and c == 0) else ""))
     prev_exit = max(int(t[i, 0, 7]), int(t[i, 1, 7])) - t0
 tot = max(int(t[i - 1, 0, 7]), int(t[i - 1, 1, 7])) - t0
