@@ -95,6 +95,7 @@ struct GemmParams {
   int f_u_begin;
   const float* ld_extra;  // nullable: scalar added once per row (the next block's ActNorm log-det)
   int direct;                  // tail epilogue without the smem transposition (one-wave launches)
+  int ks;                      // tail_cluster_kernel.cuh: K slices per subnetwork (cluster = 2 * ks CTAs per tile)
   int dbg;                     // debug bit mask (IPOKE_INN_DBG), 0 in production
   unsigned long long* trace;   // nullable debug timeline (ipoke_inn_debug_trace): 16 slots for this launch
   // backward (EPI_DGRAD / EPI_DU): dX = dY * W with W read MN-major straight from the forward layout

@@ -16,6 +16,7 @@
 #include "../../include/ipoke_inn.h"
 #include "elementwise.cuh"
 #include "gemm_kernel.cuh"
+#include "tail_cluster_kernel.cuh"
 #include "wgrad_kernel.cuh"
 
 using namespace inn;
@@ -59,6 +60,7 @@ struct GemmOp {
   CUtensorMap tmA[2], tmW[2], tmO[2];
   GemmParams p;
   int mode, grid, smem, cluster;
+  int tail_cluster;   // 1: inn_tail_cluster_kernel (small batches), cluster = 2 * p.ks
 };
 struct WgradOp {
   CUtensorMap tmY[2], tmX[2];
@@ -152,6 +154,7 @@ struct ipoke_inn_plan {
   int tail_bn_max = 128;
   int k_rotate = 0;
   int tail_direct = 1;
+  int tail_cluster = 1;           // small batches: coupling tails as split-K clusters (tail_cluster_kernel.cuh)
   int dbg = 0;
   int kacc_max = 1;               // K-interleaved accumulators: measured no gain once the MMA issue is uniform
   int hidden_bn_force = 0;       // debug: fixed tile width of the hidden-layer GEMMs
@@ -269,6 +272,10 @@ int ensure_device(ipoke_inn_plan* P) {
   SET_SMEM((inn_gemm_kernel<2, EPI_DGRAD>))
   SET_SMEM((inn_gemm_kernel<1, EPI_DU>))
   SET_SMEM((inn_gemm_kernel<2, EPI_DU>))
+  SET_SMEM((inn_tail_cluster_kernel<1, false>))
+  SET_SMEM((inn_tail_cluster_kernel<2, false>))
+  SET_SMEM((inn_tail_cluster_kernel<1, true>))
+  SET_SMEM((inn_tail_cluster_kernel<2, true>))
   SET_SMEM((inn_wgrad_kernel<1>))
   SET_SMEM((inn_wgrad_kernel<2>))
 #undef SET_SMEM
@@ -505,9 +512,21 @@ struct Builder {
     // two accumulators (s, t) per stage: cap the tile at 128 columns so TMEM still double-buffers and the
     // (transcendental-heavy) epilogue of tile i overlaps the MMAs of tile i+1
     TileCfg tc = pick_bn(P, g.mode, P->Np, m_tiles, P->tail_bn_max);
+    // small batches: 128 x 16 tiles, each shared by a cluster of {s, t} x ks K-slices (tail_cluster_kernel.cuh)
+    int ks = 0;
+    if (P->tail_cluster) {
+      const int tiles16 = m_tiles * (P->Np / TC_BN);
+      for (int c = 4; c >= 1; c >>= 1)
+        if ((P->Hp / BK) % c == 0 && tiles16 * 2 * c <= P->num_sms) { ks = c; break; }
+      if (P->tail_cluster > 1 && ks > P->tail_cluster / 2) ks = P->tail_cluster / 2;   // debug: cap the cluster size
+    }
+    if (ks > 0) {
+      tc = TileCfg();
+      tc.bn = TC_BN;
+    }
     const int bn = tc.bn;
     g.p.num_n_tiles = P->Np / bn;
-    tc.mc = pick_mc(P, m_tiles * (P->Np / bn), P->Np / bn, P->Np / bn);
+    if (ks == 0) tc.mc = pick_mc(P, m_tiles * (P->Np / bn), P->Np / bn, P->Np / bn);
     g.p.tiles_per_group = 1 << 30;
     g.p.num_k_blocks = P->Hp / BK;
     g.p.a_group_stride = 0;
@@ -571,6 +590,25 @@ struct Builder {
       err |= make_map(P, &g.tmA[sp], act_base(k, ci, act_layer, sp), G * P->Hp, B, 2ll * ld_act, BM / tc.mc);
       err |= make_map(P, &g.tmW[sp], packed + (sp == 0 ? t.w.hi : t.w.lo), t.w.Kp, t.w.rows, 2ll * t.w.Kp, bn);
       g.tmO[sp] = g.tmA[sp];      // unused by the tail epilogue
+    }
+    if (ks > 0) {
+      g.p.M = B;
+      g.p.num_m_tiles = m_tiles;
+      g.p.BN = TC_BN;
+      g.p.ks = ks;
+      g.p.w_prefetch = P->w_prefetch;
+      const int nkb = g.p.num_k_blocks / ks;
+      const int fit = (kMaxDynSmem - 1024 - TC_RECV_BYTES - SMEM_BARRIER_BYTES) / tail_cluster_stage_bytes(P->ksplit);
+      g.p.stages = std::max(1, std::min(std::min(nkb, MAX_STAGES), fit));
+      g.smem = tail_cluster_smem_bytes(P->ksplit, g.p.stages);
+      g.cluster = 2 * ks;
+      g.grid = m_tiles * g.p.num_n_tiles * g.cluster;
+      g.tail_cluster = 1;
+      if (P->ksplit == 1) {
+        g.tmA[1] = g.tmA[0];
+        g.tmW[1] = g.tmW[0];
+      }
+      return;
     }
     finish_gemm(g, tc);
   }
@@ -1047,8 +1085,39 @@ cudaError_t launch_gemm_t(const GemmOp& g, const GemmParams& gp, cudaStream_t st
                             g.tmO[1], gp);
 }
 
+template <int kSplit, bool kRev>
+cudaError_t launch_tail_cluster_t(const GemmOp& g, const GemmParams& gp, cudaStream_t st, int pdl) {
+  cudaLaunchConfig_t cfg;
+  std::memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)g.grid);
+  cfg.blockDim = dim3(TC_THREADS);
+  cfg.dynamicSmemBytes = (size_t)g.smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  attr[na].id = cudaLaunchAttributeClusterDimension;
+  attr[na].val.clusterDim.x = (unsigned)g.cluster;
+  attr[na].val.clusterDim.y = 1;
+  attr[na].val.clusterDim.z = 1;
+  ++na;
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  return cudaLaunchKernelEx(&cfg, inn_tail_cluster_kernel<kSplit, kRev>, g.tmA[0], g.tmA[1], g.tmW[0], g.tmW[1], gp);
+}
+
 cudaError_t launch_gemm(const ipoke_inn_plan* P, const GemmOp& g, const GemmParams& gp, cudaStream_t st) {
   const int pdl = P->use_pdl;
+  if (g.tail_cluster) {
+    const bool rev = g.mode == EPI_TAIL_REV;
+    if (P->ksplit == 2)
+      return rev ? launch_tail_cluster_t<2, true>(g, gp, st, pdl) : launch_tail_cluster_t<2, false>(g, gp, st, pdl);
+    return rev ? launch_tail_cluster_t<1, true>(g, gp, st, pdl) : launch_tail_cluster_t<1, false>(g, gp, st, pdl);
+  }
   if (P->ksplit == 2) {
     switch (g.mode) {
       case EPI_HIDDEN: return launch_gemm_t<2, EPI_HIDDEN>(g, gp, st, pdl);
@@ -1363,6 +1432,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_KROT")) P->k_rotate = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_DBG")) P->dbg = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_DIRECT")) P->tail_direct = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_TAIL_CLUSTER")) P->tail_cluster = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_KACC")) P->kacc_max = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WPREFETCH")) P->w_prefetch = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_STAGECAP_KB")) P->latency_smem_cap_kb = std::atoi(e);
