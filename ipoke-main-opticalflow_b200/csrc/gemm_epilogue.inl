@@ -35,9 +35,10 @@
           // ---- 64-column slabs: TMEM -> regs -> swizzled smem -> TMA store
           const int n_slabs = BN >> 6;
           for (int s = 0; s < n_slabs; ++s, ++slab_ctr) {
-            const int buf = (p.slab_bufs == 2) ? (slab_ctr & 1) : 0;
+            const int buf = slab_ctr & (p.slab_bufs - 1);        // slab_bufs is 1, 2 or 4
             if (tid_e == 0) {
-              if (p.slab_bufs == 2) bulk_wait_read<1>();
+              if (p.slab_bufs == 4) bulk_wait_read<3>();
+              else if (p.slab_bufs == 2) bulk_wait_read<1>();
               else bulk_wait_read<0>();
             }
             named_bar_sync(1, EPI_THREADS);                      // slab buffer `buf` is free again
@@ -174,7 +175,7 @@
         // ---- coupling tail: stage the kept half of this tile and both biases in smem (coalesced), overlapping
         //      the MMAs; then one row per thread out of smem; then coalesced write-back.
         float* keep_s = epi_f32;                                  // [128][BN + 1]
-        float* bias_s = epi_f32 + BM * (BN + 1);
+        float* bias_s = epi_f32 + keep_elems;
         float* bias_t = bias_s + BN;
         float* col_scale = bias_t + BN;                           // folded boundary: per-column constants of this tile
         float* col_loc = col_scale + BN;

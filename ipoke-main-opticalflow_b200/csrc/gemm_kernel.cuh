@@ -53,7 +53,7 @@ struct GemmParams {
   int k_rotate;           // 1: tile (m, n) walks its k-blocks starting at n (mod K/64): CTAs that share an A row
                           //    block then read different L2 lines at any moment (one-wave launches hot-spot otherwise)
   int mcast;              // cluster size along n (1, 2, 4, 8): A tiles are TMA-multicast to the CTAs sharing an m-tile
-  int slab_bufs;          // EPI_HIDDEN: 0 = direct global stores, 1 / 2 = TMA-store slab buffers per (hi|lo)
+  int slab_bufs;          // EPI_HIDDEN: 0 = direct global stores, 1 / 2 / 4 = TMA-store slab buffers per (hi|lo)
   int tiles_per_group;    // n-tiles per subnetwork group (hidden layers); >= num_n_tiles otherwise
   int a_group_stride;     // A column offset (elements) per group
   int a_off[2];           // A column offset per accumulator
@@ -117,14 +117,15 @@ __host__ inline int gemm_stage_bytes(int ksplit, int mode, int BN) {
 }
 // epilogue smem: [slabs (EPI_HIDDEN with TMA store)] [fp32 area: bias (2 x BN) | tail: keep tile + 2 biases +
 // 3 per-column arrays of the folded boundary]
-__host__ inline int gemm_epi_bytes(int ksplit, int mode, int BN, int slab_bufs) {
+// (`direct` tails keep their rows in registers: no 128 x BN staging tile, which leaves room for one more pipeline stage)
+__host__ inline int gemm_epi_bytes(int ksplit, int mode, int BN, int slab_bufs, int direct = 0) {
   if (mode == EPI_HIDDEN || mode == EPI_DGRAD) return ksplit * slab_bufs * SLAB_BYTES + 2 * BN * 4;
   if (mode == EPI_DU) return 2 * BN * 4;
-  return (BM * (BN + 1) + 5 * BN) * 4;
+  return ((direct ? 0 : BM * (BN + 1)) + 5 * BN) * 4;
 }
-__host__ inline int gemm_smem_bytes(int ksplit, int mode, int BN, int stages, int slab_bufs) {
-  return 1024 + stages * gemm_stage_bytes(ksplit, mode, BN) + ((gemm_epi_bytes(ksplit, mode, BN, slab_bufs) + 15) & ~15) +
-         SMEM_BARRIER_BYTES;
+__host__ inline int gemm_smem_bytes(int ksplit, int mode, int BN, int stages, int slab_bufs, int direct = 0) {
+  return 1024 + stages * gemm_stage_bytes(ksplit, mode, BN) +
+         ((gemm_epi_bytes(ksplit, mode, BN, slab_bufs, direct) + 15) & ~15) + SMEM_BARRIER_BYTES;
 }
 
 template <int kSplit, int kMode>
@@ -163,7 +164,8 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
   constexpr bool kTailMode = (kMode == EPI_TAIL_FWD || kMode == EPI_TAIL_REV);
   const int slab_total = kSlabMode ? kSplit * p.slab_bufs * SLAB_BYTES : 0;
   float* epi_f32 = reinterpret_cast<float*>(epi_smem + slab_total);
-  const int epi_bytes = slab_total + (kTailMode ? (BM * (BN + 1) + 5 * BN) * 4 : 2 * BN * 4);
+  const int keep_elems = (kTailMode && !p.direct) ? BM * (BN + 1) : 0;   // tail staging tile [128][BN + 1]
+  const int epi_bytes = slab_total + (kTailMode ? (keep_elems + 5 * BN) * 4 : 2 * BN * 4);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(epi_smem + ((epi_bytes + 15) & ~15));
   uint64_t* empty_bar = full_bar + MAX_STAGES;
   uint64_t* tfull_bar = empty_bar + MAX_STAGES;

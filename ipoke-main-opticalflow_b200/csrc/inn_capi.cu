@@ -154,6 +154,7 @@ struct ipoke_inn_plan {
   int tail_bn_max = 128;
   int k_rotate = 0;
   int tail_direct = 1;
+  int slab4 = 0;                  // 4 output slabs in flight where the pipeline leaves smem free
   int tail_cluster = 1;           // small batches: coupling tails as split-K clusters (tail_cluster_kernel.cuh)
   int dbg = 0;
   int kacc_max = 1;               // K-interleaved accumulators: measured no gain once the MMA issue is uniform
@@ -295,16 +296,17 @@ int make_map(const ipoke_inn_plan* P, CUtensorMap* m, const void* base, long lon
   return r == CUDA_SUCCESS ? 0 : IPOKE_INN_E_INTERNAL;
 }
 
-struct TileCfg { int bn = 0, stages = 0, slab_bufs = 0, mc = 1; };
+struct TileCfg { int bn = 0, stages = 0, slab_bufs = 0, mc = 1, direct = 0; };
 
 // smem plan for one tile width: pipeline stages + epilogue staging must fit in 227 KB
-TileCfg tile_cfg(int ksplit, int mode, int bn) {
+TileCfg tile_cfg(int ksplit, int mode, int bn, int direct = 0) {
   TileCfg t;
   t.bn = bn;
+  t.direct = direct;
   const int avail = kMaxDynSmem - 1024 - SMEM_BARRIER_BYTES;
   const int sb = gemm_stage_bytes(ksplit, mode, bn);
   auto stages_with = [&](int slabs) {
-    const int epi = (gemm_epi_bytes(ksplit, mode, bn, slabs) + 15) & ~15;
+    const int epi = (gemm_epi_bytes(ksplit, mode, bn, slabs, direct) + 15) & ~15;
     return std::min(MAX_STAGES, (avail - epi) / sb);
   };
   if ((mode == EPI_HIDDEN || mode == EPI_DGRAD) && bn >= 64) {
@@ -432,7 +434,16 @@ struct Builder {
     g.p.bn_log2 = 0;
     while ((1 << g.p.bn_log2) < t.bn) g.p.bn_log2++;
     g.p.stages = std::min(t.stages, std::max(2, g.p.num_k_blocks));
-    g.p.slab_bufs = t.slab_bufs;
+    int slab_bufs = t.slab_bufs;
+    // short-K layers (the first Linear of a subnetwork) are bound by the output stores: with the smem the unused
+    // pipeline stages leave free, keep 4 slab stores in flight instead of 2 (more bytes in flight per SM)
+    if (P->slab4 && slab_bufs == 2 && (g.mode == EPI_HIDDEN || g.mode == EPI_DGRAD)) {
+      const int st2 = std::min(t.stages, std::max(2, 2 * g.p.num_k_blocks));   // up to two tiles of loads in flight
+      const int st_min = g.p.num_k_blocks <= 4 ? std::min(g.p.stages, 3) : g.p.stages;   // store-bound: 3 stages do
+      for (int st = st2; st >= st_min; --st)
+        if (gemm_smem_bytes(P->ksplit, g.mode, t.bn, st, 4) <= kMaxDynSmem) { g.p.stages = st; slab_bufs = 4; break; }
+    }
+    g.p.slab_bufs = slab_bufs;
     g.p.mcast = t.mc;
     g.p.w_prefetch = P->w_prefetch;
     g.p.k_rotate = (P->k_rotate && g.p.num_m_tiles * g.p.num_n_tiles <= 2 * P->num_sms && !g.p.w_mn) ? 1 : 0;
@@ -440,7 +451,7 @@ struct Builder {
     if (tiles <= P->num_sms && P->latency_smem_cap_kb > 0) {
       // optional: keep the footprint small so the next kernel's CTA (PDL) can be co-resident
       while (g.p.stages > 2 &&
-             gemm_smem_bytes(P->ksplit, g.mode, t.bn, g.p.stages, t.slab_bufs) > P->latency_smem_cap_kb * 1024)
+             gemm_smem_bytes(P->ksplit, g.mode, t.bn, g.p.stages, slab_bufs, t.direct) > P->latency_smem_cap_kb * 1024)
         g.p.stages--;
     }
     // one-wave launches: split the dependent MMA chain over up to 4 K-interleaved accumulators
@@ -450,14 +461,14 @@ struct Builder {
       while (kacc > 1 && gemm_nsub(g.mode) * kacc * t.bn > 512) kacc >>= 1;
     }
     g.p.kacc = kacc;
-    g.p.direct = (P->tail_direct && tiles <= P->num_sms) ? 1 : 0;
+    g.p.direct = t.direct;
     const int acc_cols = gemm_nsub(g.mode) * kacc * t.bn;
     g.p.nacc = (2 * acc_cols <= 512) ? 2 : 1;
     int cols = 32;
     while (cols < g.p.nacc * acc_cols) cols <<= 1;
     g.p.tmem_cols = cols;
     g.p.epi_off = g.p.stages * gemm_stage_bytes(P->ksplit, g.mode, t.bn);
-    g.smem = gemm_smem_bytes(P->ksplit, g.mode, t.bn, g.p.stages, t.slab_bufs);
+    g.smem = gemm_smem_bytes(P->ksplit, g.mode, t.bn, g.p.stages, slab_bufs, t.direct);
     g.grid = t.mc > 1 ? tiles : std::min(tiles, P->num_sms);
     g.cluster = t.mc;
     if (P->ksplit == 1) {
@@ -523,6 +534,10 @@ struct Builder {
     if (ks > 0) {
       tc = TileCfg();
       tc.bn = TC_BN;
+    } else if (P->tail_direct == 2 || (P->tail_direct == 1 && m_tiles * (P->Np / tc.bn) <= P->num_sms)) {
+      // register-resident epilogue: always for one-wave launches; tail_direct = 2 also for multi-wave launches, where
+      // dropping the 128 x BN staging tile buys one more pipeline stage (2 x 64 KB in flight do not cover the TMA latency)
+      tc = tile_cfg(P->ksplit, g.mode, tc.bn, 1);
     }
     const int bn = tc.bn;
     g.p.num_n_tiles = P->Np / bn;
@@ -1433,6 +1448,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_DBG")) P->dbg = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_DIRECT")) P->tail_direct = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_TAIL_CLUSTER")) P->tail_cluster = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_SLAB4")) P->slab4 = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_KACC")) P->kacc_max = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WPREFETCH")) P->w_prefetch = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_STAGECAP_KB")) P->latency_smem_cap_kb = std::atoi(e);

@@ -52,6 +52,9 @@ inn_tail_cluster_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_c
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
 
+  unsigned long long* const tr =
+      (p.trace != nullptr && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) ? p.trace + (blockIdx.x == 0 ? 0 : 16) : nullptr;
+  if (tr != nullptr && threadIdx.x == 0) tr[0] = globaltimer_ns();
   cluster_arrive_release();                  // #1: "my CTA runs" -- waited on just before the first remote store
 
   const int KS = p.ks;
@@ -94,6 +97,7 @@ inn_tail_cluster_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (tr != nullptr && threadIdx.x == 0) tr[1] = globaltimer_ns();
   if (threadIdx.x == 0) grid_dep_launch();
 
   if (warp == 0) {
@@ -109,6 +113,7 @@ inn_tail_cluster_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_c
                        (kb0 + ki) * BK, w_row);
     }
     grid_dep_wait();
+    if (tr != nullptr && lane == 0) tr[2] = globaltimer_ns();
     int stage = 0;
     uint32_t phase = 0;
     for (int ki = 0; ki < nkb; ++ki) {
@@ -136,6 +141,7 @@ inn_tail_cluster_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_c
     for (int ki = 0; ki < nkb; ++ki) {
       mbar_wait(&full_bar[stage], phase, 13);
       tc_fence_after();
+      if (tr != nullptr && lane == 0 && ki == 0) tr[3] = globaltimer_ns();
       const uint32_t sbase = smem_u32(smem + stage * stage_bytes);
       const uint64_t da_hi = umma_desc_k_sw128(sbase);
       const uint64_t da_lo = umma_desc_k_sw128(sbase + (kSplit - 1) * A_TILE_BYTES);
@@ -154,7 +160,10 @@ inn_tail_cluster_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_c
         }
       }
       umma_commit_el(&empty_bar[stage]);
-      if (ki == nkb - 1) umma_commit_el(tfull_bar);
+      if (ki == nkb - 1) {
+        umma_commit_el(tfull_bar);
+        if (tr != nullptr && lane == 0) tr[4] = globaltimer_ns();
+      }
       if (++stage == stages) { stage = 0; phase ^= 1; }
     }
   }
@@ -213,6 +222,7 @@ inn_tail_cluster_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_c
     const int r_loc = q * 32 + lane;
     mbar_wait(tfull_bar, 0, 14);
     tc_fence_after();
+    if (tr != nullptr && tid_e == 0) tr[5] = globaltimer_ns();
     float v[16];
     tmem_ld16(tmem_base + (static_cast<uint32_t>(q * 32) << 16), v);
     tmem_ld_wait();
@@ -227,6 +237,7 @@ inn_tail_cluster_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_c
   }
   cluster_arrive_release();                                // #2: partials delivered
   cluster_wait_acquire();
+  if (tr != nullptr && threadIdx.x == 128) tr[9] = globaltimer_ns();
 
   if (warp >= 4) {
     const float neg = p.f_leaky ? (p.f_mode == 2 ? 1.0f / p.f_alpha : p.f_alpha) : 1.0f;
@@ -330,8 +341,10 @@ inn_tail_cluster_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_c
     }
   }
 
+  if (tr != nullptr && threadIdx.x == 128) tr[6] = globaltimer_ns();
   tc_fence_before();
   __syncthreads();
+  if (tr != nullptr && threadIdx.x == 0) tr[7] = globaltimer_ns();
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 32);
