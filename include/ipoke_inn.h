@@ -148,6 +148,26 @@ int ipoke_inn_actnorm_finalize(const double* moments, double count, int C, float
 int ipoke_inn_flow_loss(const float* z, const float* logdet, int B, int C, float nll_weight, float logdet_weight,
                         float* out3, float* dz, float* dlogdet, void* stream);
 
+/* Fused Adam / AMSGrad step over all parameter tensors in one launch -- replaces the reference's
+ * torch.optim.Adam(lr, betas, weight_decay, amsgrad=True).step() (models/second_stage_video_fc.py:685-687;
+ * arithmetic of torch/optim/adam.py `_single_tensor_adam`, L2 weight decay added to the gradient).
+ * jobs_dev: device array of n_jobs entries; chunk tables: chunk c updates job chunk_job[c], elements
+ * [chunk_off[c], chunk_off[c] + ipoke_inn_adam_chunk_elems()) (device arrays, built once by the caller).
+ * step counts from 1; grad_scale multiplies the gradients first (1/world_size after a sum all-reduce).
+ * vmax pointers may be NULL when amsgrad == 0.                                                         */
+typedef struct ipoke_inn_adam_job {
+  float* p;
+  const float* g;
+  float* m;
+  float* v;
+  float* vmax;
+  long long n;
+} ipoke_inn_adam_job;
+int ipoke_inn_adam_chunk_elems(void);
+int ipoke_inn_adam_step(const ipoke_inn_adam_job* jobs_dev, const int* chunk_job_dev, const long long* chunk_off_dev,
+                        int n_chunks, float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                        int amsgrad, float grad_scale, void* stream);
+
 /* Number of kernels the last forward / reverse call on this plan launched (for bench accounting). */
 int ipoke_inn_last_launch_count(const ipoke_inn_plan* plan);
 

@@ -18,6 +18,7 @@ SYMBOLS = [
     "ipoke_inn_last_launch_count", "ipoke_inn_debug_layout", "ipoke_inn_debug_trace",
     "ipoke_inn_profile_enable", "ipoke_inn_profile_read", "ipoke_inn_set_option",
     "ipoke_inn_saved_bytes", "ipoke_inn_forward_train", "ipoke_inn_backward", "ipoke_inn_profile_read_n",
+    "ipoke_inn_adam_chunk_elems", "ipoke_inn_adam_step",
 ]
 
 
@@ -90,6 +91,10 @@ def lib():
     L.ipoke_inn_backward.argtypes = [vp] * 14 + [i32, i32, i32, vp, vp]
     L.ipoke_inn_profile_read_n.restype = i32
     L.ipoke_inn_profile_read_n.argtypes = [vp, vp, vp, i32]
+    L.ipoke_inn_adam_chunk_elems.restype = i32
+    L.ipoke_inn_adam_chunk_elems.argtypes = []
+    L.ipoke_inn_adam_step.restype = i32
+    L.ipoke_inn_adam_step.argtypes = [vp, vp, vp, i32, f32, f32, f32, f32, f32, i32, i32, f32, vp]
     _lib = L
     return L
 

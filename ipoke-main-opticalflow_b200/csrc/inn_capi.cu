@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <memory>
@@ -16,6 +17,7 @@
 #include "../../include/ipoke_inn.h"
 #include "elementwise.cuh"
 #include "gemm_kernel.cuh"
+#include "optim.cuh"
 #include "tail_cluster_kernel.cuh"
 #include "wgrad_kernel.cuh"
 
@@ -1733,6 +1735,34 @@ int ipoke_inn_flow_loss(const float* z, const float* logdet, int B, int C, float
   if (!z || !logdet || !out3 || B <= 0 || C <= 0) return IPOKE_INN_E_INVALID;
   inn_flow_loss_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(z, logdet, B, C, nll_weight, logdet_weight,
                                                                           out3, dz, dlogdet);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : (int)e;
+}
+
+int ipoke_inn_adam_chunk_elems(void) { return ADAM_CHUNK; }
+
+int ipoke_inn_adam_step(const ipoke_inn_adam_job* jobs_dev, const int* chunk_job_dev, const long long* chunk_off_dev,
+                        int n_chunks, float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                        int amsgrad, float grad_scale, void* stream) {
+  if (n_chunks == 0) return 0;
+  if (!jobs_dev || !chunk_job_dev || !chunk_off_dev || n_chunks < 0 || step < 1) return IPOKE_INN_E_INVALID;
+  AdamParams a;
+  a.jobs = jobs_dev;
+  a.chunk_job = chunk_job_dev;
+  a.chunk_off = chunk_off_dev;
+  a.n_chunks = n_chunks;
+  a.beta1 = beta1;
+  a.beta2 = beta2;
+  a.eps = eps;
+  a.weight_decay = weight_decay;
+  // bias corrections in double like Python floats in torch/optim/adam.py
+  const double bc1 = 1.0 - std::pow((double)beta1, (double)step);
+  const double bc2 = 1.0 - std::pow((double)beta2, (double)step);
+  a.step_size = (float)((double)lr / bc1);
+  a.inv_sqrt_bc2 = (float)(1.0 / std::sqrt(bc2));
+  a.grad_scale = grad_scale;
+  a.amsgrad = amsgrad;
+  inn_adam_kernel<<<n_chunks, ADAM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(a);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : (int)e;
 }
