@@ -45,6 +45,20 @@ def peaks():
     return dict(hbm=6650.0, bf16=1590.0, bf16_sus=1400.0, src="fallback (B200_PROFILING.md)")
 
 
+def workload_config(cfg_name, B, world, precision):
+    """The `config` object of the JSON line -- identical for our arm and the reference arm."""
+    kind, kw, _, src = CONFIGS[cfg_name]
+    C, E = kw["flow_in_channels"], kw.get("flow_embedding_channels", 0)
+    H = kw["flow_mid_channels"] if kind == "uncond" else kw["flow_mid_channels_factor"] * C
+    wbytes = 2 if precision == "bf16" else 4
+    return {"workload": f"{cfg_name}: {src}; {B} latents per GPU per step, forward+logdet then reverse",
+            "batch_per_gpu": B, "global_batch": B * world, "C": C, "E": E, "H": H, "depth": kw["flow_hidden_depth"],
+            "n_flows": kw["n_flows"], "precision": precision, "parallelism": f"dp{world}",
+            "l2": "256 MiB buffer written between timed iterations (L2 flush); weights "
+                  f"{macs_per_sample(kind, kw) * wbytes / 1e6:.0f} MB",
+            "streams": "the forward pass and the (independent) reverse pass of a step run concurrently on 2 CUDA streams"}
+
+
 def macs_per_sample(kind, kw):
     C = kw["flow_in_channels"]
     d, n = kw["flow_hidden_depth"], kw["n_flows"]
@@ -108,38 +122,43 @@ class ClockSampler:
 
 # ----------------------------------------------------------------------------- CPU arm (oracle port)
 def cpu_port_run(cfg_name, B, steps, warmup, budget_s=20.0):
-    """Times the numpy port of the reference path (oracle/inn_oracle.py) on the host cores.  One step =
-    forward + reverse on a sample of the workload; the sample batch is bounded so a run stays short."""
-    import numpy as np
+    """Times the CPU restatement of the reference path on the host cores.  One step = forward + reverse on a sample
+    of the workload; the sample batch is bounded so a run stays short.  The timed code is oracle/inn_oracle_torch.py:
+    the reference's own torch CPU operators (F.linear / leaky_relu / tanh / exp / cat / index) on all host threads --
+    the reference module itself is Python under /root/reference and cannot travel to the GPU box."""
     import torch
     from oracle import inn_oracle as O
+    from oracle import inn_oracle_torch as OT
     import ipoke_inn_b200 as P
     kind, kw, _, _ = CONFIGS[cfg_name]
     torch.manual_seed(42)
+    torch.set_num_threads(os.cpu_count())
     net = P.SupervisedTransformer(dict(kw)) if kind == "cond" else P.UnsupervisedTransformer3(**kw)
     sd = O.state_dict_to_numpy(net.state_dict())
     C, E = kw["flow_in_channels"], kw.get("flow_embedding_channels", 0)
-    rng = np.random.default_rng(1234)
-    x = rng.standard_normal((B, C), dtype=np.float32)
-    cond = rng.standard_normal((B, E), dtype=np.float32) if kind == "cond" else None
-    zin = rng.standard_normal((B, C), dtype=np.float32)
-    O.flow_forward_with_actnorm_init(sd, x, cond)
+    g = torch.Generator().manual_seed(1234)
+    x = torch.randn(B, C, generator=g)
+    cond = torch.randn(B, E, generator=g) if kind == "cond" else None
+    zin = torch.randn(B, C, generator=g)
+    O.flow_forward_with_actnorm_init(sd, x.numpy(), None if cond is None else cond.numpy())   # ActNorm data init
+    sdt = {k: torch.from_numpy(__import__("numpy").ascontiguousarray(v)) for k, v in sd.items()}
     t_first = time.perf_counter()
-    O.flow_forward(sd, x, cond)
-    O.flow_reverse(sd, zin, cond)
+    OT.flow_forward(sdt, x, cond)
+    OT.flow_reverse(sdt, zin, cond)
     t_first = time.perf_counter() - t_first
     steps = max(1, min(steps, int(budget_s / max(t_first, 1e-6))))
-    for _ in range(min(warmup, 1)):
-        O.flow_forward(sd, x, cond)
-        O.flow_reverse(sd, zin, cond)
+    for _ in range(max(warmup, 1)):
+        OT.flow_forward(sdt, x, cond)
+        OT.flow_reverse(sdt, zin, cond)
     t0 = time.perf_counter()
     for _ in range(steps):
-        O.flow_forward(sd, x, cond)
-        O.flow_reverse(sd, zin, cond)
+        OT.flow_forward(sdt, x, cond)
+        OT.flow_reverse(sdt, zin, cond)
     dt = time.perf_counter() - t0
-    return {"value": B * steps / dt, "unit": "samples/s", "cores": os.cpu_count(), "kind": "port",
-            "sample": f"{steps} step(s) of forward+reverse on batch {B} ({cfg_name}, numpy fp32 + OpenBLAS, "
-                      f"all host threads)", "ms_per_step": 1e3 * dt / steps, "steps": steps}
+    return {"value": B * steps / dt, "unit": "samples/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{steps} step(s) of forward+reverse on batch {B} ({cfg_name}, torch {torch.__version__} CPU "
+                      f"operators as in the reference, fp32, {torch.get_num_threads()} threads of {os.cpu_count()} cores)",
+            "ms_per_step": 1e3 * dt / steps, "steps": steps}
 
 
 # ----------------------------------------------------------------------------- GPU arm
@@ -211,10 +230,28 @@ def gpu_run(args):
     eng = net.flow.engine
     eng.assume_frozen = True
 
-    def step_dev():
+    # A step = one forward (z, logdet) pass over B latents + one reverse (sampling) pass over B independent N(0,1)
+    # draws.  The two passes share nothing but the weights, so they are issued as two concurrent requests on two CUDA
+    # streams (one scratch workspace per stream); the serial single-stream figure is measured first and reported too.
+    s_f, s_r = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+
+    def step_serial():
         call(net, x)
         call(net, zin, reverse=True)
 
+    def step_dev():
+        cur = torch.cuda.current_stream(dev)
+        s_f.wait_stream(cur)
+        s_r.wait_stream(cur)
+        with torch.cuda.stream(s_f):
+            call(net, x)
+        with torch.cuda.stream(s_r):
+            call(net, zin, reverse=True)
+        cur.wait_stream(s_f)
+        cur.wait_stream(s_r)
+
+    ms_serial, _, _ = timed(net, args.steps, args.warmup, step_serial)
+    eng.set_concurrency(2)
     sampler = ClockSampler(local) if rank == 0 else None
     ms, t0, t1 = timed(net, args.steps, args.warmup, step_dev)
     clocks = sampler.stop(t0, t1) if sampler else None
@@ -233,9 +270,17 @@ def gpu_run(args):
     xoh = torch.empty(B, C).pin_memory()
 
     def step_host():
-        eng.forward_host(xh, ch, zh, ldh)
-        eng.reverse_host(zinh, ch, xoh)
-        torch.cuda.current_stream().synchronize()                       # results are on the host
+        cur = torch.cuda.current_stream(dev)
+        s_f.wait_stream(cur)
+        s_r.wait_stream(cur)
+        with torch.cuda.stream(s_f):
+            eng.forward_host(xh, ch, zh, ldh)
+        with torch.cuda.stream(s_r):
+            eng.reverse_host(zinh, ch, xoh)
+        s_f.synchronize()                                               # results are on the host
+        s_r.synchronize()
+        cur.wait_stream(s_f)
+        cur.wait_stream(s_r)
 
     ms_e2e, _, _ = timed(net, args.steps, args.warmup, step_host)
     e2e_value = world * B * args.steps / (ms_e2e * 1e-3)
@@ -268,7 +313,12 @@ def gpu_run(args):
         hidden_launches = int(cnt[1] // args.steps)
         # algorithmic bytes of the hidden GEMMs per step: weights once + activations in/out (bf16) per launch
         hidden_bytes_per_step = 2.0 * ((P_w - tail_macs) * wbytes) + hidden_launches * (2.0 * B * 2 * H * wbytes)
-        t_hidden = tot[1] / args.steps * 1e-3
+        # duration of the hidden-layer launches inside the step: the event-bracketed pass serialises the launches
+        # (no graph replay, no programmatic dependent launch, ~5 us of launch latency each), so the kernel's share
+        # of that pass is applied to the serial single-stream step time of the timed region
+        t_hidden_isolated = tot[1] / args.steps * 1e-3
+        share = float(tot[1] / max(tot.sum(), 1e-9))
+        t_hidden = share * (ms_serial / args.steps) * 1e-3
         tf = hidden_flops_per_step / t_hidden / 1e12 * (3 if args.precision == "fp32" else 1)
         gbs = hidden_bytes_per_step / t_hidden / 1e9
         tensor_bound = (hidden_flops_per_step / (pk["bf16"] * 1e12)) > (hidden_bytes_per_step / (pk["hbm"] * 1e9))
@@ -282,28 +332,31 @@ def gpu_run(args):
             "traffic": None,
             "peak_source": pk["src"] + " (burst)",
             "launches_per_step": hidden_launches,
-            "avg_launch_us": 1e3 * tot[1] / max(cnt[1], 1),
-            "share_of_step": float(tot[1] / max(tot.sum(), 1e-9)),
+            "avg_launch_us": 1e6 * t_hidden / max(hidden_launches, 1),
+            "avg_launch_us_isolated": 1e3 * tot[1] / max(cnt[1], 1),
+            "share_of_step": share,
             "tflops_bf16_equiv": tf, "gbs": gbs,
             "per_kind_ms_per_step": {"boundary": tot[0] / args.steps, "hidden": tot[1] / args.steps,
                                      "tail": tot[2] / args.steps},
-            "note": "per-launch CUDA events in a separate pass right after the timed region (same inputs, L2 "
-                    "flushed each step); fp32-split mode counts 3 MMAs per algorithmic MAC in tflops_bf16_equiv",
+            "note": "share_of_step from per-launch CUDA events in a separate pass right after the timed region (same "
+                    "inputs, L2 flushed each step; that pass serialises the launches: avg_launch_us_isolated); "
+                    "avg_launch_us = share x serial single-stream step time / launches, i.e. the duration inside the "
+                    "graph-replayed, PDL-overlapped step; fp32-split mode counts 3 MMAs per algorithmic MAC in "
+                    "tflops_bf16_equiv",
         }
-        cpu = cpu_port_run(args.config, min(B, 256), 3, 1, budget_s=15.0)
+        cpu = cpu_port_run(args.config, min(B, 256), 20, 2, budget_s=15.0)
         out = {
             "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "bf16x2-split(fp32 parity)",
             "data": "synthetic",
-            "config": {"workload": f"{args.config}: {src}; {B} latents per GPU per step, forward+logdet then reverse",
-                       "batch_per_gpu": B, "global_batch": B * world, "C": C, "E": E, "H": H, "depth": d,
-                       "n_flows": kw["n_flows"], "precision": args.precision, "parallelism": f"dp{world}",
-                       "l2": "256 MiB buffer written between timed iterations (L2 flush); weights "
-                             f"{P_w * wbytes / 1e6:.0f} MB"},
+            "config": workload_config(args.config, B, world, args.precision),
             "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps,
                     "path": "ipoke_inn_forward_host / ipoke_inn_reverse_host (pinned host buffers)"},
+            "serial": {"value": world * B * args.steps / (ms_serial * 1e-3), "unit": "samples/s",
+                       "ms_per_step": ms_serial / args.steps,
+                       "what": "same step with the forward and the reverse pass back to back on ONE stream"},
             "gpu_launches": launches * args.steps,
             "launches_per_step": launches,
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
@@ -438,17 +491,28 @@ def main():
                 "n_gpus": args.gpus, "steps": cpu["steps"], "warmup": 1, "ms_per_step": cpu["ms_per_step"],
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic",
-                "config": {"workload": f"{args.config}: {src}; CPU port of the reference path (oracle/inn_oracle.py), "
-                                       f"batch {min(B, 256)} per step, forward+logdet then reverse"},
+                "config": dict(workload_config(args.config, B, 1, "fp32"),
+                               arm=f"CPU port of the reference path (oracle/inn_oracle_torch.py: the reference's torch "
+                                   f"CPU operators, all host threads); each step = forward+reverse on a bounded sample "
+                                   f"of {min(B, 256)} latents"),
                 "cpu_baseline": {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")},
                 "e2e": {"value": cpu["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
         print(json.dumps(line))
         return
 
-    out = gpu_run(args)
+    # stdout carries exactly one JSON line: whatever libraries print (NCCL's version banner, warnings) goes to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        out = gpu_run(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
     if out is not None:
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
 
 
 if __name__ == "__main__":

@@ -172,7 +172,9 @@ int ipoke_inn_adam_step(const ipoke_inn_adam_job* jobs_dev, const int* chunk_job
 int ipoke_inn_last_launch_count(const ipoke_inn_plan* plan);
 
 /* Launch options: "graph" (default 1: replay a call as one CUDA graph when the caller's pointers repeat),
- * "pdl" (default 1: programmatic dependent launch between the GEMM kernels).  Environment overrides at plan
+ * "pdl" (default 1: programmatic dependent launch between the GEMM kernels), "streams" (default 1: how many calls
+ * the caller issues concurrently on different CUDA streams with different workspaces; one-wave launches are then
+ * sized for num_sms / streams SMs so the concurrent kernels are co-resident).  Environment overrides at plan
  * creation: IPOKE_INN_GRAPH=0/1, IPOKE_INN_PDL=0/1.                                                     */
 int ipoke_inn_set_option(ipoke_inn_plan* plan, const char* name, int value);
 

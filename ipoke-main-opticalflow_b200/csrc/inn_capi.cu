@@ -156,6 +156,8 @@ struct ipoke_inn_plan {
   int tail_bn_max = 128;
   int k_rotate = 0;
   int tail_direct = 1;
+  int streams = 1;                // calls the caller runs concurrently on different streams: one-wave launches are
+                                  // sized for num_sms / streams SMs so that the concurrent kernels are co-resident
   int slab4 = 0;                  // 4 output slabs in flight where the pipeline leaves smem free
   int tail_cluster = 1;           // small batches: coupling tails as split-K clusters (tail_cluster_kernel.cuh)
   int dbg = 0;
@@ -333,7 +335,7 @@ TileCfg pick_bn(const ipoke_inn_plan* P, int mode, int rows_per_group, int tiles
     const TileCfg t = tile_cfg(P->ksplit, mode, bn);
     if (t.stages < 2) continue;
     best = t;
-    if ((long long)tiles_other * (rows_per_group / bn) >= (long long)(P->num_sms * 4) / 5) return t;
+    if ((long long)tiles_other * (rows_per_group / bn) >= (long long)(P->num_sms / P->streams * 4) / 5) return t;
   }
   return best;
 }
@@ -530,7 +532,7 @@ struct Builder {
     if (P->tail_cluster) {
       const int tiles16 = m_tiles * (P->Np / TC_BN);
       for (int c = 4; c >= 1; c >>= 1)
-        if ((P->Hp / BK) % c == 0 && tiles16 * 2 * c <= P->num_sms) { ks = c; break; }
+        if ((P->Hp / BK) % c == 0 && tiles16 * 2 * c <= std::max(P->num_sms / P->streams, std::min(P->num_sms, tiles16 * 2))) { ks = c; break; }
       if (P->tail_cluster > 1 && ks > P->tail_cluster / 2) ks = P->tail_cluster / 2;   // debug: cap the cluster size
     }
     if (ks > 0) {
@@ -1451,6 +1453,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_DIRECT")) P->tail_direct = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_TAIL_CLUSTER")) P->tail_cluster = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_SLAB4")) P->slab4 = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_STREAMS")) P->streams = std::max(1, std::min(std::atoi(e), 8));
   if (const char* e = std::getenv("IPOKE_INN_KACC")) P->kacc_max = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WPREFETCH")) P->w_prefetch = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_STAGECAP_KB")) P->latency_smem_cap_kb = std::atoi(e);
@@ -1776,6 +1779,7 @@ int ipoke_inn_set_option(ipoke_inn_plan* P, const char* name, int value) {
   else if (std::strcmp(name, "pdl") == 0) { P->use_pdl = value != 0; P->programs.clear(); }
   else if (std::strcmp(name, "mcast") == 0) { P->use_mcast = value == 1 ? 8 : value; P->programs.clear(); }
   else if (std::strcmp(name, "fold") == 0) { P->use_fold = value != 0; P->programs.clear(); }
+  else if (std::strcmp(name, "streams") == 0) { P->streams = std::max(1, std::min(value, 8)); P->programs.clear(); }
   else return IPOKE_INN_E_INVALID;
   return 0;
 }

@@ -40,8 +40,17 @@ class FlowEngine:
         self.grad_chunk_blocks = 2
         self.last_flat_grad = None
         self._grad_layout = None
+        self.streams = 1
 
     # ------------------------------------------------------------------ plumbing
+    def set_concurrency(self, streams):
+        """Tell the plan that `streams` calls run concurrently on different CUDA streams (e.g. density evaluation and
+        sampling requests served side by side): small-batch launches are then sized for num_sms / streams SMs so
+        that the concurrent kernels are co-resident.  Every stream gets its own scratch workspace (`_workspace`)."""
+        self.streams = max(1, int(streams))
+        if self._plan is not None:
+            _capi.check(_capi.lib().ipoke_inn_set_option(self._plan, b"streams", self.streams), "set_option")
+
     def invalidate(self):
         """Force a repack before the next call (after out-of-band ``param.data`` edits)."""
         self._packed_sig = None
@@ -87,19 +96,24 @@ class FlowEngine:
             self._device = device
             self._packed = torch.empty(L.ipoke_inn_packed_bytes(plan), dtype=torch.uint8, device=device)
             self._packed_sig = None
+            if self.streams > 1:
+                _capi.check(L.ipoke_inn_set_option(plan, b"streams", self.streams), "set_option")
         return L
 
     def _stream(self):
         return ctypes.c_void_p(torch.cuda.current_stream(self._device).cuda_stream)
 
     def _workspace(self, B):
-        ws = self._ws.get(B)
+        # one scratch workspace per (batch size, CUDA stream): calls issued on different streams (e.g. a density
+        # evaluation and a sampling request served concurrently) must not share scratch state
+        key = (B, torch.cuda.current_stream(self._device).cuda_stream)
+        ws = self._ws.get(key)
         if ws is None:
-            if len(self._ws) >= 4:
+            if len(self._ws) >= 8:
                 self._ws.pop(next(iter(self._ws)))
             n = _capi.lib().ipoke_inn_workspace_bytes(self._plan, B, 1)
             ws = torch.empty(n, dtype=torch.uint8, device=self._device)
-            self._ws[B] = ws
+            self._ws[key] = ws
         return ws
 
     def _signature(self, tensors):

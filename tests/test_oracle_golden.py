@@ -103,3 +103,20 @@ def test_loss_and_backward_match_autograd(name):
 def test_macs_per_sample():
     sd, _ = load_golden("cfgS_cond")
     assert O.macs_per_sample(sd) == 307200            # BASELINE.md section 3, cfg S
+
+
+def test_torch_port_matches_reference(golden):
+    """The torch-operator restatement timed by bench.py's CPU arm (oracle/inn_oracle_torch.py) against the same
+    live-reference fixtures."""
+    import torch
+    from oracle import inn_oracle_torch as OT
+    name, sd, d = golden
+    sdt = {k: torch.from_numpy(np.ascontiguousarray(v)) for k, v in sd.items()}
+    B, C = d["x"].shape
+    c = _cond(d)
+    ct = None if c is None else torch.from_numpy(np.ascontiguousarray(c))
+    z, ld = OT.flow_forward(sdt, torch.from_numpy(d["x"]), ct)
+    assert max_rel(z.numpy(), d["z"].reshape(B, C)) < TOL
+    assert max_rel(ld.numpy(), d["logdet"]) < TOL
+    x_smp = OT.flow_reverse(sdt, torch.from_numpy(np.ascontiguousarray(d["z_in"].reshape(B, C))), ct)
+    assert max_rel(x_smp.numpy(), d["x_smp"].reshape(B, C)) < 5e-6

@@ -8,7 +8,7 @@ from bench import CONFIGS
 ap = argparse.ArgumentParser()
 ap.add_argument("--config", default="cfgB"); ap.add_argument("--batch", type=int, default=256)
 ap.add_argument("--precision", default="bf16"); ap.add_argument("--reps", type=int, default=50)
-ap.add_argument("--tag", default="")
+ap.add_argument("--tag", default=""); ap.add_argument("--dual", action="store_true")
 a = ap.parse_args()
 kind, kw, _, _ = CONFIGS[a.config]
 dev = torch.device("cuda:0"); torch.manual_seed(42)
@@ -29,6 +29,20 @@ with torch.no_grad():
         from ipoke_inn_b200 import _capi
         _capi.lib().ipoke_inn_reverse(eng._plan, eng._packed.data_ptr(), zb.data_ptr(), c2.data_ptr() if c2 is not None else None,
                                       xb.data_ptr(), B, 0, eng.n_flows, eng._workspace(B).data_ptr(), eng._stream())
+    if a.dual:      # forward and reverse (independent inputs) on two streams
+        sf, sr = torch.cuda.Stream(), torch.cuda.Stream()
+        zin = torch.randn(B, C, device=dev)
+        import ctypes
+        from ipoke_inn_b200 import _capi
+        def step():
+            cur = torch.cuda.current_stream()
+            sf.wait_stream(cur); sr.wait_stream(cur)
+            with torch.cuda.stream(sf):
+                eng._forward_raw(x2, c2, zb, ld, None, None, 0, eng.n_flows)
+            with torch.cuda.stream(sr):
+                _capi.lib().ipoke_inn_reverse(eng._plan, eng._packed.data_ptr(), zin.data_ptr(), c2.data_ptr() if c2 is not None else None,
+                                              xb.data_ptr(), B, 0, eng.n_flows, eng._workspace(B).data_ptr(), eng._stream())
+            cur.wait_stream(sf); cur.wait_stream(sr)
     for _ in range(5): step()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
