@@ -59,6 +59,16 @@ def workload_config(cfg_name, B, world, precision):
             "streams": "the forward pass and the (independent) reverse pass of a step run concurrently on 2 CUDA streams"}
 
 
+def traffic_from_profiles(cfg_name, B, precision):
+    """dram read+write bytes per hidden-GEMM launch from the committed `ncu --set full` capture of this workload
+    (profiles/r01_traffic.json, written by tools/ncu_summary.py); None when that workload was not captured."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+        return d.get(f"{cfg_name}:{B}:{precision}:streams2", d.get(f"{cfg_name}:{B}:{precision}"))["hidden_gemm_dram_bytes_per_launch"]
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def macs_per_sample(kind, kw):
     C = kw["flow_in_channels"]
     d, n = kw["flow_hidden_depth"], kw["n_flows"]
@@ -329,13 +339,14 @@ def gpu_run(args):
             "peak": pk["bf16"] if tensor_bound else pk["hbm"],
             "unit": "TFLOP/s" if tensor_bound else "GB/s",
             "frac": (tf / pk["bf16"]) if tensor_bound else (gbs / pk["hbm"]),
-            "traffic": None,
+            "traffic": traffic_from_profiles(args.config, B, args.precision),
             "peak_source": pk["src"] + " (burst)",
             "launches_per_step": hidden_launches,
             "avg_launch_us": 1e6 * t_hidden / max(hidden_launches, 1),
             "avg_launch_us_isolated": 1e3 * tot[1] / max(cnt[1], 1),
             "share_of_step": share,
             "tflops_bf16_equiv": tf, "gbs": gbs,
+            "algorithmic_bytes_per_launch": hidden_bytes_per_step / max(hidden_launches, 1),
             "per_kind_ms_per_step": {"boundary": tot[0] / args.steps, "hidden": tot[1] / args.steps,
                                      "tail": tot[2] / args.steps},
             "note": "share_of_step from per-launch CUDA events in a separate pass right after the timed region (same "
