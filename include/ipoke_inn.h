@@ -100,6 +100,23 @@ int ipoke_inn_forward(ipoke_inn_plan* plan, const void* packed, const float* x, 
 int ipoke_inn_reverse(ipoke_inn_plan* plan, const void* packed, const float* z, const float* cond, float* x,
                       int B, int block_begin, int block_end, void* workspace, void* stream);
 
+/* Sampling loop: n_draws latents per conditioning row in ONE call.  Replaces the reference's per-draw loop
+ * `for n in range(n_samples): flow(randn, cond, reverse=True)` (models/second_stage_video_fc.py:356-378, which also
+ * re-encodes the same conditioning for every draw, :362) and the repeated-label sampling of
+ * SupervisedTransformer.sample (INN.py:59-63).
+ *   z, x : [n_draws * B, C], draw j of conditioning row b at row j * B + b;  cond : [B, E]
+ * The subnetworks of the 'cond' couplings (even blocks, flow_blocks.py:27, 200-240) read only the conditioning
+ * (:224, 237), so their hidden layers run once on the B conditioning rows and every draw's coupling tail reads
+ * them; the 'normal' couplings run on all n_draws * B rows.  Results are those of ipoke_inn_reverse on the
+ * row-repeated conditioning (same operands and MMAs; only the launch shapes picked for the row count differ).
+ * n_draws > 1 needs a conditional plan and B % 128 == 0 (IPOKE_INN_E_UNSUPPORTED otherwise; callers pad B).
+ * The workspace is one for batch n_draws * B (ipoke_inn_workspace_bytes(plan, n_draws * B, 0)).           */
+int ipoke_inn_reverse_draws(ipoke_inn_plan* plan, const void* packed, const float* z, const float* cond, float* x,
+                            int B, int n_draws, void* workspace, void* stream);
+/* Same sharing for the forward (z, logdet) pass: n_draws inputs per conditioning row. */
+int ipoke_inn_forward_draws(ipoke_inn_plan* plan, const void* packed, const float* x, const float* cond, float* z,
+                            float* logdet, int B, int n_draws, void* workspace, void* stream);
+
 /* ---- training: forward that keeps what the backward pass needs, and the fused backward -----------------
  * The reference has no backward code of its own: gradients are torch.autograd over the ops of
  * flow_blocks.py:125-143, 255-267, modules.py:190-191, 292-301.  These two calls replace

@@ -33,6 +33,14 @@ class SupervisedTransformer(nn.Module):
         z_tilde = torch.randn(shape).to(device)
         return self.reverse(z_tilde, label)
 
+    def sample_many(self, n_draws, label, generator=None):
+        """n_draws samples per conditioning row in one fused call: the batched form of calling
+        ``sample((B, C, 1, 1), label)`` n_draws times (reference INN.py:59-63 under the loop of
+        second_stage_video_fc.py:360-364).  -> [n_draws, B, C, 1, 1]"""
+        B = label.shape[0]
+        z_tilde = torch.randn(n_draws, B, self.in_channels, device=label.device, generator=generator)
+        return self.flow.reverse_draws(z_tilde, label, n_draws)
+
     def forward(self, input, conditioning, reverse=False, train=False):
         if reverse:
             return self.reverse(input, conditioning)

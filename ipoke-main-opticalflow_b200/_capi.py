@@ -18,7 +18,7 @@ SYMBOLS = [
     "ipoke_inn_last_launch_count", "ipoke_inn_debug_layout", "ipoke_inn_debug_trace",
     "ipoke_inn_profile_enable", "ipoke_inn_profile_read", "ipoke_inn_set_option",
     "ipoke_inn_saved_bytes", "ipoke_inn_forward_train", "ipoke_inn_backward", "ipoke_inn_profile_read_n",
-    "ipoke_inn_adam_chunk_elems", "ipoke_inn_adam_step",
+    "ipoke_inn_adam_chunk_elems", "ipoke_inn_adam_step", "ipoke_inn_reverse_draws", "ipoke_inn_forward_draws",
 ]
 
 
@@ -61,6 +61,10 @@ def lib():
     L.ipoke_inn_forward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, vp, vp]
     L.ipoke_inn_reverse.restype = i32
     L.ipoke_inn_reverse.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, vp, vp]
+    L.ipoke_inn_reverse_draws.restype = i32
+    L.ipoke_inn_reverse_draws.argtypes = [vp, vp, vp, vp, vp, i32, i32, vp, vp]
+    L.ipoke_inn_forward_draws.restype = i32
+    L.ipoke_inn_forward_draws.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, vp, vp]
     L.ipoke_inn_forward_host.restype = i32
     L.ipoke_inn_forward_host.argtypes = [vp, vp, vp, vp, vp, vp, i32, vp, vp]
     L.ipoke_inn_reverse_host.restype = i32

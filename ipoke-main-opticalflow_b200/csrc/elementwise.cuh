@@ -26,6 +26,7 @@ struct BoundaryParams {
   __nv_bfloat16* u_hi; __nv_bfloat16* u_lo; int ld_u;                // nullable
   int u_begin, u_count, u_pad;          // columns p in [u_begin, u_begin+u_count) -> U col p-u_begin; zero to u_pad
   const float* cond; int E; int ld_cond; int u_cond_off; int e_pad;  // cond nullable
+  int cond_rows;                        // > 0: cond has cond_rows rows and row b reads row b % cond_rows (multi-draw calls)
   __nv_bfloat16* u2_hi; __nv_bfloat16* u2_lo;                         // nullable: second buffer that gets the cond columns
   float* logdet; const float* an_logdet; int logdet_init;            // logdet nullable
   float* block_logdet;                                                // nullable snapshot before the add
@@ -90,7 +91,8 @@ __global__ void __launch_bounds__(256) inn_boundary_kernel(const BoundaryParams 
     for (long long idx = tid0; idx < tot; idx += stride) {
       const int b = static_cast<int>(idx / p.e_pad);
       const int e = static_cast<int>(idx - static_cast<long long>(b) * p.e_pad);
-      const float v = e < p.E ? __ldg(p.cond + static_cast<size_t>(b) * p.ld_cond + e) : 0.f;
+      const int cb = p.cond_rows > 0 ? b % p.cond_rows : b;
+      const float v = e < p.E ? __ldg(p.cond + static_cast<size_t>(cb) * p.ld_cond + e) : 0.f;
       __nv_bfloat16 h, l;
       split_bf16(v, h, l);
       const size_t o = static_cast<size_t>(b) * p.ld_u + p.u_cond_off + e;

@@ -96,6 +96,9 @@ struct GemmParams {
   const float* ld_extra;  // nullable: scalar added once per row (the next block's ActNorm log-det)
   int direct;                  // tail epilogue without the smem transposition (one-wave launches)
   int ks;                      // tail_cluster_kernel.cuh: K slices per subnetwork (cluster = 2 * ks CTAs per tile)
+  int a_m_wrap;                // > 0: A holds only a_m_wrap row tiles and m-tile t reads tile t % a_m_wrap -- the 'cond'
+                               // couplings of a multi-draw sampling call, whose subnetworks see only the conditioning
+                               // (flow_blocks.py:224, 237) and therefore run once per conditioning row, not per draw
   int dbg;                     // debug bit mask (IPOKE_INN_DBG), 0 in production
   unsigned long long* trace;   // nullable debug timeline (ipoke_inn_debug_trace): 16 slots for this launch
   // backward (EPI_DGRAD / EPI_DU): dX = dY * W with W read MN-major straight from the forward layout
@@ -238,6 +241,7 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
       const int m_tile = tile / p.num_n_tiles;
       const int n_tile = tile - m_tile * p.num_n_tiles;
       const int group = n_tile / p.tiles_per_group;
+      const int a_row0 = (p.a_m_wrap > 0 ? m_tile % p.a_m_wrap : m_tile) * BM;
       for (int ki = 0; ki < p.num_k_blocks; ++ki) {
         const int kb = p.k_rotate ? (ki + n_tile) % p.num_k_blocks : ki;
         {
@@ -256,9 +260,9 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
               const int t = sub * kSplit + sp;
               if (mc > 1)
                 tma_load_2d_mc_el(sbase + t * A_TILE_BYTES + cta_rank * a_rows * 128, sp == 0 ? &tmA0 : &tmA1,
-                               &full_bar[stage], a_k, m_tile * BM + cta_rank * a_rows, mc_mask);
+                               &full_bar[stage], a_k, a_row0 + cta_rank * a_rows, mc_mask);
               else
-                tma_load_2d_el(sbase + t * A_TILE_BYTES, sp == 0 ? &tmA0 : &tmA1, &full_bar[stage], a_k, m_tile * BM);
+                tma_load_2d_el(sbase + t * A_TILE_BYTES, sp == 0 ? &tmA0 : &tmA1, &full_bar[stage], a_k, a_row0);
               if (p.w_mn) {
                 // contraction index = W row: {64 rows} x {BN columns} as BN/64 MN-major chunks
                 const int w_c = (n_tile - group * p.tiles_per_group) * BN;

@@ -93,9 +93,10 @@ struct Op {
 struct ProgramKey {
   const void* packed; void* ws; int B, kb, ke, dir, want_blocks;
   const void* saved;
+  int Bc = 0;   // multi-draw calls: rows of the conditioning (B = draws * Bc); 0 = one draw per conditioning row
   bool operator==(const ProgramKey& o) const {
     return packed == o.packed && ws == o.ws && B == o.B && kb == o.kb && ke == o.ke && dir == o.dir &&
-           want_blocks == o.want_blocks && saved == o.saved;
+           want_blocks == o.want_blocks && saved == o.saved && Bc == o.Bc;
   }
 };
 struct GraphEntry {
@@ -356,6 +357,10 @@ struct Builder {
   char* ws;
   WsLayout wl;
   int B, m_tiles;
+  // multi-draw calls (B = draws * Bc rows share Bc conditioning rows): the subnetworks of 'cond' couplings read only the
+  // conditioning (flow_blocks.py:224, 237), so their hidden layers run on Bc rows and every draw's tail reads them
+  int Bc = 0;
+  int gemm_rows = 0, gemm_m_tiles = 0;     // rows / row tiles of the GEMM being built (B or Bc)
   int err = 0;
   // training forward / backward: activations live in the caller's `saved` buffer instead of the ping-pong scratch
   char* saved = nullptr;
@@ -432,8 +437,8 @@ struct Builder {
     return g;
   }
   void finish_gemm(GemmOp& g, const TileCfg& t) {
-    g.p.M = B;
-    g.p.num_m_tiles = m_tiles;
+    g.p.M = gemm_rows;
+    g.p.num_m_tiles = gemm_m_tiles;
     g.p.BN = t.bn;
     g.p.bn_log2 = 0;
     while ((1 << g.p.bn_log2) < t.bn) g.p.bn_log2++;
@@ -483,8 +488,12 @@ struct Builder {
   }
 
   // hidden layers of one chain; returns the ACT buffer index holding the last hidden activation
-  int chain(const Chain& c, int k, int ci, int ui) {
+  int chain(const Chain& c, int k, int ci, int ui, bool cond_only = false) {
     const int rows = c.G * P->Hp;
+    const int B = (cond_only && Bc > 0) ? Bc : this->B;
+    const int m_tiles = (B + BM - 1) / BM;
+    gemm_rows = B;
+    gemm_m_tiles = m_tiles;
     TileCfg tc = pick_bn(P, EPI_HIDDEN, P->Hp, m_tiles * c.G);
     if (P->hidden_bn_force > 0 && P->Hp % P->hidden_bn_force == 0) tc = tile_cfg(P->ksplit, EPI_HIDDEN, P->hidden_bn_force);
     const int bn = tc.bn;
@@ -522,7 +531,11 @@ struct Builder {
   void tail(const Block& blk, int k, int i, int ci, int act_layer, int G, int state_buf, bool reverse, bool write_u,
             bool last_in_block) {
     const Tail& t = blk.tails[i];
+    gemm_rows = B;
+    gemm_m_tiles = m_tiles;
+    const bool wrap = blk.mode == MODE_COND && Bc > 0 && Bc != B;   // the hidden activations hold Bc rows
     GemmOp& g = add_gemm(reverse ? EPI_TAIL_REV : EPI_TAIL_FWD);
+    g.p.a_m_wrap = wrap ? Bc / BM : 0;
     Op& op = prog->ops.back();
     // two accumulators (s, t) per stage: cap the tile at 128 columns so TMEM still double-buffers and the
     // (transcendental-heavy) epilogue of tile i overlaps the MMAs of tile i+1
@@ -606,7 +619,7 @@ struct Builder {
     }
     const long long ld_act = save ? (long long)G * P->Hp : P->ldACT;
     for (int sp = 0; sp < P->ksplit; ++sp) {
-      err |= make_map(P, &g.tmA[sp], act_base(k, ci, act_layer, sp), G * P->Hp, B, 2ll * ld_act, BM / tc.mc);
+      err |= make_map(P, &g.tmA[sp], act_base(k, ci, act_layer, sp), G * P->Hp, wrap ? Bc : B, 2ll * ld_act, BM / tc.mc);
       err |= make_map(P, &g.tmW[sp], packed + (sp == 0 ? t.w.hi : t.w.lo), t.w.Kp, t.w.rows, 2ll * t.w.Kp, bn);
       g.tmO[sp] = g.tmA[sp];      // unused by the tail epilogue
     }
@@ -634,7 +647,7 @@ struct Builder {
 
   void coupling(const Block& blk, int k, int state_buf, bool reverse) {
     if (blk.mode == MODE_COND) {
-      const int al = chain(blk.chains[0], k, 0, 0);
+      const int al = chain(blk.chains[0], k, 0, 0, true);
       tail(blk, k, reverse ? 1 : 0, 0, al, 4, state_buf, reverse, false, false);
       tail(blk, k, reverse ? 0 : 1, 0, al, 4, state_buf, reverse, false, true);
     } else {
@@ -693,6 +706,7 @@ struct Builder {
         b.ld_cond = d.E;
         b.u_cond_off = P->C2p;
         b.e_pad = P->Ep;
+        b.cond_rows = (Bc > 0 && Bc != B) ? Bc : 0;
       }
       b.logdet = w<float>(wl.logdet);
       b.an_logdet = pk<float>(blk.an_ld);
@@ -746,6 +760,7 @@ struct Builder {
         b.ld_cond = d.E;
         b.u_cond_off = P->C2p;
         b.e_pad = P->Ep;
+        b.cond_rows = (Bc > 0 && Bc != B) ? Bc : 0;
       }
       cur = nxt;
       coupling(blk, k, cur, true);
@@ -1054,6 +1069,9 @@ Program* get_program(ipoke_inn_plan* P, const ProgramKey& key, int* err) {
   bld.wl = ws_layout(P, key.B);
   bld.B = key.B;
   bld.m_tiles = (key.B + BM - 1) / BM;
+  bld.Bc = key.Bc;
+  bld.gemm_rows = key.B;
+  bld.gemm_m_tiles = bld.m_tiles;
   if (key.saved) {
     bld.saved = static_cast<char*>(const_cast<void*>(key.saved));
     bld.sl = saved_layout(P, key.B);
@@ -1669,6 +1687,45 @@ int ipoke_inn_reverse(ipoke_inn_plan* P, const void* packed, const float* z, con
   Program* prog = get_program(P, key, &rc);
   if (!prog) return rc;
   return run_program(P, prog, z, cond, x, nullptr, nullptr, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+// Multi-draw calls: draws * B rows, draw j of conditioning row b at row j * B + b.
+static int check_draws(const ipoke_inn_plan* P, int B, int n_draws) {
+  if (n_draws <= 0 || (long long)B * n_draws > 0x7fffffffll) return IPOKE_INN_E_INVALID;
+  if (n_draws > 1 && (!P->d.conditional || P->d.E <= 0 || B % BM != 0)) return IPOKE_INN_E_UNSUPPORTED;
+  return 0;
+}
+
+int ipoke_inn_reverse_draws(ipoke_inn_plan* P, const void* packed, const float* z, const float* cond, float* x, int B,
+                            int n_draws, void* workspace, void* stream) {
+  int rc = check_common(P, packed, z, x, B, 0, P ? P->d.n_flows : 0, cond, workspace);
+  if (rc) return rc;
+  if (x == z) return IPOKE_INN_E_INVALID;
+  rc = check_draws(P, B, n_draws);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> lock(P->mu);
+  rc = ensure_device(P);
+  if (rc) return rc;
+  ProgramKey key{packed, workspace, B * n_draws, 0, P->d.n_flows, 1, 0, nullptr, n_draws > 1 ? B : 0};
+  Program* prog = get_program(P, key, &rc);
+  if (!prog) return rc;
+  return run_program(P, prog, z, cond, x, nullptr, nullptr, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+int ipoke_inn_forward_draws(ipoke_inn_plan* P, const void* packed, const float* x, const float* cond, float* z,
+                            float* logdet, int B, int n_draws, void* workspace, void* stream) {
+  int rc = check_common(P, packed, x, z, B, 0, P ? P->d.n_flows : 0, cond, workspace);
+  if (rc) return rc;
+  if (!logdet || x == z) return IPOKE_INN_E_INVALID;
+  rc = check_draws(P, B, n_draws);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> lock(P->mu);
+  rc = ensure_device(P);
+  if (rc) return rc;
+  ProgramKey key{packed, workspace, B * n_draws, 0, P->d.n_flows, 0, 0, nullptr, n_draws > 1 ? B : 0};
+  Program* prog = get_program(P, key, &rc);
+  if (!prog) return rc;
+  return run_program(P, prog, x, cond, z, logdet, nullptr, nullptr, static_cast<cudaStream_t>(stream));
 }
 
 int ipoke_inn_forward_host(ipoke_inn_plan* P, const void* packed, const float* x_host, const float* cond_host,

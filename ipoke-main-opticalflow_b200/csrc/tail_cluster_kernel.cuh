@@ -126,7 +126,7 @@ inn_tail_cluster_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_c
 #pragma unroll
       for (int sp = 0; sp < kSplit; ++sp) {
         tma_load_2d_el(sbase + sp * A_TILE_BYTES, sp == 0 ? &tmA0 : &tmA1, &full_bar[stage],
-                       p.a_off[net] + (kb0 + ki) * BK, m_tile * BM);
+                       p.a_off[net] + (kb0 + ki) * BK, (p.a_m_wrap > 0 ? m_tile % p.a_m_wrap : m_tile) * BM);
         if (!w_done)
           tma_load_2d_el(sbase + kSplit * A_TILE_BYTES + sp * TC_W_TILE_BYTES, sp == 0 ? &tmW0 : &tmW1,
                          &full_bar[stage], (kb0 + ki) * BK, w_row);

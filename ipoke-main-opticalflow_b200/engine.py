@@ -246,6 +246,63 @@ class FlowEngine:
         self.launches = L.ipoke_inn_last_launch_count(self._plan)
         return x
 
+    # ------------------------------------------------------------------ sampling loop: several draws per conditioning row
+    DRAW_ROW_TILE = 128        # ipoke_inn_*_draws needs the conditioning rows in multiples of one GEMM row tile
+
+    def _prep_draws(self, x, cond, n_draws):
+        """x: [n_draws, B, C] (any trailing singleton dims), cond: [B, E(,1,1)] -> padded 2-D views.
+        B is padded to a multiple of 128 rows (zero latents / zero conditioning; the pad rows are dropped)."""
+        if self.E <= 0:
+            raise RuntimeError("multi-draw calls need a conditional flow")
+        n_draws = int(n_draws)
+        if x.dtype != torch.float32 or cond.dtype != torch.float32 or cond.device != x.device:
+            raise TypeError("ipoke_inn_b200 computes in fp32 I/O on one device")
+        if x.shape[0] != n_draws:
+            raise RuntimeError(f"expected {n_draws} draws along dim 0, got {tuple(x.shape)}")
+        B = cond.shape[0]
+        c2 = cond.reshape(B, -1)
+        x3 = x.reshape(n_draws, -1, self.C)
+        if c2.shape[1] != self.E or x3.shape[1] != B:
+            raise RuntimeError(f"expected draws [{n_draws},{B},{self.C}] and conditioning [{B},{self.E}], got "
+                               f"{tuple(x.shape)} and {tuple(cond.shape)}")
+        T = self.DRAW_ROW_TILE
+        Bp = B if n_draws == 1 else (B + T - 1) // T * T
+        if Bp != B:
+            xp = x3.new_zeros(n_draws, Bp, self.C)
+            xp[:, :B] = x3
+            cp = c2.new_zeros(Bp, self.E)
+            cp[:B] = c2
+            x3, c2 = xp, cp
+        return n_draws, B, Bp, x3.contiguous(), c2.contiguous()
+
+    def reverse_draws(self, z, cond, n_draws):
+        """n_draws latents per conditioning row in one call: z [n_draws, B, C], cond [B, E] -> x [n_draws, B, C].
+        The cond-only subnetworks of the 'cond' couplings run once per conditioning row (include/ipoke_inn.h)."""
+        n, B, Bp, z3, c2 = self._prep_draws(z, cond, n_draws)
+        L = self._ensure(z3.device)
+        self.pack()
+        x = torch.empty(n, Bp, self.C, dtype=torch.float32, device=self._device)
+        ws = self._workspace(n * Bp)
+        _capi.check(L.ipoke_inn_reverse_draws(self._plan, self._packed.data_ptr(), z3.data_ptr(), c2.data_ptr(),
+                                              x.data_ptr(), Bp, n, ws.data_ptr(), self._stream()), "reverse_draws")
+        self.launches = L.ipoke_inn_last_launch_count(self._plan)
+        return x[:, :B]
+
+    def forward_draws(self, x, cond, n_draws):
+        """-> z [n_draws, B, C], logdet [n_draws, B] for n_draws inputs per conditioning row."""
+        n, B, Bp, x3, c2 = self._prep_draws(x, cond, n_draws)
+        L = self._ensure(x3.device)
+        self._maybe_actnorm_init(x3.reshape(n * Bp, self.C)[:B], c2[:B])
+        self.pack()
+        z = torch.empty(n, Bp, self.C, dtype=torch.float32, device=self._device)
+        ld = torch.empty(n, Bp, dtype=torch.float32, device=self._device)
+        ws = self._workspace(n * Bp)
+        _capi.check(L.ipoke_inn_forward_draws(self._plan, self._packed.data_ptr(), x3.data_ptr(), c2.data_ptr(),
+                                              z.data_ptr(), ld.data_ptr(), Bp, n, ws.data_ptr(), self._stream()),
+                    "forward_draws")
+        self.launches = L.ipoke_inn_last_launch_count(self._plan)
+        return z[:, :B], ld[:, :B]
+
     # ------------------------------------------------------------------ training (forward with saved state, backward)
     def forward_train(self, x, cond):
         """Forward that keeps what the fused backward needs.  -> z, logdet, block_outs [n,B,C], block_logdets [n,B], saved"""

@@ -217,6 +217,28 @@ class ConditionalFlow(_FusedFlowMixin, nn.Module):
     def reverse(self, out, xcond):
         return self(out, xcond, reverse=True)
 
+    def reverse_draws(self, out, xcond, n_draws=None):
+        """Sampling loop in one call: ``out`` [n_draws, B, C(,1,1)] latents for ``xcond`` [B, E, 1, 1] ->
+        [n_draws, B, C, 1, 1], equal to ``stack([self(out[j], xcond, reverse=True) for j in range(n_draws)])``
+        (the loop of the reference's forward_sample, second_stage_video_fc.py:356-378).  The cond-only
+        subnetworks of the 'cond' blocks (reference :200-240) are evaluated once per conditioning row.
+        Inference only (no autograd graph)."""
+        assert len(xcond.shape) == 4                                # reference flow_blocks.py:127
+        n_draws = out.shape[0] if n_draws is None else n_draws
+        self._reset_last()
+        with torch.no_grad():
+            x = self._engine.reverse_draws(out, xcond, n_draws)
+        return x.unsqueeze(-1).unsqueeze(-1)
+
+    def forward_draws(self, x, xcond, n_draws=None):
+        """-> (z [n_draws, B, C, 1, 1], logdet [n_draws, B]) for n_draws inputs per conditioning row (no autograd)."""
+        assert len(xcond.shape) == 4
+        n_draws = x.shape[0] if n_draws is None else n_draws
+        self._reset_last()
+        with torch.no_grad():
+            z, ld = self._engine.forward_draws(x, xcond, n_draws)
+        return z.unsqueeze(-1).unsqueeze(-1), ld
+
 
 class UnconditionalFlow2(_FusedFlowMixin, nn.Module):
     """Flat unconditional flow.  Reference flow_blocks.py:432-465."""

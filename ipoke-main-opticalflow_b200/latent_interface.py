@@ -1,0 +1,92 @@
+"""Latent interface either side of the INN: what the reference's LightningModules do
+between their frozen encoders / decoders and ``flow(x, cond, reverse=...)``.
+
+Mirrors, with the same argument meaning, RNG consumption order and tensor shapes,
+  * ``PokeMotionModelFC.make_flow_input / forward_sample / forward_density``
+    (models/second_stage_video_fc.py:273-345, 356-378, 380-387) -> :class:`SecondStageLatentInterface`
+  * ``FCAEINNModel.forward_sample / forward_density`` (experiments/fully_connected_ae_INN.py:104-127)
+    -> :class:`FlowAELatentInterface`
+
+The encoders / decoders themselves (CNN poke and image encoders, GRU video decoder, BigAE) are outside the hot path
+(SURVEY.md section 8f, N2): they are passed in as callables.  What changes against the reference is the sampling loop:
+the reference re-encodes the same image + poke and calls the flow once per draw; here the conditioning is encoded once
+and all ``n_samples`` draws go through ONE ``flow.reverse_draws`` call, in which the cond-only subnetworks of the 'cond'
+couplings run once per conditioning row (include/ipoke_inn.h, ipoke_inn_reverse_draws).  The latents are drawn exactly
+as the reference draws them (one ``torch.randn(shape)`` on the CPU default generator per draw, in draw order), so with
+deterministic encoders the samples are those of the reference's loop under the same seed.
+"""
+import torch
+
+
+def _squeeze_latent(t):
+    """flow returns 4-D, the fully connected first stage wants 2-D (second_stage_video_fc.py:366-368)."""
+    return t.squeeze(-1).squeeze(-1) if t.dim() == 4 else t
+
+
+class SecondStageLatentInterface:
+    """Host logic of PokeMotionModelFC around its flow (models/second_stage_video_fc.py:273-387).
+
+    flow                  SupervisedTransformer (``flow.flow.reshape`` is read as in :309)
+    poke_encoder(poke)    -> poke embedding (``self.poke_embedder.encoder``, :293)
+    cond_encoder(X0)      -> image embedding or None (``self.conditioner.encoder``, :300-304); with
+                             ``cond_deterministic=False`` it returns a tuple whose 2nd entry is used (:304)
+    encode_first_stage(X) -> (motion, mu)  (:389-396)        decode_first_stage(motion, X) -> video (:398-443)
+    """
+
+    def __init__(self, flow, poke_encoder, cond_encoder=None, encode_first_stage=None, decode_first_stage=None, *,
+                 flow_in_channels, min_spatial_size=1, poke_key="poke", embed_poke_and_image=False,
+                 cond_deterministic=True, base_distribution="normal", augment_channels=0, scale_augment=None,
+                 shift_augment=None):
+        self.flow = flow
+        self.poke_encoder = poke_encoder
+        self.cond_encoder = cond_encoder
+        self.use_cond = cond_encoder is not None
+        self.encode_first_stage = encode_first_stage
+        self.decode_first_stage = decode_first_stage
+        self.flow_in_channels = flow_in_channels
+        self.min_spatial_size = min_spatial_size
+        self.poke_key = poke_key
+        self.embed_poke_and_image = embed_poke_and_image
+        self.cond_deterministic = cond_deterministic
+        self.base_distribution = base_distribution
+        self.augment_input = augment_channels > 0
+        self.augment_channels = augment_channels
+        self.scale_augment = scale_augment
+        self.shift_augment = shift_augment
+
+    # ------------------------------------------------------------------ pieces of make_flow_input
+    def encode_condition(self, batch):
+        """(image, poke) -> cond [B, E, 1, 1]: second_stage_video_fc.py:274-306 and :338-343."""
+        X = batch["images"]
+        poke = batch[self.poke_key]
+        poke = poke[0] if isinstance(poke, list) else poke                       # :281
+        if self.embed_poke_and_image:
+            poke = torch.cat([poke, X[:, 0]], dim=1)                             # :284
+        with torch.no_grad():
+            poke_emb = self.poke_encoder(poke)                                   # :293
+            if self.use_cond:
+                cond = self.cond_encoder(X[:, 0])                                # :301
+                if not self.cond_deterministic:
+                    _, cond, _ = cond                                            # :304
+        cond = torch.cat([cond, poke_emb], dim=1) if self.use_cond else poke_emb  # :338-341
+        if cond.dim() != 4:
+            cond = cond.unsqueeze(-1).unsqueeze(-1)                              # :342-343
+        return cond
+
+    def latent_shape(self, batch_size):
+        if self.flow.flow.reshape != "none":                                     # :309-314
+            down = self.flow.flow.reshape == "down"
+            cn, sp = (4, 2) if down else (1 / 4, .5)
+            return [batch_size, int(cn * self.flow_in_channels), int(self.min_spatial_size / sp),
+                    int(self.min_spatial_size / sp)]
+        return (batch_size, self.flow_in_channels, self.min_spatial_size, self.min_spatial_size)   # :320-321
+
+    def draw_latent(self, X):
+        """One reverse-pass input, drawn as the reference draws it (:316, :322, :325-328)."""
+        shape = self.latent_shape(X.size(0))
+        flow_input = torch.randn(shape).type_as(X).detach()
+        if self.base_distribution == "radial":
+            flow_input = torch.nn.functional.normalize(flow_input.view(shape[0], -1))
+            flow_input = flow_input.T * torch.abs(torch.randn(shape[0]).type_as(X))
+            flow_input = flow_input.T.view(shape).detach()
+        return flow_input
