@@ -12,12 +12,14 @@ from .flow_blocks import (ConditionalFlow, UnconditionalFlow2, ConditionalFlatDo
                           UnconditionalFlatDoubleCouplingFlowBlock2, ConditionalDoubleVectorCouplingBlock,
                           ConditionalDoubleVectorCouplingBlock_cond, DoubleVectorCouplingBlock2)
 from .loss import FlowLoss
+from .latent_interface import SecondStageLatentInterface, FlowAELatentInterface
 from .optim import FusedAdam, linear_var
 from .modules import ActNorm, BasicFullyConnectedNet, IgnoreLeakyRelu, InvLeakyRelu, Shuffle
 
 __all__ = ["SupervisedTransformer", "UnsupervisedTransformer3", "ConditionalFlow", "UnconditionalFlow2",
            "FlowLoss", "ActNorm", "BasicFullyConnectedNet", "Shuffle", "InvLeakyRelu", "IgnoreLeakyRelu",
-           "FusedAdam", "linear_var", "install_as_reference"]
+           "FusedAdam", "linear_var", "install_as_reference", "SecondStageLatentInterface",
+           "FlowAELatentInterface"]
 
 
 def install_as_reference():

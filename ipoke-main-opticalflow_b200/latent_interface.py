@@ -18,11 +18,6 @@ deterministic encoders the samples are those of the reference's loop under the s
 import torch
 
 
-def _squeeze_latent(t):
-    """flow returns 4-D, the fully connected first stage wants 2-D (second_stage_video_fc.py:366-368)."""
-    return t.squeeze(-1).squeeze(-1) if t.dim() == 4 else t
-
-
 class SecondStageLatentInterface:
     """Host logic of PokeMotionModelFC around its flow (models/second_stage_video_fc.py:273-387).
 
@@ -90,3 +85,86 @@ class SecondStageLatentInterface:
             flow_input = flow_input.T * torch.abs(torch.randn(shape[0]).type_as(X))
             flow_input = flow_input.T.view(shape).detach()
         return flow_input
+
+    # ------------------------------------------------------------------ the reference's three entry points
+    def make_flow_input(self, batch, reverse=False):
+        """-> (flow_input, cond), second_stage_video_fc.py:273-345.  reverse=True: a fresh N(0, I) (or radial) latent;
+        reverse=False: the first-stage motion encoding (+ learnable-affine noise channels when augment_input, :332-336)."""
+        X = batch["images"]
+        cond = self.encode_condition(batch)
+        if reverse:
+            flow_input = self.draw_latent(X)
+        else:
+            with torch.no_grad():
+                flow_input, *_ = self.encode_first_stage(X)                      # :330-331
+            if self.augment_input:
+                aug = torch.randn((flow_input.size(0), self.augment_channels, *flow_input.shape[-2:])).type_as(X)
+                aug = self.scale_augment[None, :, None, None] * aug + self.shift_augment[None, :, None, None]
+                flow_input = torch.cat([flow_input, aug], dim=1)                 # :334-336
+        return flow_input, cond
+
+    def forward_density(self, batch, return_cond=False):
+        """-> out, logdet [, cond]  (second_stage_video_fc.py:380-387)."""
+        flow_input, cond = self.make_flow_input(batch)
+        out, logdet = self.flow(flow_input.detach(), cond, reverse=False)
+        if return_cond:
+            return out, logdet, cond
+        return out, logdet
+
+    def sample_latents(self, batch, n_samples=1):
+        """The INN part of forward_sample for all draws at once -> motion [n_samples, B, C'] (squeezed, augment
+        channels dropped: :366-371).  cond is encoded once; latents are drawn per draw in the reference's order."""
+        X = batch["images"]
+        with torch.no_grad():
+            cond = self.encode_condition(batch)
+            z = torch.stack([self.draw_latent(X) for _ in range(n_samples)])     # [n, B, C, s, s]
+            if self.flow.flow.reshape != "none" or self.min_spatial_size != 1:
+                raise NotImplementedError("the fused path covers the fully connected latent ([B, C, 1, 1]); spatial "
+                                          "latents belong to the MaCow conv flow (SURVEY.md section 8f, N3)")
+            out = self.flow.flow.reverse_draws(z, cond, n_samples)               # [n, B, C, 1, 1]
+            out = out.squeeze(-1).squeeze(-1)
+            if self.augment_input:
+                out = out[..., :-self.augment_channels]
+        return out
+
+    def forward_sample(self, batch, n_samples=1, n_logged_vids=1, add_first_frame=False):
+        """-> list of n_samples decoded videos (first n_logged_vids of the batch, on the CPU), as
+        second_stage_video_fc.py:356-378."""
+        X = batch["images"]
+        motion = self.sample_latents(batch, n_samples)
+        video_samples = []
+        with torch.no_grad():
+            for n in range(n_samples):
+                out_video = self.decode_first_stage(motion[n], X)                # :372
+                if add_first_frame:
+                    out_video = torch.cat([X[:, 0].unsqueeze(1), out_video], dim=1)   # :373-374
+                video_samples.append(out_video[:n_logged_vids].cpu())            # :376
+        return video_samples
+
+
+class FlowAELatentInterface:
+    """Host logic of FCAEINNModel around its INN (experiments/fully_connected_ae_INN.py:104-127): ``ae`` is the frozen
+    flow autoencoder (``encode(x)`` returns a distribution with ``.sample()`` / ``.mode()``, ``decode(z)`` an image)."""
+
+    def __init__(self, INN, ae):
+        self.INN = INN
+        self.ae = ae
+
+    def forward_density(self, batch):
+        X = batch["flow"]
+        with torch.no_grad():
+            encv = self.ae.encode(X).sample()                                    # :119-120
+        return self.INN(encv, reverse=False)                                     # :125
+
+    def forward_sample(self, batch, n_samples=1, n_logged_imgs=1):
+        """The reference encodes the batch once per draw only to get the latent's shape (:108-110); here once."""
+        image_samples = []
+        with torch.no_grad():
+            like = self.ae.encode(batch["flow"]).mode()
+            z = torch.stack([torch.randn_like(like) for _ in range(n_samples)])  # :110, draw order kept
+            B = like.shape[0]
+            out = self.INN(z.reshape(n_samples * B, *like.shape[1:]), reverse=True)   # unconditional: rows independent
+            out = out.reshape(n_samples, B, *out.shape[1:])
+            for n in range(n_samples):
+                image_samples.append(self.ae.decode(out[n])[:n_logged_imgs])     # :112-113
+        return image_samples
