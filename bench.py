@@ -418,6 +418,49 @@ def gpu_run(args):
             except Exception as e:      # the sweep is informational; never lose the headline line
                 sweep.append({"config": cname, "batch": cb, "precision": prec, "error": str(e)[:200]})
         out["sweep"] = sweep
+        # ---- second-stage sampling loop (second_stage_video_fc.py:356-378): n draws per conditioning row, informational
+        loops = []
+        for cb, nd in [(4096, 5), (20, 5)]:         # 20 x 5 is the reference's test setting (second_stage.yaml:78-79)
+            try:
+                k2, kw2, _, _ = CONFIGS["cfgA"]
+                torch.manual_seed(42)
+                n2 = P.SupervisedTransformer(dict(kw2), precision="bf16").to(dev).eval()
+                C2, E2 = kw2["flow_in_channels"], kw2["flow_embedding_channels"]
+                cs = torch.randn(cb, E2, 1, 1, device=dev, generator=g)
+                zs = torch.randn(nd, cb, C2, device=dev, generator=g)
+                with torch.no_grad():
+                    n2(zs[0], cs)                                  # ActNorm data init
+                    n2.flow.engine.assume_frozen = True
+                    cs_rep, zs_flat = cs.repeat(nd, 1, 1, 1), zs.reshape(nd * cb, C2)
+                    variants = {"per_draw_loop": lambda: [n2(zs[j], cs, reverse=True) for j in range(nd)],
+                                "one_call_repeated_cond": lambda: n2(zs_flat, cs_rep, reverse=True),
+                                "reverse_draws": lambda: n2.flow.reverse_draws(zs, cs)}
+                    res = {}
+                    for vname, fn in variants.items():
+                        for _ in range(3):
+                            fn()
+                        torch.cuda.synchronize()
+                        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        reps = 10
+                        e0.record()
+                        for _ in range(reps):
+                            fn()
+                        e1.record()
+                        torch.cuda.synchronize()
+                        res[vname] = e0.elapsed_time(e1) / reps
+                pw2 = macs_per_sample(k2, kw2)
+                t = res["reverse_draws"] * 1e-3
+                loops.append({"config": "cfgA", "cond_rows": cb, "draws": nd, "precision": "bf16", "ms": res,
+                              "samples_per_s": nd * cb / t, "tflops_algorithmic": nd * cb * 2 * pw2 / t / 1e12,
+                              "speedup_vs_per_draw_loop": res["per_draw_loop"] / res["reverse_draws"],
+                              "what": "reverse sampling of `draws` latents per conditioning row; reverse_draws runs the "
+                                      "cond-only subnetworks of the 'cond' couplings once per conditioning row "
+                                      "(algorithmic FLOPs counted as the reference's 2*P_w per draw)"})
+                del n2, cs, zs
+                torch.cuda.empty_cache()
+            except Exception as e:  # noqa: BLE001
+                loops.append({"config": "cfgA", "cond_rows": cb, "draws": nd, "error": str(e)[:200]})
+        out["sampling_loop"] = loops
         # ---- training step (forward with saved state + FlowLoss + fused backward), informational
         train = []
         for cname, cb, prec in [("cfgB", 256, "bf16"), ("cfgA", 64, "bf16"), ("cfgA", 4096, "bf16"), ("cfgA", 4096, "fp32")]:
