@@ -31,7 +31,108 @@
         mbar_wait(&tfull_bar[acc], acc_phase, 4);
         tc_fence_after();
         if (tr != nullptr && tid_e == 0) tr[5] = globaltimer_ns();
-        if (p.slab_bufs > 0) {
+        if (p.slab_warp) {
+          // ---- warp-private slabs: every epilogue warp owns the 32 rows of its TMEM lane quarter: TMEM -> regs -> its own
+          // swizzled smem buffer -> one TMA store per warp.  No CTA-wide barrier inside the tile: the warps drift apart
+          // and overlap each other's TMEM-load and store-drain latencies (ncu, r01 v6: the CTA-wide version with one
+          // slab buffer serialises drain -> barrier -> load -> math -> barrier -> store, 1.3 us per slab).
+          //   slab_warp 1 (slab_bufs >= 2): 32 x 128 B buffers, 64-column boxes, warps 4-7 take the even slabs, 8-11 the odd
+          //   slab_warp 2 (slab_bufs == 1): 32 x  64 B buffers, 32-column boxes (64-B swizzle), warp `ch` takes its half
+          const int we = warp - 4;
+          const bool wide = p.slab_warp == 1;
+          const int nbw = wide ? (p.slab_bufs >> 1) : 1;         // buffers per warp
+          const int wbytes = wide ? 4096 : 2048;
+          const int n_slabs = BN >> 6;
+          bool arrived = false;
+          for (int s = wide ? ch : 0; s < n_slabs; s += wide ? 2 : 1, ++slab_ctr) {
+            uint8_t* wb_hi = epi_smem + ((we * nbw + (slab_ctr & (nbw - 1))) * kSplit) * wbytes + lane * (wide ? 128 : 64);
+            uint8_t* wb_lo = wb_hi + wbytes;
+            for (int h = 0; h < (wide ? 2 : 1); ++h) {
+              const int c_in = wide ? h * 32 : ch * 32;          // first column of this half inside the slab
+              float v[32];
+#pragma unroll
+              for (int c = 0; c < 2; ++c) tmem_ld16(t_row + s * 64 + c_in + c * 16, v + c * 16);
+              tmem_ld_wait();
+              for (int a = 1; a < kacc; ++a) {
+                float w[32];
+#pragma unroll
+                for (int c = 0; c < 2; ++c) tmem_ld16(t_row + a * BN + s * 64 + c_in + c * 16, w + c * 16);
+                tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < 32; ++c) v[c] += w[c];
+              }
+              if (wide ? (h == 1 && s + 2 >= n_slabs) : (s + 1 >= n_slabs)) {   // this warp has read its part of the accumulator
+                tc_fence_before();
+                mbar_arrive(&tempty_bar[acc]);
+                arrived = true;
+              }
+              if (h == 0) {                                      // the store that last read this buffer has drained
+                if (lane == 0) {
+                  if (nbw == 2) bulk_wait_read<1>();
+                  else bulk_wait_read<0>();
+                }
+                __syncwarp();
+              }
+              const float* bs = bias_s + s * 64 + c_in;
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                uint32_t hi[4], lo[4];
+                if (kMode == EPI_HIDDEN) {
+                  const float4 b0 = *reinterpret_cast<const float4*>(bs + j * 8);
+                  const float4 b1 = *reinterpret_cast<const float4*>(bs + j * 8 + 4);
+                  const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) {
+                    float a = v[j * 8 + 2 * e] + bb[2 * e];
+                    float b = v[j * 8 + 2 * e + 1] + bb[2 * e + 1];
+                    a = fmaxf(a, a * p.slope);                   // LeakyReLU for 0 <= slope <= 1 (checked at plan creation)
+                    b = fmaxf(b, b * p.slope);
+                    if (kSplit == 1) {
+                      hi[e] = cvt_bf16x2(a, b);
+                    } else {
+                      __nv_bfloat16 h0, l0, h1, l1;
+                      split_bf16(a, h0, l0);
+                      split_bf16(b, h1, l1);
+                      hi[e] = pack_bf16x2(h0, h1);
+                      lo[e] = pack_bf16x2(l0, l1);
+                    }
+                  }
+                } else {
+                  uint4 mk = make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u);
+                  if (mask_row != nullptr) mk = __ldg(reinterpret_cast<const uint4*>(mask_row + s * 64 + c_in) + j);
+                  const uint32_t mw[4] = {mk.x, mk.y, mk.z, mk.w};
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) {
+                    const float a = v[j * 8 + 2 * e] * (bf16_bits_positive(mw[e] & 0xFFFFu) ? 1.f : p.slope);
+                    const float b = v[j * 8 + 2 * e + 1] * (bf16_bits_positive(mw[e] >> 16) ? 1.f : p.slope);
+                    __nv_bfloat16 h0, l0, h1, l1;
+                    split_bf16(a, h0, l0);
+                    split_bf16(b, h1, l1);
+                    hi[e] = pack_bf16x2(h0, h1);
+                    lo[e] = pack_bf16x2(l0, l1);
+                  }
+                }
+                // 128-B swizzle: 16-B chunk index XOR (row % 8); 64-B swizzle: XOR ((row / 2) % 4)
+                const int chunk = (wide ? ((h * 4 + j) ^ (lane & 7)) : (j ^ ((lane >> 1) & 3))) << 4;
+                *reinterpret_cast<uint4*>(wb_hi + chunk) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                if (kSplit == 2) *reinterpret_cast<uint4*>(wb_lo + chunk) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+              }
+            }
+            fence_proxy_async();                                 // generic-proxy smem writes -> visible to TMA
+            __syncwarp();
+            if (lane == 0) {
+              const int col = ocol0 + s * 64 + (wide ? 0 : ch * 32);
+              const int loff = lane * (wide ? 128 : 64);
+              tma_store_2d(&tmO0, wb_hi - loff, col, m_tile * BM + q * 32);
+              if (kSplit == 2) tma_store_2d(&tmO1, wb_lo - loff, col, m_tile * BM + q * 32);
+              bulk_commit();
+            }
+          }
+          if (!arrived) {                                        // BN = 64: the odd-slab warps read nothing
+            tc_fence_before();
+            mbar_arrive(&tempty_bar[acc]);
+          }
+        } else if (p.slab_bufs > 0) {
           // ---- 64-column slabs: TMEM -> regs -> swizzled smem -> TMA store
           const int n_slabs = BN >> 6;
           for (int s = 0; s < n_slabs; ++s, ++slab_ctr) {
@@ -586,5 +687,5 @@
         named_bar_sync(1, EPI_THREADS);                           // keep_s is reused by the next tile
       }
     }
-    if (kSlabMode && p.slab_bufs > 0 && tid_e == 0) bulk_wait<0>();   // stores landed before exit
+    if (kSlabMode && p.slab_bufs > 0 && (p.slab_warp ? lane == 0 : tid_e == 0)) bulk_wait<0>();   // stores landed before exit
     if (tr != nullptr && tid_e == 0) tr[6] = globaltimer_ns();

@@ -54,6 +54,8 @@ struct GemmParams {
                           //    block then read different L2 lines at any moment (one-wave launches hot-spot otherwise)
   int mcast;              // cluster size along n (1, 2, 4, 8): A tiles are TMA-multicast to the CTAs sharing an m-tile
   int slab_bufs;          // EPI_HIDDEN: 0 = direct global stores, 1 / 2 / 4 = TMA-store slab buffers per (hi|lo)
+  int slab_warp;          // warp-private output slabs, no CTA barrier inside a tile: 1 = tmO box 64 x 32 (128-B swizzle,
+                          // slab_bufs >= 2), 2 = tmO box 32 x 32 (64-B swizzle, slab_bufs == 1)
   int tiles_per_group;    // n-tiles per subnetwork group (hidden layers); >= num_n_tiles otherwise
   int a_group_stride;     // A column offset (elements) per group
   int a_off[2];           // A column offset per accumulator

@@ -160,6 +160,7 @@ struct ipoke_inn_plan {
   int streams = 1;                // calls the caller runs concurrently on different streams: one-wave launches are
                                   // sized for num_sms / streams SMs so that the concurrent kernels are co-resident
   int slab4 = 0;                  // 4 output slabs in flight where the pipeline leaves smem free
+  int warp_slab = 1;              // hidden / dgrad epilogue: warp-private output slabs (no CTA barrier inside a tile)
   int tail_cluster = 1;           // small batches: coupling tails as split-K clusters (tail_cluster_kernel.cuh)
   int dbg = 0;
   int kacc_max = 1;               // K-interleaved accumulators: measured no gain once the MMA issue is uniform
@@ -290,15 +291,21 @@ int ensure_device(ipoke_inn_plan* P) {
 }
 
 int make_map(const ipoke_inn_plan* P, CUtensorMap* m, const void* base, long long inner, long long outer,
-             long long row_stride_bytes, int box_outer) {
+             long long row_stride_bytes, int box_outer, int box_inner = BK) {
   cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
   cuuint64_t strides[1] = {(cuuint64_t)row_stride_bytes};
-  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_outer};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
   cuuint32_t estr[2] = {1, 1};
+  // 64 bf16 per box row = one 128-B swizzle row; 32 per row (warp-private half slabs) = 64-B swizzle
   CUresult r = P->encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, box_inner == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? 0 : IPOKE_INN_E_INTERNAL;
+}
+// slab_warp mode of a hidden / dgrad GEMM with `slab_bufs` slab buffers (0 = CTA-wide slabs)
+inline int slab_warp_mode(const ipoke_inn_plan* P, int slab_bufs) {
+  if (!P->warp_slab || slab_bufs < 1) return 0;
+  return slab_bufs >= 2 ? 1 : 2;
 }
 
 struct TileCfg { int bn = 0, stages = 0, slab_bufs = 0, mc = 1, direct = 0; };
@@ -453,6 +460,7 @@ struct Builder {
         if (gemm_smem_bytes(P->ksplit, g.mode, t.bn, st, 4) <= kMaxDynSmem) { g.p.stages = st; slab_bufs = 4; break; }
     }
     g.p.slab_bufs = slab_bufs;
+    g.p.slab_warp = (g.mode == EPI_HIDDEN || g.mode == EPI_DGRAD) ? slab_warp_mode(P, slab_bufs) : 0;
     g.p.mcast = t.mc;
     g.p.w_prefetch = P->w_prefetch;
     g.p.k_rotate = (P->k_rotate && g.p.num_m_tiles * g.p.num_n_tiles <= 2 * P->num_sms && !g.p.w_mn) ? 1 : 0;
@@ -520,7 +528,10 @@ struct Builder {
         }
         err |= make_map(P, &g.tmW[sp], packed + (sp == 0 ? L.hi : L.lo), L.Kp, L.rows, 2ll * L.Kp, bn);
         // output slabs (TMA store): same 64 x 128 box as the next layer's A loads
-        err |= make_map(P, &g.tmO[sp], act_base(k, ci, (int)l, sp), rows, B, 2ll * ld_act, BM);
+        {                                                  // warp-private slabs: 64 x 32 or 32 x 32 boxes
+          const int swm = slab_warp_mode(P, tc.slab_bufs);
+          err |= make_map(P, &g.tmO[sp], act_base(k, ci, (int)l, sp), rows, B, 2ll * ld_act, swm ? 32 : BM, swm == 2 ? 32 : BK);
+        }
       }
       finish_gemm(g, tc);
     }
@@ -863,7 +874,8 @@ struct BwdBuilder : Builder {
     g.p.ld_mask = (int)ld_mask;
     g.p.mask_col0 = 0;
     for (int sp = 0; sp < P->ksplit; ++sp)
-      err |= make_map(P, &g.tmO[sp], d_base(d_idx, sp), out_cols, B, 2ll * P->ldACT, BM);
+      err |= make_map(P, &g.tmO[sp], d_base(d_idx, sp), out_cols, B, 2ll * P->ldACT, g.p.slab_warp ? 32 : BM,
+                      g.p.slab_warp == 2 ? 32 : BK);
   }
 
   // dW_g = dY_g^T X_g, db_g = colsum(dY_g) for the `groups` nets of one layer
@@ -1441,7 +1453,7 @@ const char* ipoke_inn_last_error_string(int code) {
   switch (code) {
     case IPOKE_INN_OK: return "ok";
     case IPOKE_INN_E_INVALID: return "ipoke_inn: invalid argument";
-    case IPOKE_INN_E_UNSUPPORTED: return "ipoke_inn: unsupported shape (C must be even and >= 2; H, depth, n_flows >= 1; E == 0 iff unconditional)";
+    case IPOKE_INN_E_UNSUPPORTED: return "ipoke_inn: unsupported shape (C must be even and >= 2; H, depth, n_flows >= 1; E == 0 iff unconditional; 0 <= mlp_slope <= 1)";
     case IPOKE_INN_E_NO_DEVICE: return "ipoke_inn: no sm_100 CUDA device / driver entry point unavailable";
     case IPOKE_INN_E_INTERNAL: return "ipoke_inn: internal error (tensor map encode failed)";
     default: break;
@@ -1455,6 +1467,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   const ipoke_inn_desc& d = *desc;
   if (d.C < 2 || (d.C & 1) || d.H < 1 || d.depth < 0 || d.n_flows < 1 || d.E < 0) return IPOKE_INN_E_UNSUPPORTED;
   if (d.conditional ? d.E < 1 : d.E != 0) return IPOKE_INN_E_UNSUPPORTED;
+  if (!(d.mlp_slope >= 0.f && d.mlp_slope <= 1.f)) return IPOKE_INN_E_UNSUPPORTED;   // LeakyReLU evaluated as max(a, slope * a)
   if (d.precision != IPOKE_INN_PREC_FP32_SPLIT && d.precision != IPOKE_INN_PREC_BF16) return IPOKE_INN_E_INVALID;
   ipoke_inn_plan* P = new (std::nothrow) ipoke_inn_plan();
   if (!P) return IPOKE_INN_E_INTERNAL;
@@ -1471,6 +1484,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_DIRECT")) P->tail_direct = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_TAIL_CLUSTER")) P->tail_cluster = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_SLAB4")) P->slab4 = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_WARPSLAB")) P->warp_slab = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_STREAMS")) P->streams = std::max(1, std::min(std::atoi(e), 8));
   if (const char* e = std::getenv("IPOKE_INN_KACC")) P->kacc_max = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WPREFETCH")) P->w_prefetch = std::atoi(e) != 0;

@@ -304,4 +304,11 @@ __device__ __forceinline__ uint32_t pack_bf16x2(__nv_bfloat16 a, __nv_bfloat16 b
   return static_cast<uint32_t>(__bfloat16_as_ushort(a)) | (static_cast<uint32_t>(__bfloat16_as_ushort(b)) << 16);
 }
 
+// two fp32 -> one packed bf16x2 word (lo half = a, hi half = b), round to nearest even: one CVT instead of two + PRMT
+__device__ __forceinline__ uint32_t cvt_bf16x2(float a, float b) {
+  uint32_t d;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
+  return d;
+}
+
 }  // namespace inn
