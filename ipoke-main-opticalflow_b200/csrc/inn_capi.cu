@@ -19,6 +19,7 @@
 #include "gemm_kernel.cuh"
 #include "optim.cuh"
 #include "tail_cluster_kernel.cuh"
+#include "hidden_pair_kernel.cuh"
 #include "wgrad_kernel.cuh"
 
 using namespace inn;
@@ -63,6 +64,8 @@ struct GemmOp {
   GemmParams p;
   int mode, grid, smem, cluster;
   int tail_cluster;   // 1: inn_tail_cluster_kernel (small batches), cluster = 2 * p.ks
+  int pair;           // 1: inn_hidden_pair_kernel (multi-wave hidden layers as tcgen05 CTA pairs), params in pp
+  PairParams pp;
 };
 struct WgradOp {
   CUtensorMap tmY[2], tmX[2];
@@ -160,6 +163,7 @@ struct ipoke_inn_plan {
   int streams = 1;                // calls the caller runs concurrently on different streams: one-wave launches are
                                   // sized for num_sms / streams SMs so that the concurrent kernels are co-resident
   int slab4 = 0;                  // 4 output slabs in flight where the pipeline leaves smem free
+  int use_pair = 1;               // multi-wave hidden layers as CTA pairs (hidden_pair_kernel.cuh)
   int warp_slab = 1;              // hidden / dgrad epilogue: warp-private output slabs (no CTA barrier inside a tile)
   int tail_cluster = 1;           // small batches: coupling tails as split-K clusters (tail_cluster_kernel.cuh)
   int dbg = 0;
@@ -269,6 +273,8 @@ int ensure_device(ipoke_inn_plan* P) {
 #define SET_SMEM(K)                                                                                    \
   e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);               \
   if (e != cudaSuccess) return (int)e;
+  SET_SMEM((inn_hidden_pair_kernel<1>))
+  SET_SMEM((inn_hidden_pair_kernel<2>))
   SET_SMEM((inn_gemm_kernel<1, EPI_HIDDEN>))
   SET_SMEM((inn_gemm_kernel<2, EPI_HIDDEN>))
   SET_SMEM((inn_gemm_kernel<1, EPI_TAIL_FWD>))
@@ -507,9 +513,56 @@ struct Builder {
     const int bn = tc.bn;
     tc.mc = pick_mc(P, m_tiles * (rows / bn), rows / bn, P->Hp / bn);
     const int a_box = BM / tc.mc;
+    // multi-wave launches: CTA pairs (cta_group::2) on 256 x bn tiles, each CTA staging half of the W tile
+    const int m_pairs = (m_tiles + 1) / 2;
+    const bool pair = P->use_pair && tc.mc == 1 && (bn == 128 || bn == 256) && P->trace_buf == nullptr &&
+                      (P->use_pair > 1 ? (long long)m_tiles * (rows / bn) > P->num_sms      // 2: every multi-wave launch
+                                       : 2ll * m_tiles * (rows / bn) >= 5ll * P->num_sms);  // default: >= 2.5 waves (measured:
+                                                                                           // 1.7 waves at cfg B / 4096 lose 3 %)
     for (size_t l = 0; l < c.L.size(); ++l) {
       const LayerW& L = c.L[l];
       GemmOp& g = add_gemm(EPI_HIDDEN);
+      if (pair) {
+        const long long ld_act = save ? rows : P->ldACT;
+        PairParams& q = g.pp;
+        g.pair = 1;
+        q.M = B;
+        q.num_m_pairs = m_pairs;
+        q.num_n_tiles = rows / bn;
+        q.tiles_per_group = P->Hp / bn;
+        q.num_k_blocks = L.Kp / BK;
+        q.BN = bn;
+        q.a_group_stride = l == 0 ? 0 : P->Hp;
+        q.a_m_wrap = 0;
+        q.bias = pk<float>(L.bias);
+        q.slope = P->d.mlp_slope;
+        q.nacc = 2 * bn <= 512 ? 2 : 1;
+        q.tmem_cols = 32;
+        while (q.tmem_cols < q.nacc * bn) q.tmem_cols <<= 1;
+        // 32-column store boxes (16 KB of epilogue smem per split) when they buy a pipeline stage, else 64-column ones
+        const int avail = kMaxDynSmem - 1024 - SMEM_BARRIER_BYTES;
+        const int sb = pair_stage_bytes(P->ksplit, bn);
+        const int st_wide = (avail - pair_epi_bytes(P->ksplit, 1)) / sb, st_half = (avail - pair_epi_bytes(P->ksplit, 0)) / sb;
+        q.wide = st_wide >= st_half ? 1 : 0;
+        q.stages = std::max(2, std::min(std::min(MAX_STAGES, q.wide ? st_wide : st_half), std::max(2, q.num_k_blocks)));
+        q.epi_off = q.stages * sb;
+        g.smem = pair_smem_bytes(P->ksplit, bn, q.stages, q.wide);
+        g.cluster = 2;
+        g.grid = 2 * (int)std::min<long long>((long long)m_pairs * q.num_n_tiles, P->num_sms / 2);
+        g.p.num_k_blocks = q.num_k_blocks;      // read by the profiling / accounting code
+        for (int sp = 0; sp < P->ksplit; ++sp) {
+          if (l == 0) err |= make_map(P, &g.tmA[sp], u_base(k, ui, sp) + 2ll * c.a_col_off, c.Kin_p, B, 2ll * P->ldU, BM);
+          else err |= make_map(P, &g.tmA[sp], act_base(k, ci, (int)l - 1, sp), rows, B, 2ll * ld_act, BM);
+          err |= make_map(P, &g.tmW[sp], packed + (sp == 0 ? L.hi : L.lo), L.Kp, L.rows, 2ll * L.Kp, bn / 2);
+          err |= make_map(P, &g.tmO[sp], act_base(k, ci, (int)l, sp), rows, B, 2ll * ld_act, 32, q.wide ? BK : 32);
+        }
+        if (P->ksplit == 1) {
+          g.tmA[1] = g.tmA[0];
+          g.tmW[1] = g.tmW[0];
+          g.tmO[1] = g.tmO[0];
+        }
+        continue;
+      }
       g.p.num_n_tiles = rows / bn;
       g.p.tiles_per_group = P->Hp / bn;
       g.p.num_k_blocks = L.Kp / BK;
@@ -1159,8 +1212,35 @@ cudaError_t launch_tail_cluster_t(const GemmOp& g, const GemmParams& gp, cudaStr
   return cudaLaunchKernelEx(&cfg, inn_tail_cluster_kernel<kSplit, kRev>, g.tmA[0], g.tmA[1], g.tmW[0], g.tmW[1], gp);
 }
 
+template <int kSplit>
+cudaError_t launch_pair_t(const GemmOp& g, cudaStream_t st, int pdl) {
+  cudaLaunchConfig_t cfg;
+  std::memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)g.grid);
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = (size_t)g.smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  attr[na].id = cudaLaunchAttributeClusterDimension;
+  attr[na].val.clusterDim.x = 2;
+  attr[na].val.clusterDim.y = 1;
+  attr[na].val.clusterDim.z = 1;
+  ++na;
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  return cudaLaunchKernelEx(&cfg, inn_hidden_pair_kernel<kSplit>, g.tmA[0], g.tmA[1], g.tmW[0], g.tmW[1], g.tmO[0],
+                            g.tmO[1], g.pp);
+}
+
 cudaError_t launch_gemm(const ipoke_inn_plan* P, const GemmOp& g, const GemmParams& gp, cudaStream_t st) {
   const int pdl = P->use_pdl;
+  if (g.pair) return P->ksplit == 2 ? launch_pair_t<2>(g, st, pdl) : launch_pair_t<1>(g, st, pdl);
   if (g.tail_cluster) {
     const bool rev = g.mode == EPI_TAIL_REV;
     if (P->ksplit == 2)
@@ -1485,6 +1565,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_TAIL_CLUSTER")) P->tail_cluster = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_SLAB4")) P->slab4 = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WARPSLAB")) P->warp_slab = std::atoi(e) != 0;
+  if (const char* e = std::getenv("IPOKE_INN_PAIR")) P->use_pair = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_STREAMS")) P->streams = std::max(1, std::min(std::atoi(e), 8));
   if (const char* e = std::getenv("IPOKE_INN_KACC")) P->kacc_max = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WPREFETCH")) P->w_prefetch = std::atoi(e) != 0;
