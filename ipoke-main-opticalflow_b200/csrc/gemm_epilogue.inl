@@ -31,7 +31,7 @@
         mbar_wait(&tfull_bar[acc], acc_phase, 4);
         tc_fence_after();
         if (tr != nullptr && tid_e == 0) tr[5] = globaltimer_ns();
-        if (p.slab_warp) {
+        if (kWarpSlab && p.slab_warp) {
           // ---- warp-private slabs: every epilogue warp owns the 32 rows of its TMEM lane quarter: TMEM -> regs -> its own
           // swizzled smem buffer -> one TMA store per warp.  No CTA-wide barrier inside the tile: the warps drift apart
           // and overlap each other's TMEM-load and store-drain latencies (ncu, r01 v6: the CTA-wide version with one
@@ -687,5 +687,5 @@
         named_bar_sync(1, EPI_THREADS);                           // keep_s is reused by the next tile
       }
     }
-    if (kSlabMode && p.slab_bufs > 0 && (p.slab_warp ? lane == 0 : tid_e == 0)) bulk_wait<0>();   // stores landed before exit
+    if (kSlabMode && p.slab_bufs > 0 && ((kWarpSlab && p.slab_warp) ? lane == 0 : tid_e == 0)) bulk_wait<0>();   // stores landed before exit
     if (tr != nullptr && tid_e == 0) tr[6] = globaltimer_ns();

@@ -133,7 +133,9 @@ __host__ inline int gemm_smem_bytes(int ksplit, int mode, int BN, int stages, in
          ((gemm_epi_bytes(ksplit, mode, BN, slab_bufs, direct) + 15) & ~15) + SMEM_BARRIER_BYTES;
 }
 
-template <int kSplit, int kMode>
+// kWarpSlab: instantiate the warp-private-slab epilogue (p.slab_warp; multi-wave hidden / dgrad launches).  Small-batch
+// launches use the kWarpSlab = false instantiation: carrying the unused path cost them 130 ns per launch (r01 A/B).
+template <int kSplit, int kMode, bool kWarpSlab = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                 const __grid_constant__ CUtensorMap tmW0, const __grid_constant__ CUtensorMap tmW1,
@@ -236,14 +238,23 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                         sp == 0 ? &tmW0 : &tmW1, &full_bar[ki], kb * BK, p.w_row0[sub] + n_tile0 * BN);
       }
     }
+    // tile coordinates of the first tile (integer divisions) before the dependency wait, off the critical path
+    int m_tile = static_cast<int>(blockIdx.x) / p.num_n_tiles;
+    int n_tile = static_cast<int>(blockIdx.x) - m_tile * p.num_n_tiles;
+    int group = n_tile / p.tiles_per_group;
+    int a_row0 = m_tile * BM;
+    if (p.a_m_wrap > 0) a_row0 = (m_tile % p.a_m_wrap) * BM;
     grid_dep_wait();
     if (tr != nullptr && lane == 0) tr[2] = globaltimer_ns();
     bool first_tile = true;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m_tile = tile / p.num_n_tiles;
-      const int n_tile = tile - m_tile * p.num_n_tiles;
-      const int group = n_tile / p.tiles_per_group;
-      const int a_row0 = (p.a_m_wrap > 0 ? m_tile % p.a_m_wrap : m_tile) * BM;
+      if (!first_tile) {
+        m_tile = tile / p.num_n_tiles;
+        n_tile = tile - m_tile * p.num_n_tiles;
+        group = n_tile / p.tiles_per_group;
+        a_row0 = m_tile * BM;
+        if (p.a_m_wrap > 0) a_row0 = (m_tile % p.a_m_wrap) * BM;
+      }
       for (int ki = 0; ki < p.num_k_blocks; ++ki) {
         const int kb = p.k_rotate ? (ki + n_tile) % p.num_k_blocks : ki;
         {

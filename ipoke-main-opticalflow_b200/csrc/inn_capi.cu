@@ -276,6 +276,10 @@ int ensure_device(ipoke_inn_plan* P) {
   SET_SMEM((inn_hidden_pair_kernel<1>))
   SET_SMEM((inn_hidden_pair_kernel<2>))
   SET_SMEM((inn_gemm_kernel<1, EPI_HIDDEN>))
+  SET_SMEM((inn_gemm_kernel<1, EPI_HIDDEN, true>))
+  SET_SMEM((inn_gemm_kernel<2, EPI_HIDDEN, true>))
+  SET_SMEM((inn_gemm_kernel<1, EPI_DGRAD, true>))
+  SET_SMEM((inn_gemm_kernel<2, EPI_DGRAD, true>))
   SET_SMEM((inn_gemm_kernel<2, EPI_HIDDEN>))
   SET_SMEM((inn_gemm_kernel<1, EPI_TAIL_FWD>))
   SET_SMEM((inn_gemm_kernel<2, EPI_TAIL_FWD>))
@@ -1159,7 +1163,7 @@ Program* get_program(ipoke_inn_plan* P, const ProgramKey& key, int* err) {
   return P->programs.back().get();
 }
 
-template <int kSplit, int kMode>
+template <int kSplit, int kMode, bool kWarpSlab = false>
 cudaError_t launch_gemm_t(const GemmOp& g, const GemmParams& gp, cudaStream_t st, int pdl) {
   cudaLaunchConfig_t cfg;
   std::memset(&cfg, 0, sizeof(cfg));
@@ -1183,7 +1187,7 @@ cudaError_t launch_gemm_t(const GemmOp& g, const GemmParams& gp, cudaStream_t st
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
-  return cudaLaunchKernelEx(&cfg, inn_gemm_kernel<kSplit, kMode>, g.tmA[0], g.tmA[1], g.tmW[0], g.tmW[1], g.tmO[0],
+  return cudaLaunchKernelEx(&cfg, inn_gemm_kernel<kSplit, kMode, kWarpSlab>, g.tmA[0], g.tmA[1], g.tmW[0], g.tmW[1], g.tmO[0],
                             g.tmO[1], gp);
 }
 
@@ -1249,18 +1253,18 @@ cudaError_t launch_gemm(const ipoke_inn_plan* P, const GemmOp& g, const GemmPara
   }
   if (P->ksplit == 2) {
     switch (g.mode) {
-      case EPI_HIDDEN: return launch_gemm_t<2, EPI_HIDDEN>(g, gp, st, pdl);
+      case EPI_HIDDEN: return gp.slab_warp ? launch_gemm_t<2, EPI_HIDDEN, true>(g, gp, st, pdl) : launch_gemm_t<2, EPI_HIDDEN>(g, gp, st, pdl);
       case EPI_TAIL_FWD: return launch_gemm_t<2, EPI_TAIL_FWD>(g, gp, st, pdl);
       case EPI_TAIL_REV: return launch_gemm_t<2, EPI_TAIL_REV>(g, gp, st, pdl);
-      case EPI_DGRAD: return launch_gemm_t<2, EPI_DGRAD>(g, gp, st, pdl);
+      case EPI_DGRAD: return gp.slab_warp ? launch_gemm_t<2, EPI_DGRAD, true>(g, gp, st, pdl) : launch_gemm_t<2, EPI_DGRAD>(g, gp, st, pdl);
       default: return launch_gemm_t<2, EPI_DU>(g, gp, st, pdl);
     }
   }
   switch (g.mode) {
-    case EPI_HIDDEN: return launch_gemm_t<1, EPI_HIDDEN>(g, gp, st, pdl);
+    case EPI_HIDDEN: return gp.slab_warp ? launch_gemm_t<1, EPI_HIDDEN, true>(g, gp, st, pdl) : launch_gemm_t<1, EPI_HIDDEN>(g, gp, st, pdl);
     case EPI_TAIL_FWD: return launch_gemm_t<1, EPI_TAIL_FWD>(g, gp, st, pdl);
     case EPI_TAIL_REV: return launch_gemm_t<1, EPI_TAIL_REV>(g, gp, st, pdl);
-    case EPI_DGRAD: return launch_gemm_t<1, EPI_DGRAD>(g, gp, st, pdl);
+    case EPI_DGRAD: return gp.slab_warp ? launch_gemm_t<1, EPI_DGRAD, true>(g, gp, st, pdl) : launch_gemm_t<1, EPI_DGRAD>(g, gp, st, pdl);
     default: return launch_gemm_t<1, EPI_DU>(g, gp, st, pdl);
   }
 }

@@ -65,6 +65,8 @@ inn_tail_cluster_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_c
   const int tile = blockIdx.x / cs;
   const int m_tile = tile / p.num_n_tiles;
   const int n_tile = tile - m_tile * p.num_n_tiles;
+  int a_row0 = m_tile * BM;                  // computed in the prologue, off the dependent-launch critical path
+  if (p.a_m_wrap > 0) a_row0 = (m_tile % p.a_m_wrap) * BM;
   const int nkb = p.num_k_blocks / KS;
   const int kb0 = kh * nkb;
   const int stages = p.stages;
@@ -126,7 +128,7 @@ inn_tail_cluster_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_c
 #pragma unroll
       for (int sp = 0; sp < kSplit; ++sp) {
         tma_load_2d_el(sbase + sp * A_TILE_BYTES, sp == 0 ? &tmA0 : &tmA1, &full_bar[stage],
-                       p.a_off[net] + (kb0 + ki) * BK, (p.a_m_wrap > 0 ? m_tile % p.a_m_wrap : m_tile) * BM);
+                       p.a_off[net] + (kb0 + ki) * BK, a_row0);
         if (!w_done)
           tma_load_2d_el(sbase + kSplit * A_TILE_BYTES + sp * TC_W_TILE_BYTES, sp == 0 ? &tmW0 : &tmW1,
                          &full_bar[stage], (kb0 + ki) * BK, w_row);
