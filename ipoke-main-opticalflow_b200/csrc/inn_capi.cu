@@ -20,6 +20,7 @@
 #include "optim.cuh"
 #include "tail_cluster_kernel.cuh"
 #include "hidden_pair_kernel.cuh"
+#include "hidden_cluster_kernel.cuh"
 #include "wgrad_kernel.cuh"
 
 using namespace inn;
@@ -64,6 +65,7 @@ struct GemmOp {
   GemmParams p;
   int mode, grid, smem, cluster;
   int tail_cluster;   // 1: inn_tail_cluster_kernel (small batches), cluster = 2 * p.ks
+  int hidden_cluster; // 1: inn_hidden_cluster_kernel (small batches: split-K cluster of p.ks CTAs per tile)
   int pair;           // 1: inn_hidden_pair_kernel (multi-wave hidden layers as tcgen05 CTA pairs), params in pp
   PairParams pp;
 };
@@ -163,6 +165,9 @@ struct ipoke_inn_plan {
   int streams = 1;                // calls the caller runs concurrently on different streams: one-wave launches are
                                   // sized for num_sms / streams SMs so that the concurrent kernels are co-resident
   int slab4 = 0;                  // 4 output slabs in flight where the pipeline leaves smem free
+  int hidden_cluster = 0;         // one-wave hidden layers as split-K clusters (hidden_cluster_kernel.cuh): measured SLOWER
+                                  // (cfg B b256 734 -> 893 us/step: 16-byte remote stores of a 64 KB partial cost more than
+                                  // the halved operand ingest saves; profiles/r01_ab_hcluster_v9.txt) -> off
   int use_pair = 1;               // multi-wave hidden layers as CTA pairs (hidden_pair_kernel.cuh)
   int warp_slab = 1;              // hidden / dgrad epilogue: warp-private output slabs (no CTA barrier inside a tile)
   int tail_cluster = 1;           // small batches: coupling tails as split-K clusters (tail_cluster_kernel.cuh)
@@ -273,6 +278,8 @@ int ensure_device(ipoke_inn_plan* P) {
 #define SET_SMEM(K)                                                                                    \
   e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);               \
   if (e != cudaSuccess) return (int)e;
+  SET_SMEM((inn_hidden_cluster_kernel<1>))
+  SET_SMEM((inn_hidden_cluster_kernel<2>))
   SET_SMEM((inn_hidden_pair_kernel<1>))
   SET_SMEM((inn_hidden_pair_kernel<2>))
   SET_SMEM((inn_gemm_kernel<1, EPI_HIDDEN>))
@@ -526,6 +533,61 @@ struct Builder {
     for (size_t l = 0; l < c.L.size(); ++l) {
       const LayerW& L = c.L[l];
       GemmOp& g = add_gemm(EPI_HIDDEN);
+      // one-wave launches: split-K cluster when it cuts the bytes one SM has to pull through its L2 port
+      if (!pair && P->hidden_cluster && tc.mc == 1 && P->trace_buf == nullptr && P->kacc_max == 1 &&
+          (long long)m_tiles * (rows / bn) <= P->num_sms) {
+        const int cap = P->hidden_cluster > 1 ? P->num_sms : std::max(1, P->num_sms / P->streams);
+        const int nkb_all = L.Kp / BK;
+        const long long base_cost = (long long)(BM + bn) * L.Kp * 2;
+        long long best = (base_cost * 4) / 5;                      // must save >= 20 % of the per-SM bytes
+        int cbn = 0, cks = 0, cst = 0;
+        static const int bns[2] = {128, 64}, kss[3] = {8, 4, 2};
+        for (int bi = 0; bi < 2; ++bi)
+          for (int ki = 0; ki < 3; ++ki) {
+            const int b2 = bns[bi], ks = kss[ki];
+            if (P->Hp % b2 != 0 || nkb_all % ks != 0 || nkb_all / ks < 2) continue;
+            if ((long long)m_tiles * (rows / b2) * ks > cap) continue;
+            const int nkb = nkb_all / ks;
+            const int fit = (kMaxDynSmem - 1024 - SMEM_BARRIER_BYTES - hidden_cluster_recv_bytes(b2)) /
+                            hidden_cluster_stage_bytes(P->ksplit, b2);
+            if (fit < 2) continue;
+            const long long cost = (long long)(BM + b2) * BK * 2 * nkb + (long long)BM * b2 * 4 * (ks - 1) / ks;
+            if (cost < best) { best = cost; cbn = b2; cks = ks; cst = std::min(std::min(nkb, MAX_STAGES), fit); }
+          }
+        if (cks > 0) {
+          const long long ld_act = save ? rows : P->ldACT;
+          g.hidden_cluster = 1;
+          g.p.M = B;
+          g.p.BN = cbn;
+          g.p.num_n_tiles = rows / cbn;
+          g.p.tiles_per_group = P->Hp / cbn;
+          g.p.num_k_blocks = nkb_all;
+          g.p.ks = cks;
+          g.p.stages = cst;
+          g.p.w_prefetch = P->w_prefetch;
+          g.p.a_group_stride = l == 0 ? 0 : P->Hp;
+          g.p.bias = pk<float>(L.bias);
+          g.p.slope = P->d.mlp_slope;
+          g.p.out_hi = reinterpret_cast<__nv_bfloat16*>(act_base(k, ci, (int)l, 0));
+          g.p.out_lo = P->ksplit == 2 ? reinterpret_cast<__nv_bfloat16*>(act_base(k, ci, (int)l, 1)) : nullptr;
+          g.p.ld_out = (int)ld_act;
+          g.smem = hidden_cluster_smem_bytes(P->ksplit, cbn, cst);
+          g.cluster = cks;
+          g.grid = m_tiles * g.p.num_n_tiles * cks;
+          for (int sp = 0; sp < P->ksplit; ++sp) {
+            if (l == 0) err |= make_map(P, &g.tmA[sp], u_base(k, ui, sp) + 2ll * c.a_col_off, c.Kin_p, B, 2ll * P->ldU, BM);
+            else err |= make_map(P, &g.tmA[sp], act_base(k, ci, (int)l - 1, sp), rows, B, 2ll * ld_act, BM);
+            err |= make_map(P, &g.tmW[sp], packed + (sp == 0 ? L.hi : L.lo), L.Kp, L.rows, 2ll * L.Kp, cbn);
+            g.tmO[sp] = g.tmA[sp];
+          }
+          if (P->ksplit == 1) {
+            g.tmA[1] = g.tmA[0];
+            g.tmW[1] = g.tmW[0];
+            g.tmO[1] = g.tmO[0];
+          }
+          continue;
+        }
+      }
       if (pair) {
         const long long ld_act = save ? rows : P->ldACT;
         PairParams& q = g.pp;
@@ -1242,8 +1304,35 @@ cudaError_t launch_pair_t(const GemmOp& g, cudaStream_t st, int pdl) {
                             g.tmO[1], g.pp);
 }
 
+template <int kSplit>
+cudaError_t launch_hidden_cluster_t(const GemmOp& g, const GemmParams& gp, cudaStream_t st, int pdl) {
+  cudaLaunchConfig_t cfg;
+  std::memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)g.grid);
+  cfg.blockDim = dim3(HC_THREADS);
+  cfg.dynamicSmemBytes = (size_t)g.smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  attr[na].id = cudaLaunchAttributeClusterDimension;
+  attr[na].val.clusterDim.x = (unsigned)g.cluster;
+  attr[na].val.clusterDim.y = 1;
+  attr[na].val.clusterDim.z = 1;
+  ++na;
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  return cudaLaunchKernelEx(&cfg, inn_hidden_cluster_kernel<kSplit>, g.tmA[0], g.tmA[1], g.tmW[0], g.tmW[1], gp);
+}
+
 cudaError_t launch_gemm(const ipoke_inn_plan* P, const GemmOp& g, const GemmParams& gp, cudaStream_t st) {
   const int pdl = P->use_pdl;
+  if (g.hidden_cluster)
+    return P->ksplit == 2 ? launch_hidden_cluster_t<2>(g, gp, st, pdl) : launch_hidden_cluster_t<1>(g, gp, st, pdl);
   if (g.pair) return P->ksplit == 2 ? launch_pair_t<2>(g, st, pdl) : launch_pair_t<1>(g, st, pdl);
   if (g.tail_cluster) {
     const bool rev = g.mode == EPI_TAIL_REV;
@@ -1570,6 +1659,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_SLAB4")) P->slab4 = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WARPSLAB")) P->warp_slab = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_PAIR")) P->use_pair = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_HCLUSTER")) P->hidden_cluster = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_STREAMS")) P->streams = std::max(1, std::min(std::atoi(e), 8));
   if (const char* e = std::getenv("IPOKE_INN_KACC")) P->kacc_max = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WPREFETCH")) P->w_prefetch = std::atoi(e) != 0;
