@@ -542,7 +542,7 @@ def main():
         B = args.batch or defB
         cpu = cpu_port_run(args.config, min(B, 256), args.steps, args.warmup, budget_s=60.0)
         line = {"impl": "reference", "metric": METRIC, "value": cpu["value"], "unit": "samples/s",
-                "n_gpus": args.gpus, "steps": cpu["steps"], "warmup": 1, "ms_per_step": cpu["ms_per_step"],
+                "n_gpus": args.gpus, "steps": cpu["steps"], "warmup": max(args.warmup, 1), "ms_per_step": cpu["ms_per_step"],
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic",
                 "config": dict(workload_config(args.config, B, 1, "fp32"),
