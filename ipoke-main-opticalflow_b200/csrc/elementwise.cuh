@@ -32,6 +32,9 @@ struct BoundaryParams {
   float* block_logdet;                                                // nullable snapshot before the add
   float* block_logdet2;                                               // nullable second snapshot
   int B, C;
+  int fast_rows;                        // 1: warp-per-row path (C % 4 == 0, all row strides % 4 == 0, u_begin / u_count % 4 == 0,
+                                        //    dynamic smem = 13 * C floats): coalesced row load -> smem -> permuted read ->
+                                        //    coalesced float4 stores, instead of one uncoalesced gather per element
 };
 
 __global__ void __launch_bounds__(256) inn_boundary_kernel(const BoundaryParams p) {
@@ -40,6 +43,72 @@ __global__ void __launch_bounds__(256) inn_boundary_kernel(const BoundaryParams 
   const long long total = static_cast<long long>(p.B) * p.C;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   const long long tid0 = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (p.fast_rows) {
+    extern __shared__ float bsm[];
+    const int C = p.C;
+    float* c_pre_s = bsm;                 // indexed by SOURCE column q
+    float* c_pre_l = bsm + C;
+    float* c_post_s = bsm + 2 * C;        // indexed by destination column c
+    float* c_post_l = bsm + 3 * C;
+    int* c_src = reinterpret_cast<int*>(bsm + 4 * C);
+    float* rowbuf = bsm + 5 * C + (threadIdx.x >> 5) * C;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      c_src[c] = p.src ? __ldg(p.src + c) : c;
+      c_pre_s[c] = p.pre_scale ? __ldg(p.pre_scale + c) : 1.f;
+      c_pre_l[c] = p.pre_scale ? __ldg(p.pre_loc + c) : 0.f;
+      c_post_s[c] = p.post_scale ? __ldg(p.post_scale + c) : 1.f;
+      c_post_l[c] = p.post_scale ? __ldg(p.post_loc + c) : 0.f;
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    const float an_ld = (p.logdet && p.an_logdet) ? __ldg(p.an_logdet) : 0.f;
+    for (int b = blockIdx.x * wpb + (threadIdx.x >> 5); b < p.B; b += gridDim.x * wpb) {
+      const float4* src4 = reinterpret_cast<const float4*>(p.in + static_cast<size_t>(b) * p.ld_in);
+      for (int g = lane; g < (C >> 2); g += 32) reinterpret_cast<float4*>(rowbuf)[g] = __ldg(src4 + g);
+      __syncwarp();
+      for (int g = lane; g < (C >> 2); g += 32) {
+        const int c = g << 2;
+        float v[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int q = c_src[c + e];
+          float x = rowbuf[q];
+          if (p.pre_scale) {
+            if (p.pre_leaky) x = x / (x >= 0.f ? 1.0f : p.alpha);      // same operations as the element path
+            x = x / c_pre_s[q] - c_pre_l[q];
+          }
+          v[e] = x;
+        }
+        if (p.raw_out) *reinterpret_cast<float4*>(p.raw_out + static_cast<size_t>(b) * p.ld_raw + c) = make_float4(v[0], v[1], v[2], v[3]);
+        if (p.raw_out2) *reinterpret_cast<float4*>(p.raw_out2 + static_cast<size_t>(b) * p.ld_raw + c) = make_float4(v[0], v[1], v[2], v[3]);
+        if (p.post_scale) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float x = c_post_s[c + e] * (v[e] + c_post_l[c + e]);
+            if (p.post_leaky) x = x * (x >= 0.f ? 1.0f : p.alpha);
+            v[e] = x;
+          }
+        }
+        if (p.out) *reinterpret_cast<float4*>(p.out + static_cast<size_t>(b) * p.ld_out + c) = make_float4(v[0], v[1], v[2], v[3]);
+        if (p.u_hi && c >= p.u_begin && c < p.u_begin + p.u_count) {
+          __nv_bfloat16 h[4], l[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) split_bf16(v[e], h[e], l[e]);
+          const size_t o = static_cast<size_t>(b) * p.ld_u + (c - p.u_begin);
+          *reinterpret_cast<uint2*>(p.u_hi + o) = make_uint2(pack_bf16x2(h[0], h[1]), pack_bf16x2(h[2], h[3]));
+          if (p.u_lo) *reinterpret_cast<uint2*>(p.u_lo + o) = make_uint2(pack_bf16x2(l[0], l[1]), pack_bf16x2(l[2], l[3]));
+        }
+      }
+      if (lane == 0 && p.logdet) {
+        const float cur = p.logdet_init ? 0.f : p.logdet[b];
+        if (p.block_logdet) p.block_logdet[b] = cur;
+        if (p.block_logdet2) p.block_logdet2[b] = cur;
+        p.logdet[b] = cur + an_ld;
+      }
+      __syncwarp();                                           // rowbuf is rewritten by the next row
+    }
+  } else
   for (long long idx = tid0; idx < total; idx += stride) {
     const int b = static_cast<int>(idx / p.C);
     const int c = static_cast<int>(idx - static_cast<long long>(b) * p.C);

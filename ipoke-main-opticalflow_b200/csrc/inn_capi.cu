@@ -177,6 +177,11 @@ struct ipoke_inn_plan {
   unsigned long long* trace_buf = nullptr;   // ipoke_inn_debug_trace
   int trace_slots = 0;
   int use_fold = 1;              // inference programs: block boundaries folded into the coupling tails
+  int fast_boundary = 512;       // boundary kernel: warp-per-row path from this many rows (0 = never)
+  int fold_max_rows = -1;        // ... for batches up to this many rows (larger: separate warp-per-row boundary kernels);
+                                 // -1 = by width: the folded scatter costs one 32-byte sector per element, which wide states
+                                 // (C >= 256) pay for from ~2048 rows on (cfg B: -3 % at 2048, -11 % at 4096, -17 % at 8192, -2 % at
+                                 // 32768; cfg A, C = 128: folding stays ahead) -- profiles/r01_ab_unfold_v10.txt
   int w_prefetch = 1;
   int latency_smem_cap_kb = 0;   // > 0: cap smem of one-wave launches so two kernels can be co-resident under PDL
   cudaStream_t cap_stream = nullptr;
@@ -791,10 +796,15 @@ struct Builder {
     }
   }
 
+  int fold_limit() const {
+    if (P->fold_max_rows >= 0) return P->fold_max_rows;
+    return P->d.C >= 256 ? 2047 : (1 << 30);
+  }
+
   void build_forward(int kb, int ke, bool want_blocks) {
     const ipoke_inn_desc& d = P->d;
     int cur = 0;
-    fold = P->use_fold && !save && !want_blocks;
+    fold = P->use_fold && !save && !want_blocks && B <= fold_limit();
     f_kb = kb;
     f_ke = ke;
     for (int k = kb; k < ke; ++k) {
@@ -856,7 +866,7 @@ struct Builder {
   void build_reverse(int kb, int ke) {
     const ipoke_inn_desc& d = P->d;
     int cur = 0;
-    fold = P->use_fold && !save;
+    fold = P->use_fold && !save && B <= fold_limit();
     f_kb = kb;
     f_ke = ke;
     for (int k = ke - 1; k >= kb; --k) {
@@ -1531,6 +1541,18 @@ int issue_program(ipoke_inn_plan* P, Program* prog, const float* in, const float
       cfg.gridDim = dim3((unsigned)o.b_grid);
       cfg.blockDim = dim3(256);
       cfg.stream = st;
+      {
+        // warp-per-row path (coalesced rows through smem) for larger batches when every access can be a 16-byte one
+        auto a16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
+        auto a8 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 7u) == 0; };
+        const bool u_ok = b.u_hi == nullptr || (b.ld_u % 4 == 0 && b.u_begin % 4 == 0 && b.u_count % 4 == 0 && a8(b.u_hi) && a8(b.u_lo));
+        if (P->fast_boundary && b.B >= P->fast_boundary && b.C % 4 == 0 && b.C <= 896 && b.ld_in % 4 == 0 && b.ld_out % 4 == 0 &&
+            b.ld_raw % 4 == 0 && u_ok && a16(b.in) && a16(b.out) && a16(b.raw_out) && a16(b.raw_out2)) {
+          b.fast_rows = 1;
+          cfg.gridDim = dim3((unsigned)std::min((b.B + 7) / 8, P->num_sms * 8));
+          cfg.dynamicSmemBytes = (size_t)13 * b.C * sizeof(float);
+        }
+      }
       cudaLaunchAttribute attr[1];
       attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
       attr[0].val.programmaticStreamSerializationAllowed = 1;
@@ -1650,6 +1672,8 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_PDL")) P->use_pdl = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_MCAST")) P->use_mcast = std::atoi(e) == 1 ? 8 : std::atoi(e);   // max cluster size (1 = 8)
   if (const char* e = std::getenv("IPOKE_INN_FOLD")) P->use_fold = std::atoi(e) != 0;
+  if (const char* e = std::getenv("IPOKE_INN_FOLD_MAXB")) P->fold_max_rows = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_FASTB")) P->fast_boundary = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_TAIL_BN")) P->tail_bn_max = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_HIDDEN_BN")) P->hidden_bn_force = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_KROT")) P->k_rotate = std::atoi(e);
