@@ -1573,12 +1573,67 @@ int issue_program(ipoke_inn_plan* P, Program* prog, const float* in, const float
   return 0;
 }
 
+// Host-buffer calls (ipoke_inn_*_host): the copies around the kernels, so that a pinned-memory call replays as ONE graph
+// (H2D nodes, kernels, D2H nodes) instead of one graph launch plus 3-5 separate copy calls per request.
+struct HostIO {
+  const float* in_host; const float* cond_host; float* out_host; float* ld_host;   // ld_host nullable (reverse)
+  size_t in_bytes, cond_bytes, out_bytes, ld_bytes;
+};
+int issue_with_io(ipoke_inn_plan* P, Program* prog, const float* in, const float* cond, float* out, float* logdet_out,
+                  float* block_outs, float* block_lds, cudaStream_t st, const HostIO* io) {
+  if (io) {
+    cudaError_t e = cudaMemcpyAsync(const_cast<float*>(in), io->in_host, io->in_bytes, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return (int)e;
+    if (io->cond_host) {
+      e = cudaMemcpyAsync(const_cast<float*>(cond), io->cond_host, io->cond_bytes, cudaMemcpyHostToDevice, st);
+      if (e != cudaSuccess) return (int)e;
+    }
+  }
+  int rc = issue_program(P, prog, in, cond, out, logdet_out, block_outs, block_lds, st);
+  if (rc) return rc;
+  if (io) {
+    cudaError_t e = cudaMemcpyAsync(io->out_host, out, io->out_bytes, cudaMemcpyDeviceToHost, st);
+    if (e != cudaSuccess) return (int)e;
+    if (io->ld_host) {
+      e = cudaMemcpyAsync(io->ld_host, logdet_out, io->ld_bytes, cudaMemcpyDeviceToHost, st);
+      if (e != cudaSuccess) return (int)e;
+    }
+  }
+  return 0;
+}
+bool host_pinned(const void* q) {
+  if (!q) return true;
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, q) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeHost;
+}
+
 // Replay as a CUDA graph when the caller's pointers repeat (steady-state loops); plain launches otherwise.
 int run_program(ipoke_inn_plan* P, Program* prog, const float* in, const float* cond, float* out, float* logdet_out,
-                float* block_outs, float* block_lds, cudaStream_t st) {
+                float* block_outs, float* block_lds, cudaStream_t st, const HostIO* io = nullptr) {
   if (!P->use_graph || P->profile || prog->graph_misses > 8 + 4 * prog->graph_hits)
-    return issue_program(P, prog, in, cond, out, logdet_out, block_outs, block_lds, st);
+    return issue_with_io(P, prog, in, cond, out, logdet_out, block_outs, block_lds, st, io);
+  // pageable host memory cannot be captured: such calls copy outside the graph
+  if (io && !(host_pinned(io->in_host) && host_pinned(io->cond_host) && host_pinned(io->out_host) && host_pinned(io->ld_host))) {
+    HostIO pre = *io;
+    cudaError_t e = cudaMemcpyAsync(const_cast<float*>(in), pre.in_host, pre.in_bytes, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return (int)e;
+    if (pre.cond_host) {
+      e = cudaMemcpyAsync(const_cast<float*>(cond), pre.cond_host, pre.cond_bytes, cudaMemcpyHostToDevice, st);
+      if (e != cudaSuccess) return (int)e;
+    }
+    int rc = run_program(P, prog, in, cond, out, logdet_out, block_outs, block_lds, st, nullptr);
+    if (rc) return rc;
+    e = cudaMemcpyAsync(pre.out_host, out, pre.out_bytes, cudaMemcpyDeviceToHost, st);
+    if (e != cudaSuccess) return (int)e;
+    if (pre.ld_host) e = cudaMemcpyAsync(pre.ld_host, logdet_out, pre.ld_bytes, cudaMemcpyDeviceToHost, st);
+    return e == cudaSuccess ? 0 : (int)e;
+  }
   const void* ptrs[6] = {in, cond, out, logdet_out, block_outs, block_lds};
+  if (io) {                            // host calls are keyed by the host pointers (the device side is workspace scratch)
+    ptrs[0] = io->in_host; ptrs[1] = io->cond_host; ptrs[2] = io->out_host; ptrs[3] = io->ld_host;
+    ptrs[4] = in; ptrs[5] = out;
+  }
   ++P->tick;
   for (auto& g : prog->graphs) {
     if (std::memcmp(g.ptrs, ptrs, sizeof(ptrs)) == 0) {
@@ -1596,14 +1651,14 @@ int run_program(ipoke_inn_plan* P, Program* prog, const float* in, const float* 
   }
   cudaError_t e = cudaStreamBeginCapture(P->cap_stream, cudaStreamCaptureModeThreadLocal);
   if (e != cudaSuccess) return (int)e;
-  int rc = issue_program(P, prog, in, cond, out, logdet_out, block_outs, block_lds, P->cap_stream);
+  int rc = issue_with_io(P, prog, in, cond, out, logdet_out, block_outs, block_lds, P->cap_stream, io);
   cudaGraph_t graph = nullptr;
   e = cudaStreamEndCapture(P->cap_stream, &graph);
   if (rc != 0 || e != cudaSuccess || graph == nullptr) {
     if (graph) cudaGraphDestroy(graph);
     cudaGetLastError();
     P->use_graph = 0;          // capture unsupported here: fall back to plain launches for good
-    return issue_program(P, prog, in, cond, out, logdet_out, block_outs, block_lds, st);
+    return issue_with_io(P, prog, in, cond, out, logdet_out, block_outs, block_lds, st, io);
   }
   cudaGraphExec_t exec = nullptr;
   e = cudaGraphInstantiate(&exec, graph, 0);
@@ -1611,7 +1666,7 @@ int run_program(ipoke_inn_plan* P, Program* prog, const float* in, const float* 
   if (e != cudaSuccess || exec == nullptr) {
     cudaGetLastError();
     P->use_graph = 0;
-    return issue_program(P, prog, in, cond, out, logdet_out, block_outs, block_lds, st);
+    return issue_with_io(P, prog, in, cond, out, logdet_out, block_outs, block_lds, st, io);
   }
   if (prog->graphs.size() >= 4) {                       // evict the least recently used
     size_t lru = 0;
@@ -1943,49 +1998,45 @@ int ipoke_inn_forward_draws(ipoke_inn_plan* P, const void* packed, const float* 
 
 int ipoke_inn_forward_host(ipoke_inn_plan* P, const void* packed, const float* x_host, const float* cond_host,
                            float* z_host, float* logdet_host, int B, void* workspace, void* stream) {
-  if (!P || !x_host || !z_host || !logdet_host || !workspace || B <= 0) return IPOKE_INN_E_INVALID;
+  if (!P || !packed || !x_host || !z_host || !logdet_host || !workspace || B <= 0) return IPOKE_INN_E_INVALID;
   if (P->d.E > 0 && !cond_host) return IPOKE_INN_E_INVALID;
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
   const WsLayout wl = ws_layout(P, B);
   char* ws = static_cast<char*>(workspace);
   const size_t bc = sizeof(float) * (size_t)B * P->d.C;
-  cudaError_t e = cudaMemcpyAsync(ws + wl.xin, x_host, bc, cudaMemcpyHostToDevice, st);
-  if (e != cudaSuccess) return (int)e;
-  if (P->d.E > 0) {
-    e = cudaMemcpyAsync(ws + wl.condin, cond_host, sizeof(float) * (size_t)B * P->d.E, cudaMemcpyHostToDevice, st);
-    if (e != cudaSuccess) return (int)e;
-  }
-  int rc = ipoke_inn_forward(P, packed, reinterpret_cast<float*>(ws + wl.xin),
-                             P->d.E > 0 ? reinterpret_cast<float*>(ws + wl.condin) : nullptr,
-                             reinterpret_cast<float*>(ws + wl.zout), reinterpret_cast<float*>(ws + wl.ldout), nullptr,
-                             nullptr, B, 0, P->d.n_flows, workspace, stream);
+  float* x = reinterpret_cast<float*>(ws + wl.xin);
+  float* cond = P->d.E > 0 ? reinterpret_cast<float*>(ws + wl.condin) : nullptr;
+  float* z = reinterpret_cast<float*>(ws + wl.zout);
+  float* ld = reinterpret_cast<float*>(ws + wl.ldout);
+  std::lock_guard<std::mutex> lock(P->mu);
+  int rc = ensure_device(P);
   if (rc) return rc;
-  e = cudaMemcpyAsync(z_host, ws + wl.zout, bc, cudaMemcpyDeviceToHost, st);
-  if (e != cudaSuccess) return (int)e;
-  e = cudaMemcpyAsync(logdet_host, ws + wl.ldout, sizeof(float) * (size_t)B, cudaMemcpyDeviceToHost, st);
-  return e == cudaSuccess ? 0 : (int)e;
+  ProgramKey key{packed, workspace, B, 0, P->d.n_flows, 0, 0, nullptr};
+  Program* prog = get_program(P, key, &rc);
+  if (!prog) return rc;
+  const HostIO io{x_host, P->d.E > 0 ? cond_host : nullptr, z_host, logdet_host, bc,
+                  sizeof(float) * (size_t)B * std::max(0, (int)P->d.E), bc, sizeof(float) * (size_t)B};
+  return run_program(P, prog, x, cond, z, ld, nullptr, nullptr, static_cast<cudaStream_t>(stream), &io);
 }
 
 int ipoke_inn_reverse_host(ipoke_inn_plan* P, const void* packed, const float* z_host, const float* cond_host,
                            float* x_host, int B, void* workspace, void* stream) {
-  if (!P || !z_host || !x_host || !workspace || B <= 0) return IPOKE_INN_E_INVALID;
+  if (!P || !packed || !z_host || !x_host || !workspace || B <= 0) return IPOKE_INN_E_INVALID;
   if (P->d.E > 0 && !cond_host) return IPOKE_INN_E_INVALID;
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
   const WsLayout wl = ws_layout(P, B);
   char* ws = static_cast<char*>(workspace);
   const size_t bc = sizeof(float) * (size_t)B * P->d.C;
-  cudaError_t e = cudaMemcpyAsync(ws + wl.xin, z_host, bc, cudaMemcpyHostToDevice, st);
-  if (e != cudaSuccess) return (int)e;
-  if (P->d.E > 0) {
-    e = cudaMemcpyAsync(ws + wl.condin, cond_host, sizeof(float) * (size_t)B * P->d.E, cudaMemcpyHostToDevice, st);
-    if (e != cudaSuccess) return (int)e;
-  }
-  int rc = ipoke_inn_reverse(P, packed, reinterpret_cast<float*>(ws + wl.xin),
-                             P->d.E > 0 ? reinterpret_cast<float*>(ws + wl.condin) : nullptr,
-                             reinterpret_cast<float*>(ws + wl.zout), B, 0, P->d.n_flows, workspace, stream);
+  float* z = reinterpret_cast<float*>(ws + wl.xin);
+  float* cond = P->d.E > 0 ? reinterpret_cast<float*>(ws + wl.condin) : nullptr;
+  float* x = reinterpret_cast<float*>(ws + wl.zout);
+  std::lock_guard<std::mutex> lock(P->mu);
+  int rc = ensure_device(P);
   if (rc) return rc;
-  e = cudaMemcpyAsync(x_host, ws + wl.zout, bc, cudaMemcpyDeviceToHost, st);
-  return e == cudaSuccess ? 0 : (int)e;
+  ProgramKey key{packed, workspace, B, 0, P->d.n_flows, 1, 0, nullptr};
+  Program* prog = get_program(P, key, &rc);
+  if (!prog) return rc;
+  const HostIO io{z_host, P->d.E > 0 ? cond_host : nullptr, x_host, nullptr, bc,
+                  sizeof(float) * (size_t)B * std::max(0, (int)P->d.E), bc, 0};
+  return run_program(P, prog, z, cond, x, nullptr, nullptr, nullptr, static_cast<cudaStream_t>(stream), &io);
 }
 
 int ipoke_inn_actnorm_stats(const float* x, int B, int C, double* moments, void* stream) {
