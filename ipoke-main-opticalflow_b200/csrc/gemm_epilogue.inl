@@ -258,7 +258,26 @@
           float v[16];
           tmem_ld16(t_row + c0, v);
           tmem_ld_wait();
+          // whole 16-column group inside one destination and 16-byte aligned: 4 float4 read-modify-writes in flight
+          // (the scalar += chain below is one dependent load-add-store per element: 57 us per launch at cfg A / 4096)
+          float* dst16 = nullptr;
           if (row_ok) {
+            const int cb = n_tile * BN + c0;
+            if (cb + 16 <= p.du_x_cols)
+              dst16 = p.du_state + static_cast<size_t>(row) * p.du_ld_state + p.du_state_off + cb;
+            else if (cb >= p.du_cond_col0 && cb + 16 <= p.du_cond_col0 + p.du_E)
+              dst16 = p.du_cond + static_cast<size_t>(row) * p.du_ld_cond + (cb - p.du_cond_col0);
+            if ((reinterpret_cast<uintptr_t>(dst16) & 15u) != 0) dst16 = nullptr;
+          }
+          if (dst16 != nullptr) {
+            float4* d4 = reinterpret_cast<float4*>(dst16);
+            float4 a4[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) a4[j] = d4[j];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              d4[j] = make_float4(a4[j].x + v[4 * j], a4[j].y + v[4 * j + 1], a4[j].z + v[4 * j + 2], a4[j].w + v[4 * j + 3]);
+          } else if (row_ok) {
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
               const int c = n_tile * BN + c0 + j;

@@ -168,6 +168,8 @@ struct ipoke_inn_plan {
   int hidden_cluster = 0;         // one-wave hidden layers as split-K clusters (hidden_cluster_kernel.cuh): measured SLOWER
                                   // (cfg B b256 734 -> 893 us/step: 16-byte remote stores of a 64 KB partial cost more than
                                   // the halved operand ingest saves; profiles/r01_ab_hcluster_v9.txt) -> off
+  int wgrad_wide = 0;             // wgrad: 128 x 256 tiles with the staging tile aliased onto the pipeline stages: parity green,
+                                  // no gain (cfg A / 4096: 3.59 vs 3.47 ms -- the MN-major wgrad is not ingest-bound) -> off
   int use_pair = 1;               // multi-wave hidden layers as CTA pairs (hidden_pair_kernel.cuh)
   int warp_slab = 1;              // hidden / dgrad epilogue: warp-private output slabs (no CTA barrier inside a tile)
   int tail_cluster = 1;           // small batches: coupling tails as split-K clusters (tail_cluster_kernel.cuh)
@@ -1023,7 +1025,17 @@ struct BwdBuilder : Builder {
     q.m_tiles = (rows_p + BM - 1) / BM;
     int bn = kin_p >= 128 ? 128 : 64;
     if (P->ksplit == 2 && kin_p >= 128) bn = 128;
+    // 128 x 256 tiles when they make one wave (one tile per CTA): the epilogue staging tile (131 KB) then reuses the
+    // idle pipeline stages.  A 128 x 128 tile needs 32 KB per 0.15 us of tensor work (213 GB/s per SM, twice what one
+    // SM ingests: tensor pipe 31 % active, ncu r01 v10); 128 x 256 needs 48 KB per 0.3 us.
+    int alias = 0;
+    if (P->wgrad_wide && kin_p % 256 == 0 && groups * q.m_tiles * (kin_p / 256) <= P->num_sms && q.num_kb >= 8 &&
+        2 * groups * q.m_tiles * (kin_p / 256) > P->num_sms) {
+      bn = 256;
+      alias = 1;
+    }
     q.BN = bn;
+    q.epi_alias = alias;
     q.n_tiles = (kin_p + bn - 1) / bn;
     const int tiles = groups * q.m_tiles * q.n_tiles;
     int ks = 1;
@@ -1034,9 +1046,10 @@ struct BwdBuilder : Builder {
       ks = (q.num_kb + per - 1) / per;                  // no empty slice
     }
     q.kslices = ks;
-    const int avail = kMaxDynSmem - 1024 - SMEM_BARRIER_BYTES - WG_ONES_BYTES - ((wgrad_epi_bytes(bn) + 15) & ~15);
+    const int avail = kMaxDynSmem - 1024 - SMEM_BARRIER_BYTES - WG_ONES_BYTES - (alias ? 0 : ((wgrad_epi_bytes(bn) + 15) & ~15));
     q.stages = std::max(2, std::min(MAX_STAGES, avail / wgrad_stage_bytes(P->ksplit, bn)));
-    q.stages = std::min(q.stages, std::max(2, (q.num_kb + ks - 1) / ks));
+    if (!alias) q.stages = std::min(q.stages, std::max(2, (q.num_kb + ks - 1) / ks));
+    while (alias && q.stages * wgrad_stage_bytes(P->ksplit, bn) < wgrad_epi_bytes(bn)) q.stages++;   // room for the staging tile
     const int acc_cols = bn + 16;
     q.nacc = (2 * acc_cols <= 512) ? 2 : 1;
     int cols = 32;
@@ -1061,7 +1074,7 @@ struct BwdBuilder : Builder {
       wgo.tmY[1] = wgo.tmY[0];
       wgo.tmX[1] = wgo.tmX[0];
     }
-    wgo.smem = wgrad_smem_bytes(P->ksplit, bn, q.stages);
+    wgo.smem = wgrad_smem_bytes(P->ksplit, bn, q.stages, alias);
     wgo.grid = std::min(tiles * ks, P->num_sms);
     if (ks > 1) {
       // split-batch partial sums are added with atomics: clear the destinations first
@@ -1738,6 +1751,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_SLAB4")) P->slab4 = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WARPSLAB")) P->warp_slab = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_PAIR")) P->use_pair = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_WGRAD_WIDE")) P->wgrad_wide = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_HCLUSTER")) P->hidden_cluster = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_STREAMS")) P->streams = std::max(1, std::min(std::atoi(e), 8));
   if (const char* e = std::getenv("IPOKE_INN_KACC")) P->kacc_max = std::atoi(e);

@@ -38,6 +38,8 @@ struct WgradParams {
   int stages;
   int tmem_cols, nacc;
   int epi_off;            // byte offset of the epilogue staging tile
+  int epi_alias;          // 1: the staging tile reuses the pipeline stages (one tile per CTA: they are idle once the last
+                          //    MMA has retired), which is what lets a 128 x 256 tile keep 4 stages in flight
   int dy_col0, dy_group_stride;   // columns of dY: dy_col0 + g * stride + m_tile * 128
   int x_col0, x_group_stride;     // columns of X
   int rows_valid;         // true number of output features per group (H or C/2)
@@ -52,9 +54,9 @@ struct WgradParams {
 
 __host__ inline int wgrad_stage_bytes(int ksplit, int BN) { return ksplit * (2 + BN / 64) * WG_CHUNK_BYTES; }
 __host__ __device__ inline int wgrad_epi_bytes(int BN) { return BM * (BN + 1) * 4; }
-__host__ inline int wgrad_smem_bytes(int ksplit, int BN, int stages) {
-  return 1024 + stages * wgrad_stage_bytes(ksplit, BN) + WG_ONES_BYTES + ((wgrad_epi_bytes(BN) + 15) & ~15) +
-         SMEM_BARRIER_BYTES;
+__host__ inline int wgrad_smem_bytes(int ksplit, int BN, int stages, int epi_alias = 0) {
+  return 1024 + stages * wgrad_stage_bytes(ksplit, BN) + WG_ONES_BYTES +
+         (epi_alias ? 0 : ((wgrad_epi_bytes(BN) + 15) & ~15)) + SMEM_BARRIER_BYTES;
 }
 
 template <int kSplit>
@@ -74,8 +76,9 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
   const int nacc = p.nacc;
 
   uint8_t* ones_smem = smem + stages * stage_bytes;
-  float* epi_tile = reinterpret_cast<float*>(ones_smem + WG_ONES_BYTES);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(epi_tile) + ((wgrad_epi_bytes(BN) + 15) & ~15));
+  float* epi_tile = p.epi_alias ? reinterpret_cast<float*>(smem) : reinterpret_cast<float*>(ones_smem + WG_ONES_BYTES);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(ones_smem + WG_ONES_BYTES +
+                                                   (p.epi_alias ? 0 : ((wgrad_epi_bytes(BN) + 15) & ~15)));
   uint64_t* empty_bar = full_bar + MAX_STAGES;
   uint64_t* tfull_bar = empty_bar + MAX_STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;

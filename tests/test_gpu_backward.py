@@ -160,3 +160,33 @@ def test_chunked_backward_equals_single_call_and_accumulates():
     ((z.reshape(B, -1) * dz.to(dev)).sum() + (ld * dld.to(dev)).sum()).backward()
     for a, p in zip(g1, net.parameters()):
         assert torch.allclose(p.grad, 2 * a, rtol=0, atol=2e-6 * float(a.abs().max()) + 1e-12)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_wide_wgrad_tiles_equal_the_128_column_path(precision):
+    """128 x 256 wgrad tiles (epilogue staging aliased onto the pipeline stages, one tile per CTA) against the 128 x 128
+    path the oracle tests above cover: same products, same accumulation order per element."""
+    import os
+    cfg = dict(flow_in_channels=64, flow_mid_channels_factor=16, flow_hidden_depth=1, n_flows=2,
+               flow_conditioning_option="none", flow_embedding_channels=32)      # H = 1024: 'cond' block = 128 wide tiles
+    dev, B = _dev(), 512
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(B, 64, generator=g).to(dev)
+    cond = torch.randn(B, 32, 1, 1, generator=g).to(dev)
+    dz, dld = torch.randn(B, 64, generator=g).to(dev), torch.randn(B, generator=g).to(dev)
+    grads = {}
+    for wide in ("1", "0"):
+        os.environ["IPOKE_INN_WGRAD_WIDE"] = wide                 # read at plan creation (first call)
+        try:
+            torch.manual_seed(42)
+            net = P.SupervisedTransformer(dict(cfg), precision=precision).to(dev)
+            with torch.no_grad():
+                net(x, cond)                                       # ActNorm data init (identical for both)
+            z, ld = net(x, cond)
+            ((z.reshape(B, -1) * dz).sum() + (ld * dld).sum()).backward()
+            grads[wide] = {k: p.grad.detach().cpu().numpy().copy() for k, p in net.named_parameters()}
+        finally:
+            del os.environ["IPOKE_INN_WGRAD_WIDE"]
+    for k in grads["1"]:
+        assert np.isfinite(grads["1"][k]).all(), k
+        assert max_rel(grads["1"][k], grads["0"][k]) < 1e-5, k
