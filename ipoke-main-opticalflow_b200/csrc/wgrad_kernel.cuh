@@ -213,7 +213,6 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
     // ============================ epilogue ================================
     grid_dep_wait();
     const int q = warp - 4;
-    const int tid_e = threadIdx.x - 128;
     const int r_loc = q * 32 + lane;
     const int ldt = BN + 1;
     const bool atomic = p.kslices > 1;
@@ -257,21 +256,44 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
       // coalesced write-out: consecutive threads -> consecutive gradient columns of one row
       float* gw = p.gw[g];
       const int col_base = n_tile * BN;
-      // one warp per row, lanes along the columns: no per-element index arithmetic (an `idx / BN` loop here cost 22 % of
-      // the kernel's instructions and left the last tile's write-out exposed: ncu r01 v10)
-      for (int r = q; r < BM; r += 4) {
-        const int grow = m_tile * BM + r;
-        if (grow >= p.rows_valid) break;                            // rows only grow with r
-        float* drow = gw + static_cast<size_t>(grow) * p.ld_gw;
-        const float* srow = epi_tile + r * ldt;
-        for (int c = lane; c < BN; c += 32) {
-          const int xcol = col_base + c;
-          int gcol = -1;
-          if (xcol < p.seg0_valid) gcol = xcol;
-          else if (xcol >= p.seg1_start && xcol < p.seg1_start + p.seg1_valid) gcol = xcol - p.seg1_start + p.seg0_valid;
-          if (gcol >= 0) {
-            if (atomic) atomicAdd(drow + gcol, srow[c]);
-            else drow[gcol] = srow[c];
+      // one warp per row, lanes along the columns: the column -> gradient-column map is row-invariant (computed once
+      // per tile), and two rows' smem reads are issued before their stores so the loop is not one dependent
+      // ld.shared -> st.global chain per element (at batch 64 the write-out IS the kernel: ncu r01 v11)
+      const int ncb = BN >> 5;                                      // 32-column groups per row: 2, 4 or 8
+      int gc[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int xcol = col_base + lane + 32 * k;
+        gc[k] = -1;
+        if (k < ncb) {
+          if (xcol < p.seg0_valid) gc[k] = xcol;
+          else if (xcol >= p.seg1_start && xcol < p.seg1_start + p.seg1_valid) gc[k] = xcol - p.seg1_start + p.seg0_valid;
+        }
+      }
+      const int rows_here = min(BM, p.rows_valid - m_tile * BM);
+      for (int r = q; r < rows_here; r += 8) {
+        const int r2 = r + 4;
+        const bool two = r2 < rows_here;
+        float va[8], vb[8];
+        const float* sa = epi_tile + r * ldt + lane;
+        const float* sb = epi_tile + r2 * ldt + lane;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          va[k] = (k < ncb) ? sa[32 * k] : 0.f;
+          vb[k] = (k < ncb && two) ? sb[32 * k] : 0.f;
+        }
+        float* da = gw + static_cast<size_t>(m_tile * BM + r) * p.ld_gw;
+        float* db = gw + static_cast<size_t>(m_tile * BM + r2) * p.ld_gw;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          if (k < ncb && gc[k] >= 0) {
+            if (atomic) {
+              atomicAdd(da + gc[k], va[k]);
+              if (two) atomicAdd(db + gc[k], vb[k]);
+            } else {
+              da[gc[k]] = va[k];
+              if (two) db[gc[k]] = vb[k];
+            }
           }
         }
       }
