@@ -28,8 +28,8 @@ constexpr int SLAB_BYTES = BM * 128;    // one 128 x 64 bf16 output slab (TMA st
 constexpr int MAX_STAGES = 8;
 constexpr int GEMM_THREADS = 384;       // warps 0-3: TMA / MMA / TMEM alloc / idle; warps 4-11: epilogue
 constexpr int EPI_THREADS = 256;        // two warps per TMEM lane quarter, each takes half of the columns
-constexpr int WG_THREADS = 256;         // wgrad kernel (wgrad_kernel.cuh) keeps one epilogue warp per quarter
-constexpr int WG_EPI_THREADS = 128;
+constexpr int WG_THREADS = 384;         // wgrad kernel (wgrad_kernel.cuh): two epilogue warps per TMEM lane quarter as well
+constexpr int WG_EPI_THREADS = 256;
 constexpr int SMEM_BARRIER_BYTES = 256;
 
 enum EpiMode { EPI_HIDDEN = 0, EPI_TAIL_FWD = 1, EPI_TAIL_REV = 2, EPI_DGRAD = 3, EPI_DU = 4 };

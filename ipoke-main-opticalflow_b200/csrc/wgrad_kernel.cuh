@@ -16,7 +16,7 @@
 //
 // kSplit = 2 (fp32-parity mode): lo*hi + hi*lo + hi*hi as in the forward kernel.
 // Warp roles as in gemm_kernel.cuh: warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator,
-// warps 4-7 epilogue (TMEM -> regs -> padded smem tile -> coalesced fp32 stores / atomics into the
+// warps 4-11 epilogue (TMEM -> regs -> padded smem tile -> coalesced fp32 stores / atomics into the
 // parameter-gradient tensors, which keep the reference's [out, in] layout and true sizes).
 #pragma once
 #include "gemm_kernel.cuh"
@@ -212,7 +212,9 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
   } else if (warp >= 4) {
     // ============================ epilogue ================================
     grid_dep_wait();
-    const int q = warp - 4;
+    const int q = warp & 3;                                       // TMEM lane quarter (== warp % 4)
+    const int ch = (warp - 4) >> 2;                               // column half this warp moves out of TMEM
+    const int we = warp - 4;                                      // 0..7: row phase of the write-out
     const int r_loc = q * 32 + lane;
     const int ldt = BN + 1;
     const bool atomic = p.kslices > 1;
@@ -233,7 +235,7 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
       mbar_wait(&tfull_bar[acc], acc_phase, 14);
       tc_fence_after();
       float* my = epi_tile + r_loc * ldt;
-      for (int c0 = 0; c0 < BN; c0 += 16) {
+      for (int c0 = ch * (BN >> 1); c0 < (ch + 1) * (BN >> 1); c0 += 16) {
         float v[16];
         tmem_ld16(t_row + c0, v);
         tmem_ld_wait();
@@ -241,7 +243,7 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
         for (int j = 0; j < 16; ++j) my[c0 + j] = v[j];
       }
       const int row = m_tile * BM + r_loc;                       // output feature inside the group
-      if (n_tile == 0) {
+      if (n_tile == 0 && ch == 0) {
         float v[16];
         tmem_ld16(t_row + BN, v);
         tmem_ld_wait();
@@ -271,8 +273,8 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
         }
       }
       const int rows_here = min(BM, p.rows_valid - m_tile * BM);
-      for (int r = q; r < rows_here; r += 8) {
-        const int r2 = r + 4;
+      for (int r = we; r < rows_here; r += 16) {
+        const int r2 = r + 8;
         const bool two = r2 < rows_here;
         float va[8], vb[8];
         const float* sa = epi_tile + r * ldt + lane;
