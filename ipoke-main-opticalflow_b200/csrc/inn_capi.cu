@@ -117,8 +117,16 @@ struct Program {
   int launches = 0;
   std::vector<GraphEntry> graphs;     // instantiated CUDA graphs keyed by the caller's pointers
   int graph_misses = 0, graph_hits = 0;
+  struct BwdGraph {                   // backward programs: keyed by every pointer the launches are patched with
+    std::vector<const void*> key;
+    cudaGraphExec_t exec = nullptr;
+    unsigned long long last_use = 0;
+  };
+  std::vector<BwdGraph> bwd_graphs;
   ~Program() {
     for (auto& g : graphs)
+      if (g.exec) cudaGraphExecDestroy(g.exec);
+    for (auto& g : bwd_graphs)
       if (g.exec) cudaGraphExecDestroy(g.exec);
   }
 };
@@ -168,6 +176,7 @@ struct ipoke_inn_plan {
   int hidden_cluster = 0;         // one-wave hidden layers as split-K clusters (hidden_cluster_kernel.cuh): measured SLOWER
                                   // (cfg B b256 734 -> 893 us/step: 16-byte remote stores of a 64 KB partial cost more than
                                   // the halved operand ingest saves; profiles/r01_ab_hcluster_v9.txt) -> off
+  int bwd_graph = 1;              // replay the backward pass as a CUDA graph when the caller's pointers repeat
   int wgrad_wide = 0;             // wgrad: 128 x 256 tiles with the staging tile aliased onto the pipeline stages: parity green,
                                   // no gain (cfg A / 4096: 3.59 vs 3.47 ms -- the MN-major wgrad is not ingest-bound) -> off
   int use_pair = 1;               // multi-wave hidden layers as CTA pairs (hidden_pair_kernel.cuh)
@@ -1507,6 +1516,63 @@ int issue_backward(ipoke_inn_plan* P, Program* prog, const BwdArgs& a, cudaStrea
   return 0;
 }
 
+// Backward as a CUDA graph when every pointer of the call repeats (a steady training loop under the caching allocator):
+// at the reference's batch of 64 the step is bound by the host issuing ~150 launches, not by the kernels.
+int run_backward(ipoke_inn_plan* P, Program* prog, const BwdArgs& a, cudaStream_t st) {
+  if (!P->use_graph || !P->bwd_graph || P->profile || prog->graph_misses > 8 + 4 * prog->graph_hits)
+    return issue_backward(P, prog, a, st);
+  std::vector<const void*> key;
+  key.reserve(8 + 2 * prog->ops.size());
+  key.push_back(a.x); key.push_back(a.block_outs); key.push_back(a.dz); key.push_back(a.dlogdet);
+  key.push_back(a.dx); key.push_back(a.dcond);
+  for (const Op& o : prog->ops) {
+    if (o.kind == OP_ZERO_GRAD) { key.push_back(a.grad_w[o.lin]); key.push_back(a.grad_b[o.lin]); }
+    else if (o.kind == OP_WGRAD) {
+      const WgradOp& wg = prog->wgrads[o.wgrad];
+      for (int g = 0; g < wg.p.G; ++g) { key.push_back(a.grad_w[wg.lin[g]]); key.push_back(a.grad_b[wg.lin[g]]); }
+    } else if (o.kind == OP_BOUNDARY_BWD) { key.push_back(a.grad_loc[o.block_index]); key.push_back(a.grad_scale[o.block_index]); }
+  }
+  ++P->tick;
+  for (auto& g : prog->bwd_graphs)
+    if (g.key == key) {
+      g.last_use = P->tick;
+      ++prog->graph_hits;
+      cudaError_t e = cudaGraphLaunch(g.exec, st);
+      P->last_launches = prog->launches;
+      return e == cudaSuccess ? 0 : (int)e;
+    }
+  ++prog->graph_misses;
+  if (!P->cap_stream) {
+    cudaError_t e = cudaStreamCreateWithFlags(&P->cap_stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) return (int)e;
+  }
+  cudaError_t e = cudaStreamBeginCapture(P->cap_stream, cudaStreamCaptureModeThreadLocal);
+  if (e != cudaSuccess) return (int)e;
+  const int rc = issue_backward(P, prog, a, P->cap_stream);
+  cudaGraph_t graph = nullptr;
+  e = cudaStreamEndCapture(P->cap_stream, &graph);
+  cudaGraphExec_t exec = nullptr;
+  if (rc == 0 && e == cudaSuccess && graph != nullptr) e = cudaGraphInstantiate(&exec, graph, 0);
+  if (graph) cudaGraphDestroy(graph);
+  if (rc != 0 || e != cudaSuccess || exec == nullptr) {
+    cudaGetLastError();
+    P->bwd_graph = 0;                 // capture unsupported here: plain launches for good
+    return issue_backward(P, prog, a, st);
+  }
+  if (prog->bwd_graphs.size() >= 2) {
+    size_t lru = prog->bwd_graphs[0].last_use <= prog->bwd_graphs[1].last_use ? 0 : 1;
+    cudaGraphExecDestroy(prog->bwd_graphs[lru].exec);
+    prog->bwd_graphs.erase(prog->bwd_graphs.begin() + lru);
+  }
+  Program::BwdGraph bg;
+  bg.key = std::move(key);
+  bg.exec = exec;
+  bg.last_use = P->tick;
+  prog->bwd_graphs.push_back(std::move(bg));
+  e = cudaGraphLaunch(exec, st);
+  return e == cudaSuccess ? 0 : (int)e;
+}
+
 int issue_program(ipoke_inn_plan* P, Program* prog, const float* in, const float* cond, float* out, float* logdet_out,
                   float* block_outs, float* block_lds, cudaStream_t st) {
   const long long BC = (long long)prog->key.B * P->d.C;
@@ -1752,6 +1818,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_WARPSLAB")) P->warp_slab = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_PAIR")) P->use_pair = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WGRAD_WIDE")) P->wgrad_wide = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_BWD_GRAPH")) P->bwd_graph = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_HCLUSTER")) P->hidden_cluster = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_STREAMS")) P->streams = std::max(1, std::min(std::atoi(e), 8));
   if (const char* e = std::getenv("IPOKE_INN_KACC")) P->kacc_max = std::atoi(e);
@@ -1954,7 +2021,7 @@ int ipoke_inn_backward(ipoke_inn_plan* P, const void* packed, const float* x, co
   Program* prog = get_program(P, key, &rc);
   if (!prog) return rc;
   BwdArgs a{x, block_outs, dz, dlogdet, dx, dcond, grad_w, grad_b, grad_loc, grad_scale};
-  return issue_backward(P, prog, a, static_cast<cudaStream_t>(stream));
+  return run_backward(P, prog, a, static_cast<cudaStream_t>(stream));
 }
 
 int ipoke_inn_reverse(ipoke_inn_plan* P, const void* packed, const float* z, const float* cond, float* x, int B,

@@ -190,3 +190,37 @@ def test_wide_wgrad_tiles_equal_the_128_column_path(precision):
     for k in grads["1"]:
         assert np.isfinite(grads["1"][k]).all(), k
         assert max_rel(grads["1"][k], grads["0"][k]) < 1e-5, k
+
+
+def test_backward_graph_replay_equals_plain_launches():
+    """A steady training loop hands the backward the same pointers every step (caching allocator): from the second
+    step on it replays a captured CUDA graph.  Gradients of replayed steps must equal those of plain launches
+    (IPOKE_INN_BWD_GRAPH=0) -- same kernels, same order; fp32 atomics (log-det, split-batch wgrad) allow last-bit noise."""
+    import os
+    name, B = "cfgA_mini", 96
+    dev = _dev()
+    g = torch.Generator().manual_seed(21)
+    kind, kw = CFG[name]
+    x = torch.randn(B, kw["flow_in_channels"], generator=g).to(dev)
+    cond = torch.randn(B, kw["flow_embedding_channels"], 1, 1, generator=g).to(dev)
+    dz, dld = torch.randn(B, kw["flow_in_channels"], generator=g).to(dev), torch.randn(B, generator=g).to(dev)
+    res = {}
+    for mode in ("1", "0"):
+        os.environ["IPOKE_INN_BWD_GRAPH"] = mode
+        try:
+            net, _, _ = _load(name, "fp32")
+            steps = []
+            for it in range(4):
+                net.zero_grad(set_to_none=True)
+                xg = x.clone().requires_grad_(True)
+                z, ld = net(xg, cond)
+                ((z.reshape(B, -1) * dz).sum() + (ld * dld).sum()).backward()
+                steps.append({k: p.grad.detach().cpu().numpy().copy() for k, p in net.named_parameters()})
+                steps[-1]["__dx"] = xg.grad.detach().cpu().numpy().copy()
+            res[mode] = steps
+        finally:
+            del os.environ["IPOKE_INN_BWD_GRAPH"]
+    for it in range(4):
+        for k in res["1"][it]:
+            assert max_rel(res["1"][it][k], res["0"][it][k]) < 1e-5, (it, k)
+            assert max_rel(res["1"][it][k], res["1"][0][k]) < 1e-5, (it, k)
