@@ -2178,6 +2178,7 @@ int ipoke_inn_set_option(ipoke_inn_plan* P, const char* name, int value) {
   if (!P || !name) return IPOKE_INN_E_INVALID;
   std::lock_guard<std::mutex> lock(P->mu);
   if (std::strcmp(name, "graph") == 0) P->use_graph = value != 0;
+  else if (std::strcmp(name, "bwd_graph") == 0) P->bwd_graph = value != 0;
   else if (std::strcmp(name, "pdl") == 0) { P->use_pdl = value != 0; P->programs.clear(); }
   else if (std::strcmp(name, "mcast") == 0) { P->use_mcast = value == 1 ? 8 : value; P->programs.clear(); }
   else if (std::strcmp(name, "fold") == 0) { P->use_fold = value != 0; P->programs.clear(); }
