@@ -216,7 +216,7 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
     const int ch = (warp - 4) >> 2;                               // column half this warp moves out of TMEM
     const int we = warp - 4;                                      // 0..7: row phase of the write-out
     const int r_loc = q * 32 + lane;
-    const int ldt = BN + 1;
+    const int ldt = BN;
     const bool atomic = p.kslices > 1;
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
@@ -234,13 +234,16 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
       if (kb0 >= kb1) continue;                                  // empty slice (never scheduled by the host)
       mbar_wait(&tfull_bar[acc], acc_phase, 14);
       tc_fence_after();
-      float* my = epi_tile + r_loc * ldt;
+      // staging tile: row stride BN floats, the 16-byte chunk index XORed with (row & 7) -- the drain (lanes = rows) and
+      // the write-out (lanes = chunks of one row) are both conflict-free with 128-bit shared accesses
+      float4* my4 = reinterpret_cast<float4*>(epi_tile + r_loc * ldt);
       for (int c0 = ch * (BN >> 1); c0 < (ch + 1) * (BN >> 1); c0 += 16) {
         float v[16];
         tmem_ld16(t_row + c0, v);
         tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 16; ++j) my[c0 + j] = v[j];
+        for (int j = 0; j < 4; ++j)
+          my4[((c0 >> 2) + j) ^ (r_loc & 7)] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
       }
       const int row = m_tile * BM + r_loc;                       // output feature inside the group
       if (n_tile == 0 && ch == 0) {
@@ -273,16 +276,53 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
         }
       }
       const int rows_here = min(BM, p.rows_valid - m_tile * BM);
+      const bool vec = !atomic && ((p.seg0_valid | p.seg1_start | p.seg1_valid | p.ld_gw) & 3) == 0 &&
+                       (reinterpret_cast<uintptr_t>(gw) & 15) == 0;
+      if (vec) {
+        // one warp per row, one 16-byte chunk per lane, four rows in flight
+        const int nch = BN >> 2;                                    // chunks per row: 16, 32 or 64
+        int gc4[2];
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          const int chunk = lane + 32 * k;
+          const int xcol = col_base + 4 * chunk;
+          gc4[k] = -1;
+          if (chunk < nch) {
+            if (xcol < p.seg0_valid) gc4[k] = xcol;
+            else if (xcol >= p.seg1_start && xcol < p.seg1_start + p.seg1_valid) gc4[k] = xcol - p.seg1_start + p.seg0_valid;
+          }
+        }
+        for (int r0 = we; r0 < rows_here; r0 += 32) {
+          float4 v[4][2];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int r = r0 + 8 * i;
+            const float4* s4 = reinterpret_cast<const float4*>(epi_tile + r * ldt);
+#pragma unroll
+            for (int k = 0; k < 2; ++k)
+              if (r < rows_here && gc4[k] >= 0) v[i][k] = s4[(lane + 32 * k) ^ (r & 7)];
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int r = r0 + 8 * i;
+            float* d = gw + static_cast<size_t>(m_tile * BM + r) * p.ld_gw;
+#pragma unroll
+            for (int k = 0; k < 2; ++k)
+              if (r < rows_here && gc4[k] >= 0) *reinterpret_cast<float4*>(d + gc4[k]) = v[i][k];
+          }
+        }
+      } else {
       for (int r = we; r < rows_here; r += 16) {
         const int r2 = r + 8;
         const bool two = r2 < rows_here;
         float va[8], vb[8];
-        const float* sa = epi_tile + r * ldt + lane;
-        const float* sb = epi_tile + r2 * ldt + lane;
+        const float* sa = epi_tile + r * ldt;
+        const float* sb = epi_tile + r2 * ldt;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          va[k] = (k < ncb) ? sa[32 * k] : 0.f;
-          vb[k] = (k < ncb && two) ? sb[32 * k] : 0.f;
+          const int c = lane + 32 * k;
+          va[k] = (k < ncb) ? sa[((((c >> 2) ^ (r & 7)) << 2) | (c & 3))] : 0.f;
+          vb[k] = (k < ncb && two) ? sb[((((c >> 2) ^ (r2 & 7)) << 2) | (c & 3))] : 0.f;
         }
         float* da = gw + static_cast<size_t>(m_tile * BM + r) * p.ld_gw;
         float* db = gw + static_cast<size_t>(m_tile * BM + r2) * p.ld_gw;
@@ -298,6 +338,7 @@ inn_wgrad_kernel(const __grid_constant__ CUtensorMap tmY0, const __grid_constant
             }
           }
         }
+      }
       }
       named_bar_sync(1, WG_EPI_THREADS);                            // staging tile is reused by the next tile
     }
