@@ -6,6 +6,7 @@ Parameter gradients are written by the kernels straight into ONE flat fp32 buffe
 ``flow.parameters()`` order; autograd receives views of it (AccumulateGrad adopts them without a copy when
 ``.grad`` is None), and ``engine.last_flat_grad`` / ``engine.grad_layout()`` expose the buffer so that the
 gradient all-reduce of the training step is a few large NCCL calls on contiguous memory (parallel.GradSync).
+``engine.direct_param_grads = True`` (opt-in) assigns the views to ``p.grad`` inside backward() instead.
 """
 import torch
 
@@ -54,4 +55,21 @@ class FlowFunction(torch.autograd.Function):
         ctx.saved_buf = None
         gx = dx.view(ctx.x_shape) if (need_x and dx is not None) else None
         gc = dcond.view(ctx.cond_shape) if (need_c and dcond is not None) else None
+        if engine.direct_param_grads:
+            # opt-in (engine.direct_param_grads = True): hand the views to the parameters here instead of through one
+            # AccumulateGrad node per parameter -- the autograd engine's per-tensor bookkeeping for the few hundred
+            # parameters of a flow costs more host time than the batch-64 kernels take.  Same values in ``.grad``
+            # (adopted when it is None, accumulated otherwise); per-parameter autograd hooks do not fire and
+            # ``torch.autograd.grad(..., params)`` sees None, which is why it is not the default.
+            params = engine.grad_layout()[3]
+            acc_p, acc_v = [], []
+            for p, v in zip(params, views):
+                if p.grad is None:
+                    p.grad = v
+                else:
+                    acc_p.append(p.grad)
+                    acc_v.append(v)
+            if acc_p:
+                torch._foreach_add_(acc_p, acc_v)
+            return (None, gx, gc) + (None,) * len(views)
         return (None, gx, gc) + tuple(views)

@@ -39,6 +39,7 @@ class FlowEngine:
         self.grad_ready_hook = None           # callable(engine, flat_grad, block_begin, block_end): see parallel.GradSync
         self.grad_chunk_blocks = 2
         self.last_flat_grad = None
+        self.direct_param_grads = False       # True: backward() assigns / accumulates p.grad itself (see backward.py)
         self._grad_layout = None
         self.streams = 1
 
@@ -68,6 +69,22 @@ class FlowEngine:
             pass
 
     def _tensors(self):
+        # walked once and cached: the walk over 16 blocks x 4 subnetworks costs as much host time per call as a
+        # third of the batch-64 forward.  Parameter objects survive .to() / load_state_dict() / optimizer steps; the
+        # key (identity of every block's ActNorm parameters and of the first / last Linear) catches rebuilt blocks.
+        blocks = self.flow.sub_layers
+        key = tuple(id(b.norm_layer.loc) for b in blocks) + (
+            id(blocks[0].coupling.s[0].linears()[0].weight), id(blocks[-1].coupling.t[1].linears()[-1].weight))
+        cached = getattr(self, "_tensors_cache", None)
+        if cached is not None and cached[0] == key:
+            return cached[1]
+        out = self._walk_tensors()
+        self._tensors_cache = (key, out)
+        self._grad_layout = None
+        self._grad_ptr_offs = None
+        return out
+
+    def _walk_tensors(self):
         blocks = self.flow.sub_layers
         lin_w, lin_b = [], []
         for blk in blocks:
@@ -346,15 +363,13 @@ class FlowEngine:
         offs, total, block_ranges, params = self.grad_layout()
         flat = torch.empty(total, dtype=torch.float32, device=self._device)
         base = flat.data_ptr()
-        lin_w, lin_b, loc, scale, _, _ = self._tensors()
-
-        def ptrs(tensors):
-            arr = (ctypes.c_void_p * len(tensors))()
-            for i, t in enumerate(tensors):
-                arr[i] = base + 4 * offs[id(t)][0]
-            return arr
-        views = [flat[offs[id(p)][0]: offs[id(p)][0] + offs[id(p)][1]].view(offs[id(p)][2]) for p in params]
-        return flat, views, (ptrs(lin_w), ptrs(lin_b), ptrs(loc), ptrs(scale))
+        if getattr(self, "_grad_ptr_offs", None) is None:          # byte offsets per C-ABI pointer array, built once
+            lin_w, lin_b, loc, scale, _, _ = self._tensors()
+            self._grad_ptr_offs = [[4 * offs[id(t)][0] for t in ts] for ts in (lin_w, lin_b, loc, scale)]
+        arrays = tuple((ctypes.c_void_p * len(o))(*[base + b for b in o]) for o in self._grad_ptr_offs)
+        # one C++ call for all the views (a Python slice + view per parameter costs more than the batch-64 kernels)
+        views = list(torch._utils._unflatten_dense_tensors(flat, params))
+        return flat, views, arrays
 
     def backward(self, x2, c2, outs, saved, dz, dld, grad_ptrs, want_dx=True, want_dcond=True, block_begin=0,
                  block_end=None, dcond=None):

@@ -224,3 +224,32 @@ def test_backward_graph_replay_equals_plain_launches():
         for k in res["1"][it]:
             assert max_rel(res["1"][it][k], res["0"][it][k]) < 1e-5, (it, k)
             assert max_rel(res["1"][it][k], res["1"][0][k]) < 1e-5, (it, k)
+
+
+def test_direct_param_grads_equal_autograd_accumulation():
+    """engine.direct_param_grads = True assigns the flat-buffer views to p.grad inside backward(): same gradients as
+    the AccumulateGrad route after one backward, and the same sums after a second backward without zero_grad."""
+    name, B = "cfgS_cond", 40
+    dev = _dev()
+    g = torch.Generator().manual_seed(5)
+    kind, kw = CFG[name]
+    x = torch.randn(B, kw["flow_in_channels"], generator=g).to(dev)
+    cond = torch.randn(B, kw["flow_embedding_channels"], 1, 1, generator=g).to(dev)
+    res = {}
+    for direct in (False, True):
+        net, _, _ = _load(name, "fp32")
+        net.flow.engine.direct_param_grads = direct
+        out = []
+        for it in range(2):                                   # second pass accumulates into the existing .grad
+            xg = x.clone().requires_grad_(True)
+            z, ld = net(xg, cond)
+            loss, _ = P.FlowLoss()(z, ld)
+            loss.backward()
+            out.append({k: p.grad.detach().cpu().numpy().copy() for k, p in net.named_parameters()})
+            out[-1]["__dx"] = xg.grad.detach().cpu().numpy().copy()
+        res[direct] = out
+    for it in range(2):
+        for k in res[False][it]:
+            assert max_rel(res[True][it][k], res[False][it][k]) < 1e-5, (it, k)
+    k0 = next(k for k in res[True][0] if k != "__dx")
+    assert max_rel(res[True][1][k0], 2 * res[True][0][k0]) < 1e-4      # really accumulated
