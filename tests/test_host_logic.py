@@ -155,3 +155,21 @@ def test_install_as_reference_shadows_import_paths():
     assert FlowLoss is P.FlowLoss
     for k in [k for k in sys.modules if k.startswith("models")]:
         del sys.modules[k]
+
+
+def test_engine_parameter_walk_is_cached_and_follows_replaced_parameters():
+    """engine._tensors() walks the module tree once; load_state_dict keeps the Parameter objects (cache stays valid),
+    a rebuilt ActNorm parameter changes the key and triggers a new walk (and a new gradient layout)."""
+    net = build("cfgS_cond")
+    eng = net.flow.engine
+    t0 = eng._tensors()
+    assert eng._tensors() is t0
+    net.load_state_dict(net.state_dict())
+    assert eng._tensors() is t0
+    lay0 = eng.grad_layout()
+    blk = net.flow.sub_layers[3]
+    blk.norm_layer.loc = torch.nn.Parameter(blk.norm_layer.loc.detach().clone())
+    t1 = eng._tensors()
+    assert t1 is not t0 and t1[2][3] is blk.norm_layer.loc
+    assert eng.grad_layout() is not lay0
+    assert set(id(p) for p in eng.grad_layout()[3]) == set(id(p) for p in net.flow.parameters())
