@@ -185,6 +185,8 @@ struct ipoke_inn_plan {
   int dbg = 0;
   int kacc_max = 1;               // K-interleaved accumulators: measured no gain once the MMA issue is uniform
   int hidden_bn_force = 0;       // debug: fixed tile width of the hidden-layer GEMMs
+  int widek_cover = 30;          // SM coverage target (%) of the hidden GEMMs when Hp > 1024 and ...
+  int widek_mtiles = 8;          // ... the batch has at most this many 128-row tiles (one request at a time)
   unsigned long long* trace_buf = nullptr;   // ipoke_inn_debug_trace
   int trace_slots = 0;
   int use_fold = 1;              // inference programs: block boundaries folded into the coupling tails
@@ -367,7 +369,8 @@ TileCfg tile_cfg(int ksplit, int mode, int bn, int direct = 0) {
 
 // Largest UMMA N that divides `rows_per_group`, keeps >= 2 pipeline stages and still yields about one CTA
 // per SM; otherwise the smallest (most tiles) -- small batches are latency/weight-streaming bound.
-TileCfg pick_bn(const ipoke_inn_plan* P, int mode, int rows_per_group, int tiles_other, int bn_max = 256) {
+TileCfg pick_bn(const ipoke_inn_plan* P, int mode, int rows_per_group, int tiles_other, int bn_max = 256,
+                int cover_pct = 80) {
   static const int cand[5] = {256, 128, 64, 32, 16};
   TileCfg best;
   for (int i = 0; i < 5; ++i) {
@@ -376,7 +379,7 @@ TileCfg pick_bn(const ipoke_inn_plan* P, int mode, int rows_per_group, int tiles
     const TileCfg t = tile_cfg(P->ksplit, mode, bn);
     if (t.stages < 2) continue;
     best = t;
-    if ((long long)tiles_other * (rows_per_group / bn) >= (long long)(P->num_sms / P->streams * 4) / 5) return t;
+    if ((long long)tiles_other * (rows_per_group / bn) * 100 >= (long long)(P->num_sms / P->streams) * cover_pct) return t;
   }
   return best;
 }
@@ -535,7 +538,13 @@ struct Builder {
     const int m_tiles = (B + BM - 1) / BM;
     gemm_rows = B;
     gemm_m_tiles = m_tiles;
-    TileCfg tc = pick_bn(P, EPI_HIDDEN, P->Hp, m_tiles * c.G);
+    // Every CTA pulls a whole 128 x K activation panel through its L2 port: for wide hidden layers (K = Hp > 1024,
+    // > 256 KB per panel) at one or two row tiles, covering 80 % of the SMs with narrow tiles multiplies that traffic --
+    // cfg A (Hp 1536) batch 64 / 256: 48 CTAs of 64- / 128-wide tiles beat the 96 - 192 CTAs of the 80 % rule by 25 % /
+    // 23 % per step, batch 512 / 1024 gain 6 % / 4 % (profiles/r01_ab_hidden_bn_v13.txt).  cfg B (Hp 1024) keeps the
+    // 80 % rule it was tuned on, and so do plans sized for concurrent requests (streams > 1: measured 3 % slower).
+    const int cover = (P->Hp > 1024 && m_tiles <= P->widek_mtiles && P->streams == 1) ? P->widek_cover : 80;
+    TileCfg tc = pick_bn(P, EPI_HIDDEN, P->Hp, m_tiles * c.G, 256, cover);
     if (P->hidden_bn_force > 0 && P->Hp % P->hidden_bn_force == 0) tc = tile_cfg(P->ksplit, EPI_HIDDEN, P->hidden_bn_force);
     const int bn = tc.bn;
     tc.mc = pick_mc(P, m_tiles * (rows / bn), rows / bn, P->Hp / bn);
@@ -1810,6 +1819,8 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_FASTB")) P->fast_boundary = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_TAIL_BN")) P->tail_bn_max = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_HIDDEN_BN")) P->hidden_bn_force = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_WIDEK_COVER")) P->widek_cover = std::max(1, std::atoi(e));
+  if (const char* e = std::getenv("IPOKE_INN_WIDEK_MT")) P->widek_mtiles = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_KROT")) P->k_rotate = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_DBG")) P->dbg = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_DIRECT")) P->tail_direct = std::atoi(e);
