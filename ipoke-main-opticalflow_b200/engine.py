@@ -53,9 +53,13 @@ class FlowEngine:
             _capi.check(_capi.lib().ipoke_inn_set_option(self._plan, b"streams", self.streams), "set_option")
 
     def invalidate(self):
-        """Force a repack before the next call (after out-of-band ``param.data`` edits)."""
+        """Force a repack (and a fresh walk of the module's parameters) before the next call: after out-of-band
+        ``param.data`` edits or after replacing Parameter objects inside the blocks."""
         self._packed_sig = None
         self._init_epoch = None
+        self._tensors_cache = None
+        self._grad_layout = None
+        self._grad_ptr_offs = None
 
     def release(self):
         if self._plan is not None:
