@@ -1,7 +1,10 @@
 #!/bin/bash
 # same-box A/B of the weight-gradient write-out: libipoke_inn_prev.so (scalar, padded staging) vs the current library
 # (XOR-swizzled staging, 128-bit shared reads and global stores).  Runs on the GPU box's scratch copy of the repo.
+# needs $P/libipoke_inn_prev.so: the library built from the commit to compare against (nvcc command of build.py on
+# that commit's csrc/, output name libipoke_inn_prev.so); *.so files are git-ignored but travel with gpurun
 P=ipoke-main-opticalflow_b200
+[ -f $P/libipoke_inn_prev.so ] || { echo "build $P/libipoke_inn_prev.so first"; exit 1; }
 cp $P/libipoke_inn.so $P/libipoke_inn_new.so
 for v in prev new prev new; do
   cp $P/libipoke_inn_$v.so $P/libipoke_inn.so
