@@ -173,3 +173,43 @@ def test_engine_parameter_walk_is_cached_and_follows_replaced_parameters():
     assert t1 is not t0 and t1[2][3] is blk.norm_layer.loc
     assert eng.grad_layout() is not lay0
     assert set(id(p) for p in eng.grad_layout()[3]) == set(id(p) for p in net.flow.parameters())
+
+
+def test_direct_param_grads_host_logic_with_a_stub_engine():
+    """FlowFunction.backward with engine.direct_param_grads: the views of the flat buffer become p.grad on the first
+    backward and are accumulated on the second; autograd itself receives None for the parameters.  The kernels are
+    replaced by a stub engine that fills the flat buffer with a known pattern (CPU, host logic only)."""
+    from ipoke_inn_b200.backward import FlowFunction
+
+    params = [torch.nn.Parameter(torch.zeros(3, 2)), torch.nn.Parameter(torch.zeros(5))]
+
+    class StubEngine:
+        grad_ready_hook = None
+        direct_param_grads = True
+        last_flat_grad = None
+        n_flows = 1
+
+        def forward_train(self, x, cond):
+            B = x.shape[0]
+            z, ld = x * 2.0, torch.zeros(B)
+            return z, ld, torch.zeros(1, B, x.shape[1]), torch.zeros(1, B), torch.zeros(1, dtype=torch.uint8), x, None
+
+        def grad_layout(self):
+            return None, 11, [(0, 11)], params
+
+        def new_grad_buffer(self):
+            flat = torch.arange(11, dtype=torch.float32)
+            return flat, list(torch._utils._unflatten_dense_tensors(flat, params)), (None, None, None, None)
+
+        def backward(self, x2, c2, outs, saved, dz, dld, ptrs, want_dx=True, want_dcond=True, **kw):
+            return dz * 2.0, None
+
+    eng = StubEngine()
+    x = torch.randn(4, 6, requires_grad=True)
+    for it in (1, 2):
+        z, ld, _, _ = FlowFunction.apply(eng, x, None, *params)
+        (z.sum() + ld.sum()).backward()
+        assert torch.equal(params[0].grad, it * torch.arange(6, dtype=torch.float32).view(3, 2))
+        assert torch.equal(params[1].grad, it * torch.arange(6, 11, dtype=torch.float32))
+    assert torch.allclose(x.grad, torch.full((4, 6), 4.0))           # 2 backward passes x dz * 2
+    assert eng.last_flat_grad is not None
