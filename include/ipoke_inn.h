@@ -14,7 +14,9 @@
  *     allocates nothing on the device and never synchronises the host;
  *   - return value: 0 = ok, < 0 = IPOKE_INN_E_*, > 0 = a cudaError_t value;
  *     ipoke_inn_last_error_string() decodes both.  Nothing throws or aborts.
- *   - a plan is immutable after creation and may be shared by streams of one device.
+ *   - a plan's architecture and layouts are fixed at creation; its launch-program and CUDA-graph caches are filled
+ *     lazily and guarded by a mutex held for the duration of each entry point, so calls on one plan are serialised on
+ *     the host (concurrency comes from issuing them on different streams, each with its own workspace).
  */
 #ifndef IPOKE_INN_H_
 #define IPOKE_INN_H_
@@ -26,7 +28,7 @@
 extern "C" {
 #endif
 
-#define IPOKE_INN_VERSION 100 /* major*100 + minor */
+#define IPOKE_INN_VERSION 110 /* major*100 + minor */
 
 enum {
   IPOKE_INN_OK = 0,
@@ -184,6 +186,33 @@ int ipoke_inn_adam_chunk_elems(void);
 int ipoke_inn_adam_step(const ipoke_inn_adam_job* jobs_dev, const int* chunk_job_dev, const long long* chunk_off_dev,
                         int n_chunks, float lr, float beta1, float beta2, float eps, float weight_decay, int step,
                         int amsgrad, float grad_scale, void* stream);
+
+/* ---- packed-master training: the sharded optimizer step of the data-parallel training step --------------------
+ * The reference's training step is DDP's bucketed all-reduce of every gradient followed by a replicated
+ * torch.optim.Adam (experiments/experiment.py:86, models/second_stage_video_fc.py:670-700).  These entry points let the
+ * host side run it as reduce-scatter -> Adam on the rank's shard -> all-gather of the low-precision weights, with the
+ * packed buffer itself as the all-gather target (no fp32 -> bf16 repack pass):
+ *
+ * ipoke_inn_param_layout: the packed buffer is [hi arena | lo arena | biases, ActNorm, maps].  out[0] = 1 when every
+ *   nn.Linear weight is one unpadded contiguous [out,in] span of the hi arena and the spans tile it (H, E, C/2 multiples
+ *   of 64; true for every reference config), out[1] = byte offset of the hi arena, out[2] = its bf16 elements, out[3] =
+ *   byte offset of the lo arena (-1 in the bf16 mode; a weight's lo image has the same element offset there), out[4] =
+ *   num_linears, out[5] = n_flows, out[8 + li] = element offset of Linear li's weight (order of ipoke_inn_pack),
+ *   out[8 + num_linears + 2k], [.. + 2k + 1] = element range of flow block k.  n >= 8 + num_linears + 2 * n_flows.   */
+int ipoke_inn_param_layout(const ipoke_inn_plan* plan, long long* out, int n);
+/* Refresh only the small part of the packed buffer (fp32 biases, ActNorm loc / scale / sum log|scale|, gather maps)
+ * from the tensors given to the last ipoke_inn_pack on this buffer (its job tables live in the buffer). */
+int ipoke_inn_pack_small(const ipoke_inn_plan* plan, void* packed, void* stream);
+/* Adam / AMSGrad (arithmetic of ipoke_inn_adam_step) on one contiguous span of n weights (n % 4 == 0, 16-byte aligned):
+ * p = fp32 master (updated in place), exactly one of g (fp32) / g_bf16 (bf16 wire format) non-NULL, m / v / vmax =
+ * moments of the span, hi / lo = where the span's bf16 images live in the packed buffer (lo NULL in the bf16 mode). */
+int ipoke_inn_adam_shard_step(float* p, const float* g, const void* g_bf16, float* m, float* v, float* vmax, void* hi,
+                              void* lo, long long n, float lr, float beta1, float beta2, float eps, float weight_decay,
+                              int step, int amsgrad, float grad_scale, void* stream);
+/* fp32 master span -> its bf16 hi / lo images (after load_state_dict / out-of-band edits of the master). */
+int ipoke_inn_master_to_packed(const float* p, void* hi, void* lo, long long n, void* stream);
+/* fp32 gradient span * scale -> bf16 (wire format of the reduce-scatter when the caller asks for bf16 gradients). */
+int ipoke_inn_grad_to_bf16(const float* g, void* out_bf16, long long n, float scale, void* stream);
 
 /* Number of kernels the last forward / reverse call on this plan launched (for bench accounting). */
 int ipoke_inn_last_launch_count(const ipoke_inn_plan* plan);

@@ -14,13 +14,14 @@ from .flow_blocks import (ConditionalFlow, UnconditionalFlow2, ConditionalFlatDo
 from .loss import FlowLoss
 from .latent_interface import SecondStageLatentInterface, FlowAELatentInterface
 from .optim import FusedAdam, linear_var
+from .optim_sharded import ShardedAdam, plan_pieces
 from .parallel import GradSync, broadcast_parameters, shard_batch, shard_bounds
 from .modules import ActNorm, BasicFullyConnectedNet, IgnoreLeakyRelu, InvLeakyRelu, Shuffle
 
 __all__ = ["SupervisedTransformer", "UnsupervisedTransformer3", "ConditionalFlow", "UnconditionalFlow2",
            "FlowLoss", "ActNorm", "BasicFullyConnectedNet", "Shuffle", "InvLeakyRelu", "IgnoreLeakyRelu",
            "FusedAdam", "linear_var", "install_as_reference", "SecondStageLatentInterface",
-           "FlowAELatentInterface", "GradSync", "broadcast_parameters", "shard_batch", "shard_bounds"]
+           "FlowAELatentInterface", "GradSync", "ShardedAdam", "broadcast_parameters", "shard_batch", "shard_bounds"]
 
 
 def install_as_reference():

@@ -19,6 +19,8 @@ SYMBOLS = [
     "ipoke_inn_profile_enable", "ipoke_inn_profile_read", "ipoke_inn_set_option",
     "ipoke_inn_saved_bytes", "ipoke_inn_forward_train", "ipoke_inn_backward", "ipoke_inn_profile_read_n",
     "ipoke_inn_adam_chunk_elems", "ipoke_inn_adam_step", "ipoke_inn_reverse_draws", "ipoke_inn_forward_draws",
+    "ipoke_inn_param_layout", "ipoke_inn_pack_small", "ipoke_inn_adam_shard_step", "ipoke_inn_master_to_packed",
+    "ipoke_inn_grad_to_bf16",
 ]
 
 
@@ -99,6 +101,17 @@ def lib():
     L.ipoke_inn_adam_chunk_elems.argtypes = []
     L.ipoke_inn_adam_step.restype = i32
     L.ipoke_inn_adam_step.argtypes = [vp, vp, vp, i32, f32, f32, f32, f32, f32, i32, i32, f32, vp]
+    i64 = ctypes.c_longlong
+    L.ipoke_inn_param_layout.restype = i32
+    L.ipoke_inn_param_layout.argtypes = [vp, vp, i32]
+    L.ipoke_inn_pack_small.restype = i32
+    L.ipoke_inn_pack_small.argtypes = [vp, vp, vp]
+    L.ipoke_inn_adam_shard_step.restype = i32
+    L.ipoke_inn_adam_shard_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i32, i32, f32, vp]
+    L.ipoke_inn_master_to_packed.restype = i32
+    L.ipoke_inn_master_to_packed.argtypes = [vp, vp, vp, i64, vp]
+    L.ipoke_inn_grad_to_bf16.restype = i32
+    L.ipoke_inn_grad_to_bf16.argtypes = [vp, vp, i64, f32, vp]
     _lib = L
     return L
 

@@ -332,11 +332,12 @@ struct PackJob {
   long long bias_off;  // float offset into the packed buffer viewed as fp32
 };
 
-__global__ void __launch_bounds__(256) inn_pack_linear_kernel(const PackJob* __restrict__ jobs, void* packed) {
+// bias_only = 1: refresh the fp32 biases only (packed-master training: the weights are written by the optimizer)
+__global__ void __launch_bounds__(256) inn_pack_linear_kernel(const PackJob* __restrict__ jobs, void* packed, int bias_only) {
   const PackJob j = jobs[blockIdx.y];
   __nv_bfloat16* pk = reinterpret_cast<__nv_bfloat16*>(packed);
   float* pf = reinterpret_cast<float*>(packed);
-  const long long total = static_cast<long long>(j.N) * j.K;
+  const long long total = bias_only ? 0 : static_cast<long long>(j.N) * j.K;
   for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
        idx += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int n = static_cast<int>(idx / j.K);

@@ -158,6 +158,8 @@ struct ipoke_inn_plan {
   long long packed_bytes = 0;
   // device-side job tables live inside the packed buffer
   long long jobs_linear = -1, jobs_block = -1;
+  long long w_arena_bytes = 0, lo_arena_off = -1;       // hi arena = [0, w_arena_bytes); lo arena right after it
+  std::vector<long long> block_w_begin, block_w_end;    // bf16 element range of every flow block inside the hi arena
   // lazy device state
   bool dev_ready = false;
   int num_sms = 148;
@@ -214,12 +216,17 @@ long long bump(long long& cur, long long bytes) {
   return o;
 }
 
-void layout_layer(ipoke_inn_plan* P, long long& cur, LayerW& L, int rows, int Kp) {
+// The packed buffer is three arenas: [bf16 hi matrices of every layer | their lo residuals (parity mode) | fp32 biases,
+// ActNorm state, gather maps, job tables].  A layer's hi and lo matrix sit at the same offset of their arenas, and the hi
+// arena is ordered block by block -- for shapes without padding it is, element for element, the concatenation of the
+// nn.Linear weights, which is what lets an optimizer shard own a contiguous span of it (ipoke_inn_param_layout).
+struct ArenaCur { long long w = 0, small = 0; };
+void layout_layer(ipoke_inn_plan* P, ArenaCur& cur, LayerW& L, int rows, int Kp) {
   L.rows = rows;
   L.Kp = Kp;
-  L.hi = bump(cur, 2ll * rows * Kp);
-  if (P->ksplit == 2) L.lo = bump(cur, 2ll * rows * Kp);
-  L.bias = bump(cur, 4ll * rows);
+  L.hi = bump(cur.w, 2ll * rows * Kp);            // relative to the hi arena; rebased in ipoke_inn_plan_create
+  L.lo = P->ksplit == 2 ? L.hi : -1;              // same offset inside the lo arena
+  L.bias = bump(cur.small, 4ll * rows);           // relative to the small arena
 }
 
 WsLayout ws_layout(const ipoke_inn_plan* P, int B) {
@@ -1845,10 +1852,14 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   P->ldU = P->C2p + P->Ep;
   P->Gmax = d.conditional ? 4 : 2;
   P->ldACT = P->Gmax * P->Hp;
-  long long cur = 0;
+  ArenaCur cur;
   P->blocks.resize(d.n_flows);
+  P->block_w_begin.assign(d.n_flows, 0);
+  P->block_w_end.assign(d.n_flows, 0);
   for (int k = 0; k < d.n_flows; ++k) {
     Block& b = P->blocks[k];
+    cur.w = round_up(cur.w, 1024);
+    P->block_w_begin[k] = cur.w / 2;
     b.mode = !d.conditional ? MODE_UNCOND : (k % 2 == 0 ? MODE_COND : MODE_NORMAL);   // flow_blocks.py:27
     b.n_chains = b.mode == MODE_COND ? 1 : 2;
     for (int c = 0; c < b.n_chains; ++c) {
@@ -1867,18 +1878,39 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
       t.g_s = b.mode == MODE_COND ? 2 * i : 0;
       t.g_t = t.g_s + 1;
     }
-    b.loc = bump(cur, 4ll * d.C);
-    b.scale = bump(cur, 4ll * d.C);
-    b.an_ld = bump(cur, 16);
-    b.map_fwd = bump(cur, 4ll * d.C);
-    b.map_rev = bump(cur, 4ll * d.C);
-    b.map_fwd_inv = bump(cur, 4ll * d.C);
-    b.map_rev_inv = bump(cur, 4ll * d.C);
+    P->block_w_end[k] = cur.w / 2;
+    b.loc = bump(cur.small, 4ll * d.C);
+    b.scale = bump(cur.small, 4ll * d.C);
+    b.an_ld = bump(cur.small, 16);
+    b.map_fwd = bump(cur.small, 4ll * d.C);
+    b.map_rev = bump(cur.small, 4ll * d.C);
+    b.map_fwd_inv = bump(cur.small, 4ll * d.C);
+    b.map_rev_inv = bump(cur.small, 4ll * d.C);
   }
   const int n_lin = d.n_flows * 4 * (d.depth + 2);
-  P->jobs_linear = bump(cur, (long long)sizeof(PackJob) * n_lin);
-  P->jobs_block = bump(cur, (long long)sizeof(PackBlockJob) * d.n_flows);
-  P->packed_bytes = round_up(cur, 1024);
+  P->jobs_linear = bump(cur.small, (long long)sizeof(PackJob) * n_lin);
+  P->jobs_block = bump(cur.small, (long long)sizeof(PackBlockJob) * d.n_flows);
+  // rebase: hi arena at 0, lo arena after it, small arena last
+  P->w_arena_bytes = round_up(cur.w, 1024);
+  P->lo_arena_off = P->ksplit == 2 ? P->w_arena_bytes : -1;
+  const long long small_off = P->w_arena_bytes * (P->ksplit == 2 ? 2 : 1);
+  auto rebase = [&](LayerW& L) {
+    if (L.lo >= 0) L.lo += P->lo_arena_off;
+    L.bias += small_off;
+  };
+  for (Block& b : P->blocks) {
+    for (int c = 0; c < b.n_chains; ++c)
+      for (LayerW& L : b.chains[c].L) rebase(L);
+    for (int i = 0; i < 2; ++i) {
+      rebase(b.tails[i].w);
+      b.tails[i].bias_t += small_off;
+    }
+    b.loc += small_off; b.scale += small_off; b.an_ld += small_off;
+    b.map_fwd += small_off; b.map_rev += small_off; b.map_fwd_inv += small_off; b.map_rev_inv += small_off;
+  }
+  P->jobs_linear += small_off;
+  P->jobs_block += small_off;
+  P->packed_bytes = round_up(small_off + cur.small, 1024);
   *out = P;
   return 0;
 }
@@ -1975,7 +2007,7 @@ int ipoke_inn_pack(const ipoke_inn_plan* cplan, const float* const* linear_w, co
   if (e != cudaSuccess) return (int)e;
   const int max_elems = std::max(d.H * std::max(d.H, P->C2 + d.E), P->C2 * d.H);
   dim3 grid((unsigned)std::min(64, (max_elems + 255) / 256), (unsigned)jobs.size());
-  inn_pack_linear_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const PackJob*>(pk + P->jobs_linear), packed);
+  inn_pack_linear_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const PackJob*>(pk + P->jobs_linear), packed, 0);
   e = cudaGetLastError();
   if (e != cudaSuccess) return (int)e;
   inn_pack_block_kernel<<<d.n_flows, 256, 0, st>>>(reinterpret_cast<const PackBlockJob*>(pk + P->jobs_block), packed, d.C);
@@ -2179,6 +2211,116 @@ int ipoke_inn_adam_step(const ipoke_inn_adam_job* jobs_dev, const int* chunk_job
   a.grad_scale = grad_scale;
   a.amsgrad = amsgrad;
   inn_adam_kernel<<<n_chunks, ADAM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : (int)e;
+}
+
+// ---- packed-master training (ShardedAdam): the packed buffer as the parameter store ------------------------------
+int ipoke_inn_param_layout(const ipoke_inn_plan* P, long long* out, int n) {
+  if (!P || !out) return IPOKE_INN_E_INVALID;
+  const ipoke_inn_desc& d = P->d;
+  const int nl = d.depth + 2, n_lin = d.n_flows * 4 * nl;
+  if (n < 8 + n_lin + 2 * d.n_flows) return IPOKE_INN_E_INVALID;
+  // direct = every nn.Linear weight is one unpadded, contiguous [out, in] span of the hi arena and the spans tile it
+  bool direct = d.H == P->Hp && P->C2 == P->C2p && P->C2 == P->Np && (d.E == 0 || d.E == P->Ep);
+  long long covered = 0;
+  for (int k = 0; k < d.n_flows; ++k) {
+    const Block& b = P->blocks[k];
+    for (int i = 0; i < 2; ++i)
+      for (int net = 0; net < 2; ++net)
+        for (int l = 0; l < nl; ++l) {
+          const int li = ((k * 2 + i) * 2 + net) * nl + l;
+          long long off, numel;
+          if (l <= d.depth) {
+            const LayerW& L = b.chains[b.mode == MODE_COND ? 0 : i].L[l];
+            const int g = b.mode == MODE_COND ? 2 * i + net : net;
+            off = L.hi / 2 + (long long)g * P->Hp * L.Kp;
+            numel = (long long)P->Hp * L.Kp;
+          } else {
+            const LayerW& L = b.tails[i].w;
+            off = L.hi / 2 + (long long)net * P->Np * L.Kp;
+            numel = (long long)P->Np * L.Kp;
+          }
+          out[8 + li] = off;
+          covered += numel;
+        }
+    out[8 + n_lin + 2 * k] = P->block_w_begin[k];
+    out[8 + n_lin + 2 * k + 1] = P->block_w_end[k];
+  }
+  if (covered != P->w_arena_bytes / 2) direct = false;        // alignment gaps between matrices
+  out[0] = direct ? 1 : 0;
+  out[1] = 0;                                                  // hi arena byte offset
+  out[2] = P->w_arena_bytes / 2;                               // bf16 elements of the hi arena
+  out[3] = P->lo_arena_off;                                    // byte offset of the lo arena, -1 in the bf16 mode
+  out[4] = n_lin;
+  out[5] = d.n_flows;
+  out[6] = out[7] = 0;
+  return 0;
+}
+
+int ipoke_inn_pack_small(const ipoke_inn_plan* cplan, void* packed, void* stream) {
+  ipoke_inn_plan* P = const_cast<ipoke_inn_plan*>(cplan);
+  if (!P || !packed) return IPOKE_INN_E_INVALID;
+  std::lock_guard<std::mutex> lock(P->mu);
+  int rc = ensure_device(P);
+  if (rc) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  char* pk = static_cast<char*>(packed);
+  const int n_lin = P->d.n_flows * 4 * (P->d.depth + 2);
+  inn_pack_linear_kernel<<<dim3(1, (unsigned)n_lin), 256, 0, st>>>(reinterpret_cast<const PackJob*>(pk + P->jobs_linear), packed, 1);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return (int)e;
+  inn_pack_block_kernel<<<P->d.n_flows, 256, 0, st>>>(reinterpret_cast<const PackBlockJob*>(pk + P->jobs_block), packed, P->d.C);
+  e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : (int)e;
+}
+
+static int shard_grid(long long n) {
+  const long long per_cta = 2ll * 4 * ADAM_THREADS * 4;         // 4 double-float4 iterations per thread
+  return (int)std::max<long long>(1, std::min<long long>((n + per_cta - 1) / per_cta, 148 * 16));
+}
+static bool al16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; }
+
+int ipoke_inn_adam_shard_step(float* p, const float* g, const void* g_bf16, float* m, float* v, float* vmax, void* hi,
+                              void* lo, long long n, float lr, float beta1, float beta2, float eps, float weight_decay,
+                              int step, int amsgrad, float grad_scale, void* stream) {
+  if (n == 0) return 0;
+  if (!p || (!g) == (!g_bf16) || !m || !v || !hi || (amsgrad && !vmax) || n < 0 || (n & 3) || step < 1) return IPOKE_INN_E_INVALID;
+  if (!al16(p) || !al16(g) || !al16(m) || !al16(v) || !al16(vmax) || (reinterpret_cast<uintptr_t>(g_bf16) & 7u) ||
+      (reinterpret_cast<uintptr_t>(hi) & 7u) || (reinterpret_cast<uintptr_t>(lo) & 7u)) return IPOKE_INN_E_INVALID;
+  AdamShardParams q;
+  q.p = p; q.g = g; q.g16 = static_cast<const __nv_bfloat16*>(g_bf16);
+  q.m = m; q.v = v; q.vmax = vmax;
+  q.hi = static_cast<__nv_bfloat16*>(hi); q.lo = static_cast<__nv_bfloat16*>(lo);
+  q.n = n;
+  std::memset(&q.a, 0, sizeof(q.a));
+  q.a.beta1 = beta1; q.a.beta2 = beta2; q.a.eps = eps; q.a.weight_decay = weight_decay;
+  const double bc1 = 1.0 - std::pow((double)beta1, (double)step);
+  const double bc2 = 1.0 - std::pow((double)beta2, (double)step);
+  q.a.step_size = (float)((double)lr / bc1);
+  q.a.inv_sqrt_bc2 = (float)(1.0 / std::sqrt(bc2));
+  q.a.grad_scale = grad_scale;
+  q.a.amsgrad = amsgrad;
+  inn_adam_shard_kernel<<<shard_grid(n), ADAM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(q);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : (int)e;
+}
+
+int ipoke_inn_master_to_packed(const float* p, void* hi, void* lo, long long n, void* stream) {
+  if (n == 0) return 0;
+  if (!p || !hi || n < 0 || (n & 3) || !al16(p) || (reinterpret_cast<uintptr_t>(hi) & 7u) || (reinterpret_cast<uintptr_t>(lo) & 7u))
+    return IPOKE_INN_E_INVALID;
+  inn_master_split_kernel<<<shard_grid(n), ADAM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+      p, static_cast<__nv_bfloat16*>(hi), static_cast<__nv_bfloat16*>(lo), n);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : (int)e;
+}
+
+int ipoke_inn_grad_to_bf16(const float* g, void* out_bf16, long long n, float scale, void* stream) {
+  if (n == 0) return 0;
+  if (!g || !out_bf16 || n < 0 || (n & 3) || !al16(g) || (reinterpret_cast<uintptr_t>(out_bf16) & 7u)) return IPOKE_INN_E_INVALID;
+  inn_grad_to_bf16_kernel<<<shard_grid(n), ADAM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+      g, static_cast<__nv_bfloat16*>(out_bf16), n, scale);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : (int)e;
 }

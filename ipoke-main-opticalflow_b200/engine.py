@@ -42,6 +42,7 @@ class FlowEngine:
         self.direct_param_grads = False       # True: backward() assigns / accumulates p.grad itself (see backward.py)
         self._grad_layout = None
         self.streams = 1
+        self._pm = None                       # packed-master state (adopt_packed_master)
 
     # ------------------------------------------------------------------ plumbing
     def set_concurrency(self, streams):
@@ -65,6 +66,34 @@ class FlowEngine:
         if self._plan is not None:
             _capi.lib().ipoke_inn_plan_destroy(self._plan)
         self._plan, self._packed, self._packed_sig, self._ws, self._device = None, None, None, {}, None
+        self._pm = None                       # the Linear weights keep their (valid) storage inside the old master
+        self._grad_layout = None
+        self._grad_ptr_offs = None
+
+    # copies / pickles of the module rebuild the plan, the packed buffer and the workspaces lazily (ctypes handles
+    # cannot be pickled)
+    def __getstate__(self):
+        st = dict(self.__dict__)
+        for k in ("_plan", "_packed", "_packed_sig", "_device", "_pm", "_init_epoch", "_tensors_cache", "_grad_layout",
+                  "_grad_ptr_offs", "last_flat_grad", "grad_ready_hook"):
+            st[k] = None
+        st["_ws"] = {}
+        return st
+
+    def __setstate__(self, st):
+        self.__dict__.update(st)
+
+    def __deepcopy__(self, memo):
+        import copy
+        new = FlowEngine.__new__(FlowEngine)
+        memo[id(self)] = new
+        st = self.__getstate__()
+        flow = st.pop("flow")
+        desc = st.pop("desc")
+        new.__dict__.update(copy.deepcopy(st, memo))
+        new.flow = copy.deepcopy(flow, memo)
+        new.desc = _capi.InnDesc.from_buffer_copy(desc)
+        return new
 
     def __del__(self):
         try:
@@ -153,6 +182,25 @@ class FlowEngine:
         sig = self._signature(tensors)
         if not force and sig == self._packed_sig:
             return
+        if self._pm is not None:
+            if self._pm_valid(tensors):
+                # packed-master mode: the Linear weights live in the fp32 master whose layout is the packed hi arena;
+                # an out-of-band change (load_state_dict, ActNorm init, a foreign optimizer) re-splits the master and
+                # refreshes the small part -- no gather / scatter pass
+                pm = self._pm
+                if pm.stale:
+                    raise RuntimeError("ipoke_inn_b200: the fp32 master weights are sharded across ranks; call "
+                                       "ShardedAdam.gather_master() before editing or repacking parameters")
+                L = _capi.lib()
+                _capi.check(L.ipoke_inn_master_to_packed(pm.master.data_ptr(), pm.hi.data_ptr(),
+                                                         pm.lo.data_ptr() if pm.lo is not None else None, pm.n,
+                                                         self._stream()), "master_to_packed")
+                _capi.check(L.ipoke_inn_pack_small(self._plan, self._packed.data_ptr(), self._stream()), "pack_small")
+                self._packed_sig = sig
+                return
+            self._pm = None                   # parameters were moved / replaced: back to the plain repack
+            self._grad_layout = None
+            self._grad_ptr_offs = None
         lin_w, lin_b, loc, scale, pf, pb = tensors
         for t in lin_w + lin_b + loc + scale:
             if t.dtype != torch.float32 or not t.is_contiguous() or t.device != self._device:
@@ -345,10 +393,80 @@ class FlowEngine:
         self.launches = L.ipoke_inn_last_launch_count(self._plan)
         return z, ld, outs, lds, saved, x2, c2
 
+    # ------------------------------------------------------------------ packed-master training (sharded optimizer)
+    def _pm_valid(self, tensors=None):
+        pm = self._pm
+        if pm is None or self._packed is None or pm.packed_ptr != self._packed.data_ptr():
+            return False
+        lin_w = (tensors or self._tensors())[0]
+        base = pm.master.data_ptr()
+        return (lin_w[0].data_ptr() == base + 4 * pm.w_off[0] and lin_w[-1].data_ptr() == base + 4 * pm.w_off[-1])
+
+    def adopt_packed_master(self):
+        """Make one flat fp32 buffer whose element layout IS the packed hi arena the storage of every nn.Linear weight
+        (``weight.data`` becomes a view of it; names, shapes, values and the Parameter objects are unchanged).  An
+        optimizer shard can then own a contiguous span of that buffer and write the fp32 master and the bf16 hi / lo
+        images the GEMMs read in one pass, and an all-gather can deliver the other ranks' spans straight into the
+        packed buffer (optim_sharded.ShardedAdam).  Needs shapes without padding (H, E, C/2 multiples of 64: every
+        reference config); raises NotImplementedError otherwise.  -> the packed-master record."""
+        import types
+        lin_w = self._tensors()[0]
+        dev = lin_w[0].device
+        L = self._ensure(dev)
+        if self._pm is not None and self._pm_valid():
+            return self._pm
+        n_lin = len(lin_w)
+        n = 8 + n_lin + 2 * self.n_flows
+        out = (ctypes.c_longlong * n)()
+        _capi.check(L.ipoke_inn_param_layout(self._plan, out, n), "param_layout")
+        if out[0] != 1:
+            raise NotImplementedError("packed-master training needs H, E and C/2 to be multiples of 64 (no padding inside "
+                                      "the packed weight arena); use FusedAdam + GradSync for this shape")
+        self._pm = None
+        self.pack(force=True)                               # plain repack while every parameter still owns its storage
+        N = int(out[2])
+        master = torch.zeros(N, dtype=torch.float32, device=dev)
+        w_off = [int(out[8 + i]) for i in range(n_lin)]
+        with torch.no_grad():
+            for w, off in zip(lin_w, w_off):
+                v = master[off:off + w.numel()].view(w.shape)
+                v.copy_(w)
+                w.data = v
+        pk16 = self._packed.view(torch.bfloat16)
+        lo_off = int(out[3])
+        self._pm = types.SimpleNamespace(
+            master=master, w_off=w_off, n=N, packed_ptr=self._packed.data_ptr(), stale=False,
+            hi=pk16[:N], lo=pk16[lo_off // 2:lo_off // 2 + N] if lo_off >= 0 else None,
+            block_ranges=[(int(out[8 + n_lin + 2 * k]), int(out[8 + n_lin + 2 * k + 1])) for k in range(self.n_flows)])
+        self._grad_layout = None
+        self._grad_ptr_offs = None
+        self._packed_sig = self._signature(self._tensors())  # the packed images equal the master just copied
+        return self._pm
+
     def grad_layout(self):
-        """Flat fp32 gradient buffer layout: every parameter of the flow in ``flow.parameters()`` order (which is
-        block by block), so a block's gradients are one contiguous slice (per-block all-reduce chunks)."""
+        """Flat fp32 gradient buffer layout.  Plain mode: every parameter of the flow in ``flow.parameters()`` order
+        (block by block), so a block's gradients are one contiguous slice (per-block all-reduce chunks).  Packed-master
+        mode: the Linear weights first, in the element order of the packed hi arena (block by block as well), then the
+        biases and the ActNorm parameters.  -> (offsets by id, total, per-block ranges, params in parameters() order)."""
+        if getattr(self, "_grad_layout", None) is None and self._pm is not None:
+            lin_w, lin_b, loc, scale, _, _ = self._tensors()
+            pm = self._pm
+            order = sorted(range(len(lin_w)), key=lambda i: pm.w_off[i])
+            flat_params = [lin_w[i] for i in order] + list(lin_b) + list(loc) + list(scale)
+            offs, cur = {}, 0
+            for p in flat_params:
+                offs[id(p)] = (cur, p.numel(), tuple(p.shape))
+                cur += p.numel()
+            for i, w in enumerate(lin_w):
+                assert offs[id(w)][0] == pm.w_off[i], "packed hi arena is not the concatenation of the Linear weights"
+            params = [p for blk in self.flow.sub_layers for p in blk.parameters()]
+            pos = {id(p): j for j, p in enumerate(flat_params)}
+            self._grad_flat_params = flat_params
+            self._grad_perm = [pos[id(p)] for p in params]
+            self._grad_layout = (offs, cur, list(pm.block_ranges), params)
         if getattr(self, "_grad_layout", None) is None:
+            self._grad_flat_params = None
+            self._grad_perm = None
             offs, cur = {}, 0
             block_ranges = []
             for k, blk in enumerate(self.flow.sub_layers):
@@ -372,7 +490,11 @@ class FlowEngine:
             self._grad_ptr_offs = [[4 * offs[id(t)][0] for t in ts] for ts in (lin_w, lin_b, loc, scale)]
         arrays = tuple((ctypes.c_void_p * len(o))(*[base + b for b in o]) for o in self._grad_ptr_offs)
         # one C++ call for all the views (a Python slice + view per parameter costs more than the batch-64 kernels)
-        views = list(torch._utils._unflatten_dense_tensors(flat, params))
+        if self._grad_perm is None:
+            views = list(torch._utils._unflatten_dense_tensors(flat, params))
+        else:
+            fv = torch._utils._unflatten_dense_tensors(flat, self._grad_flat_params)
+            views = [fv[j] for j in self._grad_perm]
         return flat, views, arrays
 
     def backward(self, x2, c2, outs, saved, dz, dld, grad_ptrs, want_dx=True, want_dcond=True, block_begin=0,
@@ -396,8 +518,15 @@ class FlowEngine:
         return dx, dcond
 
     # host-buffer entry points (pinned CPU tensors in, pinned CPU tensors out; stream-ordered, caller syncs)
+    def _ready_for_host_call(self):
+        if self._plan is None or self._packed is None:
+            raise RuntimeError("ipoke_inn_b200: run one device call first (it creates the plan on the module's device "
+                               "and does the ActNorm data init), then use the *_host entry points")
+        self.pack()
+
     def forward_host(self, x_host, cond_host, z_host, logdet_host):
         L = _capi.lib()
+        self._ready_for_host_call()
         B = x_host.shape[0]
         ws = self._workspace(B)
         _capi.check(L.ipoke_inn_forward_host(self._plan, self._packed.data_ptr(), x_host.data_ptr(),
@@ -408,6 +537,7 @@ class FlowEngine:
 
     def reverse_host(self, z_host, cond_host, x_host):
         L = _capi.lib()
+        self._ready_for_host_call()
         B = z_host.shape[0]
         ws = self._workspace(B)
         _capi.check(L.ipoke_inn_reverse_host(self._plan, self._packed.data_ptr(), z_host.data_ptr(),

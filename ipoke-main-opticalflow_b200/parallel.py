@@ -91,6 +91,18 @@ class GradSync:
             else:
                 self._reduce(chunk, world)
         if block_begin == 0:
+            if getattr(engine, "_pm", None) is not None and world > 1:
+                # packed-master layout: biases and ActNorm parameters sit behind the weight arena, not inside the
+                # per-block ranges -- one more (small) message
+                lo, hi = engine._pm.n, flat.numel()
+                self.messages.append((lo, hi - lo))
+                tail = flat[lo:hi]
+                if flat.is_cuda:
+                    self._stream.wait_stream(torch.cuda.current_stream(flat.device))
+                    with torch.cuda.stream(self._stream):
+                        self._reduce(tail, world)
+                else:
+                    self._reduce(tail, world)
             self.finish(flat)
 
     def _reduce(self, chunk, world):
