@@ -417,18 +417,27 @@ def flow_backward(sd, x, cond, dz, dlogdet, dtype=np.float64):
 _KINK_LOG = None
 
 
-def kink_distance(sd, x, cond=None):
+def kink_distance(sd, x, cond=None, dtype=np.float64, chunk=0):
     """Per sample: min over every hidden unit of every subnetwork of |pre-activation| / rms(layer).
 
     LeakyReLU' is discontinuous at 0, so a gradient comparison between two arithmetics is only meaningful for
     samples whose pre-activations all stay clear of 0 by more than the forward error of the less exact one.
-    Samples of the flow are independent (ActNorm is already initialised), so tests simply drop the others."""
+    Samples of the flow are independent (ActNorm is already initialised), so tests simply drop the others.
+    `chunk` > 0 walks the rows in slices (bounded memory at the full shapes); `dtype` float32 is enough for picking
+    samples (its error is two orders below any useful margin)."""
     global _KINK_LOG
-    _KINK_LOG = []
+    x = np.asarray(x, dtype=dtype)
+    n = x.shape[0]
+    step = chunk if chunk > 0 else n
+    out = []
     try:
-        x = np.asarray(x, dtype=np.float64)
-        flow_backward(sd, x, cond, np.zeros_like(x), np.zeros(x.shape[0]))
-        return np.min(np.stack(_KINK_LOG, axis=0), axis=0)
+        for lo in range(0, n, step):
+            _KINK_LOG = []
+            xs = x[lo:lo + step]
+            cs = None if cond is None else np.asarray(cond[lo:lo + step], dtype=dtype)
+            flow_backward(sd, xs, cs, np.zeros_like(xs), np.zeros(xs.shape[0], dtype=dtype), dtype=dtype)
+            out.append(np.min(np.stack(_KINK_LOG, axis=0), axis=0))
+        return np.concatenate(out)
     finally:
         _KINK_LOG = None
 

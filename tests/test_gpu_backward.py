@@ -19,7 +19,7 @@ import torch
 import ipoke_inn_b200 as P
 from oracle import inn_oracle as O
 from conftest import load_golden, max_rel
-from test_host_logic import CFG, build
+from test_host_logic import CFG, FULL_CFG, build
 
 pytestmark = pytest.mark.gpu
 
@@ -98,9 +98,106 @@ def _oracle_case(name, B, precision, seed=5):
 
 
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])
-@pytest.mark.parametrize("name,B", [("cfgA_mini", 200), ("cfgB_mini", 130), ("cfgS_cond", 700), ("uncond_small", 1)])
+@pytest.mark.parametrize("name,B", [("cfgA_mini", 200), ("cfgB_mini", 130), ("cfgS_cond", 700), ("uncond_small", 1),
+                                    ("cfgA_mini", 640), ("cfgB_mini", 1152)])
 def test_backward_matches_fp64_oracle(name, B, precision):
     net, sd_ref, x, cond, dz, dld = _oracle_case(name, B, precision)
+    _check_against_oracle(net, sd_ref, x, cond, dz, dld, precision)
+
+
+# ~2e5 (cfg A) / ~1e5 (cfg B) hidden units per sample: a unit sits within m * rms of the kink with probability 0.8 m, so
+# only exp(-0.8 m units) of the samples are clear: 4 % (cfg A) / 21 % (cfg B) at this margin -- candidates are drawn until
+# enough are found (selection in fp32, row-chunked; the verification below is the fp64 oracle)
+FULL_KINK_MARGIN = 2e-5
+
+
+def _full_case(name, B, precision, seed=5, margin=FULL_KINK_MARGIN):
+    """A full benchmark shape (no fixture): weights from the seed, ActNorm data-initialised on the device, then B
+    kink-clear samples picked with the oracle on the resulting state_dict."""
+    dev = _dev()
+    net = build(name, precision=precision).to(dev)
+    kind, kw = FULL_CFG[name]
+    C, E = kw["flow_in_channels"], kw.get("flow_embedding_channels", 0)
+    g = torch.Generator().manual_seed(seed)
+    x0 = torch.randn(256, C, generator=g)
+    c0 = torch.randn(256, E, 1, 1, generator=g) if kind == "cond" else None
+    with torch.no_grad():
+        net(x0.to(dev), c0.to(dev)) if c0 is not None else net(x0.to(dev))      # ActNorm data init
+    sd_ref = O.state_dict_to_numpy(net.state_dict())
+    xs, cs, found = [], [], 0
+    for _ in range(40):
+        x = torch.randn(512, C, generator=g)
+        cond = torch.randn(512, E, 1, 1, generator=g) if kind == "cond" else None
+        dist = O.kink_distance(sd_ref, x.numpy(), None if cond is None else cond.numpy().reshape(512, -1),
+                               dtype=np.float32)
+        keep = torch.from_numpy(np.nonzero(dist > margin)[0])
+        xs.append(x[keep])
+        if cond is not None:
+            cs.append(cond[keep])
+        found += len(keep)
+        if found >= B:
+            break
+    assert found >= B, f"only {found} candidate samples clear the kink margin"
+    x = torch.cat(xs)[:B].contiguous()
+    cond = torch.cat(cs)[:B].contiguous() if kind == "cond" else None
+    return net, sd_ref, x, cond, torch.randn(B, C, generator=g), torch.randn(B, generator=g)
+
+
+@pytest.mark.parametrize("name,B", [("cfgA", 64), ("cfgB", 256)])
+def test_backward_matches_fp64_oracle_at_the_benchmark_shapes(name, B):
+    """The shapes whose training-step timings are quoted (H = 1536 / 1024: K-wide dgrad, 148-CTA wgrad, EPI_DU)."""
+    net, sd_ref, x, cond, dz, dld = _full_case(name, B, "fp32")
+    _check_against_oracle(net, sd_ref, x, cond, dz, dld, "fp32", stray_flips=True)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_large_batch_backward_rows_and_linearity(precision):
+    """cfg A at 4096 rows (multi-wave dgrad / wgrad with K = batch = 4096): dx / dcond of 48 kink-clear rows embedded
+    in the batch equal the fp64 oracle's (rows are independent), and the parameter gradients equal the sum of the
+    gradients of the 8 row slices of 512 computed separately (linearity in the batch)."""
+    B, nsub = 4096, 48
+    net, sd_ref, xs, cs, dzs, dlds = _full_case("cfgA", nsub, precision)
+    dev = _dev()
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(B, 128, generator=g)
+    cond = torch.randn(B, 128, 1, 1, generator=g)
+    dz = torch.randn(B, 128, generator=g)
+    dld = torch.randn(B, generator=g)
+    rows = torch.arange(nsub) * 85 + 3
+    x[rows], cond[rows], dz[rows], dld[rows] = xs, cs, dzs, dlds
+
+    def grads_of(lo, hi):
+        net.zero_grad(set_to_none=True)
+        xg = x[lo:hi].to(dev).requires_grad_(True)
+        cg = cond[lo:hi].to(dev).requires_grad_(True)
+        z, ld = net(xg, cg)
+        ((z.reshape(hi - lo, -1) * dz[lo:hi].to(dev)).sum() + (ld * dld[lo:hi].to(dev)).sum()).backward()
+        return xg.grad.cpu(), cg.grad.cpu().reshape(hi - lo, -1), [p.grad.detach().clone() for p in net.parameters()]
+
+    dx, dc, full = grads_of(0, B)
+    if precision == "fp32":
+        with O.gemm_rounding(None):
+            _, dx_ref, dc_ref = O.flow_backward(sd_ref, xs.numpy(), cs.numpy().reshape(nsub, -1), dzs.numpy(), dlds.numpy())
+        assert max_rel(dx[rows].numpy(), dx_ref) < GTOL["fp32"]
+        assert max_rel(dc[rows].numpy(), dc_ref) < GTOL["fp32"]
+        from conftest import rel_l2
+        assert rel_l2(dx[rows].numpy(), dx_ref) < 1e-4 and rel_l2(dc[rows].numpy(), dc_ref) < 1e-4
+    acc = None
+    for lo in range(0, B, 512):
+        _, _, gs = grads_of(lo, lo + 512)
+        acc = gs if acc is None else [a + b for a, b in zip(acc, gs)]
+    # the slices run other tile shapes than the whole batch, and these 4096 rows are not kink-filtered: a unit whose
+    # pre-activation lies within the forward rounding error of 0 flips its LeakyReLU mask between the two runs and moves
+    # single-sample contributions (per-tensor maxima up to 1e-2 at ~2e5 units x 4096 samples); the batch sum as a whole
+    # must agree -- a tiling or indexing bug in the multi-wave dgrad / wgrad would not stay below 1e-2 globally
+    num = sum(float(((a - b).double() ** 2).sum()) for a, b in zip(full, acc))
+    den = sum(float((b.double() ** 2).sum()) for b in acc)
+    print(f"large-batch linearity, {precision}: global rel-L2 {np.sqrt(num / den):.3e}")
+    assert np.sqrt(num / den) < (2e-3 if precision == "fp32" else 2e-2)
+
+
+def _check_against_oracle(net, sd_ref, x, cond, dz, dld, precision, stray_flips=False):
+    B = x.shape[0]
     dev = _dev()
     xg = x.to(dev).requires_grad_(True)
     cg = cond.to(dev).requires_grad_(True) if cond is not None else None
@@ -127,6 +224,16 @@ def test_backward_matches_fp64_oracle(name, B, precision):
         assert np.sqrt(num / den) < 2e-2, f"global rel-L2 {np.sqrt(num / den):.3e}"
         n_bad = sum(1 for e in errs.values() if not e < tol)
         assert n_bad <= max(2, len(errs) // 10), f"{n_bad}/{len(errs)} tensors above {tol}"
+        return
+    if stray_flips:
+        # reduced kink clearance (full shapes): a stray unit may still flip its LeakyReLU mask in one sample, which moves
+        # a few entries of the tensors behind it; a tiling / indexing bug would break most tensors and the global norm
+        num = sum(float(((p.grad.cpu().numpy().astype(np.float64) - np.asarray(grads[k]).reshape(p.shape)) ** 2).sum())
+                  for k, p in net.named_parameters())
+        den = sum(float((np.asarray(grads[k]) ** 2).sum()) for k, p in net.named_parameters())
+        assert np.sqrt(num / den) < 2e-4, f"global rel-L2 {np.sqrt(num / den):.3e}"
+        bad = {k: e for k, e in errs.items() if not e < tol}
+        assert len(bad) <= max(2, len(errs) // 50), bad
         return
     _report(errs, tol)
 

@@ -20,10 +20,16 @@ CFG = {
                                flow_conditioning_option="none", flow_embedding_channels=128)),
     "cfgB_mini": ("uncond", dict(flow_in_channels=512, flow_mid_channels=64, flow_hidden_depth=2, n_flows=2)),
 }
+# the full benchmark shapes: no fixtures, weights from the seed
+FULL_CFG = {
+    "cfgA": ("cond", dict(flow_in_channels=128, flow_mid_channels_factor=12, flow_hidden_depth=3, n_flows=8,
+                          flow_conditioning_option="none", flow_embedding_channels=128)),
+    "cfgB": ("uncond", dict(flow_in_channels=512, flow_mid_channels=1024, flow_hidden_depth=2, n_flows=8)),
+}
 
 
 def build(name, seed=42, **extra):
-    kind, kw = CFG[name]
+    kind, kw = (CFG.get(name) or FULL_CFG[name])
     torch.manual_seed(seed)
     if kind == "cond":
         return P.SupervisedTransformer(dict(kw), **extra)
