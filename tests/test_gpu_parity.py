@@ -2,13 +2,14 @@
 (1) the committed live-reference fixtures, (2) the numpy oracle on seeded inputs at BASELINE sizes,
 (3) size-independent properties (forward->reverse round trip, batch-slice independence).
 
-Tolerances (max-abs error relative to the tensor's max-abs, and rel-L2):
-  precision="fp32" (split-bf16, 3 MMAs): <= 1e-4   -- the north star's fp32 bound
-  precision="bf16" (single pass)       : the stated looser bound of the bf16 variant: z / reverse <= 1e-2 (measured
-                                          worst case 4.1e-3, tiny nets with K=16..64 average least); logdet is a
-                                          sum of n_flows*C tanh outputs each carrying ~1e-3 of bf16 GEMM error, so
-                                          its bound is absolute: |dlogdet| <= 2e-3*sqrt(n_flows*C) (measured 0.03 of
-                                          the allowed 0.128 at cfg B)
+Tolerances: max-abs error relative to the tensor's max-abs ("max_rel", conftest.py -- the most lenient reading of
+"relative"; rel-L2 is asserted beside it where stated), against the oracle / the live-reference fixtures:
+  precision="fp32" (split-bf16, 3 MMAs): <= 1e-4 for z, logdet, reverse -- the north star's fp32 bound
+                                          (measured <= 1.4e-5 at random init, profiles/r02_precision_report.txt)
+  precision="bf16" (single pass)       : the stated looser bound of the bf16 variant:
+      z / reverse <= 2e-3 max_rel and <= 1.5e-3 rel-L2 at >= 64 rows of the benchmark and mini shapes (measured <= 1.35e-3
+      / 7.9e-4); <= 5e-3 on the tiny fixtures (K = 16..64 average least; measured worst 4.1e-3);
+      logdet <= 6e-3 max_rel (measured <= 4.3e-3: it sums n_flows*C tanh outputs that each carry ~1e-3 of bf16 error)
 """
 import numpy as np
 import pytest
@@ -21,14 +22,13 @@ from test_host_logic import CFG, build
 
 pytestmark = pytest.mark.gpu
 
-TOL = {"fp32": dict(z=1e-4, ld=1e-4), "bf16": dict(z=1e-2, ld=None)}
+TOL = {"fp32": dict(z=1e-4, ld=1e-4), "bf16": dict(z=5e-3, ld=6e-3)}          # fixtures (tiny nets)
+TOL_FULL = {"fp32": dict(z=1e-4, l2=5e-5, ld=1e-4), "bf16": dict(z=2e-3, l2=1.5e-3, ld=6e-3)}
 
 
-def _ld_ok(got, ref, precision, n_flows, C):
+def _ld_ok(got, ref, precision, n_flows=None, C=None):
     got, ref = np.asarray(got, dtype=np.float64), np.asarray(ref, dtype=np.float64)
-    if precision == "fp32":
-        return np.max(np.abs(got - ref)) < 1e-4 * np.max(np.abs(ref))
-    return np.max(np.abs(got - ref)) < 2e-3 * np.sqrt(n_flows * C)
+    return np.max(np.abs(got - ref)) < TOL[precision]["ld"] * np.max(np.abs(ref))
 
 
 def _dev():
@@ -148,12 +148,78 @@ def test_full_size_against_oracle(name, B, precision):
     c2b = None if c2 is None else c2[:B]
     z_ref, ld_ref = O.flow_forward(sd, xb.numpy(), c2b)
     z, ld = _call(net, xb.to(_dev()), None if cb is None else cb.to(_dev()))
-    t = TOL[precision]
+    t = TOL_FULL[precision] if B >= 64 else TOL[precision]
     assert max_rel(z.cpu().numpy().reshape(B, C), z_ref) < t["z"]
-    assert _ld_ok(ld.cpu().numpy(), ld_ref, precision, kw["n_flows"], C)
+    assert _ld_ok(ld.cpu().numpy(), ld_ref, precision)
     x_ref = O.flow_reverse(sd, z_ref, c2b)
     x_rec = _call(net, torch.from_numpy(z_ref).to(_dev()), None if cb is None else cb.to(_dev()), reverse=True)
     assert max_rel(x_rec.cpu().numpy().reshape(B, C), x_ref) < t["z"]
+    if B >= 64:
+        assert rel_l2(z.cpu().numpy().reshape(B, C), z_ref) < t["l2"]
+        assert rel_l2(x_rec.cpu().numpy().reshape(B, C), x_ref) < t["l2"]
+
+
+def _oracle_initialised(name, precision, wscale=1.0, n0=256):
+    """Full-shape module whose ActNorms were data-initialised by the ORACLE on a first batch (so both sides hold the
+    same state), optionally with every Linear weight scaled first."""
+    net, kind, kw = _full(name, precision)
+    if wscale != 1.0:
+        with torch.no_grad():
+            for k, p in net.named_parameters():
+                if ".main." in k and k.endswith(".weight"):
+                    p.mul_(wscale)
+    C, E = kw["flow_in_channels"], kw.get("flow_embedding_channels", 0)
+    g = torch.Generator().manual_seed(4321)
+    x0 = torch.randn(n0, C, generator=g)
+    c0 = torch.randn(n0, E, generator=g) if kind == "cond" else None
+    sd = O.state_dict_to_numpy(net.state_dict())
+    O.flow_forward_with_actnorm_init(sd, x0.numpy(), None if c0 is None else c0.numpy())
+    net.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()})
+    return net.to(_dev()), sd, kind, C, E
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("name,B", [("cfgA", 4096), ("cfgA", 32768), ("cfgB", 4096), ("cfgB", 32768)])
+def test_large_batch_rows_against_oracle(name, B, precision):
+    """The batch sizes behind the tensor-regime figures (CTA-pair hidden GEMMs, unfolded boundary kernels, multi-wave
+    tails): 256 rows spread over the batch against the oracle -- rows are independent -- forward, logdet and reverse,
+    in both precisions."""
+    net, sd, kind, C, E = _oracle_initialised(name, precision)
+    dev = _dev()
+    g = torch.Generator(device="cuda").manual_seed(77)
+    x = torch.randn(B, C, device=dev, generator=g)
+    cond = torch.randn(B, E, 1, 1, device=dev, generator=g) if kind == "cond" else None
+    sel = torch.linspace(0, B - 1, 256).long()
+    z, ld = _call(net, x, cond)
+    xs = x[sel.to(dev)].cpu().numpy()
+    cs = None if cond is None else cond[sel.to(dev)].reshape(256, E).cpu().numpy()
+    z_ref, ld_ref = O.flow_forward(sd, xs, cs)
+    t = TOL_FULL[precision]
+    zg = z.reshape(B, C)[sel.to(dev)].cpu().numpy()
+    assert max_rel(zg, z_ref) < t["z"] and rel_l2(zg, z_ref) < t["l2"]
+    assert _ld_ok(ld[sel.to(dev)].cpu().numpy(), ld_ref, precision)
+    zin = torch.randn(B, C, device=dev, generator=g)
+    zin[sel.to(dev)] = torch.from_numpy(z_ref).to(dev)
+    xr = _call(net, zin, cond, reverse=True).reshape(B, C)[sel.to(dev)].cpu().numpy()
+    x_ref = O.flow_reverse(sd, z_ref, cs)
+    assert max_rel(xr, x_ref) < t["z"] and rel_l2(xr, x_ref) < t["l2"]
+
+
+@pytest.mark.parametrize("name,B,bound", [("cfgA", 64, 1e-4), ("cfgB", 256, 5e-4)])
+def test_parity_mode_with_weights_scaled_by_two(name, B, bound):
+    """Trained weights are larger than the default init and amplify the error of every reduced-precision operand
+    format.  With every Linear weight doubled (pre-activations 2-16x larger, tanh partly saturated)
+    the parity mode still meets 1e-4 at cfg A; at cfg B it measures 2.5e-4 (plain fp32 numpy: 1.1e-5 against fp64) --
+    the stated limit of the 16-bit hi+lo operand split (profiles/r02_precision_report.txt)."""
+    net, sd, kind, C, E = _oracle_initialised(name, "fp32", wscale=2.0)
+    g = torch.Generator().manual_seed(99)
+    x = torch.randn(B, C, generator=g)
+    cond = torch.randn(B, E, generator=g) if kind == "cond" else None
+    z_ref, ld_ref = O.flow_forward(sd, x.numpy().astype(np.float64),
+                                   None if cond is None else cond.numpy().astype(np.float64), dtype=np.float64)
+    z, ld = _call(net, x.to(_dev()), None if cond is None else cond.reshape(B, E, 1, 1).to(_dev()))
+    assert max_rel(z.cpu().numpy().reshape(B, C), z_ref) < bound
+    assert max_rel(ld.cpu().numpy(), ld_ref) < 1e-4
 
 
 @pytest.mark.parametrize("name,B", [("cfgA", 4096 + 77), ("cfgB", 2048)])
@@ -235,4 +301,7 @@ def test_concurrent_streams_match_serial(name, B):
             assert _ld_ok(ld1.cpu().numpy(), ld0.cpu().numpy(), "bf16", kw["n_flows"], C)
             if prev is not None:
                 assert torch.equal(z1, prev[0]) and torch.equal(x1, prev[1])
-            prev = (z1.clone(), x1.clone())
+                # logdet: the partial row sums of a half-step's column tiles are added with fp32 atomics, so it is
+                # reproducible up to the order of those 2-8 additions, not bitwise
+                assert float((ld1 - prev[2]).abs().max()) <= 4e-6 * float(ld1.abs().max())
+            prev = (z1.clone(), x1.clone(), ld1.clone())
