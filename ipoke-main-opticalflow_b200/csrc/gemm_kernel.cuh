@@ -44,15 +44,8 @@ struct GemmParams {
   int stages;
   int tmem_cols;          // power of two >= nacc * NSUB * BN
   int nacc;               // accumulator stages in TMEM (1 or 2)
-  int kacc;               // K-interleaved accumulators per output tile (1, 2, 4): consecutive MMAs go to different TMEM
-                          // accumulators and the epilogue adds them. An MMA that accumulates into the tile the previous
-                          // one wrote waits ~90 ns for it whatever N is (measured, r01 trace), so a one-wave launch
-                          // (K/16 dependent MMAs per CTA) is bound by that chain unless it is split.
   int epi_off;            // byte offset of the epilogue smem region (1024-aligned) = stages * stage_bytes
   int w_prefetch;         // 1: fetch the first stages' W tiles before griddepcontrol.wait
-  int k_rotate;           // 1: tile (m, n) walks its k-blocks starting at n (mod K/64): CTAs that share an A row
-                          //    block then read different L2 lines at any moment (one-wave launches hot-spot otherwise)
-  int mcast;              // cluster size along n (1, 2, 4, 8): A tiles are TMA-multicast to the CTAs sharing an m-tile
   int slab_bufs;          // EPI_HIDDEN: 0 = direct global stores, 1 / 2 / 4 = TMA-store slab buffers per (hi|lo)
   int slab_warp;          // warp-private output slabs, no CTA barrier inside a tile: 1 = tmO box 64 x 32 (128-B swizzle,
                           // slab_bufs >= 2), 2 = tmO box 32 x 32 (64-B swizzle, slab_bufs == 1)
@@ -158,11 +151,11 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
   const int w_tile_bytes = BN * BK * 2;
   const int stage_bytes = NSUB * kSplit * (A_TILE_BYTES + w_tile_bytes);
   const int stages = p.stages;
-  const int kacc = p.kacc;
+  constexpr int kacc = 1;                    // K-interleaved accumulators: measured no gain (r01) -- compiled out
   const int sub_cols = kacc * BN;            // TMEM columns of one accumulator set (s or t)
   const int acc_cols = NSUB * sub_cols;
   const int nacc = p.nacc;
-  const int mc = p.mcast;
+  constexpr int mc = 1;                      // TMA-multicast clusters along n: measured slower at one wave (r01) -- compiled out
   const uint32_t cta_rank = mc > 1 ? cluster_ctarank() : 0u;
   const uint16_t mc_mask = static_cast<uint16_t>((1u << mc) - 1u);
 
@@ -227,7 +220,7 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
       const int n_tile0 = blockIdx.x % p.num_n_tiles;
       pre = p.num_k_blocks < stages ? p.num_k_blocks : stages;
       for (int ki = 0; ki < pre; ++ki) {
-        const int kb = p.k_rotate ? (ki + n_tile0) % p.num_k_blocks : ki;
+        const int kb = ki;
         mbar_arrive_expect_tx_el(&full_bar[ki], stage_bytes);
         uint8_t* sbase = smem + ki * stage_bytes;
 #pragma unroll
@@ -256,7 +249,7 @@ inn_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
         if (p.a_m_wrap > 0) a_row0 = (m_tile % p.a_m_wrap) * BM;
       }
       for (int ki = 0; ki < p.num_k_blocks; ++ki) {
-        const int kb = p.k_rotate ? (ki + n_tile) % p.num_k_blocks : ki;
+        const int kb = ki;
         {
           uint8_t* sbase = smem + stage * stage_bytes;
           const bool w_done = first_tile && ki < pre;

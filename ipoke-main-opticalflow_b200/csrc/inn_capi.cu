@@ -20,7 +20,6 @@
 #include "optim.cuh"
 #include "tail_cluster_kernel.cuh"
 #include "hidden_pair_kernel.cuh"
-#include "hidden_cluster_kernel.cuh"
 #include "wgrad_kernel.cuh"
 
 using namespace inn;
@@ -65,7 +64,6 @@ struct GemmOp {
   GemmParams p;
   int mode, grid, smem, cluster;
   int tail_cluster;   // 1: inn_tail_cluster_kernel (small batches), cluster = 2 * p.ks
-  int hidden_cluster; // 1: inn_hidden_cluster_kernel (small batches: split-K cluster of p.ks CTAs per tile)
   int pair;           // 1: inn_hidden_pair_kernel (multi-wave hidden layers as tcgen05 CTA pairs), params in pp
   PairParams pp;
 };
@@ -168,24 +166,16 @@ struct ipoke_inn_plan {
   std::vector<std::unique_ptr<Program>> programs;
   int last_launches = 0;
   // launch options: 1 = replay the program as a CUDA graph (captured on an internal stream), PDL attribute on GEMMs
-  int use_graph = 1, use_pdl = 1, use_mcast = 0;
+  int use_graph = 1, use_pdl = 1;
   int tail_bn_max = 128;
-  int k_rotate = 0;
   int tail_direct = 1;
   int streams = 1;                // calls the caller runs concurrently on different streams: one-wave launches are
                                   // sized for num_sms / streams SMs so that the concurrent kernels are co-resident
-  int slab4 = 0;                  // 4 output slabs in flight where the pipeline leaves smem free
-  int hidden_cluster = 0;         // one-wave hidden layers as split-K clusters (hidden_cluster_kernel.cuh): measured SLOWER
-                                  // (cfg B b256 734 -> 893 us/step: 16-byte remote stores of a 64 KB partial cost more than
-                                  // the halved operand ingest saves; profiles/r01_ab_hcluster_v9.txt) -> off
   int bwd_graph = 1;              // replay the backward pass as a CUDA graph when the caller's pointers repeat
-  int wgrad_wide = 0;             // wgrad: 128 x 256 tiles with the staging tile aliased onto the pipeline stages: parity green,
-                                  // no gain (cfg A / 4096: 3.59 vs 3.47 ms -- the MN-major wgrad is not ingest-bound) -> off
   int use_pair = 1;               // multi-wave hidden layers as CTA pairs (hidden_pair_kernel.cuh)
   int warp_slab = 1;              // hidden / dgrad epilogue: warp-private output slabs (no CTA barrier inside a tile)
   int tail_cluster = 1;           // small batches: coupling tails as split-K clusters (tail_cluster_kernel.cuh)
   int dbg = 0;
-  int kacc_max = 1;               // K-interleaved accumulators: measured no gain once the MMA issue is uniform
   int hidden_bn_force = 0;       // debug: fixed tile width of the hidden-layer GEMMs
   int widek_cover = 30;          // SM coverage target (%) of the hidden GEMMs when Hp > 1024 and ...
   int widek_mtiles = 8;          // ... the batch has at most this many 128-row tiles (one request at a time)
@@ -303,8 +293,6 @@ int ensure_device(ipoke_inn_plan* P) {
 #define SET_SMEM(K)                                                                                    \
   e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);               \
   if (e != cudaSuccess) return (int)e;
-  SET_SMEM((inn_hidden_cluster_kernel<1>))
-  SET_SMEM((inn_hidden_cluster_kernel<2>))
   SET_SMEM((inn_hidden_pair_kernel<1>))
   SET_SMEM((inn_hidden_pair_kernel<2>))
   SET_SMEM((inn_gemm_kernel<1, EPI_HIDDEN>))
@@ -350,7 +338,7 @@ inline int slab_warp_mode(const ipoke_inn_plan* P, int slab_bufs) {
   return slab_bufs >= 2 ? 1 : 2;
 }
 
-struct TileCfg { int bn = 0, stages = 0, slab_bufs = 0, mc = 1, direct = 0; };
+struct TileCfg { int bn = 0, stages = 0, slab_bufs = 0, direct = 0; };
 
 // smem plan for one tile width: pipeline stages + epilogue staging must fit in 227 KB
 TileCfg tile_cfg(int ksplit, int mode, int bn, int direct = 0) {
@@ -389,15 +377,6 @@ TileCfg pick_bn(const ipoke_inn_plan* P, int mode, int rows_per_group, int tiles
     if ((long long)tiles_other * (rows_per_group / bn) * 100 >= (long long)(P->num_sms / P->streams) * cover_pct) return t;
   }
   return best;
-}
-
-// Latency mode (one wave of tiles): CTAs of consecutive n-tiles share their A tile -> cluster + TMA multicast.
-int pick_mc(const ipoke_inn_plan* P, int tiles, int n_tiles, int tiles_per_group) {
-  if (!P->use_mcast || tiles > P->num_sms) return 1;
-  static const int cand[3] = {8, 4, 2};
-  for (int i = 0; i < 3; ++i)
-    if (cand[i] <= P->use_mcast && n_tiles % cand[i] == 0 && tiles_per_group % cand[i] == 0) return cand[i];
-  return 1;
 }
 
 struct Builder {
@@ -494,19 +473,9 @@ struct Builder {
     while ((1 << g.p.bn_log2) < t.bn) g.p.bn_log2++;
     g.p.stages = std::min(t.stages, std::max(2, g.p.num_k_blocks));
     int slab_bufs = t.slab_bufs;
-    // short-K layers (the first Linear of a subnetwork) are bound by the output stores: with the smem the unused
-    // pipeline stages leave free, keep 4 slab stores in flight instead of 2 (more bytes in flight per SM)
-    if (P->slab4 && slab_bufs == 2 && (g.mode == EPI_HIDDEN || g.mode == EPI_DGRAD)) {
-      const int st2 = std::min(t.stages, std::max(2, 2 * g.p.num_k_blocks));   // up to two tiles of loads in flight
-      const int st_min = g.p.num_k_blocks <= 4 ? std::min(g.p.stages, 3) : g.p.stages;   // store-bound: 3 stages do
-      for (int st = st2; st >= st_min; --st)
-        if (gemm_smem_bytes(P->ksplit, g.mode, t.bn, st, 4) <= kMaxDynSmem) { g.p.stages = st; slab_bufs = 4; break; }
-    }
     g.p.slab_bufs = slab_bufs;
     g.p.slab_warp = (g.mode == EPI_HIDDEN || g.mode == EPI_DGRAD) ? slab_warp_mode(P, slab_bufs) : 0;
-    g.p.mcast = t.mc;
     g.p.w_prefetch = P->w_prefetch;
-    g.p.k_rotate = (P->k_rotate && g.p.num_m_tiles * g.p.num_n_tiles <= 2 * P->num_sms && !g.p.w_mn) ? 1 : 0;
     const int tiles = g.p.num_m_tiles * g.p.num_n_tiles;
     if (tiles <= P->num_sms && P->latency_smem_cap_kb > 0) {
       // optional: keep the footprint small so the next kernel's CTA (PDL) can be co-resident
@@ -514,23 +483,16 @@ struct Builder {
              gemm_smem_bytes(P->ksplit, g.mode, t.bn, g.p.stages, slab_bufs, t.direct) > P->latency_smem_cap_kb * 1024)
         g.p.stages--;
     }
-    // one-wave launches: split the dependent MMA chain over up to 4 K-interleaved accumulators
-    int kacc = 1;
-    if (tiles <= P->num_sms && (g.mode == EPI_HIDDEN || g.mode == EPI_TAIL_FWD || g.mode == EPI_TAIL_REV)) {
-      kacc = P->kacc_max;
-      while (kacc > 1 && gemm_nsub(g.mode) * kacc * t.bn > 512) kacc >>= 1;
-    }
-    g.p.kacc = kacc;
     g.p.direct = t.direct;
-    const int acc_cols = gemm_nsub(g.mode) * kacc * t.bn;
+    const int acc_cols = gemm_nsub(g.mode) * t.bn;
     g.p.nacc = (2 * acc_cols <= 512) ? 2 : 1;
     int cols = 32;
     while (cols < g.p.nacc * acc_cols) cols <<= 1;
     g.p.tmem_cols = cols;
     g.p.epi_off = g.p.stages * gemm_stage_bytes(P->ksplit, g.mode, t.bn);
     g.smem = gemm_smem_bytes(P->ksplit, g.mode, t.bn, g.p.stages, slab_bufs, t.direct);
-    g.grid = t.mc > 1 ? tiles : std::min(tiles, P->num_sms);
-    g.cluster = t.mc;
+    g.grid = std::min(tiles, P->num_sms);
+    g.cluster = 1;
     if (P->ksplit == 1) {
       g.tmA[1] = g.tmA[0];
       g.tmW[1] = g.tmW[0];
@@ -554,72 +516,16 @@ struct Builder {
     TileCfg tc = pick_bn(P, EPI_HIDDEN, P->Hp, m_tiles * c.G, 256, cover);
     if (P->hidden_bn_force > 0 && P->Hp % P->hidden_bn_force == 0) tc = tile_cfg(P->ksplit, EPI_HIDDEN, P->hidden_bn_force);
     const int bn = tc.bn;
-    tc.mc = pick_mc(P, m_tiles * (rows / bn), rows / bn, P->Hp / bn);
-    const int a_box = BM / tc.mc;
+    const int a_box = BM;
     // multi-wave launches: CTA pairs (cta_group::2) on 256 x bn tiles, each CTA staging half of the W tile
     const int m_pairs = (m_tiles + 1) / 2;
-    const bool pair = P->use_pair && tc.mc == 1 && (bn == 128 || bn == 256) && P->trace_buf == nullptr &&
+    const bool pair = P->use_pair && (bn == 128 || bn == 256) && P->trace_buf == nullptr &&
                       (P->use_pair > 1 ? (long long)m_tiles * (rows / bn) > P->num_sms      // 2: every multi-wave launch
                                        : 2ll * m_tiles * (rows / bn) >= 5ll * P->num_sms);  // default: >= 2.5 waves (measured:
                                                                                            // 1.7 waves at cfg B / 4096 lose 3 %)
     for (size_t l = 0; l < c.L.size(); ++l) {
       const LayerW& L = c.L[l];
       GemmOp& g = add_gemm(EPI_HIDDEN);
-      // one-wave launches: split-K cluster when it cuts the bytes one SM has to pull through its L2 port
-      if (!pair && P->hidden_cluster && tc.mc == 1 && P->trace_buf == nullptr && P->kacc_max == 1 &&
-          (long long)m_tiles * (rows / bn) <= P->num_sms) {
-        const int cap = P->hidden_cluster > 1 ? P->num_sms : std::max(1, P->num_sms / P->streams);
-        const int nkb_all = L.Kp / BK;
-        const long long base_cost = (long long)(BM + bn) * L.Kp * 2;
-        long long best = (base_cost * 4) / 5;                      // must save >= 20 % of the per-SM bytes
-        int cbn = 0, cks = 0, cst = 0;
-        static const int bns[2] = {128, 64}, kss[3] = {8, 4, 2};
-        for (int bi = 0; bi < 2; ++bi)
-          for (int ki = 0; ki < 3; ++ki) {
-            const int b2 = bns[bi], ks = kss[ki];
-            if (P->Hp % b2 != 0 || nkb_all % ks != 0 || nkb_all / ks < 2) continue;
-            if ((long long)m_tiles * (rows / b2) * ks > cap) continue;
-            const int nkb = nkb_all / ks;
-            const int fit = (kMaxDynSmem - 1024 - SMEM_BARRIER_BYTES - hidden_cluster_recv_bytes(b2)) /
-                            hidden_cluster_stage_bytes(P->ksplit, b2);
-            if (fit < 2) continue;
-            const long long cost = (long long)(BM + b2) * BK * 2 * nkb + (long long)BM * b2 * 4 * (ks - 1) / ks;
-            if (cost < best) { best = cost; cbn = b2; cks = ks; cst = std::min(std::min(nkb, MAX_STAGES), fit); }
-          }
-        if (cks > 0) {
-          const long long ld_act = save ? rows : P->ldACT;
-          g.hidden_cluster = 1;
-          g.p.M = B;
-          g.p.BN = cbn;
-          g.p.num_n_tiles = rows / cbn;
-          g.p.tiles_per_group = P->Hp / cbn;
-          g.p.num_k_blocks = nkb_all;
-          g.p.ks = cks;
-          g.p.stages = cst;
-          g.p.w_prefetch = P->w_prefetch;
-          g.p.a_group_stride = l == 0 ? 0 : P->Hp;
-          g.p.bias = pk<float>(L.bias);
-          g.p.slope = P->d.mlp_slope;
-          g.p.out_hi = reinterpret_cast<__nv_bfloat16*>(act_base(k, ci, (int)l, 0));
-          g.p.out_lo = P->ksplit == 2 ? reinterpret_cast<__nv_bfloat16*>(act_base(k, ci, (int)l, 1)) : nullptr;
-          g.p.ld_out = (int)ld_act;
-          g.smem = hidden_cluster_smem_bytes(P->ksplit, cbn, cst);
-          g.cluster = cks;
-          g.grid = m_tiles * g.p.num_n_tiles * cks;
-          for (int sp = 0; sp < P->ksplit; ++sp) {
-            if (l == 0) err |= make_map(P, &g.tmA[sp], u_base(k, ui, sp) + 2ll * c.a_col_off, c.Kin_p, B, 2ll * P->ldU, BM);
-            else err |= make_map(P, &g.tmA[sp], act_base(k, ci, (int)l - 1, sp), rows, B, 2ll * ld_act, BM);
-            err |= make_map(P, &g.tmW[sp], packed + (sp == 0 ? L.hi : L.lo), L.Kp, L.rows, 2ll * L.Kp, cbn);
-            g.tmO[sp] = g.tmA[sp];
-          }
-          if (P->ksplit == 1) {
-            g.tmA[1] = g.tmA[0];
-            g.tmW[1] = g.tmW[0];
-            g.tmO[1] = g.tmO[0];
-          }
-          continue;
-        }
-      }
       if (pair) {
         const long long ld_act = save ? rows : P->ldACT;
         PairParams& q = g.pp;
@@ -720,7 +626,6 @@ struct Builder {
     }
     const int bn = tc.bn;
     g.p.num_n_tiles = P->Np / bn;
-    if (ks == 0) tc.mc = pick_mc(P, m_tiles * (P->Np / bn), P->Np / bn, P->Np / bn);
     g.p.tiles_per_group = 1 << 30;
     g.p.num_k_blocks = P->Hp / BK;
     g.p.a_group_stride = 0;
@@ -781,7 +686,7 @@ struct Builder {
     }
     const long long ld_act = save ? (long long)G * P->Hp : P->ldACT;
     for (int sp = 0; sp < P->ksplit; ++sp) {
-      err |= make_map(P, &g.tmA[sp], act_base(k, ci, act_layer, sp), G * P->Hp, wrap ? Bc : B, 2ll * ld_act, BM / tc.mc);
+      err |= make_map(P, &g.tmA[sp], act_base(k, ci, act_layer, sp), G * P->Hp, wrap ? Bc : B, 2ll * ld_act, BM);
       err |= make_map(P, &g.tmW[sp], packed + (sp == 0 ? t.w.hi : t.w.lo), t.w.Kp, t.w.rows, 2ll * t.w.Kp, bn);
       g.tmO[sp] = g.tmA[sp];      // unused by the tail epilogue
     }
@@ -1016,7 +921,6 @@ struct BwdBuilder : Builder {
       err |= make_map(P, &g.tmW[sp], packed + (sp == 0 ? W.hi : W.lo), W.Kp, W.rows, 2ll * W.Kp, 64);
       g.tmO[sp] = g.tmA[sp];
     }
-    tc.mc = 1;
     finish_gemm(g, tc);
     g.p.w_prefetch = 0;
     return g;
@@ -1050,15 +954,7 @@ struct BwdBuilder : Builder {
     q.m_tiles = (rows_p + BM - 1) / BM;
     int bn = kin_p >= 128 ? 128 : 64;
     if (P->ksplit == 2 && kin_p >= 128) bn = 128;
-    // 128 x 256 tiles when they make one wave (one tile per CTA): the epilogue staging tile (131 KB) then reuses the
-    // idle pipeline stages.  A 128 x 128 tile needs 32 KB per 0.15 us of tensor work (213 GB/s per SM, twice what one
-    // SM ingests: tensor pipe 31 % active, ncu r01 v10); 128 x 256 needs 48 KB per 0.3 us.
-    int alias = 0;
-    if (P->wgrad_wide && kin_p % 256 == 0 && groups * q.m_tiles * (kin_p / 256) <= P->num_sms && q.num_kb >= 8 &&
-        2 * groups * q.m_tiles * (kin_p / 256) > P->num_sms) {
-      bn = 256;
-      alias = 1;
-    }
+    const int alias = 0;      // 128 x 256 tiles aliased onto the pipeline stages: parity green, no gain (r01 v11) -- not built
     q.BN = bn;
     q.epi_alias = alias;
     q.n_tiles = (kin_p + bn - 1) / bn;
@@ -1352,35 +1248,8 @@ cudaError_t launch_pair_t(const GemmOp& g, cudaStream_t st, int pdl) {
                             g.tmO[1], g.pp);
 }
 
-template <int kSplit>
-cudaError_t launch_hidden_cluster_t(const GemmOp& g, const GemmParams& gp, cudaStream_t st, int pdl) {
-  cudaLaunchConfig_t cfg;
-  std::memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = dim3((unsigned)g.grid);
-  cfg.blockDim = dim3(HC_THREADS);
-  cfg.dynamicSmemBytes = (size_t)g.smem;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[2];
-  int na = 0;
-  if (pdl) {
-    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[na].val.programmaticStreamSerializationAllowed = 1;
-    ++na;
-  }
-  attr[na].id = cudaLaunchAttributeClusterDimension;
-  attr[na].val.clusterDim.x = (unsigned)g.cluster;
-  attr[na].val.clusterDim.y = 1;
-  attr[na].val.clusterDim.z = 1;
-  ++na;
-  cfg.attrs = attr;
-  cfg.numAttrs = na;
-  return cudaLaunchKernelEx(&cfg, inn_hidden_cluster_kernel<kSplit>, g.tmA[0], g.tmA[1], g.tmW[0], g.tmW[1], gp);
-}
-
 cudaError_t launch_gemm(const ipoke_inn_plan* P, const GemmOp& g, const GemmParams& gp, cudaStream_t st) {
   const int pdl = P->use_pdl;
-  if (g.hidden_cluster)
-    return P->ksplit == 2 ? launch_hidden_cluster_t<2>(g, gp, st, pdl) : launch_hidden_cluster_t<1>(g, gp, st, pdl);
   if (g.pair) return P->ksplit == 2 ? launch_pair_t<2>(g, st, pdl) : launch_pair_t<1>(g, st, pdl);
   if (g.tail_cluster) {
     const bool rev = g.mode == EPI_TAIL_REV;
@@ -1820,7 +1689,6 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   P->device = device;
   if (const char* e = std::getenv("IPOKE_INN_GRAPH")) P->use_graph = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_PDL")) P->use_pdl = std::atoi(e) != 0;
-  if (const char* e = std::getenv("IPOKE_INN_MCAST")) P->use_mcast = std::atoi(e) == 1 ? 8 : std::atoi(e);   // max cluster size (1 = 8)
   if (const char* e = std::getenv("IPOKE_INN_FOLD")) P->use_fold = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_FOLD_MAXB")) P->fold_max_rows = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_FASTB")) P->fast_boundary = std::atoi(e);
@@ -1828,18 +1696,13 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_HIDDEN_BN")) P->hidden_bn_force = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WIDEK_COVER")) P->widek_cover = std::max(1, std::atoi(e));
   if (const char* e = std::getenv("IPOKE_INN_WIDEK_MT")) P->widek_mtiles = std::atoi(e);
-  if (const char* e = std::getenv("IPOKE_INN_KROT")) P->k_rotate = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_DBG")) P->dbg = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_DIRECT")) P->tail_direct = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_TAIL_CLUSTER")) P->tail_cluster = std::atoi(e);
-  if (const char* e = std::getenv("IPOKE_INN_SLAB4")) P->slab4 = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WARPSLAB")) P->warp_slab = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_PAIR")) P->use_pair = std::atoi(e);
-  if (const char* e = std::getenv("IPOKE_INN_WGRAD_WIDE")) P->wgrad_wide = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_BWD_GRAPH")) P->bwd_graph = std::atoi(e);
-  if (const char* e = std::getenv("IPOKE_INN_HCLUSTER")) P->hidden_cluster = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_STREAMS")) P->streams = std::max(1, std::min(std::atoi(e), 8));
-  if (const char* e = std::getenv("IPOKE_INN_KACC")) P->kacc_max = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WPREFETCH")) P->w_prefetch = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_STAGECAP_KB")) P->latency_smem_cap_kb = std::atoi(e);
   P->ksplit = d.precision == IPOKE_INN_PREC_FP32_SPLIT ? 2 : 1;
@@ -2333,7 +2196,6 @@ int ipoke_inn_set_option(ipoke_inn_plan* P, const char* name, int value) {
   if (std::strcmp(name, "graph") == 0) P->use_graph = value != 0;
   else if (std::strcmp(name, "bwd_graph") == 0) P->bwd_graph = value != 0;
   else if (std::strcmp(name, "pdl") == 0) { P->use_pdl = value != 0; P->programs.clear(); }
-  else if (std::strcmp(name, "mcast") == 0) { P->use_mcast = value == 1 ? 8 : value; P->programs.clear(); }
   else if (std::strcmp(name, "fold") == 0) { P->use_fold = value != 0; P->programs.clear(); }
   else if (std::strcmp(name, "streams") == 0) { P->streams = std::max(1, std::min(value, 8)); P->programs.clear(); }
   else return IPOKE_INN_E_INVALID;

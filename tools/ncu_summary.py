@@ -15,7 +15,7 @@ import subprocess
 import sys
 
 KIND = [("inn_gemm_kernel<1, 0", "hidden"), ("inn_gemm_kernel<2, 0", "hidden"), ("inn_hidden_pair", "hidden"),
-        ("inn_hidden_cluster", "hidden"), ("inn_tail_cluster", "tail"),
+        ("inn_tail_cluster", "tail"),
         ("inn_gemm_kernel<1, 1", "tail"), ("inn_gemm_kernel<1, 2", "tail"), ("inn_gemm_kernel<2, 1", "tail"),
         ("inn_gemm_kernel<2, 2", "tail"), ("inn_boundary", "boundary")]
 
