@@ -12,7 +12,7 @@ from .flow_blocks import (ConditionalFlow, UnconditionalFlow2, ConditionalFlatDo
                           UnconditionalFlatDoubleCouplingFlowBlock2, ConditionalDoubleVectorCouplingBlock,
                           ConditionalDoubleVectorCouplingBlock_cond, DoubleVectorCouplingBlock2)
 from .loss import FlowLoss
-from .latent_interface import SecondStageLatentInterface, FlowAELatentInterface
+from .latent_interface import SecondStageLatentInterface, FlowAELatentInterface, ThirdStageLatentInterface
 from .optim import FusedAdam, linear_var
 from .optim_sharded import ShardedAdam, plan_pieces
 from .parallel import GradSync, broadcast_parameters, shard_batch, shard_bounds
@@ -21,7 +21,7 @@ from .modules import ActNorm, BasicFullyConnectedNet, IgnoreLeakyRelu, InvLeakyR
 __all__ = ["SupervisedTransformer", "UnsupervisedTransformer3", "ConditionalFlow", "UnconditionalFlow2",
            "FlowLoss", "ActNorm", "BasicFullyConnectedNet", "Shuffle", "InvLeakyRelu", "IgnoreLeakyRelu",
            "FusedAdam", "linear_var", "install_as_reference", "SecondStageLatentInterface",
-           "FlowAELatentInterface", "GradSync", "ShardedAdam", "broadcast_parameters", "shard_batch", "shard_bounds"]
+           "FlowAELatentInterface", "ThirdStageLatentInterface", "GradSync", "ShardedAdam", "broadcast_parameters", "shard_batch", "shard_bounds"]
 
 
 def install_as_reference():

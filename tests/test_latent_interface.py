@@ -160,3 +160,118 @@ def test_flow_ae_interface_draw_order_and_shapes():
         assert torch.equal(imgs[k], ((z * 2).reshape(4, 7, 1, 1) * 3)[:2])
     out, ld = it.forward_density(batch)
     assert torch.equal(out, (batch["flow"].mean((2, 3)) + 1) * 0.5)
+
+
+# ----------------------------------------------------------------------------- third stage
+from ipoke_inn_b200.latent_interface import ThirdStageLatentInterface  # noqa: E402
+
+ZD, CF, BS = 5, 8, 6          # flow-AE z_dim, flow_in_channels, config batch size
+
+
+class _Dist:
+    def __init__(self, m): self.m = m
+    def sample(self): return self.m + 1
+    def mode(self): return self.m
+
+
+def _flow_ae():
+    calls = []
+    ae = types.SimpleNamespace(encode=lambda x: (calls.append("enc"), _Dist(x.mean((2, 3))[:, :ZD]))[1],
+                               decode=lambda z: (calls.append("dec"), z * 3)[1])
+    return ae, calls
+
+
+class _UncondINN:
+    def __init__(self): self.calls = []
+
+    def __call__(self, x, reverse=False):
+        self.calls.append((tuple(x.shape), reverse))
+        if reverse:
+            return x.reshape(x.shape[0], -1, 1, 1) * 2
+        return x.reshape(x.shape[0], -1, 1, 1) * 0.5, torch.zeros(x.shape[0])
+
+
+def test_third_stage_make_flow_input_pads_with_noise_and_keeps_rng_order():
+    ae, _ = _flow_ae()
+    it = ThirdStageLatentInterface(_UncondINN(), ae, flow_in_channels=CF, flow_z_dim=ZD, batch_size=BS)
+    batch = {"flow": torch.randn(4, 7, 3, 3)}
+    torch.manual_seed(21)
+    fi = it.make_flow_input(batch)
+    torch.manual_seed(21)
+    enc = batch["flow"].mean((2, 3))[:, :ZD] + 1
+    rest = torch.randn([4, CF - ZD])                                         # :192-196
+    assert torch.equal(fi, torch.cat((enc, rest), 1))
+    torch.manual_seed(22)
+    z = it.make_flow_input(batch, reverse=True)
+    torch.manual_seed(22)
+    assert torch.equal(z, torch.randn([BS, CF, 1, 1])) and z.shape[0] == BS   # config batch size, not the batch's (:183)
+    same = ThirdStageLatentInterface(_UncondINN(), ae, flow_in_channels=ZD, flow_z_dim=ZD, batch_size=BS)
+    assert torch.equal(same.make_flow_input(batch), enc)                      # no padding channels (:198-199)
+    with pytest.raises(AssertionError):
+        ThirdStageLatentInterface(_UncondINN(), ae, flow_in_channels=ZD - 1, flow_z_dim=ZD, batch_size=BS)
+
+
+def test_third_stage_density_returns_untouched_copy_and_poke_half_of_cond():
+    ae, _ = _flow_ae()
+    flow = _Flow()
+    second = types.SimpleNamespace(forward_density=lambda b, return_cond=False: (
+        torch.full((4, CF, 1, 1), 7.0), torch.zeros(4), torch.arange(4 * (EI + EP), dtype=torch.float32).reshape(4, EI + EP, 1, 1)))
+    it = ThirdStageLatentInterface(flow, ae, second, flow_in_channels=CF, flow_z_dim=ZD, batch_size=BS, poke_z_dim=EP)
+    batch = {"flow": torch.randn(4, 7, 3, 3)}
+    torch.manual_seed(5)
+    out, logdet, vec, out_hat = it.density_with_second_stage(batch)
+    torch.manual_seed(5)
+    expect_in = it.make_flow_input(batch)
+    assert torch.equal(vec, expect_in) and not vec.requires_grad
+    assert flow.calls[-1] == ("call", (4, CF), (4, EP, 1, 1), False)          # cond[:, -poke_z_dim:] (:246)
+    assert torch.equal(out, expect_in.reshape(4, CF, 1, 1) * 0.5) and torch.equal(out_hat, torch.full((4, CF, 1, 1), 7.0))
+
+
+def test_third_stage_forward_sample_equals_reference_loop():
+    ae, _ = _flow_ae()
+    batch = {"flow": torch.randn(BS, 7, 3, 3)}
+    nl, n = 3, 4
+    # conditional INN: one reverse_draws call on the shared conditioning
+    flow = _Flow()
+    it = ThirdStageLatentInterface(flow, ae, flow_in_channels=CF, flow_z_dim=ZD, batch_size=BS, poke_z_dim=EP)
+    cond = torch.randn(BS, EP, 1, 1)
+    torch.manual_seed(31)
+    imgs, residual = it.forward_sample(batch, cond, n_samples=n, n_logged_imgs=nl)
+    assert [c[0] for c in flow.calls].count("draws") == 1 and flow.calls[0] == ("draws", (n, nl, CF, 1, 1), (nl, EP, 1, 1), n)
+    ref = _Flow()
+    torch.manual_seed(31)
+    for k in range(n):                                                        # :219-230 restated
+        fi = torch.randn([BS, CF, 1, 1])
+        out = ref(fi[:nl], cond[:nl], reverse=True)
+        o, res = out[:, :ZD], out[:, ZD:]
+        assert torch.equal(imgs[k], o.squeeze(-1).squeeze(-1) * 3), k
+    assert torch.equal(residual, res) and residual.shape == (nl, CF - ZD, 1, 1)
+    # unconditional INN: one stacked reverse call; a given flow_input replaces the single draw
+    inn = _UncondINN()
+    it2 = ThirdStageLatentInterface(inn, ae, flow_in_channels=CF, flow_z_dim=ZD, batch_size=BS)
+    torch.manual_seed(32)
+    imgs2, _ = it2.forward_sample(batch, None, n_samples=n, n_logged_imgs=nl)
+    assert inn.calls == [((n * nl, CF, 1, 1), True)]
+    torch.manual_seed(32)
+    for k in range(n):
+        fi = torch.randn([BS, CF, 1, 1])
+        assert torch.equal(imgs2[k], (fi[:nl] * 2)[:, :ZD].squeeze(-1).squeeze(-1) * 3)
+    given = torch.randn(BS, CF, 1, 1)
+    imgs3, _ = it2.forward_sample(None, None, 1, 2, given)                    # batch may be None then (:269)
+    assert torch.equal(imgs3[0], (given[:2] * 2)[:, :ZD].squeeze(-1).squeeze(-1) * 3)
+    with pytest.raises(AssertionError):
+        it2.forward_sample(batch, None, 2, 2, given)
+
+
+def test_second_stage_keypoint_pokes():
+    count = {"poke": 0, "cond": 0}
+    it = _iface(_Flow(), count)
+    batch = _batch()
+    kp = torch.randint(0, 5, (B, 2, 4, 4))
+    batch["keypoint_poke"] = (kp, "ids")
+    _, cond = it.make_flow_input(batch, reverse=True, use_kp_poke=True)       # :276-278
+    pe, ce, _, _ = _parts({"poke": 0, "cond": 0})
+    c_ref = torch.cat([ce(batch["images"][:, 0]), pe(kp.to(torch.float))], dim=1)[:, :, None, None]
+    assert torch.equal(cond, c_ref)
+    vids = it.forward_sample(batch, n_samples=2, n_logged_vids=1, use_keypoint_pokes=True)
+    assert len(vids) == 2
