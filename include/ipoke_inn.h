@@ -166,6 +166,10 @@ int ipoke_inn_actnorm_finalize(const double* moments, double count, int C, float
  * dz = nll_weight * z / B, dlogdet = -logdet_weight / B (either may be NULL).                 */
 int ipoke_inn_flow_loss(const float* z, const float* logdet, int B, int C, float nll_weight, float logdet_weight,
                         float* out3, float* dz, float* dlogdet, void* stream);
+/* Same launch plus the reference NLL the reference logs every step: out4[3] = mean(0.5 * sum ref_sample^2) for the
+ * N(0, I) sample it draws with randn_like (loss.py:27, 32; the draw stays with the caller: same RNG consumption). */
+int ipoke_inn_flow_loss_ref(const float* z, const float* logdet, const float* ref_sample, int B, int C, float nll_weight,
+                            float logdet_weight, float* out4, float* dz, float* dlogdet, void* stream);
 
 /* Fused Adam / AMSGrad step over all parameter tensors in one launch -- replaces the reference's
  * torch.optim.Adam(lr, betas, weight_decay, amsgrad=True).step() (models/second_stage_video_fc.py:685-687;

@@ -430,18 +430,24 @@ __global__ void inn_actnorm_finalize_kernel(const double* __restrict__ moments, 
 
 // ----------------------------------------------------------------------------- FlowLoss
 // single CTA: B*C is small next to the GEMMs; deterministic tree reduction
+// `ref` (nullable): the N(0, I) sample the reference draws for its logged reference NLL (loss.py:27, 32); its mean NLL goes
+// to out3[3] in the same launch
 __global__ void __launch_bounds__(1024) inn_flow_loss_kernel(const float* __restrict__ z, const float* __restrict__ logdet,
                                                              int B, int C, float nll_w, float ld_w, float* out3,
-                                                             float* dz, float* dlogdet) {
+                                                             float* dz, float* dlogdet, const float* __restrict__ ref) {
   __shared__ double r_nll[1024];
   __shared__ double r_ld[1024];
-  double a = 0.0, l = 0.0;
+  double a = 0.0, l = 0.0, r = 0.0;
   const long long total = static_cast<long long>(B) * C;
   const float inv_b = 1.0f / static_cast<float>(B);
   for (long long i = threadIdx.x; i < total; i += blockDim.x) {
     const float v = z[i];
     a += 0.5 * static_cast<double>(v) * v;
     if (dz) dz[i] = nll_w * v * inv_b;
+    if (ref) {
+      const float w = ref[i];
+      r += 0.5 * static_cast<double>(w) * w;
+    }
   }
   for (int b = threadIdx.x; b < B; b += blockDim.x) {
     l += logdet[b];
@@ -462,6 +468,16 @@ __global__ void __launch_bounds__(1024) inn_flow_loss_kernel(const float* __rest
     out3[0] = static_cast<float>(nll_w * nll + ld_w * nld);
     out3[1] = static_cast<float>(nll);
     out3[2] = static_cast<float>(nld);
+  }
+  if (ref) {                                    // third reduction, same tree
+    __syncthreads();
+    r_nll[threadIdx.x] = r;
+    __syncthreads();
+    for (int s = 512; s > 0; s >>= 1) {
+      if (threadIdx.x < s) r_nll[threadIdx.x] += r_nll[threadIdx.x + s];
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) out3[3] = static_cast<float>(r_nll[0] / B);
   }
 }
 

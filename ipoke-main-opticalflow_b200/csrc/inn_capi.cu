@@ -2045,7 +2045,16 @@ int ipoke_inn_flow_loss(const float* z, const float* logdet, int B, int C, float
                         float* out3, float* dz, float* dlogdet, void* stream) {
   if (!z || !logdet || !out3 || B <= 0 || C <= 0) return IPOKE_INN_E_INVALID;
   inn_flow_loss_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(z, logdet, B, C, nll_weight, logdet_weight,
-                                                                          out3, dz, dlogdet);
+                                                                          out3, dz, dlogdet, nullptr);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : (int)e;
+}
+
+int ipoke_inn_flow_loss_ref(const float* z, const float* logdet, const float* ref_sample, int B, int C, float nll_weight,
+                            float logdet_weight, float* out4, float* dz, float* dlogdet, void* stream) {
+  if (!z || !logdet || !ref_sample || !out4 || B <= 0 || C <= 0) return IPOKE_INN_E_INVALID;
+  inn_flow_loss_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(z, logdet, B, C, nll_weight, logdet_weight,
+                                                                          out4, dz, dlogdet, ref_sample);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : (int)e;
 }

@@ -6,29 +6,31 @@ import torch.nn as nn
 from . import _capi
 
 
-def _loss_kernel(z2, logdet, nll_w, ld_w, want_grads):
+def _loss_kernel(z2, logdet, ref2, nll_w, ld_w, want_grads):
+    """One launch: loss, mean nll, -mean logdet, mean nll of the reference sample (+ dz, dlogdet) -> out4."""
     B, C = z2.shape
-    out3 = torch.empty(3, dtype=torch.float32, device=z2.device)
+    out4 = torch.empty(4, dtype=torch.float32, device=z2.device)
     dz = torch.empty_like(z2) if want_grads else None
     dld = torch.empty_like(logdet) if want_grads else None
     stream = torch.cuda.current_stream(z2.device).cuda_stream
-    _capi.check(_capi.lib().ipoke_inn_flow_loss(z2.data_ptr(), logdet.data_ptr(), B, C, float(nll_w), float(ld_w),
-                                                out3.data_ptr(), dz.data_ptr() if want_grads else None,
-                                                dld.data_ptr() if want_grads else None, stream), "flow_loss")
-    return out3, dz, dld
+    _capi.check(_capi.lib().ipoke_inn_flow_loss_ref(z2.data_ptr(), logdet.data_ptr(), ref2.data_ptr(), B, C, float(nll_w),
+                                                    float(ld_w), out4.data_ptr(), dz.data_ptr() if want_grads else None,
+                                                    dld.data_ptr() if want_grads else None, stream), "flow_loss")
+    return out4, dz, dld
 
 
 class _FlowLossFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, z2, logdet, nll_w, ld_w):
-        out3, dz, dld = _loss_kernel(z2, logdet, nll_w, ld_w, True)
+    def forward(ctx, z2, logdet, ref2, nll_w, ld_w):
+        out4, dz, dld = _loss_kernel(z2, logdet, ref2, nll_w, ld_w, True)
         ctx.save_for_backward(dz, dld)
-        return out3
+        ctx.mark_non_differentiable(ref2)
+        return out4
 
     @staticmethod
     def backward(ctx, g):
         dz, dld = ctx.saved_tensors
-        return dz * g[0], dld * g[0], None, None      # only out3[0] (the loss) is differentiated
+        return dz * g[0], dld * g[0], None, None, None      # only out4[0] (the loss) is differentiated
 
 
 class FlowLoss(nn.Module):
@@ -49,14 +51,15 @@ class FlowLoss(nn.Module):
         B = sample.shape[0]
         z2 = sample.reshape(B, -1).contiguous()
         ld = logdet.contiguous()
+        # the reference draws a fresh N(0,1) sample for a logged reference NLL (loss.py:27,32) -- same RNG use; its
+        # reduction rides in the loss kernel's launch
+        ref2 = torch.randn_like(sample).reshape(B, -1)
         if torch.is_grad_enabled() and (z2.requires_grad or ld.requires_grad):
-            out3 = _FlowLossFn.apply(z2, ld, self.nll_weight, self.logdet_weight)
+            out4 = _FlowLossFn.apply(z2, ld, ref2, self.nll_weight, self.logdet_weight)
         else:
-            out3, _, _ = _loss_kernel(z2, ld, self.nll_weight, self.logdet_weight, False)
-        loss = out3[0]
-        # reference draws a fresh N(0,1) sample for a logged reference NLL (loss.py:27,32) -- same RNG use
-        ref_sample = torch.randn_like(sample)
-        ref3, _, _ = _loss_kernel(ref_sample.reshape(B, -1), torch.zeros_like(ld), 1.0, 0.0, False)
-        log = {"flow_loss": loss.detach(), "reference_nll_loss": ref3[1], "nlogdet_loss": out3[2].detach(),
-               "nll_loss": out3[1].detach(), "logdet_w": self.logdet_weight, "nll_w": self.nll_weight}
+            out4, _, _ = _loss_kernel(z2, ld, ref2, self.nll_weight, self.logdet_weight, False)
+        loss = out4[0]
+        logged = out4.detach()
+        log = {"flow_loss": logged[0], "reference_nll_loss": logged[3], "nlogdet_loss": logged[2],
+               "nll_loss": logged[1], "logdet_w": self.logdet_weight, "nll_w": self.nll_weight}
         return loss, log
