@@ -32,6 +32,12 @@ struct PairParams {
   int wide;               // 1: 64-column store boxes (4 KB per warp and split), 0: 32-column boxes (2 KB)
   const float* bias;      // [G * Hp]
   float slope;
+  // kDgrad (dX = dY * W, W read MN-major from the forward layout; epilogue = LeakyReLU' mask instead of bias + LeakyReLU)
+  int w_row0;             // first W row (contraction index) of group 0
+  int w_group_rows;       // W rows per group
+  int out_col0;           // first output column; tile (., n) writes columns out_col0 + n * BN ...
+  const __nv_bfloat16* mask_act;   // saved post-LeakyReLU activation (hi part) at the output position
+  int ld_mask, mask_col0;
 };
 
 __host__ inline int pair_stage_bytes(int ksplit, int BN) { return ksplit * (A_TILE_BYTES + (BN / 2) * BK * 2); }
@@ -40,7 +46,7 @@ __host__ inline int pair_smem_bytes(int ksplit, int BN, int stages, int wide) {
   return 1024 + stages * pair_stage_bytes(ksplit, BN) + pair_epi_bytes(ksplit, wide) + SMEM_BARRIER_BYTES;
 }
 
-template <int kSplit>
+template <int kSplit, bool kDgrad = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                        const __grid_constant__ CUtensorMap tmW0, const __grid_constant__ CUtensorMap tmW1,
@@ -110,6 +116,8 @@ inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
       const int m_tile = 2 * m_pair + static_cast<int>(rank);
       const int a_row0 = (p.a_m_wrap > 0 ? m_tile % p.a_m_wrap : m_tile) * BM;
       const int w_row0 = n_tile * BN + static_cast<int>(rank) * (BN / 2);
+      // kDgrad: this CTA's half of the tile's W columns, inside the group's column range
+      const int w_c0 = (n_tile - group * p.tiles_per_group) * BN + static_cast<int>(rank) * (BN / 2);
       for (int kb = 0; kb < p.num_k_blocks; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1, 21);
         if (rank == 0) mbar_arrive_expect_tx_el(&full_bar[stage], 2 * stage_bytes);
@@ -118,15 +126,23 @@ inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
 #pragma unroll
         for (int sp = 0; sp < kSplit; ++sp) {
           tma_load_2d_pair_el(sbase + sp * A_TILE_BYTES, sp == 0 ? &tmA0 : &tmA1, leader_full[stage], a_k, a_row0);
-          tma_load_2d_pair_el(sbase + kSplit * A_TILE_BYTES + sp * w_half_bytes, sp == 0 ? &tmW0 : &tmW1,
-                              leader_full[stage], kb * BK, w_row0);
+          if (kDgrad) {
+            // contraction index = W row: {64 rows} x {BN / 2 columns} as MN-major chunks of 64 columns (8 KB each)
+            const int w_rk = p.w_row0 + group * p.w_group_rows + kb * BK;
+            for (int c = 0; c < (BN >> 7); ++c)
+              tma_load_2d_pair_el(sbase + kSplit * A_TILE_BYTES + sp * w_half_bytes + c * (64 * 128),
+                                  sp == 0 ? &tmW0 : &tmW1, leader_full[stage], w_c0 + c * 64, w_rk);
+          } else {
+            tma_load_2d_pair_el(sbase + kSplit * A_TILE_BYTES + sp * w_half_bytes, sp == 0 ? &tmW0 : &tmW1,
+                                leader_full[stage], kb * BK, w_row0);
+          }
         }
         if (++stage == stages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1 && rank == 0) {
     // ============================ MMA issuer (leader CTA only) ============================
-    const uint32_t idesc = umma_idesc_bf16(2 * BM, BN);
+    const uint32_t idesc = umma_idesc_bf16(2 * BM, BN, 0, kDgrad ? 1 : 0);
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
@@ -142,19 +158,22 @@ inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
         const uint32_t sbase = smem_u32(smem + stage * stage_bytes);
         const uint32_t w0 = sbase + kSplit * A_TILE_BYTES;
         const uint64_t da_hi = umma_desc_k_sw128(sbase);
-        const uint64_t dw_hi = umma_desc_k_sw128(w0);
+        const uint64_t dw_hi = kDgrad ? umma_desc_mn_sw128(w0, 64 * 128) : umma_desc_k_sw128(w0);
         const uint64_t da_lo = umma_desc_k_sw128(sbase + (kSplit - 1) * A_TILE_BYTES);
-        const uint64_t dw_lo = umma_desc_k_sw128(w0 + (kSplit - 1) * w_half_bytes);
+        const uint64_t dw_lo = kDgrad ? umma_desc_mn_sw128(w0 + (kSplit - 1) * w_half_bytes, 64 * 128)
+                                      : umma_desc_k_sw128(w0 + (kSplit - 1) * w_half_bytes);
 #pragma unroll
         for (int kk = 0; kk < BK / UMMA_K; ++kk) {
           const uint64_t koff = static_cast<uint64_t>((kk * UMMA_K * 2) >> 4);
+          // MN-major W: one k-row is 128 B, UMMA_K rows further = UMMA_K * 128 B
+          const uint64_t woff = kDgrad ? static_cast<uint64_t>((kk * UMMA_K * 128) >> 4) : koff;
           const uint32_t first = (kb == 0 && kk == 0) ? 0u : 1u;
           if (kSplit == 2) {                                 // hi*hi + hi*lo + lo*hi (drops lo*lo, ~2^-16 relative)
-            umma_bf16_ss_pair_el(d_base, da_lo + koff, dw_hi + koff, idesc, first);
-            umma_bf16_ss_pair_el(d_base, da_hi + koff, dw_lo + koff, idesc, 1u);
-            umma_bf16_ss_pair_el(d_base, da_hi + koff, dw_hi + koff, idesc, 1u);
+            umma_bf16_ss_pair_el(d_base, da_lo + koff, dw_hi + woff, idesc, first);
+            umma_bf16_ss_pair_el(d_base, da_hi + koff, dw_lo + woff, idesc, 1u);
+            umma_bf16_ss_pair_el(d_base, da_hi + koff, dw_hi + woff, idesc, 1u);
           } else {
-            umma_bf16_ss_pair_el(d_base, da_hi + koff, dw_hi + koff, idesc, first);
+            umma_bf16_ss_pair_el(d_base, da_hi + koff, dw_hi + woff, idesc, first);
           }
         }
         umma_commit_pair_el(&empty_bar[stage]);              // frees the slot in BOTH CTAs when the MMAs retire
@@ -182,7 +201,22 @@ inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
       const uint32_t acc_phase = ((nacc == 2) ? (it >> 1) : it) & 1;
       const int row0 = (2 * m_pair + static_cast<int>(rank)) * BM + q * 32;     // first row of this warp's slab
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
-      const float* bias_t = p.bias + n_tile * BN;
+      const float* bias_t = kDgrad ? nullptr : p.bias + n_tile * BN;
+      const int ocol0 = (kDgrad ? p.out_col0 : 0) + n_tile * BN;              // first output column of this tile
+      // kDgrad: LeakyReLU'(pre) from the sign of the saved activation at the output position (modules.py:174)
+      const int my_row = row0 + lane;
+      const __nv_bfloat16* mask_row = (kDgrad && my_row < p.M)
+          ? p.mask_act + static_cast<size_t>(my_row) * p.ld_mask + p.mask_col0 + ocol0 : nullptr;
+      // the mask of a 32-column chunk is fetched one chunk ahead (and the first one before the accumulator is ready):
+      // a dependent 16-byte load per thread and chunk costs ~0.8 us of exposed latency otherwise, 8 times per tile
+      uint4 mk[4], mkn[4];
+      auto load_mask = [&](int s_, int c_in_, uint4* dst) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          dst[j] = mask_row != nullptr ? __ldg(reinterpret_cast<const uint4*>(mask_row + s_ * 64 + c_in_) + j)
+                                       : make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u);   // bf16 ones
+      };
+      if (kDgrad) load_mask(wide ? ch : 0, wide ? 0 : ch * 32, mk);
       mbar_wait(&tfull_bar[acc], acc_phase, 24);
       tc_fence_after();
       for (int s = wide ? ch : 0; s < n_slabs; s += wide ? 2 : 1) {
@@ -191,6 +225,11 @@ inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
           float v[32];
 #pragma unroll
           for (int c = 0; c < 2; ++c) tmem_ld16(t_row + s * 64 + c_in + c * 16, v + c * 16);
+          if (kDgrad) {                                      // next chunk's mask, in flight with the TMEM load and the math
+            const int sn = wide ? (h == 0 ? s : s + 2) : s + 1;
+            const int cn = wide ? (h == 0 ? 32 : 0) : ch * 32;
+            if (sn < n_slabs) load_mask(sn, cn, mkn);
+          }
           tmem_ld_wait();
           if (wide ? (h == 1 && s + 2 >= n_slabs) : (s + 1 >= n_slabs)) {     // this warp is done with the accumulator
             tc_fence_before();
@@ -201,18 +240,28 @@ inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
             if (lane == 0) bulk_wait_read<0>();
             __syncwarp();
           }
-          const float4* b4 = reinterpret_cast<const float4*>(bias_t + s * 64 + c_in);
+          const float4* b4 = kDgrad ? nullptr : reinterpret_cast<const float4*>(bias_t + s * 64 + c_in);
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const float4 b0 = __ldg(b4 + 2 * j), b1 = __ldg(b4 + 2 * j + 1);
-            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+            float bb[8];
+            const uint32_t mw[4] = {mk[j].x, mk[j].y, mk[j].z, mk[j].w};
+            if (!kDgrad) {
+              const float4 b0 = __ldg(b4 + 2 * j), b1 = __ldg(b4 + 2 * j + 1);
+              bb[0] = b0.x; bb[1] = b0.y; bb[2] = b0.z; bb[3] = b0.w; bb[4] = b1.x; bb[5] = b1.y; bb[6] = b1.z; bb[7] = b1.w;
+            }
             uint32_t hi[4], lo[4];
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-              float a = v[j * 8 + 2 * e] + bb[2 * e];
-              float b = v[j * 8 + 2 * e + 1] + bb[2 * e + 1];
-              a = fmaxf(a, a * p.slope);                     // LeakyReLU, 0 <= slope <= 1
-              b = fmaxf(b, b * p.slope);
+              float a, b;
+              if (kDgrad) {
+                a = v[j * 8 + 2 * e] * (bf16_bits_positive(mw[e] & 0xFFFFu) ? 1.f : p.slope);
+                b = v[j * 8 + 2 * e + 1] * (bf16_bits_positive(mw[e] >> 16) ? 1.f : p.slope);
+              } else {
+                a = v[j * 8 + 2 * e] + bb[2 * e];
+                b = v[j * 8 + 2 * e + 1] + bb[2 * e + 1];
+                a = fmaxf(a, a * p.slope);                   // LeakyReLU, 0 <= slope <= 1
+                b = fmaxf(b, b * p.slope);
+              }
               if (kSplit == 1) {
                 hi[e] = cvt_bf16x2(a, b);
               } else {
@@ -227,11 +276,15 @@ inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
             *reinterpret_cast<uint4*>(wb_hi + chunk) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
             if (kSplit == 2) *reinterpret_cast<uint4*>(wb_lo + chunk) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
           }
+          if (kDgrad) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) mk[j] = mkn[j];
+          }
         }
         fence_proxy_async();
         __syncwarp();
         if (lane == 0 && row0 < p.M) {
-          const int col = n_tile * BN + s * 64 + (wide ? 0 : ch * 32);
+          const int col = ocol0 + s * 64 + (wide ? 0 : ch * 32);
           const int loff = lane * (wide ? 128 : 64);
           tma_store_2d(&tmO0, wb_hi - loff, col, row0);
           if (kSplit == 2) tma_store_2d(&tmO1, wb_lo - loff, col, row0);

@@ -173,6 +173,7 @@ struct ipoke_inn_plan {
                                   // sized for num_sms / streams SMs so that the concurrent kernels are co-resident
   int bwd_graph = 1;              // replay the backward pass as a CUDA graph when the caller's pointers repeat
   int use_pair = 1;               // multi-wave hidden layers as CTA pairs (hidden_pair_kernel.cuh)
+  int pair_dgrad = 1;             // ... and the multi-wave dgrad GEMMs of the backward pass
   int warp_slab = 1;              // hidden / dgrad epilogue: warp-private output slabs (no CTA barrier inside a tile)
   int tail_cluster = 1;           // small batches: coupling tails as split-K clusters (tail_cluster_kernel.cuh)
   int dbg = 0;
@@ -293,8 +294,10 @@ int ensure_device(ipoke_inn_plan* P) {
 #define SET_SMEM(K)                                                                                    \
   e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);               \
   if (e != cudaSuccess) return (int)e;
-  SET_SMEM((inn_hidden_pair_kernel<1>))
-  SET_SMEM((inn_hidden_pair_kernel<2>))
+  SET_SMEM((inn_hidden_pair_kernel<1, false>))
+  SET_SMEM((inn_hidden_pair_kernel<2, false>))
+  SET_SMEM((inn_hidden_pair_kernel<1, true>))
+  SET_SMEM((inn_hidden_pair_kernel<2, true>))
   SET_SMEM((inn_gemm_kernel<1, EPI_HIDDEN>))
   SET_SMEM((inn_gemm_kernel<1, EPI_HIDDEN, true>))
   SET_SMEM((inn_gemm_kernel<2, EPI_HIDDEN, true>))
@@ -936,6 +939,47 @@ struct BwdBuilder : Builder {
     for (int sp = 0; sp < P->ksplit; ++sp)
       err |= make_map(P, &g.tmO[sp], d_base(d_idx, sp), out_cols, B, 2ll * P->ldACT, g.p.slab_warp ? 32 : BM,
                       g.p.slab_warp == 2 ? 32 : BK);
+    // multi-wave launches: the same CTA-pair kernel as the forward hidden layers (cta_group::2 on 256 x bn tiles, each CTA
+    // staging its own 128 rows of dY and half of the MN-major W tile), with the LeakyReLU' mask in the epilogue
+    const int bn = g.p.BN;
+    const long long tiles = (long long)m_tiles * g.p.num_n_tiles;
+    const bool pair = P->use_pair && P->pair_dgrad && (bn == 128 || bn == 256) && P->trace_buf == nullptr &&
+                      (P->use_pair > 1 ? tiles > P->num_sms : 2 * tiles >= 5ll * P->num_sms);
+    if (!pair) return;
+    PairParams& q = g.pp;
+    std::memset(&q, 0, sizeof(q));
+    g.pair = 2;                                  // 2 = the dgrad instantiation
+    q.M = B;
+    q.num_m_pairs = (m_tiles + 1) / 2;
+    q.num_n_tiles = g.p.num_n_tiles;
+    q.tiles_per_group = g.p.tiles_per_group;
+    q.num_k_blocks = g.p.num_k_blocks;
+    q.BN = bn;
+    q.a_group_stride = g.p.a_group_stride;
+    q.a_m_wrap = 0;
+    q.bias = nullptr;
+    q.slope = P->d.mlp_slope;
+    q.w_row0 = g.p.w_row0[0];
+    q.w_group_rows = g.p.w_group_rows;
+    q.out_col0 = out_col0;
+    q.mask_act = g.p.mask_act;
+    q.ld_mask = g.p.ld_mask;
+    q.mask_col0 = g.p.mask_col0;
+    q.nacc = 2 * bn <= 512 ? 2 : 1;
+    q.tmem_cols = 32;
+    while (q.tmem_cols < q.nacc * bn) q.tmem_cols <<= 1;
+    const int avail = kMaxDynSmem - 1024 - SMEM_BARRIER_BYTES;
+    const int sb = pair_stage_bytes(P->ksplit, bn);
+    const int st_wide = (avail - pair_epi_bytes(P->ksplit, 1)) / sb, st_half = (avail - pair_epi_bytes(P->ksplit, 0)) / sb;
+    q.wide = st_wide >= st_half ? 1 : 0;
+    q.stages = std::max(2, std::min(std::min(MAX_STAGES, q.wide ? st_wide : st_half), std::max(2, q.num_k_blocks)));
+    q.epi_off = q.stages * sb;
+    g.smem = pair_smem_bytes(P->ksplit, bn, q.stages, q.wide);
+    g.cluster = 2;
+    g.grid = 2 * (int)std::min<long long>((long long)q.num_m_pairs * q.num_n_tiles, P->num_sms / 2);
+    for (int sp = 0; sp < P->ksplit; ++sp)
+      err |= make_map(P, &g.tmO[sp], d_base(d_idx, sp), out_cols, B, 2ll * P->ldACT, 32, q.wide ? BK : 32);
+    if (P->ksplit == 1) g.tmO[1] = g.tmO[0];
   }
 
   // dW_g = dY_g^T X_g, db_g = colsum(dY_g) for the `groups` nets of one layer
@@ -1244,7 +1288,10 @@ cudaError_t launch_pair_t(const GemmOp& g, cudaStream_t st, int pdl) {
   ++na;
   cfg.attrs = attr;
   cfg.numAttrs = na;
-  return cudaLaunchKernelEx(&cfg, inn_hidden_pair_kernel<kSplit>, g.tmA[0], g.tmA[1], g.tmW[0], g.tmW[1], g.tmO[0],
+  if (g.pair == 2)
+    return cudaLaunchKernelEx(&cfg, inn_hidden_pair_kernel<kSplit, true>, g.tmA[0], g.tmA[1], g.tmW[0], g.tmW[1], g.tmO[0],
+                              g.tmO[1], g.pp);
+  return cudaLaunchKernelEx(&cfg, inn_hidden_pair_kernel<kSplit, false>, g.tmA[0], g.tmA[1], g.tmW[0], g.tmW[1], g.tmO[0],
                             g.tmO[1], g.pp);
 }
 
@@ -1701,6 +1748,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_TAIL_CLUSTER")) P->tail_cluster = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_WARPSLAB")) P->warp_slab = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_PAIR")) P->use_pair = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_PAIR_DGRAD")) P->pair_dgrad = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_BWD_GRAPH")) P->bwd_graph = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_STREAMS")) P->streams = std::max(1, std::min(std::atoi(e), 8));
   if (const char* e = std::getenv("IPOKE_INN_WPREFETCH")) P->w_prefetch = std::atoi(e) != 0;

@@ -18,7 +18,7 @@ ap.add_argument("--config", default="cfgA")
 ap.add_argument("--batch", type=int, default=4096)
 ap.add_argument("--precision", default="bf16")
 ap.add_argument("--reps", type=int, default=10)
-ap.add_argument("--opt", default="none", choices=["none", "adam", "fused"])
+ap.add_argument("--opt", default="none", choices=["none", "adam", "fused", "sharded"])
 ap.add_argument("--tag", default="")
 ap.add_argument("--direct-grads", action="store_true", help="engine.direct_param_grads = True")
 ap.add_argument("--host-times", action="store_true", help="host time of each part of the step (no syncs)")
@@ -34,7 +34,8 @@ x = torch.randn(B, C, device=dev)
 cond = torch.randn(B, E, 1, 1, device=dev) if kind == "cond" else None
 loss_fn = P.FlowLoss()
 opt = (torch.optim.Adam(net.parameters(), lr=1e-4, amsgrad=True) if a.opt == "adam" else
-       P.FusedAdam(net.parameters(), lr=1e-4, amsgrad=True) if a.opt == "fused" else None)
+       P.FusedAdam(net.parameters(), lr=1e-4, amsgrad=True) if a.opt == "fused" else
+       P.ShardedAdam(net, lr=1e-4, amsgrad=True) if a.opt == "sharded" else None)
 eng = net.flow.engine
 eng.direct_param_grads = bool(a.direct_grads)
 
