@@ -76,7 +76,7 @@ def full(rep, dst, traffic_key=None):
                 hidden.append(val("dram__bytes_read.sum") + val("dram__bytes_write.sum"))
     print(open(dst).read()[:3000])
     if traffic_key and hidden:
-        path = "profiles/r01_traffic.json"
+        path = "profiles/r02_traffic.json"
         try:
             d = json.load(open(path))
         except Exception:
