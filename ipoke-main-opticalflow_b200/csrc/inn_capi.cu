@@ -20,6 +20,7 @@
 #include "optim.cuh"
 #include "tail_cluster_kernel.cuh"
 #include "hidden_pair_kernel.cuh"
+#include "tail_pair_kernel.cuh"
 #include "wgrad_kernel.cuh"
 
 using namespace inn;
@@ -66,6 +67,8 @@ struct GemmOp {
   int tail_cluster;   // 1: inn_tail_cluster_kernel (small batches), cluster = 2 * p.ks
   int pair;           // 1: inn_hidden_pair_kernel (multi-wave hidden layers as tcgen05 CTA pairs), params in pp
   PairParams pp;
+  int tail_pair;      // 1: inn_tail_pair_kernel (multi-wave unfolded coupling tails as CTA pairs), config in tp
+  TailPairCfg tp;
 };
 struct WgradOp {
   CUtensorMap tmY[2], tmX[2];
@@ -174,6 +177,11 @@ struct ipoke_inn_plan {
   int bwd_graph = 1;              // replay the backward pass as a CUDA graph when the caller's pointers repeat
   int use_pair = 1;               // multi-wave hidden layers as CTA pairs (hidden_pair_kernel.cuh)
   int pair_dgrad = 1;             // ... and the multi-wave dgrad GEMMs of the backward pass
+  int pair_tail = 1;              // multi-wave unfolded coupling tails as CTA pairs over the full N (tail_pair_kernel.cuh)
+  int pair_tail_bn = 128;         // widest column tile of the pair tail: 256 covers the full N of cfg B (operands once per 128
+                                  // rows: 302 MB instead of 572 MB through the L2 -> SM path, ncu r02) but fills TMEM with one
+                                  // accumulator set, and the exposed epilogue gives the saving back (74 us either way); at 128
+                                  // TMEM double-buffers and the launch measures 69 us against 74 (profiles/r02_ab_tail_pair.txt)
   int warp_slab = 1;              // hidden / dgrad epilogue: warp-private output slabs (no CTA barrier inside a tile)
   int tail_cluster = 1;           // small batches: coupling tails as split-K clusters (tail_cluster_kernel.cuh)
   int dbg = 0;
@@ -312,6 +320,10 @@ int ensure_device(ipoke_inn_plan* P) {
   SET_SMEM((inn_gemm_kernel<2, EPI_DGRAD>))
   SET_SMEM((inn_gemm_kernel<1, EPI_DU>))
   SET_SMEM((inn_gemm_kernel<2, EPI_DU>))
+  SET_SMEM((inn_tail_pair_kernel<1, false>))
+  SET_SMEM((inn_tail_pair_kernel<2, false>))
+  SET_SMEM((inn_tail_pair_kernel<1, true>))
+  SET_SMEM((inn_tail_pair_kernel<2, true>))
   SET_SMEM((inn_tail_cluster_kernel<1, false>))
   SET_SMEM((inn_tail_cluster_kernel<2, false>))
   SET_SMEM((inn_tail_cluster_kernel<1, true>))
@@ -713,6 +725,37 @@ struct Builder {
       return;
     }
     finish_gemm(g, tc);
+    // multi-wave unfolded tails: a CTA pair per 256 rows x the widest column tile that fits, so that every activation
+    // panel goes through the L2 -> SM path once per pair instead of once per 128 x bn tile (tail_pair_kernel.cuh)
+    if (P->pair_tail && !fold && P->trace_buf == nullptr && g.p.vec4 &&
+        (P->pair_tail > 1 ? m_tiles >= 2          // 2 (debug / tests): every multi-tile unfolded tail
+                          : (long long)m_tiles * g.p.num_n_tiles * 2 >= 3ll * P->num_sms)) {
+      static const int cand[5] = {256, 128, 64, 32, 16};
+      for (int ci2 = 0; ci2 < 5; ++ci2) {
+        const int pbn = cand[ci2];
+        if (P->Np % pbn != 0 || pbn > P->pair_tail_bn) continue;
+        const int sb = tail_pair_stage_bytes(P->ksplit, pbn);
+        const int st = (kMaxDynSmem - 1024 - SMEM_BARRIER_BYTES) / sb;
+        if (st < 2) continue;
+        TailPairCfg& q = g.tp;
+        q.num_m_pairs = (m_tiles + 1) / 2;
+        q.BN = pbn;
+        q.stages = std::min(std::min(st, MAX_STAGES), std::max(2, g.p.num_k_blocks));
+        q.nacc = 4 * pbn <= 512 ? 2 : 1;
+        q.tmem_cols = 32;
+        while (q.tmem_cols < q.nacc * 2 * pbn) q.tmem_cols <<= 1;
+        g.tail_pair = 1;
+        g.p.BN = pbn;
+        g.p.num_n_tiles = P->Np / pbn;
+        g.smem = tail_pair_smem_bytes(P->ksplit, pbn, q.stages);
+        g.cluster = 2;
+        g.grid = 2 * (int)std::min<long long>((long long)q.num_m_pairs * g.p.num_n_tiles, P->num_sms / 2);
+        for (int sp = 0; sp < P->ksplit; ++sp)
+          err |= make_map(P, &g.tmW[sp], packed + (sp == 0 ? t.w.hi : t.w.lo), t.w.Kp, t.w.rows, 2ll * t.w.Kp, pbn / 2);
+        if (P->ksplit == 1) g.tmW[1] = g.tmW[0];
+        break;
+      }
+    }
   }
 
   void coupling(const Block& blk, int k, int state_buf, bool reverse) {
@@ -1295,8 +1338,39 @@ cudaError_t launch_pair_t(const GemmOp& g, cudaStream_t st, int pdl) {
                             g.tmO[1], g.pp);
 }
 
+template <int kSplit, bool kRev>
+cudaError_t launch_tail_pair_t(const GemmOp& g, const GemmParams& gp, cudaStream_t st, int pdl) {
+  cudaLaunchConfig_t cfg;
+  std::memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)g.grid);
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = (size_t)g.smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  attr[na].id = cudaLaunchAttributeClusterDimension;
+  attr[na].val.clusterDim.x = 2;
+  attr[na].val.clusterDim.y = 1;
+  attr[na].val.clusterDim.z = 1;
+  ++na;
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  return cudaLaunchKernelEx(&cfg, inn_tail_pair_kernel<kSplit, kRev>, g.tmA[0], g.tmA[1], g.tmW[0], g.tmW[1], gp, g.tp);
+}
+
 cudaError_t launch_gemm(const ipoke_inn_plan* P, const GemmOp& g, const GemmParams& gp, cudaStream_t st) {
   const int pdl = P->use_pdl;
+  if (g.tail_pair) {
+    const bool rev = g.mode == EPI_TAIL_REV;
+    if (P->ksplit == 2)
+      return rev ? launch_tail_pair_t<2, true>(g, gp, st, pdl) : launch_tail_pair_t<2, false>(g, gp, st, pdl);
+    return rev ? launch_tail_pair_t<1, true>(g, gp, st, pdl) : launch_tail_pair_t<1, false>(g, gp, st, pdl);
+  }
   if (g.pair) return P->ksplit == 2 ? launch_pair_t<2>(g, st, pdl) : launch_pair_t<1>(g, st, pdl);
   if (g.tail_cluster) {
     const bool rev = g.mode == EPI_TAIL_REV;
@@ -1749,6 +1823,8 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_WARPSLAB")) P->warp_slab = std::atoi(e) != 0;
   if (const char* e = std::getenv("IPOKE_INN_PAIR")) P->use_pair = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_PAIR_DGRAD")) P->pair_dgrad = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_PAIR_TAIL")) P->pair_tail = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_PAIR_TAIL_BN")) P->pair_tail_bn = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_BWD_GRAPH")) P->bwd_graph = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_STREAMS")) P->streams = std::max(1, std::min(std::atoi(e), 8));
   if (const char* e = std::getenv("IPOKE_INN_WPREFETCH")) P->w_prefetch = std::atoi(e) != 0;
