@@ -52,7 +52,7 @@ class FlowFunction(torch.autograd.Function):
                 g = dx
                 ke = kb
         engine.last_flat_grad = flat
-        ctx.saved_buf = None
+        # ctx.saved_buf stays alive with the graph (retain_graph=True / a second backward read it again)
         gx = dx.view(ctx.x_shape) if (need_x and dx is not None) else None
         gc = dcond.view(ctx.cond_shape) if (need_c and dcond is not None) else None
         if engine.direct_param_grads:

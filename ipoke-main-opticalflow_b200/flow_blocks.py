@@ -169,6 +169,12 @@ class _FusedFlowMixin:
         z, logdet, outs, lds = flow_forward(self._engine, x, cond)
         if outs is not None:
             self._fill_last(outs, lds)
+            if z.requires_grad:
+                # the last block's output IS the flow output: hand out the differentiable tensors there, so that a loss
+                # built from ``last_outs[-1]`` / ``last_logdets[-1]`` (the wrappers' train=True return, reference
+                # INN.py:80-81) reaches the parameters; the earlier blocks' entries are detached (fused backward)
+                self._last_outs[-1] = z.unsqueeze(-1).unsqueeze(-1) if not bool(self._engine.desc.conditional) else z
+                self._last_logdets[-1] = logdet
         else:
             self._last_lazy = (x, cond)
         return z.unsqueeze(-1).unsqueeze(-1), logdet                # reference :57

@@ -360,3 +360,24 @@ def test_direct_param_grads_equal_autograd_accumulation():
             assert max_rel(res[True][it][k], res[False][it][k]) < 1e-5, (it, k)
     k0 = next(k for k in res[True][0] if k != "__dx")
     assert max_rel(res[True][1][k0], 2 * res[True][0][k0]) < 1e-4      # really accumulated
+
+
+def test_train_lists_carry_gradients_and_graph_can_be_retained():
+    """the wrappers' train=True return (reference INN.py:80-81) must reach the parameters through its last
+    entries, and retain_graph=True / a second backward must work."""
+    net, sd_ref, d = _load("cfgS_cond", "fp32")
+    dev = _dev()
+    x = torch.from_numpy(d["x"]).to(dev)
+    cond = torch.from_numpy(d["cond"]).to(dev)
+    outs, lds = net(x, cond, train=True)
+    loss = 0.5 * (outs[-1].reshape(x.shape[0], -1) ** 2).sum(1).mean() - lds[-1].mean()
+    assert loss.requires_grad and not outs[0].requires_grad
+    loss.backward(retain_graph=True)
+    g1 = [p.grad.clone() for p in net.parameters()]
+    net.zero_grad(set_to_none=True)
+    loss.backward()
+    for a, p in zip(g1, net.parameters()):
+        assert torch.allclose(a, p.grad, rtol=1e-5, atol=1e-7 * float(a.abs().max()) + 1e-12)
+    z, ld = net(x, cond)
+    ref, _ = P.FlowLoss()(z, ld)
+    assert abs(float(ref.detach()) - float(loss.detach())) < 1e-5 * max(1.0, abs(float(loss.detach())))
