@@ -74,6 +74,7 @@ struct WgradOp {
   CUtensorMap tmY[2], tmX[2];
   WgradParams p;
   int grid, smem;
+  int pair;                 // 1: CTA-pair instantiation (cluster of 2)
   int lin[WG_MAX_GROUPS];   // index of each group's nn.Linear in the caller's gradient pointer arrays
 };
 enum OpKind { OP_BOUNDARY = 0, OP_GEMM = 1, OP_BWD_INIT = 2, OP_TAIL_BWD = 3, OP_BOUNDARY_BWD = 4, OP_WGRAD = 5,
@@ -177,6 +178,8 @@ struct ipoke_inn_plan {
   int bwd_graph = 1;              // replay the backward pass as a CUDA graph when the caller's pointers repeat
   int use_pair = 1;               // multi-wave hidden layers as CTA pairs (hidden_pair_kernel.cuh)
   int pair_dgrad = 1;             // ... and the multi-wave dgrad GEMMs of the backward pass
+  int pair_wgrad = 1;             // large-batch weight-gradient GEMMs as CTA pairs on 256 x 256 (or 256 x 128) tiles
+  int pair_wgrad_bn = 256;
   int pair_tail = 1;              // multi-wave unfolded coupling tails as CTA pairs over the full N (tail_pair_kernel.cuh)
   int pair_tail_bn = 128;         // widest column tile of the pair tail: 256 covers the full N of cfg B (operands once per 128
                                   // rows: 302 MB instead of 572 MB through the L2 -> SM path, ncu r02) but fills TMEM with one
@@ -328,8 +331,10 @@ int ensure_device(ipoke_inn_plan* P) {
   SET_SMEM((inn_tail_cluster_kernel<2, false>))
   SET_SMEM((inn_tail_cluster_kernel<1, true>))
   SET_SMEM((inn_tail_cluster_kernel<2, true>))
-  SET_SMEM((inn_wgrad_kernel<1>))
-  SET_SMEM((inn_wgrad_kernel<2>))
+  SET_SMEM((inn_wgrad_kernel<1, false>))
+  SET_SMEM((inn_wgrad_kernel<2, false>))
+  SET_SMEM((inn_wgrad_kernel<1, true>))
+  SET_SMEM((inn_wgrad_kernel<2, true>))
 #undef SET_SMEM
   P->dev_ready = true;
   return 0;
@@ -1042,22 +1047,36 @@ struct BwdBuilder : Builder {
     int bn = kin_p >= 128 ? 128 : 64;
     if (P->ksplit == 2 && kin_p >= 128) bn = 128;
     const int alias = 0;      // 128 x 256 tiles aliased onto the pipeline stages: parity green, no gain (r01 v11) -- not built
+    // large batches: CTA pairs on 256 x 128 tiles (2.7 x fewer operand bytes per FLOP, wgrad_kernel.cuh) when the
+    // launch fills at least one wave of pairs
+    const bool pair = P->pair_wgrad && P->trace_buf == nullptr && q.num_kb >= 16 && kin_p % 128 == 0 && rows_p % 256 == 0 &&
+                      (long long)groups * (rows_p / 256) * (kin_p / 128) * 2 >= P->num_sms;
+    if (pair) {
+      // 256 x 256 when the width allows: 32 KB per CTA and k-block for 8 MMAs balances one SM's ingest (~120 GB/s) against
+      // the tensor pipe; 256 x 128 (24 KB for 4 MMAs) is still ingest-bound (measured: 48 -> 43 us per hidden x hidden launch)
+      bn = (kin_p % 256 == 0 && P->pair_wgrad_bn >= 256) ? 256 : 128;
+      q.m_tiles = rows_p / 256;                  // 256-row tiles: one per CTA pair
+    }
+    const int epi_bn = pair ? 128 : bn;          // staging tile width (256-wide pair tiles drain in two passes)
+    wgo.pair = pair ? 1 : 0;
     q.BN = bn;
     q.epi_alias = alias;
     q.n_tiles = (kin_p + bn - 1) / bn;
     const int tiles = groups * q.m_tiles * q.n_tiles;
     int ks = 1;
-    if (tiles * 2 <= P->num_sms && q.num_kb >= 8) {
+    if (!pair && tiles * 2 <= P->num_sms && q.num_kb >= 8) {
       ks = std::min(P->num_sms / tiles, q.num_kb / 4);
       ks = std::max(ks, 1);
       const int per = (q.num_kb + ks - 1) / ks;
       ks = (q.num_kb + per - 1) / per;                  // no empty slice
     }
     q.kslices = ks;
-    const int avail = kMaxDynSmem - 1024 - SMEM_BARRIER_BYTES - WG_ONES_BYTES - (alias ? 0 : ((wgrad_epi_bytes(bn) + 15) & ~15));
-    q.stages = std::max(2, std::min(MAX_STAGES, avail / wgrad_stage_bytes(P->ksplit, bn)));
+    const int avail = kMaxDynSmem - 1024 - SMEM_BARRIER_BYTES - WG_ONES_BYTES - (alias ? 0 : ((wgrad_epi_bytes(epi_bn) + 15) & ~15));
+    // a pair CTA stages half of the X^T columns: its stage is the one of a tile half as wide
+    const int stage_b = wgrad_stage_bytes(P->ksplit, pair ? bn / 2 : bn);
+    q.stages = std::max(2, std::min(MAX_STAGES, avail / stage_b));
     if (!alias) q.stages = std::min(q.stages, std::max(2, (q.num_kb + ks - 1) / ks));
-    while (alias && q.stages * wgrad_stage_bytes(P->ksplit, bn) < wgrad_epi_bytes(bn)) q.stages++;   // room for the staging tile
+    while (alias && q.stages * stage_b < wgrad_epi_bytes(bn)) q.stages++;   // room for the staging tile
     const int acc_cols = bn + 16;
     q.nacc = (2 * acc_cols <= 512) ? 2 : 1;
     int cols = 32;
@@ -1082,8 +1101,9 @@ struct BwdBuilder : Builder {
       wgo.tmY[1] = wgo.tmY[0];
       wgo.tmX[1] = wgo.tmX[0];
     }
-    wgo.smem = wgrad_smem_bytes(P->ksplit, bn, q.stages, alias);
-    wgo.grid = std::min(tiles * ks, P->num_sms);
+    wgo.smem = pair ? 1024 + q.stages * stage_b + WG_ONES_BYTES + ((wgrad_epi_bytes(epi_bn) + 15) & ~15) + SMEM_BARRIER_BYTES
+                    : wgrad_smem_bytes(P->ksplit, bn, q.stages, alias);
+    wgo.grid = pair ? 2 * std::min(tiles, P->num_sms / 2) : std::min(tiles * ks, P->num_sms);
     if (ks > 1) {
       // split-batch partial sums are added with atomics: clear the destinations first
       Op wg_op = prog->ops.back();
@@ -1418,13 +1438,30 @@ cudaError_t launch_wgrad(const ipoke_inn_plan* P, const WgradOp& wg, const Wgrad
   cfg.blockDim = dim3(WG_THREADS);
   cfg.dynamicSmemBytes = (size_t)wg.smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (P->use_pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (wg.pair) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 2;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = P->use_pdl ? 1 : 0;
-  if (P->ksplit == 2) return cudaLaunchKernelEx(&cfg, inn_wgrad_kernel<2>, wg.tmY[0], wg.tmY[1], wg.tmX[0], wg.tmX[1], q);
-  return cudaLaunchKernelEx(&cfg, inn_wgrad_kernel<1>, wg.tmY[0], wg.tmY[1], wg.tmX[0], wg.tmX[1], q);
+  cfg.numAttrs = na;
+  if (wg.pair) {
+    if (P->ksplit == 2)
+      return cudaLaunchKernelEx(&cfg, inn_wgrad_kernel<2, true>, wg.tmY[0], wg.tmY[1], wg.tmX[0], wg.tmX[1], q);
+    return cudaLaunchKernelEx(&cfg, inn_wgrad_kernel<1, true>, wg.tmY[0], wg.tmY[1], wg.tmX[0], wg.tmX[1], q);
+  }
+  if (P->ksplit == 2)
+    return cudaLaunchKernelEx(&cfg, inn_wgrad_kernel<2, false>, wg.tmY[0], wg.tmY[1], wg.tmX[0], wg.tmX[1], q);
+  return cudaLaunchKernelEx(&cfg, inn_wgrad_kernel<1, false>, wg.tmY[0], wg.tmY[1], wg.tmX[0], wg.tmX[1], q);
 }
 
 // caller-owned pointers of one backward call
@@ -1824,6 +1861,8 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_PAIR")) P->use_pair = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_PAIR_DGRAD")) P->pair_dgrad = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_PAIR_TAIL")) P->pair_tail = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_PAIR_WGRAD")) P->pair_wgrad = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_PAIR_WGRAD_BN")) P->pair_wgrad_bn = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_PAIR_TAIL_BN")) P->pair_tail_bn = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_BWD_GRAPH")) P->bwd_graph = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_STREAMS")) P->streams = std::max(1, std::min(std::atoi(e), 8));
