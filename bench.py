@@ -417,14 +417,18 @@ def hidden_roofline(ctx, cfg_name, r, streams):
         "share_of_step": share,
         "ms_per_step": ms_step,
         "algorithmic_bytes_per_launch": bytes_step / max(n_launch, 1),
+        "issued_flops_per_launch": flops_step / max(n_launch, 1),
+        "gbs": gbs, "tflops_issued": tf,
         "avg_launch_us": 1e6 * t_hidden * streams / max(n_launch, 1),
         "avg_launch_us_isolated": 1e3 * tot[1] / max(n_launch, 1),
         "per_kind_ms_isolated": {"boundary": tot[0], "hidden": tot[1], "tail": tot[2]},
         "step_algorithmic_bytes": step_bytes,
         "step_frac": step_bytes / (ms_step * 1e-3) / 1e9 / pk["hbm"],
-        "how": "achieved = launches_per_step x algorithmic_bytes_per_launch / (share_of_step x ms_per_step); "
-               "algorithmic bytes = hidden-layer weights once per direction (SURVEY.md 8d; activations stay in L2 and "
-               "are not counted); share_of_step from per-launch CUDA events of a separate serialised pass; "
+        "how": "bound = whichever of issued FLOPs / bf16 peak and algorithmic bytes / HBM peak is larger (the parity mode "
+               "issues 3 bf16 MMAs per MAC and reads 4 B per weight: past the ridge from ~170 rows); achieved = "
+               "launches_per_step x (issued_flops_per_launch | algorithmic_bytes_per_launch) / (share_of_step x "
+               "ms_per_step); algorithmic bytes = hidden-layer weights once per direction (SURVEY.md 8d; activations stay "
+               "in L2 and are not counted); share_of_step from per-launch CUDA events of a separate serialised pass; "
                "avg_launch_us = share x ms_per_step x concurrent_streams / launches; step_frac = whole-step bytes "
                "(weights + I/O, both directions) / ms_per_step / peak",
     }

@@ -43,3 +43,33 @@ def test_algorithmic_work_matches_survey():
     assert bench.macs_per_sample(kind, kw) == 237_502_464          # SURVEY.md 8d, probe-verified
     kind, kw, _, _ = bench.CONFIGS["cfgB"]
     assert bench.macs_per_sample(kind, kw) == 83_886_080
+
+
+def test_roofline_fraction_follows_from_the_lines_own_fields():
+    """`roofline.frac` must be recomputable from the fields the line carries: algorithmic bytes = the hidden
+    layers' weights once per direction, duration = the kernel's share of the step that `value` times."""
+    class Ctx:
+        pk = dict(hbm=6546.2, bf16=1679.4, bf16_sus=1409.5, src="test")
+    for prec, wbytes in (("bf16", 2), ("fp32", 4)):
+        r = {"B": 256, "precision": prec, "ms": 0.44, "ms_serial": 0.74, "kind_ms": [0.02, 1.0, 0.3],
+             "kind_launches": [2, 96, 32]}
+        for streams in (1, 2):
+            out = bench.hidden_roofline(Ctx(), "cfgB", r, streams)
+            kind, kw, C, E, H = bench.dims("cfgB")
+            hid_w = bench.macs_per_sample(kind, kw) - bench.tail_macs("cfgB")
+            assert out["launches_per_step"] == 96 and out["concurrent_streams"] == streams
+            assert abs(out["algorithmic_bytes_per_launch"] * 96 - 2 * hid_w * wbytes) < 1
+            t = out["share_of_step"] * out["ms_per_step"] * 1e-3
+            assert abs(out["share_of_step"] - 1.0 / 1.32) < 1e-12
+            assert out["ms_per_step"] == (0.44 if streams == 2 else 0.74)
+            if out["bound"] == "hbm":
+                gbs = out["launches_per_step"] * out["algorithmic_bytes_per_launch"] / t / 1e9
+                assert abs(out["achieved"] - gbs) < 1e-6 * gbs and abs(out["frac"] - gbs / 6546.2) < 1e-9
+            else:                       # parity mode at batch 256: 3 MMA passes, 4 B per weight -> past the ridge
+                tf = 2 * 2.0 * hid_w * 256 * 3 / t / 1e12
+                assert prec == "fp32" and abs(out["achieved"] - tf) < 1e-6 * tf and abs(out["frac"] - tf / 1679.4) < 1e-9
+            assert abs(out["avg_launch_us"] - 1e6 * t * streams / 96) < 1e-9
+            step_bytes = 2 * bench.pass_bytes("cfgB", 256, prec)
+            assert abs(out["step_frac"] - step_bytes / (out["ms_per_step"] * 1e-3) / 1e9 / 6546.2) < 1e-12
+    # SURVEY.md 8d: minimum HBM bytes per pass = weights once + B * (2C + E + 1) * 4
+    assert bench.pass_bytes("cfgA", 64, "bf16") == 237_502_464 * 2 + 64 * (2 * 128 + 128 + 1) * 4
