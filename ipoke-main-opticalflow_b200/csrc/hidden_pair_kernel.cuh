@@ -46,6 +46,33 @@ __host__ inline int pair_smem_bytes(int ksplit, int BN, int stages, int wide) {
   return 1024 + stages * pair_stage_bytes(ksplit, BN) + pair_epi_bytes(ksplit, wide) + SMEM_BARRIER_BYTES;
 }
 
+// Sign mask of a 32-row x 32-column bf16 block, fetched by the whole warp with coalesced loads: lanes 0-15 read the 64
+// bytes of an even row, lanes 16-31 those of the next row (16 independent 4-byte loads per lane, all issued before the
+// first use), two ballots per row pair turn the signs into bit masks, and lane L keeps row L's: bit k of `even` / `odd`
+// = (element [L][2k] / [L][2k + 1] > 0).  A 16-byte load per thread and row instead costs 32 LSU transactions per
+// instruction (rows are ld * 2 bytes apart): 17 % of the pair dgrad at cfg A / 4096 (measured with the mask switched off).
+__device__ __forceinline__ void warp_sign_mask32(const __nv_bfloat16* base, int ld, int rows_valid, int lane,
+                                                 uint32_t& even, uint32_t& odd) {
+  uint32_t v[16];
+  const int sub = lane >> 4, cl = lane & 15;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const int r = 2 * i + sub;
+    v[i] = (base != nullptr && r < rows_valid)
+               ? __ldg(reinterpret_cast<const uint32_t*>(base + static_cast<size_t>(r) * ld) + cl) : 0x3F803F80u;
+  }
+  even = odd = 0xFFFFFFFFu;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const uint32_t b0 = __ballot_sync(0xffffffffu, bf16_bits_positive(v[i] & 0xFFFFu));
+    const uint32_t b1 = __ballot_sync(0xffffffffu, bf16_bits_positive(v[i] >> 16));
+    if ((lane >> 1) == i) {
+      even = (lane & 1) ? (b0 >> 16) : (b0 & 0xFFFFu);
+      odd = (lane & 1) ? (b1 >> 16) : (b1 & 0xFFFFu);
+    }
+  }
+}
+
 template <int kSplit, bool kDgrad = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
@@ -203,20 +230,22 @@ inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
       const float* bias_t = kDgrad ? nullptr : p.bias + n_tile * BN;
       const int ocol0 = (kDgrad ? p.out_col0 : 0) + n_tile * BN;              // first output column of this tile
-      // kDgrad: LeakyReLU'(pre) from the sign of the saved activation at the output position (modules.py:174)
-      const int my_row = row0 + lane;
-      const __nv_bfloat16* mask_row = (kDgrad && my_row < p.M)
-          ? p.mask_act + static_cast<size_t>(my_row) * p.ld_mask + p.mask_col0 + ocol0 : nullptr;
-      // the mask of a 32-column chunk is fetched one chunk ahead (and the first one before the accumulator is ready):
-      // a dependent 16-byte load per thread and chunk costs ~0.8 us of exposed latency otherwise, 8 times per tile
-      uint4 mk[4], mkn[4];
-      auto load_mask = [&](int s_, int c_in_, uint4* dst) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          dst[j] = mask_row != nullptr ? __ldg(reinterpret_cast<const uint4*>(mask_row + s_ * 64 + c_in_) + j)
-                                       : make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u);   // bf16 ones
-      };
-      if (kDgrad) load_mask(wide ? ch : 0, wide ? 0 : ch * 32, mk);
+      // kDgrad: LeakyReLU'(pre) from the sign of the saved activation at the output position (modules.py:174); the
+      // 32 x 32 sign block of a chunk is fetched one chunk ahead (and the first one before the accumulator is ready)
+      const __nv_bfloat16* mask_blk = (kDgrad && p.mask_act != nullptr && row0 < p.M)
+          ? p.mask_act + static_cast<size_t>(row0) * p.ld_mask + p.mask_col0 + ocol0 : nullptr;
+      const int mask_rows = p.M - row0;
+      // all of this warp's sign blocks of the tile (<= 4: BN <= 256) are fetched here, while the tile's MMAs still run
+      uint32_t me[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, mo[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};
+      if (kDgrad) {
+        int ci = 0;
+        for (int s = wide ? ch : 0; s < n_slabs; s += wide ? 2 : 1)
+          for (int h = 0; h < (wide ? 2 : 1); ++h, ++ci)
+            if (ci < 4)
+              warp_sign_mask32(mask_blk != nullptr ? mask_blk + s * 64 + (wide ? h * 32 : ch * 32) : nullptr, p.ld_mask,
+                               mask_rows, lane, me[ci], mo[ci]);
+      }
+      int chunk_i = 0;
       mbar_wait(&tfull_bar[acc], acc_phase, 24);
       tc_fence_after();
       for (int s = wide ? ch : 0; s < n_slabs; s += wide ? 2 : 1) {
@@ -225,11 +254,8 @@ inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
           float v[32];
 #pragma unroll
           for (int c = 0; c < 2; ++c) tmem_ld16(t_row + s * 64 + c_in + c * 16, v + c * 16);
-          if (kDgrad) {                                      // next chunk's mask, in flight with the TMEM load and the math
-            const int sn = wide ? (h == 0 ? s : s + 2) : s + 1;
-            const int cn = wide ? (h == 0 ? 32 : 0) : ch * 32;
-            if (sn < n_slabs) load_mask(sn, cn, mkn);
-          }
+          const uint32_t mk_e = me[chunk_i & 3], mk_o = mo[chunk_i & 3];
+          ++chunk_i;
           tmem_ld_wait();
           if (wide ? (h == 1 && s + 2 >= n_slabs) : (s + 1 >= n_slabs)) {     // this warp is done with the accumulator
             tc_fence_before();
@@ -244,7 +270,6 @@ inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             float bb[8];
-            const uint32_t mw[4] = {mk[j].x, mk[j].y, mk[j].z, mk[j].w};
             if (!kDgrad) {
               const float4 b0 = __ldg(b4 + 2 * j), b1 = __ldg(b4 + 2 * j + 1);
               bb[0] = b0.x; bb[1] = b0.y; bb[2] = b0.z; bb[3] = b0.w; bb[4] = b1.x; bb[5] = b1.y; bb[6] = b1.z; bb[7] = b1.w;
@@ -254,8 +279,8 @@ inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
             for (int e = 0; e < 4; ++e) {
               float a, b;
               if (kDgrad) {
-                a = v[j * 8 + 2 * e] * (bf16_bits_positive(mw[e] & 0xFFFFu) ? 1.f : p.slope);
-                b = v[j * 8 + 2 * e + 1] * (bf16_bits_positive(mw[e] >> 16) ? 1.f : p.slope);
+                a = v[j * 8 + 2 * e] * (((mk_e >> (j * 4 + e)) & 1u) ? 1.f : p.slope);
+                b = v[j * 8 + 2 * e + 1] * (((mk_o >> (j * 4 + e)) & 1u) ? 1.f : p.slope);
               } else {
                 a = v[j * 8 + 2 * e] + bb[2 * e];
                 b = v[j * 8 + 2 * e + 1] + bb[2 * e + 1];
@@ -275,10 +300,6 @@ inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
             const int chunk = (wide ? ((h * 4 + j) ^ (lane & 7)) : (j ^ ((lane >> 1) & 3))) << 4;
             *reinterpret_cast<uint4*>(wb_hi + chunk) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
             if (kSplit == 2) *reinterpret_cast<uint4*>(wb_lo + chunk) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-          }
-          if (kDgrad) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) mk[j] = mkn[j];
           }
         }
         fence_proxy_async();

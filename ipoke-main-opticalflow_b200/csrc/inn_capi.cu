@@ -1010,7 +1010,7 @@ struct BwdBuilder : Builder {
     q.w_row0 = g.p.w_row0[0];
     q.w_group_rows = g.p.w_group_rows;
     q.out_col0 = out_col0;
-    q.mask_act = g.p.mask_act;
+    q.mask_act = std::getenv("IPOKE_INN_DBG_NOMASK") ? nullptr : g.p.mask_act;   // timing experiment only
     q.ld_mask = g.p.ld_mask;
     q.mask_col0 = g.p.mask_col0;
     q.nacc = 2 * bn <= 512 ? 2 : 1;
