@@ -270,33 +270,43 @@ def test_chunked_backward_equals_single_call_and_accumulates():
 
 
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])
-def test_wide_wgrad_tiles_equal_the_128_column_path(precision):
-    """128 x 256 wgrad tiles (epilogue staging aliased onto the pipeline stages, one tile per CTA) against the 128 x 128
-    path the oracle tests above cover: same products, same accumulation order per element."""
+def test_pair_wgrad_and_dgrad_equal_the_single_cta_kernels(precision):
+    """The CTA-pair weight-gradient (256 x 256 tiles) and dgrad kernels against the single-CTA kernels the oracle tests
+    above cover: same products, fp32 accumulation over the batch in both."""
     import os
     cfg = dict(flow_in_channels=64, flow_mid_channels_factor=16, flow_hidden_depth=1, n_flows=2,
-               flow_conditioning_option="none", flow_embedding_channels=32)      # H = 1024: 'cond' block = 128 wide tiles
-    dev, B = _dev(), 512
+               flow_conditioning_option="none", flow_embedding_channels=64)      # H = 1024; the 'cond' block runs G = 4 nets
+    dev, B = _dev(), 2048
     g = torch.Generator().manual_seed(11)
     x = torch.randn(B, 64, generator=g).to(dev)
-    cond = torch.randn(B, 32, 1, 1, generator=g).to(dev)
+    cond = torch.randn(B, 64, 1, 1, generator=g).to(dev)
     dz, dld = torch.randn(B, 64, generator=g).to(dev), torch.randn(B, generator=g).to(dev)
     grads = {}
-    for wide in ("1", "0"):
-        os.environ["IPOKE_INN_WGRAD_WIDE"] = wide                 # read at plan creation (first call)
+    for pair in ("1", "0"):
+        os.environ["IPOKE_INN_PAIR_WGRAD"] = pair                 # read at plan creation (first call)
+        os.environ["IPOKE_INN_PAIR_DGRAD"] = pair
+        os.environ["IPOKE_INN_PAIR"] = "2"                        # both runs: pairs for every multi-wave launch (same forward)
         try:
             torch.manual_seed(42)
             net = P.SupervisedTransformer(dict(cfg), precision=precision).to(dev)
             with torch.no_grad():
                 net(x, cond)                                       # ActNorm data init (identical for both)
-            z, ld = net(x, cond)
+            xg = x.clone().requires_grad_(True)
+            z, ld = net(xg, cond)
             ((z.reshape(B, -1) * dz).sum() + (ld * dld).sum()).backward()
-            grads[wide] = {k: p.grad.detach().cpu().numpy().copy() for k, p in net.named_parameters()}
+            grads[pair] = {k: p.grad.detach().cpu().numpy().copy() for k, p in net.named_parameters()}
+            grads[pair]["dx"] = xg.grad.cpu().numpy().copy()
         finally:
-            del os.environ["IPOKE_INN_WGRAD_WIDE"]
+            for k in ("IPOKE_INN_PAIR_WGRAD", "IPOKE_INN_PAIR_DGRAD", "IPOKE_INN_PAIR"):
+                del os.environ[k]
+    num = sum(float(((grads["1"][k].astype(np.float64) - grads["0"][k]) ** 2).sum()) for k in grads["1"])
+    den = sum(float((grads["0"][k].astype(np.float64) ** 2).sum()) for k in grads["1"])
+    # the forward passes are identical; the backward kernels differ in tile shape only (fp32 accumulation order, and in
+    # bf16 a last-bit difference of a dgrad output can round differently downstream)
+    assert np.sqrt(num / den) < (1e-5 if precision == "fp32" else 5e-3), np.sqrt(num / den)
     for k in grads["1"]:
         assert np.isfinite(grads["1"][k]).all(), k
-        assert max_rel(grads["1"][k], grads["0"][k]) < 1e-5, k
+        assert max_rel(grads["1"][k], grads["0"][k]) < (2e-5 if precision == "fp32" else 2e-2), k
 
 
 def test_backward_graph_replay_equals_plain_launches():
