@@ -38,6 +38,8 @@ struct PairParams {
   int out_col0;           // first output column; tile (., n) writes columns out_col0 + n * BN ...
   const __nv_bfloat16* mask_act;   // saved post-LeakyReLU activation (hi part) at the output position
   int ld_mask, mask_col0;
+  int rev;                // 1: walk the tiles from the last row tile down.  Consecutive launches of a program alternate, so a
+                          // layer starts on the rows its producer wrote last (the part of its input still in L2)
 };
 
 __host__ inline int pair_stage_bytes(int ksplit, int BN) { return ksplit * (A_TILE_BYTES + (BN / 2) * BK * 2); }
@@ -137,8 +139,8 @@ inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
     int stage = 0;
     uint32_t phase = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-      const int m_pair = tile / p.num_n_tiles;
-      const int n_tile = tile - m_pair * p.num_n_tiles;
+      const int m_pair = (p.rev ? num_tiles - 1 - tile : tile) / p.num_n_tiles;
+      const int n_tile = (p.rev ? num_tiles - 1 - tile : tile) - m_pair * p.num_n_tiles;
       const int group = n_tile / p.tiles_per_group;
       const int m_tile = 2 * m_pair + static_cast<int>(rank);
       const int a_row0 = (p.a_m_wrap > 0 ? m_tile % p.a_m_wrap : m_tile) * BM;
@@ -222,8 +224,8 @@ inn_hidden_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_co
     const uint32_t leader_tempty[2] = {mapa_u32(&tempty_bar[0], 0), mapa_u32(&tempty_bar[1], 0)};
     int it = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
-      const int m_pair = tile / p.num_n_tiles;
-      const int n_tile = tile - m_pair * p.num_n_tiles;
+      const int m_pair = (p.rev ? num_tiles - 1 - tile : tile) / p.num_n_tiles;
+      const int n_tile = (p.rev ? num_tiles - 1 - tile : tile) - m_pair * p.num_n_tiles;
       const int acc = (nacc == 2) ? (it & 1) : 0;
       const uint32_t acc_phase = ((nacc == 2) ? (it >> 1) : it) & 1;
       const int row0 = (2 * m_pair + static_cast<int>(rank)) * BM + q * 32;     // first row of this warp's slab

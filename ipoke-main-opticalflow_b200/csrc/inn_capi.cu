@@ -180,6 +180,7 @@ struct ipoke_inn_plan {
   int pair_dgrad = 1;             // ... and the multi-wave dgrad GEMMs of the backward pass
   int pair_wgrad = 1;             // large-batch weight-gradient GEMMs as CTA pairs on 256 x 256 (or 256 x 128) tiles
   int pair_wgrad_bn = 256;
+  int serpentine = 1;             // pair kernels of consecutive launches walk the row tiles in alternating directions
   int pair_tail = 1;              // multi-wave unfolded coupling tails as CTA pairs over the full N (tail_pair_kernel.cuh)
   int pair_tail_bn = 128;         // widest column tile of the pair tail: 256 covers the full N of cfg B (operands once per 128
                                   // rows: 302 MB instead of 572 MB through the L2 -> SM path, ncu r02) but fills TMEM with one
@@ -469,6 +470,14 @@ struct Builder {
     b.u_pad = P->C2p;
   }
 
+  // Alternate the row-tile direction of consecutive pair launches when one layer's activations are between one and two
+  // L2 capacities: a layer then starts on the rows its producer wrote last, which are still cached (cfg B / 32768: 134 MB
+  // per layer, step 12.02 -> 11.80 ms; cfg A / 32768 with 400 MB and cfg A / 4096 with 50 MB do not move)
+  bool serpentine_ok(long long act_cols) const {
+    const long long bytes = (long long)B * act_cols * 2 * P->ksplit;
+    return P->serpentine && Bc == 0 && (P->serpentine > 1 || (bytes >= (96ll << 20) && bytes <= (256ll << 20)));
+  }
+
   GemmOp& add_gemm(int mode) {
     prog->gemms.emplace_back();
     prog->ops.emplace_back();
@@ -558,6 +567,7 @@ struct Builder {
         q.BN = bn;
         q.a_group_stride = l == 0 ? 0 : P->Hp;
         q.a_m_wrap = 0;
+        q.rev = serpentine_ok(rows) ? ((int)prog->gemms.size() & 1) : 0;
         q.bias = pk<float>(L.bias);
         q.slope = P->d.mlp_slope;
         q.nacc = 2 * bn <= 512 ? 2 : 1;
@@ -747,6 +757,7 @@ struct Builder {
         q.BN = pbn;
         q.stages = std::min(std::min(st, MAX_STAGES), std::max(2, g.p.num_k_blocks));
         q.nacc = 4 * pbn <= 512 ? 2 : 1;
+        q.rev = serpentine_ok((long long)G * P->Hp) ? ((int)prog->gemms.size() & 1) : 0;
         q.tmem_cols = 32;
         while (q.tmem_cols < q.nacc * 2 * pbn) q.tmem_cols <<= 1;
         g.tail_pair = 1;
@@ -1005,6 +1016,7 @@ struct BwdBuilder : Builder {
     q.BN = bn;
     q.a_group_stride = g.p.a_group_stride;
     q.a_m_wrap = 0;
+    q.rev = serpentine_ok(P->ldACT) ? ((int)prog->gemms.size() & 1) : 0;
     q.bias = nullptr;
     q.slope = P->d.mlp_slope;
     q.w_row0 = g.p.w_row0[0];
@@ -1861,6 +1873,7 @@ int ipoke_inn_plan_create(const ipoke_inn_desc* desc, int device, ipoke_inn_plan
   if (const char* e = std::getenv("IPOKE_INN_PAIR")) P->use_pair = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_PAIR_DGRAD")) P->pair_dgrad = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_PAIR_TAIL")) P->pair_tail = std::atoi(e);
+  if (const char* e = std::getenv("IPOKE_INN_SERPENTINE")) P->serpentine = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_PAIR_WGRAD")) P->pair_wgrad = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_PAIR_WGRAD_BN")) P->pair_wgrad_bn = std::atoi(e);
   if (const char* e = std::getenv("IPOKE_INN_PAIR_TAIL_BN")) P->pair_tail_bn = std::atoi(e);

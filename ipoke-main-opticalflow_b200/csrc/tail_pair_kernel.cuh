@@ -24,6 +24,7 @@ struct TailPairCfg {
   int stages;
   int nacc;               // accumulator sets (s | t) in TMEM: 2 when 4 * BN <= 512
   int tmem_cols;
+  int rev;                // 1: tiles from the last row tile down (see PairParams::rev)
 };
 
 __host__ inline int tail_pair_stage_bytes(int ksplit, int BN) { return ksplit * (2 * A_TILE_BYTES + 2 * (BN / 2) * BK * 2); }
@@ -91,8 +92,8 @@ inn_tail_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_cons
     int stage = 0;
     uint32_t phase = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-      const int m_pair = tile / p.num_n_tiles;
-      const int n_tile = tile - m_pair * p.num_n_tiles;
+      const int m_pair = (c.rev ? num_tiles - 1 - tile : tile) / p.num_n_tiles;
+      const int n_tile = (c.rev ? num_tiles - 1 - tile : tile) - m_pair * p.num_n_tiles;
       const int m_tile = 2 * m_pair + static_cast<int>(rank);
       const int a_row0 = (p.a_m_wrap > 0 ? m_tile % p.a_m_wrap : m_tile) * BM;
       const int w_r = n_tile * BN + static_cast<int>(rank) * (BN / 2);
@@ -164,8 +165,8 @@ inn_tail_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_cons
     const uint32_t leader_tempty[2] = {mapa_u32(&tempty_bar[0], 0), mapa_u32(&tempty_bar[1], 0)};
     int it = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
-      const int m_pair = tile / p.num_n_tiles;
-      const int n_tile = tile - m_pair * p.num_n_tiles;
+      const int m_pair = (c.rev ? num_tiles - 1 - tile : tile) / p.num_n_tiles;
+      const int n_tile = (c.rev ? num_tiles - 1 - tile : tile) - m_pair * p.num_n_tiles;
       const int acc = (nacc == 2) ? (it & 1) : 0;
       const uint32_t acc_phase = ((nacc == 2) ? (it >> 1) : it) & 1;
       const int row = (2 * m_pair + static_cast<int>(rank)) * BM + q * 32 + lane;
