@@ -202,6 +202,8 @@ class ShardedAdam(torch.optim.Optimizer):
     # ------------------------------------------------------------------ fp32 master on every rank (checkpoints)
     @torch.no_grad()
     def gather_master(self):
+        """All-gather the fp32 master spans so that every rank's parameters are current.  A COLLECTIVE: every rank must
+        call it (and therefore ``net.state_dict()``, which triggers it) at the same point; a no-op when nothing is stale."""
         pm = self.pm
         if not pm.stale:
             return

@@ -220,3 +220,23 @@ def test_n_ranks_equal_single_process(wire):
     num = sum(float(((sd3_0[k].astype(np.float64) - ref3[k]) ** 2).sum()) for k in ref3)
     den = sum(float(((ref3[k].astype(np.float64) - before[k]) ** 2).sum()) for k in ref3)
     assert np.sqrt(num / den) < (2e-2 if wire == "fp32" else 8e-2), np.sqrt(num / den)
+
+
+def test_sharded_adam_with_direct_param_grads_and_bf16_wire_on_one_gpu():
+    """engine.direct_param_grads (gradients handed to p.grad inside backward) and wire="bf16" (no exchange at N = 1) leave
+    the step unchanged."""
+    dev = torch.device("cuda:0")
+    x, cond = _data("cfgA_mini", 64)
+    x, cond = x.to(dev), cond.to(dev)
+    res = []
+    for direct, wire in ((False, "fp32"), (True, "bf16")):
+        net = build("cfgA_mini", precision="bf16").to(dev)
+        with torch.no_grad():
+            net(x, cond)
+        net.flow.engine.direct_param_grads = direct
+        opt = P.ShardedAdam(net, wire=wire, **HYPER)
+        _train(net, opt, x, cond, 3)
+        res.append({k: v.detach().cpu().numpy() for k, v in net.state_dict().items() if v.dtype == torch.float32})
+    for k in res[0]:
+        d = np.max(np.abs(res[0][k] - res[1][k]))
+        assert d <= 1e-6 + 1e-5 * np.max(np.abs(res[0][k])), (k, d)
