@@ -170,6 +170,12 @@ int ipoke_inn_flow_loss(const float* z, const float* logdet, int B, int C, float
  * N(0, I) sample it draws with randn_like (loss.py:27, 32; the draw stays with the caller: same RNG consumption). */
 int ipoke_inn_flow_loss_ref(const float* z, const float* logdet, const float* ref_sample, int B, int C, float nll_weight,
                             float logdet_weight, float* out4, float* dz, float* dlogdet, void* stream);
+/* Same again for large batches: up to 32 CTAs park fp64 partial sums in `scratch` (ipoke_inn_flow_loss_scratch_bytes()
+ * bytes of device memory, 8-byte aligned, zeroed ONCE by the caller; the kernel leaves it zeroed) and the last one adds
+ * them in block order (deterministic).  One call at a time per scratch buffer.  ref_sample nullable; scratch NULL = one CTA. */
+int ipoke_inn_flow_loss_scratch_bytes(void);
+int ipoke_inn_flow_loss_ws(const float* z, const float* logdet, const float* ref_sample, int B, int C, float nll_weight,
+                           float logdet_weight, float* out4, float* dz, float* dlogdet, void* scratch, void* stream);
 
 /* Fused Adam / AMSGrad step over all parameter tensors in one launch -- replaces the reference's
  * torch.optim.Adam(lr, betas, weight_decay, amsgrad=True).step() (models/second_stage_video_fc.py:685-687;

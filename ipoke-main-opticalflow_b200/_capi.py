@@ -20,7 +20,8 @@ SYMBOLS = [
     "ipoke_inn_saved_bytes", "ipoke_inn_forward_train", "ipoke_inn_backward", "ipoke_inn_profile_read_n",
     "ipoke_inn_adam_chunk_elems", "ipoke_inn_adam_step", "ipoke_inn_reverse_draws", "ipoke_inn_forward_draws",
     "ipoke_inn_param_layout", "ipoke_inn_pack_small", "ipoke_inn_adam_shard_step", "ipoke_inn_master_to_packed",
-    "ipoke_inn_grad_to_bf16", "ipoke_inn_flow_loss_ref",
+    "ipoke_inn_grad_to_bf16", "ipoke_inn_flow_loss_ref", "ipoke_inn_flow_loss_ws",
+    "ipoke_inn_flow_loss_scratch_bytes",
 ]
 
 
@@ -102,6 +103,10 @@ def lib():
     L.ipoke_inn_adam_step.restype = i32
     L.ipoke_inn_adam_step.argtypes = [vp, vp, vp, i32, f32, f32, f32, f32, f32, i32, i32, f32, vp]
     i64 = ctypes.c_longlong
+    L.ipoke_inn_flow_loss_scratch_bytes.restype = i32
+    L.ipoke_inn_flow_loss_scratch_bytes.argtypes = []
+    L.ipoke_inn_flow_loss_ws.restype = i32
+    L.ipoke_inn_flow_loss_ws.argtypes = [vp, vp, vp, i32, i32, f32, f32, vp, vp, vp, vp, vp]
     L.ipoke_inn_flow_loss_ref.restype = i32
     L.ipoke_inn_flow_loss_ref.argtypes = [vp, vp, vp, i32, i32, f32, f32, vp, vp, vp, vp]
     L.ipoke_inn_param_layout.restype = i32

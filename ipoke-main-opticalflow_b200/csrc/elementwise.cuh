@@ -431,16 +431,25 @@ __global__ void inn_actnorm_finalize_kernel(const double* __restrict__ moments, 
 // ----------------------------------------------------------------------------- FlowLoss
 // single CTA: B*C is small next to the GEMMs; deterministic tree reduction
 // `ref` (nullable): the N(0, I) sample the reference draws for its logged reference NLL (loss.py:27, 32); its mean NLL goes
-// to out3[3] in the same launch
+// to out3[3] in the same launch.  Up to FLOW_LOSS_MAX_BLOCKS CTAs: every CTA reduces its slice with a fixed-order tree and
+// parks three fp64 partials in `scratch`; the CTA that takes the last ticket adds them in block order (deterministic),
+// writes the results and resets the ticket counter for the next call.  scratch = FLOW_LOSS_SCRATCH_BYTES, zeroed once by
+// the caller; NULL = single CTA (small batches).
+constexpr int FLOW_LOSS_MAX_BLOCKS = 32;
+constexpr int FLOW_LOSS_SCRATCH_BYTES = 8 * (3 * FLOW_LOSS_MAX_BLOCKS + 1);
 __global__ void __launch_bounds__(1024) inn_flow_loss_kernel(const float* __restrict__ z, const float* __restrict__ logdet,
                                                              int B, int C, float nll_w, float ld_w, float* out3,
-                                                             float* dz, float* dlogdet, const float* __restrict__ ref) {
-  __shared__ double r_nll[1024];
-  __shared__ double r_ld[1024];
+                                                             float* dz, float* dlogdet, const float* __restrict__ ref,
+                                                             double* scratch) {
+  __shared__ double r_a[1024];
+  __shared__ double r_b[1024];
+  __shared__ double r_c[1024];
+  __shared__ unsigned int s_ticket;
   double a = 0.0, l = 0.0, r = 0.0;
   const long long total = static_cast<long long>(B) * C;
   const float inv_b = 1.0f / static_cast<float>(B);
-  for (long long i = threadIdx.x; i < total; i += blockDim.x) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
     const float v = z[i];
     a += 0.5 * static_cast<double>(v) * v;
     if (dz) dz[i] = nll_w * v * inv_b;
@@ -449,35 +458,50 @@ __global__ void __launch_bounds__(1024) inn_flow_loss_kernel(const float* __rest
       r += 0.5 * static_cast<double>(w) * w;
     }
   }
-  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+  for (long long b = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; b < B; b += stride) {
     l += logdet[b];
     if (dlogdet) dlogdet[b] = -ld_w * inv_b;
   }
-  r_nll[threadIdx.x] = a;
-  r_ld[threadIdx.x] = l;
+  r_a[threadIdx.x] = a;
+  r_b[threadIdx.x] = l;
+  r_c[threadIdx.x] = r;
   __syncthreads();
   for (int s = 512; s > 0; s >>= 1) {
     if (threadIdx.x < s) {
-      r_nll[threadIdx.x] += r_nll[threadIdx.x + s];
-      r_ld[threadIdx.x] += r_ld[threadIdx.x + s];
+      r_a[threadIdx.x] += r_a[threadIdx.x + s];
+      r_b[threadIdx.x] += r_b[threadIdx.x + s];
+      r_c[threadIdx.x] += r_c[threadIdx.x + s];
     }
     __syncthreads();
   }
+  double sa = r_a[0], sl = r_b[0], sr = r_c[0];
+  if (gridDim.x > 1) {
+    if (threadIdx.x == 0) {
+      scratch[3 * blockIdx.x] = sa;
+      scratch[3 * blockIdx.x + 1] = sl;
+      scratch[3 * blockIdx.x + 2] = sr;
+      __threadfence();
+      s_ticket = atomicAdd(reinterpret_cast<unsigned int*>(scratch + 3 * FLOW_LOSS_MAX_BLOCKS), 1u);
+    }
+    __syncthreads();
+    if (s_ticket != gridDim.x - 1) return;
+    if (threadIdx.x == 0) {
+      __threadfence();
+      sa = sl = sr = 0.0;
+      for (unsigned int k = 0; k < gridDim.x; ++k) {
+        sa += scratch[3 * k];
+        sl += scratch[3 * k + 1];
+        sr += scratch[3 * k + 2];
+      }
+      *reinterpret_cast<unsigned int*>(scratch + 3 * FLOW_LOSS_MAX_BLOCKS) = 0u;      // ready for the next call
+    }
+  }
   if (threadIdx.x == 0) {
-    const double nll = r_nll[0] / B, nld = -r_ld[0] / B;
+    const double nll = sa / B, nld = -sl / B;
     out3[0] = static_cast<float>(nll_w * nll + ld_w * nld);
     out3[1] = static_cast<float>(nll);
     out3[2] = static_cast<float>(nld);
-  }
-  if (ref) {                                    // third reduction, same tree
-    __syncthreads();
-    r_nll[threadIdx.x] = r;
-    __syncthreads();
-    for (int s = 512; s > 0; s >>= 1) {
-      if (threadIdx.x < s) r_nll[threadIdx.x] += r_nll[threadIdx.x + s];
-      __syncthreads();
-    }
-    if (threadIdx.x == 0) out3[3] = static_cast<float>(r_nll[0] / B);
+    if (ref) out3[3] = static_cast<float>(sr / B);
   }
 }
 

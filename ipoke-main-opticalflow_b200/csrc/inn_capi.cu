@@ -2221,7 +2221,7 @@ int ipoke_inn_flow_loss(const float* z, const float* logdet, int B, int C, float
                         float* out3, float* dz, float* dlogdet, void* stream) {
   if (!z || !logdet || !out3 || B <= 0 || C <= 0) return IPOKE_INN_E_INVALID;
   inn_flow_loss_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(z, logdet, B, C, nll_weight, logdet_weight,
-                                                                          out3, dz, dlogdet, nullptr);
+                                                                          out3, dz, dlogdet, nullptr, nullptr);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : (int)e;
 }
@@ -2230,7 +2230,22 @@ int ipoke_inn_flow_loss_ref(const float* z, const float* logdet, const float* re
                             float logdet_weight, float* out4, float* dz, float* dlogdet, void* stream) {
   if (!z || !logdet || !ref_sample || !out4 || B <= 0 || C <= 0) return IPOKE_INN_E_INVALID;
   inn_flow_loss_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(z, logdet, B, C, nll_weight, logdet_weight,
-                                                                          out4, dz, dlogdet, ref_sample);
+                                                                          out4, dz, dlogdet, ref_sample, nullptr);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : (int)e;
+}
+
+int ipoke_inn_flow_loss_scratch_bytes(void) { return FLOW_LOSS_SCRATCH_BYTES; }
+
+int ipoke_inn_flow_loss_ws(const float* z, const float* logdet, const float* ref_sample, int B, int C, float nll_weight,
+                           float logdet_weight, float* out4, float* dz, float* dlogdet, void* scratch, void* stream) {
+  if (!z || !logdet || !out4 || B <= 0 || C <= 0) return IPOKE_INN_E_INVALID;
+  if (scratch && (reinterpret_cast<uintptr_t>(scratch) & 7u)) return IPOKE_INN_E_INVALID;
+  const long long total = (long long)B * C;
+  int blocks = scratch ? (int)std::min<long long>(FLOW_LOSS_MAX_BLOCKS, (total + 32767) / 32768) : 1;
+  blocks = std::max(blocks, 1);
+  inn_flow_loss_kernel<<<blocks, 1024, 0, static_cast<cudaStream_t>(stream)>>>(
+      z, logdet, B, C, nll_weight, logdet_weight, out4, dz, dlogdet, ref_sample, static_cast<double*>(scratch));
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : (int)e;
 }

@@ -6,6 +6,20 @@ import torch.nn as nn
 from . import _capi
 
 
+_SCRATCH = {}       # (device, stream) -> zeroed partial-sum scratch of the multi-CTA loss kernel (it leaves it zeroed)
+
+
+def _scratch(device):
+    key = (device, torch.cuda.current_stream(device).cuda_stream)
+    buf = _SCRATCH.get(key)
+    if buf is None:
+        if len(_SCRATCH) >= 16:
+            _SCRATCH.pop(next(iter(_SCRATCH)))
+        buf = torch.zeros(_capi.lib().ipoke_inn_flow_loss_scratch_bytes() // 8, dtype=torch.float64, device=device)
+        _SCRATCH[key] = buf
+    return buf
+
+
 def _loss_kernel(z2, logdet, ref2, nll_w, ld_w, want_grads):
     """One launch: loss, mean nll, -mean logdet, mean nll of the reference sample (+ dz, dlogdet) -> out4."""
     B, C = z2.shape
@@ -13,9 +27,11 @@ def _loss_kernel(z2, logdet, ref2, nll_w, ld_w, want_grads):
     dz = torch.empty_like(z2) if want_grads else None
     dld = torch.empty_like(logdet) if want_grads else None
     stream = torch.cuda.current_stream(z2.device).cuda_stream
-    _capi.check(_capi.lib().ipoke_inn_flow_loss_ref(z2.data_ptr(), logdet.data_ptr(), ref2.data_ptr(), B, C, float(nll_w),
-                                                    float(ld_w), out4.data_ptr(), dz.data_ptr() if want_grads else None,
-                                                    dld.data_ptr() if want_grads else None, stream), "flow_loss")
+    scratch = _scratch(z2.device) if B * C > 32768 else None          # one CTA is enough below that
+    _capi.check(_capi.lib().ipoke_inn_flow_loss_ws(z2.data_ptr(), logdet.data_ptr(), ref2.data_ptr(), B, C, float(nll_w),
+                                                   float(ld_w), out4.data_ptr(), dz.data_ptr() if want_grads else None,
+                                                   dld.data_ptr() if want_grads else None,
+                                                   scratch.data_ptr() if scratch is not None else None, stream), "flow_loss")
     return out4, dz, dld
 
 

@@ -305,3 +305,25 @@ def test_concurrent_streams_match_serial(name, B):
                 # reproducible up to the order of those 2-8 additions, not bitwise
                 assert float((ld1 - prev[2]).abs().max()) <= 4e-6 * float(ld1.abs().max())
             prev = (z1.clone(), x1.clone(), ld1.clone())
+
+
+def test_flow_loss_kernel_large_batch_is_deterministic_and_reusable():
+    """From 32768 elements on the loss runs on up to 32 CTAs with fp64 partials added in block order: equal to the oracle,
+    bit-identical from call to call (the ticket counter resets itself), gradients as the single-CTA path writes them."""
+    dev = _dev()
+    g = torch.Generator().manual_seed(6)
+    z = torch.randn(4096, 128, 1, 1, generator=g)
+    ld = torch.randn(4096, generator=g)
+    zd, ldd = z.to(dev).requires_grad_(True), ld.to(dev).requires_grad_(True)
+    vals = []
+    for _ in range(3):
+        loss, log = P.FlowLoss(nll_weight=0.7, logdet_weight=1.3)(zd, ldd)
+        vals.append((float(loss), float(log["nll_loss"]), float(log["nlogdet_loss"])))
+    assert vals[0] == vals[1] == vals[2]
+    ref, nll_ref, nld_ref = O.flow_loss(z.numpy().astype(np.float64), ld.numpy().astype(np.float64), 0.7, 1.3)
+    assert abs(vals[0][0] - ref) < 1e-6 * abs(ref) + 1e-6
+    assert abs(vals[0][1] - nll_ref) < 1e-6 * abs(nll_ref) and abs(vals[0][2] - nld_ref) < 1e-5 * max(abs(nld_ref), 1e-2)
+    assert 0.45 * 128 < float(log["reference_nll_loss"]) < 0.55 * 128
+    loss.backward()
+    assert torch.allclose(zd.grad, 0.7 * zd.detach() / 4096, rtol=1e-6, atol=1e-9)
+    assert torch.allclose(ldd.grad, torch.full_like(ldd, -1.3 / 4096), rtol=1e-6)
