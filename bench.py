@@ -356,23 +356,26 @@ def fwd_rev_workload(ctx, cfg_name, B, precision, steps, warmup, want_clocks=Fal
 
     if want_kinds and ctx.rank == 0:
         # per-kind kernel time: library CUDA events around every launch of a forward + a reverse pass (this pass
-        # serialises the launches: no graph replay, no programmatic dependent launch); used for the kernel's SHARE
-        eng.set_concurrency(1)
+        # serialises the launches: no graph replay, no programmatic dependent launch); used for the kernel's SHARE.
+        # Once with the launch sizing of the 2-stream step (64-CTA launches) and once with the one-request sizing.
         L = _capi.lib()
-        L.ipoke_inn_profile_enable(eng._plan, 1)
-        tot, cnt = np.zeros(3), np.zeros(3, dtype=np.int64)
-        ms3, n3 = (ctypes.c_double * 3)(), (ctypes.c_int * 3)()
-        reps = max(3, min(steps, 10))
-        for s in range(reps):
-            ctx.flush.fill_(s & 0xFF)
-            for rev in (False, True):
-                call(zin if rev else x, reverse=rev)
-                L.ipoke_inn_profile_read(eng._plan, ms3, n3)
-                tot += np.array(list(ms3))
-                cnt += np.array(list(n3))
-        L.ipoke_inn_profile_enable(eng._plan, 0)
-        res["kind_ms"] = (tot / reps).tolist()                  # per step: boundary, hidden, tail
-        res["kind_launches"] = (cnt // reps).tolist()
+        res["kind_ms"], res["kind_launches"] = {}, {}
+        for conc in (2, 1):
+            eng.set_concurrency(conc)
+            L.ipoke_inn_profile_enable(eng._plan, 1)
+            tot, cnt = np.zeros(3), np.zeros(3, dtype=np.int64)
+            ms3, n3 = (ctypes.c_double * 3)(), (ctypes.c_int * 3)()
+            reps = max(3, min(steps, 10))
+            for s in range(reps):
+                ctx.flush.fill_(s & 0xFF)
+                for rev in (False, True):
+                    call(zin if rev else x, reverse=rev)
+                    L.ipoke_inn_profile_read(eng._plan, ms3, n3)
+                    tot += np.array(list(ms3))
+                    cnt += np.array(list(n3))
+            L.ipoke_inn_profile_enable(eng._plan, 0)
+            res["kind_ms"][conc] = (tot / reps).tolist()              # per step: boundary, hidden, tail
+            res["kind_launches"][conc] = (cnt // reps).tolist()
     del net
     torch.cuda.empty_cache()
     return res
@@ -390,9 +393,9 @@ def hidden_roofline(ctx, cfg_name, r, streams):
     P_w = macs_per_sample(kind, kw)
     wbytes = 2 if prec == "bf16" else 4
     hid_w = P_w - tail_macs(cfg_name)
-    tot = r["kind_ms"]
+    tot = r["kind_ms"][streams]                                # measured with this step's launch sizing
     share = tot[1] / max(sum(tot), 1e-12)
-    n_launch = int(r["kind_launches"][1])                      # per step (forward + reverse)
+    n_launch = int(r["kind_launches"][streams][1])             # per step (forward + reverse)
     ms_step = r["ms"] if streams > 1 else r["ms_serial"]
     t_hidden = share * ms_step * 1e-3                           # wall time with hidden kernels running
     bytes_step = 2.0 * hid_w * wbytes                           # both directions

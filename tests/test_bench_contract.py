@@ -51,8 +51,8 @@ def test_roofline_fraction_follows_from_the_lines_own_fields():
     class Ctx:
         pk = dict(hbm=6546.2, bf16=1679.4, bf16_sus=1409.5, src="test")
     for prec, wbytes in (("bf16", 2), ("fp32", 4)):
-        r = {"B": 256, "precision": prec, "ms": 0.44, "ms_serial": 0.74, "kind_ms": [0.02, 1.0, 0.3],
-             "kind_launches": [2, 96, 32]}
+        r = {"B": 256, "precision": prec, "ms": 0.44, "ms_serial": 0.74,
+             "kind_ms": {1: [0.02, 1.0, 0.3], 2: [0.02, 1.0, 0.3]}, "kind_launches": {1: [2, 96, 32], 2: [2, 96, 32]}}
         for streams in (1, 2):
             out = bench.hidden_roofline(Ctx(), "cfgB", r, streams)
             kind, kw, C, E, H = bench.dims("cfgB")
