@@ -215,7 +215,8 @@ int ipoke_inn_param_layout(const ipoke_inn_plan* plan, long long* out, int n);
 int ipoke_inn_pack_small(const ipoke_inn_plan* plan, void* packed, void* stream);
 /* Adam / AMSGrad (arithmetic of ipoke_inn_adam_step) on one contiguous span of n weights (n % 4 == 0, 16-byte aligned):
  * p = fp32 master (updated in place), exactly one of g (fp32) / g_bf16 (bf16 wire format) non-NULL, m / v / vmax =
- * moments of the span, hi / lo = where the span's bf16 images live in the packed buffer (lo NULL in the bf16 mode). */
+ * moments of the span, hi / lo = where the span's bf16 images live in the packed buffer (lo NULL in the bf16 mode; both NULL
+ * for parameters that have no packed image: biases and ActNorm parameters kept in one flat buffer). */
 int ipoke_inn_adam_shard_step(float* p, const float* g, const void* g_bf16, float* m, float* v, float* vmax, void* hi,
                               void* lo, long long n, float lr, float beta1, float beta2, float eps, float weight_decay,
                               int step, int amsgrad, float grad_scale, void* stream);

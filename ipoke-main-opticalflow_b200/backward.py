@@ -29,7 +29,8 @@ class FlowFunction(torch.autograd.Function):
         x2, c2, outs = ctx.saved_tensors
         need_x = ctx.needs_input_grad[1]
         need_c = c2 is not None and ctx.needs_input_grad[2]
-        flat, views, ptrs = engine.new_grad_buffer()
+        flat_only = getattr(engine, "flat_grads_only", False)
+        flat, views, ptrs = engine.new_grad_buffer() if not flat_only else engine.new_grad_buffer(want_views=False)
         dz = dz.contiguous().float()
         dld = dld.contiguous().float()
         hook = engine.grad_ready_hook
@@ -55,6 +56,10 @@ class FlowFunction(torch.autograd.Function):
         # ctx.saved_buf stays alive with the graph (retain_graph=True / a second backward read it again)
         gx = dx.view(ctx.x_shape) if (need_x and dx is not None) else None
         gc = dcond.view(ctx.cond_shape) if (need_c and dcond is not None) else None
+        if flat_only:
+            # the optimizer reads engine.last_flat_grad itself (optim_sharded.ShardedAdam): no per-parameter views, no
+            # AccumulateGrad work -- at the reference's batch of 64 that bookkeeping is a third of the step's host time
+            return (None, gx, gc) + (None,) * len(engine.grad_layout()[3])
         if engine.direct_param_grads:
             # opt-in (engine.direct_param_grads = True): hand the views to the parameters here instead of through one
             # AccumulateGrad node per parameter -- the autograd engine's per-tensor bookkeeping for the few hundred

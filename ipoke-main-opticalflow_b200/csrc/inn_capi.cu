@@ -2348,7 +2348,7 @@ int ipoke_inn_adam_shard_step(float* p, const float* g, const void* g_bf16, floa
                               void* lo, long long n, float lr, float beta1, float beta2, float eps, float weight_decay,
                               int step, int amsgrad, float grad_scale, void* stream) {
   if (n == 0) return 0;
-  if (!p || (!g) == (!g_bf16) || !m || !v || !hi || (amsgrad && !vmax) || n < 0 || (n & 3) || step < 1) return IPOKE_INN_E_INVALID;
+  if (!p || (!g) == (!g_bf16) || !m || !v || (!hi && lo) || (amsgrad && !vmax) || n < 0 || (n & 3) || step < 1) return IPOKE_INN_E_INVALID;
   if (!al16(p) || !al16(g) || !al16(m) || !al16(v) || !al16(vmax) || (reinterpret_cast<uintptr_t>(g_bf16) & 7u) ||
       (reinterpret_cast<uintptr_t>(hi) & 7u) || (reinterpret_cast<uintptr_t>(lo) & 7u)) return IPOKE_INN_E_INVALID;
   AdamShardParams q;

@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(ADAM_THREADS) inn_adam_kernel(const AdamParams
 struct AdamShardParams {
   float* p; const float* g; const __nv_bfloat16* g16;   // exactly one of g / g16
   float* m; float* v; float* vmax;
-  __nv_bfloat16* hi; __nv_bfloat16* lo;                  // lo nullable (single-pass bf16 mode)
+  __nv_bfloat16* hi; __nv_bfloat16* lo;                  // lo nullable (single-pass bf16 mode); hi nullable (no images)
   long long n;                                           // multiple of 4, all pointers 16-byte aligned
   AdamParams a;
 };
@@ -157,10 +157,12 @@ __global__ void __launch_bounds__(ADAM_THREADS) inn_adam_shard_kernel(const Adam
         reinterpret_cast<float4*>(q.m)[i] = M[u];
         reinterpret_cast<float4*>(q.v)[i] = V[u];
         if (q.a.amsgrad) reinterpret_cast<float4*>(q.vmax)[i] = X[u];
-        uint2 H, L;
-        split4(P[u], H, L);
-        reinterpret_cast<uint2*>(q.hi)[i] = H;
-        if (q.lo) reinterpret_cast<uint2*>(q.lo)[i] = L;
+        if (q.hi) {                              // NULL: parameters without packed images (biases, ActNorm)
+          uint2 H, L;
+          split4(P[u], H, L);
+          reinterpret_cast<uint2*>(q.hi)[i] = H;
+          if (q.lo) reinterpret_cast<uint2*>(q.lo)[i] = L;
+        }
       }
     }
   }

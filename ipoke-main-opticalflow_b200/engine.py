@@ -40,6 +40,8 @@ class FlowEngine:
         self.grad_chunk_blocks = 2
         self.last_flat_grad = None
         self.direct_param_grads = False       # True: backward() assigns / accumulates p.grad itself (see backward.py)
+        self.flat_grads_only = False          # True: backward() leaves p.grad alone; the flat buffer (last_flat_grad) is the
+                                              # only result (set by ShardedAdam, which consumes the buffer directly)
         self._grad_layout = None
         self.streams = 1
         self._pm = None                       # packed-master state (adopt_packed_master)
@@ -398,9 +400,11 @@ class FlowEngine:
         pm = self._pm
         if pm is None or self._packed is None or pm.packed_ptr != self._packed.data_ptr():
             return False
-        lin_w = (tensors or self._tensors())[0]
+        t = tensors or self._tensors()
+        lin_w, lin_b = t[0], t[1]
         base = pm.master.data_ptr()
-        return (lin_w[0].data_ptr() == base + 4 * pm.w_off[0] and lin_w[-1].data_ptr() == base + 4 * pm.w_off[-1])
+        return (lin_w[0].data_ptr() == base + 4 * pm.w_off[0] and lin_w[-1].data_ptr() == base + 4 * pm.w_off[-1]
+                and lin_b[0].data_ptr() == base + 4 * pm.n)
 
     def adopt_packed_master(self):
         """Make one flat fp32 buffer whose element layout IS the packed hi arena the storage of every nn.Linear weight
@@ -423,19 +427,29 @@ class FlowEngine:
             raise NotImplementedError("packed-master training needs H, E and C/2 to be multiples of 64 (no padding inside "
                                       "the packed weight arena); use FusedAdam + GradSync for this shape")
         self._pm = None
-        self.pack(force=True)                               # plain repack while every parameter still owns its storage
         N = int(out[2])
-        master = torch.zeros(N, dtype=torch.float32, device=dev)
+        _, lin_b, loc, scale, _, _ = self._tensors()
+        small = list(lin_b) + list(loc) + list(scale)       # the order of the flat gradient buffer behind the weights
+        n_small = sum(p.numel() for p in small)
+        master = torch.zeros(N + n_small, dtype=torch.float32, device=dev)
         w_off = [int(out[8 + i]) for i in range(n_lin)]
         with torch.no_grad():
-            for w, off in zip(lin_w, w_off):
+            off = N
+            for p in small:                                  # biases / ActNorm: one flat span behind the weights
+                v = master[off:off + p.numel()].view(p.shape)
+                v.copy_(p)
+                p.data = v
+                off += p.numel()
+            self._packed_sig = None
+            self.pack(force=True)                            # plain repack: its job tables keep the small parameters'
+            for w, off in zip(lin_w, w_off):                 # (new) addresses; the weights still own their storage here
                 v = master[off:off + w.numel()].view(w.shape)
                 v.copy_(w)
                 w.data = v
         pk16 = self._packed.view(torch.bfloat16)
         lo_off = int(out[3])
         self._pm = types.SimpleNamespace(
-            master=master, w_off=w_off, n=N, packed_ptr=self._packed.data_ptr(), stale=False,
+            master=master, w_off=w_off, n=N, n_small=n_small, packed_ptr=self._packed.data_ptr(), stale=False,
             hi=pk16[:N], lo=pk16[lo_off // 2:lo_off // 2 + N] if lo_off >= 0 else None,
             block_ranges=[(int(out[8 + n_lin + 2 * k]), int(out[8 + n_lin + 2 * k + 1])) for k in range(self.n_flows)])
         self._grad_layout = None
@@ -479,9 +493,9 @@ class FlowEngine:
             self._grad_layout = (offs, cur, block_ranges, params)
         return self._grad_layout
 
-    def new_grad_buffer(self):
+    def new_grad_buffer(self, want_views=True):
         """-> flat [total] fp32 (fresh storage: gradients handed to autograd must not alias a later call's),
-        the per-parameter views in ``flow.parameters()`` order and the pointer arrays of the C ABI."""
+        the per-parameter views in ``flow.parameters()`` order (None when not wanted) and the pointer arrays of the C ABI."""
         offs, total, block_ranges, params = self.grad_layout()
         flat = torch.empty(total, dtype=torch.float32, device=self._device)
         base = flat.data_ptr()
@@ -489,6 +503,8 @@ class FlowEngine:
             lin_w, lin_b, loc, scale, _, _ = self._tensors()
             self._grad_ptr_offs = [[4 * offs[id(t)][0] for t in ts] for ts in (lin_w, lin_b, loc, scale)]
         arrays = tuple((ctypes.c_void_p * len(o))(*[base + b for b in o]) for o in self._grad_ptr_offs)
+        if not want_views:
+            return flat, None, arrays
         # one C++ call for all the views (a Python slice + view per parameter costs more than the batch-64 kernels)
         if self._grad_perm is None:
             views = list(torch._utils._unflatten_dense_tensors(flat, params))

@@ -16,7 +16,11 @@ AMSGrad with L2 weight decay, arithmetic of ``ipoke_inn_adam_step``) and changes
 * the bf16 images are **all-gathered in place inside the packed buffer** -- the wire carries 2 (bf16 mode) or 4
   (parity mode) bytes per weight instead of fp32 gradients a second time, the 36-byte-per-parameter optimizer traffic
   drops to 1/N, and the separate fp32 -> bf16 repack pass of the replicated path disappears (also at N = 1);
-* biases and ActNorm parameters (0.1 % of the bytes) are all-reduced and updated replicated by ``FusedAdam``.
+* biases and ActNorm parameters (0.1 % of the bytes) sit in one flat span behind the weights; their gradients are
+  all-reduced in one small message and every rank updates them replicated with the same kernel;
+* the backward pass hands the optimizer ONE flat gradient buffer and creates no per-parameter ``.grad`` tensors
+  (``expose_param_grads=True`` restores them): at the reference's batch of 64 the views and AccumulateGrad bookkeeping
+  of 336 parameters were a third of the step's host time.
 
 The fp32 master of the spans a rank does not own goes stale between checkpoints: ``gather_master()`` (called
 automatically by the module's ``state_dict()``) all-gathers it.
@@ -25,7 +29,6 @@ import torch
 import torch.distributed as dist
 
 from . import _capi
-from .optim import FusedAdam
 
 
 def plan_pieces(block_ranges, chunk_blocks, world, rank):
@@ -59,11 +62,12 @@ class ShardedAdam(torch.optim.Optimizer):
 
     ``param_groups[0]["lr"]`` may be rewritten every step (the reference's warm-up, second_stage_video_fc.py:256-271).
     ``wire="bf16"`` sends the gradients as bf16 (pre-divided by the world size; the sum on the wire is the mean).
-    One backward pass per step (no gradient accumulation across backward calls).
+    One backward pass per step (no gradient accumulation across backward calls).  Parameters' ``.grad`` stay None unless
+    ``expose_param_grads=True``; ``gradients()`` returns views of this rank's (un-reduced) flat gradient buffer on demand.
     """
 
     def __init__(self, net, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, amsgrad=False, group=None,
-                 wire="fp32", chunk_blocks=2):
+                 wire="fp32", chunk_blocks=2, expose_param_grads=False):
         if wire not in ("fp32", "bf16"):
             raise ValueError("wire must be 'fp32' or 'bf16'")
         if lr < 0.0 or eps < 0.0 or not 0.0 <= betas[0] < 1.0 or not 0.0 <= betas[1] < 1.0 or weight_decay < 0.0:
@@ -97,10 +101,11 @@ class ShardedAdam(torch.optim.Optimizer):
                                      device=self.device)
         self._stage16 = (torch.empty(pm.n, dtype=torch.bfloat16, device=self.device)
                          if (wire == "bf16" and self.world > 1) else None)
-        lin_w = set(id(w) for w in eng._tensors()[0])
-        self.small_params = [p for p in params if id(p) not in lin_w]
-        self.small_opt = FusedAdam(self.small_params, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay,
-                                   amsgrad=amsgrad)
+        # biases / ActNorm: replicated moments for the flat span behind the weights
+        self.sm = torch.zeros(pm.n_small, dtype=torch.float32, device=self.device)
+        self.sv = torch.zeros(pm.n_small, dtype=torch.float32, device=self.device)
+        self.svmax = torch.zeros(pm.n_small, dtype=torch.float32, device=self.device) if amsgrad else None
+        eng.flat_grads_only = not expose_param_grads
         self.steps = 0
         self._side = None
         self._reduced = None                  # the flat gradient buffer whose chunks are in flight / reduced
@@ -185,16 +190,18 @@ class ShardedAdam(torch.optim.Optimizer):
                     dist.all_gather_into_tensor(pm.hi[c["lo"]:c["hi"]], pm.hi[lo:lo + n], group=self.group)
                     if pm.lo is not None:
                         dist.all_gather_into_tensor(pm.lo[c["lo"]:c["hi"]], pm.lo[lo:lo + n], group=self.group)
-        # biases / ActNorm: replicated (their gradients were all-reduced with the last chunk)
-        for sg in self.small_opt.param_groups:
-            sg["lr"], sg["betas"], sg["eps"], sg["weight_decay"] = lr, (b1, b2), eps, wd
-        self.small_opt.step()
+        # biases / ActNorm: replicated (their gradients were all-reduced with the last chunk), same kernel, no images
+        _capi.check(L.ipoke_inn_adam_shard_step(
+            pm.master.data_ptr() + 4 * pm.n, flat.data_ptr() + 4 * pm.n, None, self.sm.data_ptr(), self.sv.data_ptr(),
+            self.svmax.data_ptr() if self.svmax is not None else None, None, None, pm.n_small,
+            lr, float(b1), float(b2), eps, wd, self.steps, int(ams), 1.0, cur.cuda_stream), "adam_shard_step(small)")
         _capi.check(L.ipoke_inn_pack_small(eng._plan, eng._packed.data_ptr(), cur.cuda_stream), "pack_small")
         if side is not None:
             cur.wait_stream(side)
         pm.stale = any(c["sharded"] for c in self.pieces)
-        torch.autograd.graph.increment_version(eng._tensors()[0])
-        eng._packed_sig = eng._signature(eng._tensors())               # the packed buffer is current: no repack
+        t = eng._tensors()
+        torch.autograd.graph.increment_version(list(t[0]) + list(t[1]) + list(t[2]) + list(t[3]))
+        eng._packed_sig = eng._signature(t)                            # the packed buffer is current: no repack
         eng.last_flat_grad = None
         self._reduced = None
         return loss
@@ -213,11 +220,21 @@ class ShardedAdam(torch.optim.Optimizer):
                 dist.all_gather_into_tensor(pm.master[c["lo"]:c["hi"]], pm.master[lo:lo + n], group=self.group)
         pm.stale = False
 
+    def gradients(self):
+        """Per-parameter views (``flow.parameters()`` order) of the flat gradient buffer of the last backward pass: this
+        rank's own gradients -- the mean over ranks exists only as the reduce-scattered spans -- until ``step()``."""
+        eng = self.engine
+        flat = eng.last_flat_grad
+        if flat is None:
+            raise RuntimeError("no gradient buffer: run a backward pass first (step() consumes it)")
+        offs, _, _, params = eng.grad_layout()
+        return [flat[offs[id(p)][0]:offs[id(p)][0] + p.numel()].view(p.shape) for p in params]
+
     def state_dict(self):
-        """This rank's optimizer shard (moments of the owned spans) plus the replicated small-parameter state."""
+        """This rank's optimizer shard (moments of the owned spans) plus the replicated small-parameter moments."""
         return {"steps": self.steps, "rank": self.rank, "world": self.world, "wire": self.wire,
                 "param_groups": [{k: v for k, v in g.items() if k != "params"} for g in self.param_groups],
-                "m": self.m, "v": self.v, "vmax": self.vmax, "small": self.small_opt.state_dict()}
+                "m": self.m, "v": self.v, "vmax": self.vmax, "sm": self.sm, "sv": self.sv, "svmax": self.svmax}
 
     def load_state_dict(self, sd):
         if sd["world"] != self.world or sd["rank"] != self.rank or sd["m"].numel() != self.m.numel():
@@ -229,11 +246,15 @@ class ShardedAdam(torch.optim.Optimizer):
             self.vmax.copy_(sd["vmax"])
         for g, s in zip(self.param_groups, sd["param_groups"]):
             g.update(s)
-        self.small_opt.load_state_dict(sd["small"])
+        self.sm.copy_(sd["sm"])
+        self.sv.copy_(sd["sv"])
+        if self.svmax is not None and sd.get("svmax") is not None:
+            self.svmax.copy_(sd["svmax"])
 
     def remove(self):
         if self.engine.grad_ready_hook is self:
             self.engine.grad_ready_hook = None
+        self.engine.flat_grads_only = False
         if self._sd_hook is not None:
             self._sd_hook.remove()
             self._sd_hook = None

@@ -56,8 +56,9 @@ def test_sharded_adam_equals_torch_adam_on_the_same_gradients(name, precision):
         z, ld = _call(net, x, cond)
         loss, _ = lf(z, ld)
         loss.backward()
-        for p, q in zip(net.parameters(), ref.parameters()):
-            q.grad = p.grad.detach().clone()
+        assert all(p.grad is None for p in net.parameters())       # the optimizer owns the one flat gradient buffer
+        for g, q in zip(opt.gradients(), ref.parameters()):
+            q.grad = g.detach().clone()
         opt.param_groups[0]["lr"] = topt.param_groups[0]["lr"] = 1e-3 * (step + 1) / 4     # warm-up ramp
         opt.step()
         topt.step()
