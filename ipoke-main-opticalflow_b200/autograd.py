@@ -15,6 +15,10 @@ def flow_forward(engine, x, cond):
     """-> z [B,C], logdet [B], block_outs [n,B,C] | None, block_logdets [n,B] | None."""
     if _needs_grad(engine, x, cond):
         from .backward import FlowFunction
+        if getattr(engine, "flat_grads_only", False):
+            # the optimizer reads the flat gradient buffer itself: ONE differentiable anchor stands in for the 336
+            # parameters as the Function's input, so that backward() runs without per-parameter autograd edges
+            return FlowFunction.apply(engine, x, cond, engine.grad_anchor(x.device))
         params = engine.grad_layout()[3]
         return FlowFunction.apply(engine, x, cond, *params)
     with torch.no_grad():

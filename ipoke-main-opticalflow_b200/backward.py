@@ -59,7 +59,7 @@ class FlowFunction(torch.autograd.Function):
         if flat_only:
             # the optimizer reads engine.last_flat_grad itself (optim_sharded.ShardedAdam): no per-parameter views, no
             # AccumulateGrad work -- at the reference's batch of 64 that bookkeeping is a third of the step's host time
-            return (None, gx, gc) + (None,) * len(engine.grad_layout()[3])
+            return (None, gx, gc) + (None,) * (len(ctx.needs_input_grad) - 3)
         if engine.direct_param_grads:
             # opt-in (engine.direct_param_grads = True): hand the views to the parameters here instead of through one
             # AccumulateGrad node per parameter -- the autograd engine's per-tensor bookkeeping for the few hundred

@@ -77,7 +77,7 @@ class FlowEngine:
     def __getstate__(self):
         st = dict(self.__dict__)
         for k in ("_plan", "_packed", "_packed_sig", "_device", "_pm", "_init_epoch", "_tensors_cache", "_grad_layout",
-                  "_grad_ptr_offs", "last_flat_grad", "grad_ready_hook"):
+                  "_grad_ptr_offs", "last_flat_grad", "grad_ready_hook", "_anchor"):
             st[k] = None
         st["_ws"] = {}
         return st
@@ -394,6 +394,14 @@ class FlowEngine:
                                               self._stream()), "forward_train")
         self.launches = L.ipoke_inn_last_launch_count(self._plan)
         return z, ld, outs, lds, saved, x2, c2
+
+    def grad_anchor(self, device):
+        """A 1-element leaf that requires grad: the autograd input standing in for the parameters in flat_grads_only mode."""
+        a = getattr(self, "_anchor", None)
+        if a is None or a.device != device:
+            a = torch.zeros(1, device=device, requires_grad=True)
+            self._anchor = a
+        return a
 
     # ------------------------------------------------------------------ packed-master training (sharded optimizer)
     def _pm_valid(self, tensors=None):
