@@ -1,0 +1,169 @@
+"""GPU parity of the MaCow unit (row N3, first slice): the CUDA kernels behind include/ipoke_macow.h, called through the
+drop-in module, against the reference fixtures (tests/golden/macow_*.npz, generated from the live reference) and the
+float64 oracle (oracle/macow_oracle.py) on seeded inputs.
+
+Tolerance: the reference computes this path in float32; the kernel is float32 with a different summation order, so
+results agree to a few float32 ulps of the tensor's scale: max |a - b| / max |b| <= 2e-5 forward, 2e-4 through the
+sequential inverse (which chains H + W dependent affine inversions per flow pair)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import ipoke_inn_b200 as P
+from ipoke_inn_b200 import macow
+from oracle import macow_oracle as mo
+from conftest import max_rel
+from test_macow_emulation import random_unit
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+TOL_FWD, TOL_REV, TOL_LD = 2e-5, 2e-4, 3e-5
+
+
+def load(name):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    sd = {k[4:]: g[k] for k in g.files if k.startswith("sd::")}
+    C, k0, k1 = (int(v) for v in g["meta"][:3])
+    return g, sd, C, [k0, k1], str(g["activation"]), float(g["alpha"])
+
+
+def make_unit(sd, C, ks, act, alpha, dev):
+    unit = macow.MaCowUnit(C, ks, activation=act, alpha=alpha)
+    unit.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()})
+    return unit.to(dev).eval()
+
+
+@pytest.mark.parametrize("name", ["macow_elu", "macow_relu", "macow_lrelu"])
+def test_reference_fixtures(name):
+    dev = torch.device("cuda:0")
+    g, sd, C, ks, act, alpha = load(name)
+    unit = make_unit(sd, C, ks, act, alpha, dev)
+    with torch.no_grad():
+        out, ld = unit(torch.from_numpy(g["x"]).to(dev))
+        x_rec = unit(out, reverse=True)
+        x_smp = unit(torch.from_numpy(g["z_in"]).to(dev), reverse=True)
+    assert max_rel(out.cpu().numpy(), g["out64"]) <= TOL_FWD
+    assert max_rel(out.cpu().numpy(), g["out"]) <= TOL_FWD
+    assert max_rel(ld.cpu().numpy(), g["logdet64"]) <= TOL_LD
+    assert max_rel(x_smp.cpu().numpy(), g["x_smp"]) <= TOL_REV
+    assert max_rel(x_rec.cpu().numpy(), g["x"]) <= TOL_REV
+
+
+def test_first_call_initialisation_matches_reference():
+    """A freshly constructed unit (same seed as the fixture generator) run on the fixture's batch must end with the
+    reference's data-dependent ActNorm2dFlow parameters and zeroed 1x1 gains (macow2.py:503-541, macow_utils.py:247-250)."""
+    dev = torch.device("cuda:0")
+    g, sd, C, ks, act, alpha = load("macow_elu")
+    torch.manual_seed(42)
+    unit = macow.MaCowUnit(C, ks, activation=act, alpha=alpha).to(dev)
+    with torch.no_grad():
+        out, ld = unit(torch.from_numpy(g["x"]).to(dev))
+    new = {k: v.cpu().numpy() for k, v in unit.state_dict().items()}
+    for k in ("actnorm1.log_scale", "actnorm1.bias", "actnorm2.log_scale", "actnorm2.bias"):
+        np.testing.assert_allclose(new[k], sd[k], rtol=1e-4, atol=2e-5, err_msg=k)
+    for k, v in new.items():
+        if k.endswith("initialized"):
+            assert int(v) == 1, k
+        if k.endswith("weight_g"):
+            assert not v.any(), k
+    # with zero gains every masked flow is the identity: the output is the two ActNorms of x, normalised per channel
+    flat = out.transpose(0, 1).reshape(C, -1)
+    assert flat.mean(1).abs().max().item() < 1e-5 and (flat.std(1) - 1).abs().max().item() < 1e-4
+    want = mo.unit_forward(new, g["x"], act, alpha)
+    assert max_rel(out.cpu().numpy(), want[0]) <= TOL_FWD and max_rel(ld.cpu().numpy(), want[1]) <= TOL_LD
+
+
+SHAPES = [  # C, kernel, H, W, batch, activation
+    (32, [2, 3], 8, 8, 37, "elu"),          # config/second_stage.yaml: z_dim 32 latents at 8 x 8, kernel [2, 3], elu
+    (16, [2, 3], 16, 16, 9, "elu"),         # 16 x 16 latents (models/second_stage_video.py:142)
+    (8, [3, 5], 5, 7, 5, "leaky_relu"),     # non-square, wider kernel
+    (30, [2, 3], 8, 8, 4, "relu"),          # a later scale of the multi-scale stack: 32 - 2 channels, hidden 120
+    (3, [1, 1], 4, 9, 3, "relu"),
+]
+
+
+@pytest.mark.parametrize("C,ks,H,W,B,act", SHAPES)
+def test_against_float64_oracle(C, ks, H, W, B, act, monkeypatch):
+    dev = torch.device("cuda:0")
+    rng = np.random.default_rng(100 + C)
+    sd, _ = random_unit(rng, C, ks[0], ks[1])
+    for n in ("conv1", "conv2", "conv3", "conv4"):
+        sd[n + ".net.conv1x1.initialized"] = np.array(1, dtype=np.uint8)
+    sd["actnorm1.initialized"] = sd["actnorm2.initialized"] = np.array(1, dtype=np.uint8)
+    unit = make_unit(sd, C, ks, act, 0.9, dev)
+    x = rng.standard_normal((B, C, H, W)).astype(np.float32)
+    z = rng.standard_normal((B, C, H, W)).astype(np.float32)
+    want, want_ld = mo.unit_forward(sd, x, act, 0.9)
+    want_rev = mo.unit_reverse(sd, z, act, 0.9)
+    outs = []
+    for hid_kb in ("48", "3", "1"):                       # whole-image hidden tile, a few lines, one line per tile
+        monkeypatch.setenv("IPOKE_MACOW_HID_KB", hid_kb)
+        with torch.no_grad():
+            out, ld = unit(torch.from_numpy(x).to(dev))
+        assert max_rel(out.cpu().numpy(), want) <= TOL_FWD, hid_kb
+        assert max_rel(ld.cpu().numpy(), want_ld) <= TOL_LD, hid_kb
+        outs.append(out)
+    for threads in ("64", "256"):
+        monkeypatch.setenv("IPOKE_MACOW_THREADS", threads)
+        with torch.no_grad():
+            got = unit(torch.from_numpy(z).to(dev), reverse=True)
+            back = unit(outs[0], reverse=True)
+        assert max_rel(got.cpu().numpy(), want_rev) <= TOL_REV, threads
+        assert max_rel(back.cpu().numpy(), x) <= TOL_REV, threads
+    # deterministic: same launch geometry twice -> identical bits
+    with torch.no_grad():
+        a = unit(torch.from_numpy(x).to(dev))
+        b = unit(torch.from_numpy(x).to(dev))
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+
+
+def test_stage_ranges_alias_and_accumulate():
+    dev = torch.device("cuda:0")
+    g, sd, C, ks, act, alpha = load("macow_relu")
+    unit = make_unit(sd, C, ks, act, alpha, dev)
+    x = torch.from_numpy(g["x"]).to(dev)
+    with torch.no_grad():
+        o1, l1 = unit._forward_stages(x, 0, 1)
+        assert max_rel(o1.cpu().numpy(), g["mcf1_out"]) <= TOL_FWD and max_rel(l1.cpu().numpy(), g["mcf1_logdet"]) <= TOL_LD
+        o3, l3 = unit._forward_stages(x, 3, 4)
+        assert max_rel(o3.cpu().numpy(), g["mcf3_out"]) <= TOL_FWD and max_rel(l3.cpu().numpy(), g["mcf3_logdet"]) <= TOL_LD
+        # stage by stage with logdet accumulation == one launch
+        out, ld = x, None
+        for s in range(6):
+            out, ld = unit._forward_stages(out, s, s + 1, ld)
+        full, full_ld = unit(x)
+        assert max_rel(out.cpu().numpy(), full.cpu().numpy()) <= 1e-6
+        assert max_rel(ld.cpu().numpy(), full_ld.cpu().numpy()) <= 1e-5
+        # in place through the C ABI (out may alias x)
+        import ctypes
+        buf = x.clone()
+        P._capi.check(macow._lib().ipoke_macow_forward(ctypes.byref(unit._desc), unit.packed().data_ptr(), 1,
+                                                        buf.data_ptr(), buf.data_ptr(), None, 0, x.shape[0], x.shape[2],
+                                                        x.shape[3], 0, 6, None))
+        torch.cuda.synchronize()
+        assert torch.equal(buf, full)
+
+
+def test_parameter_update_is_picked_up_and_large_batch_round_trip():
+    dev = torch.device("cuda:0")
+    g, sd, C, ks, act, alpha = load("macow_elu")
+    unit = make_unit(sd, C, ks, act, alpha, dev)
+    x = torch.from_numpy(g["x"]).to(dev)
+    with torch.no_grad():
+        a, _ = unit(x)
+        unit.conv2.net.conv1x1.conv.bias.add_(0.25)               # in-place update bumps the version -> repack
+        b, _ = unit(x)
+    sd2 = {k: v.cpu().numpy() for k, v in unit.state_dict().items()}
+    assert not torch.equal(a, b)
+    assert max_rel(b.cpu().numpy(), mo.unit_forward(sd2, g["x"], act, alpha)[0]) <= TOL_FWD
+    # 4096 samples: every SM several CTAs deep; forward then inverse returns the input
+    big = torch.randn(4096, C, 6, 6, device=dev)
+    with torch.no_grad():
+        z, ld = unit(big)
+        back = unit(z, reverse=True)
+    assert torch.isfinite(ld).all()
+    assert max_rel(back.cpu().numpy(), big.cpu().numpy()) <= TOL_REV
+    with pytest.raises(NotImplementedError):
+        unit(big.requires_grad_())                                 # inference only

@@ -1,0 +1,82 @@
+"""CPU checks of the MaCow drop-in module (ipoke-main-opticalflow_b200/macow.py): state_dict keys and shapes, RNG draw
+order, the exported C ABI (include/ipoke_macow.h), argument errors.  No compute without a GPU."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+import ipoke_inn_b200 as P
+from ipoke_inn_b200 import _capi, macow
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def golden(name):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    C, k0, k1, B, H, W = (int(v) for v in g["meta"])
+    return g, dict(C=C, k=[k0, k1], B=B, H=H, W=W, act=str(g["activation"]), alpha=float(g["alpha"]))
+
+
+@pytest.mark.parametrize("name", ["macow_elu", "macow_relu", "macow_lrelu"])
+def test_state_dict_keys_shapes_and_rng_order(name):
+    g, m = golden(name)
+    torch.manual_seed(42)                                       # the seed tests/golden/make_macow_golden.py used
+    unit = macow.MaCowUnit(m["C"], m["k"], activation=m["act"], alpha=m["alpha"])
+    ref_keys = [k[4:] for k in g.files if k.startswith("sd::")]
+    sd = unit.state_dict()
+    assert list(sd.keys()) == ref_keys
+    for k in ref_keys:
+        assert tuple(sd[k].shape) == g["sd::" + k].shape, k
+        assert sd[k].numpy().dtype == g["sd::" + k].dtype, k
+        # tensors the reference's first forward / the fixture generator did not overwrite: identical draws
+        if k.endswith("shift_conv.weight") or k.endswith("weight_v"):
+            assert np.array_equal(sd[k].numpy(), g["sd::" + k]), k
+    # a fresh weight-norm gain is ||v|| (nn.utils.weight_norm), so the fresh 1x1 weight equals v
+    v = sd["conv1.net.conv1x1.conv.weight_v"]
+    np.testing.assert_allclose(sd["conv1.net.conv1x1.conv.weight_g"].flatten(), v.flatten(1).norm(dim=1), rtol=1e-6)
+    unit.load_state_dict({k: torch.from_numpy(g["sd::" + k]) for k in ref_keys})      # strict
+
+
+def test_header_symbols_are_exported():
+    hdr = open(os.path.join(ROOT, "include", "ipoke_macow.h")).read()
+    names = sorted(set(re.findall(r"\b(ipoke_macow_[a-z_]+)\s*\(", hdr)))
+    assert names == ["ipoke_macow_forward", "ipoke_macow_launch_info", "ipoke_macow_pack_unit", "ipoke_macow_reverse",
+                     "ipoke_macow_unit_floats"]
+    L = _capi.lib()
+    for n in names:
+        assert hasattr(L, n), n
+
+
+def test_unit_floats_and_launch_geometry_without_gpu():
+    L = macow._lib()
+    d = macow.MacowDesc(16, 64, 2, 3, 1, 1.0)
+    per_flow = 16 * 2 * 3 * 64 + 64 * 32 + 32
+    assert L.ipoke_macow_unit_floats(ctypes.byref(d)) == 4 * per_flow + 4 * 16
+    smem, thr, tile = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    assert L.ipoke_macow_launch_info(ctypes.byref(d), 8, 8, 1, ctypes.byref(smem), ctypes.byref(thr), ctypes.byref(tile)) == 0
+    assert tile.value == 1 and smem.value == (16 * 64 + 8 * 64) * 4 and thr.value % 32 == 0
+    assert L.ipoke_macow_launch_info(ctypes.byref(d), 8, 8, 0, ctypes.byref(smem), ctypes.byref(thr), ctypes.byref(tile)) == 0
+    assert tile.value == 8                                      # the whole 8 x 8 image's hidden tile fits the budget
+    bad = macow.MacowDesc(16, 64, 2, 4, 1, 1.0)                 # even centred kernel: the reference asserts
+    assert L.ipoke_macow_unit_floats(ctypes.byref(bad)) == 0
+    huge = macow.MacowDesc(512, 512, 2, 3, 1, 1.0)              # 512 x 32 x 32 floats do not fit one SM
+    assert L.ipoke_macow_launch_info(ctypes.byref(huge), 32, 32, 1, None, None, None) == -2
+
+
+def test_unbuilt_variants_and_cpu_tensors_fail_loudly():
+    with pytest.raises(NotImplementedError):
+        macow.MaCowUnit(4, [2, 3], h_channels=8)
+    with pytest.raises(NotImplementedError):
+        macow.MaCowUnit(4, [2, 3], transform="nlsq")
+    with pytest.raises(NotImplementedError):
+        macow.MaCowUnit(4, [2, 3], p_dropout=0.1)
+    with pytest.raises(AssertionError):
+        macow.MaCowUnit(4, [2, 2])                               # even width: ShiftedConv2d's own assert
+    unit = macow.MaCowUnit(4, [2, 3])
+    with torch.no_grad(), pytest.raises(RuntimeError, match="CUDA"):
+        unit(torch.randn(2, 4, 6, 6))
+    assert "MaCowUnit" in P.__all__

@@ -66,3 +66,16 @@ def test_actnorm_init_matches_reference_state():
     flat = y.transpose(1, 0, 2, 3).reshape(4, -1)
     np.testing.assert_allclose(flat.mean(1), 0, atol=1e-12)
     np.testing.assert_allclose(flat.std(1, ddof=1), 1, atol=2e-6)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_torch_restatement_is_the_reference(name):
+    """oracle/macow_oracle_torch.py (the op-for-op eager baseline tools/macow_bench.py times) on the fixtures."""
+    import torch
+    from oracle.macow_oracle_torch import TorchUnit
+    g, sd, act, alpha = load(name)
+    unit = TorchUnit(sd, act, alpha)
+    out, ld = unit.forward(torch.from_numpy(g["x"]))
+    np.testing.assert_allclose(out.numpy(), g["out"], rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(ld.numpy(), g["logdet"], rtol=1e-6, atol=1e-5)
+    np.testing.assert_allclose(unit.reverse(torch.from_numpy(g["z_in"])).numpy(), g["x_smp"], rtol=1e-5, atol=1e-5)
