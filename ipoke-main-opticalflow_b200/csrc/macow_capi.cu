@@ -13,6 +13,8 @@ constexpr int kMaxSmem = 227 * 1024;
 
 struct Geometry {
   int threads, tile_lines, smem_bytes;
+  int qc;         // pixels per phase-1 work item: 8 when a line has more than 4 pixels
+  int carveout;   // preferred shared-memory carve-out in percent, -1 = driver default
 };
 
 int check_desc(const ipoke_macow_desc* d) {
@@ -39,17 +41,25 @@ int geometry(const ipoke_macow_desc* d, int H, int W, bool reverse, Geometry* g)
   }
   const long long smem = (img + tile * line) * 4;
   if (smem > kMaxSmem) return IPOKE_INN_E_UNSUPPORTED;                   // image + one hidden line must fit one SM
+  g->qc = std::max(H, W) > 4 ? 8 : 4;
+  if (const char* e = std::getenv("IPOKE_MACOW_QC")) g->qc = std::atoi(e) == 8 ? 8 : 4;
+  g->carveout = -1;
+  if (const char* e = std::getenv("IPOKE_MACOW_CARVEOUT")) g->carveout = std::min(100, std::max(-1, std::atoi(e)));
   g->threads = threads;
   g->tile_lines = tile;
   g->smem_bytes = (int)smem;
   return IPOKE_INN_OK;
 }
 
-template <int kAct, bool kReverse, int kK1>
+template <bool kReverse, int kK1, int kQC>
 int launch_t(const macow::UnitParams& p, const Geometry& g, cudaStream_t s) {
-  auto kern = macow::macow_unit_kernel<kAct, kReverse, kK1>;
+  auto kern = macow::macow_unit_kernel<kReverse, kK1, kQC>;
   if (g.smem_bytes > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, g.smem_bytes);
+    if (e != cudaSuccess) return (int)e;
+  }
+  if (g.carveout >= 0) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, g.carveout);
     if (e != cudaSuccess) return (int)e;
   }
   kern<<<p.B, g.threads, g.smem_bytes, s>>>(p);
@@ -57,20 +67,16 @@ int launch_t(const macow::UnitParams& p, const Geometry& g, cudaStream_t s) {
 }
 
 template <bool kReverse, int kK1>
-int launch_a(int act, const macow::UnitParams& p, const Geometry& g, cudaStream_t s) {
-  switch (act) {
-    case IPOKE_MACOW_ACT_RELU: return launch_t<macow::ACT_RELU, kReverse, kK1>(p, g, s);
-    case IPOKE_MACOW_ACT_ELU: return launch_t<macow::ACT_ELU, kReverse, kK1>(p, g, s);
-    default: return launch_t<macow::ACT_LEAKY, kReverse, kK1>(p, g, s);
-  }
+int launch_q(const macow::UnitParams& p, const Geometry& g, cudaStream_t s) {
+  return g.qc == 8 ? launch_t<kReverse, kK1, 8>(p, g, s) : launch_t<kReverse, kK1, 4>(p, g, s);
 }
 
 template <bool kReverse>
 int launch(const ipoke_macow_desc* d, const macow::UnitParams& p, const Geometry& g, cudaStream_t s) {
   switch (d->k1) {
-    case 1: return launch_a<kReverse, 1>(d->activation, p, g, s);
-    case 3: return launch_a<kReverse, 3>(d->activation, p, g, s);
-    default: return launch_a<kReverse, 5>(d->activation, p, g, s);
+    case 1: return launch_q<kReverse, 1>(p, g, s);
+    case 3: return launch_q<kReverse, 3>(p, g, s);
+    default: return launch_q<kReverse, 5>(p, g, s);
   }
 }
 
@@ -92,6 +98,7 @@ int run(const ipoke_macow_desc* d, const float* packed, int n_units, const float
   p.stage_begin = s0; p.stage_end = s1;
   p.tile_lines = g.tile_lines;
   p.accumulate = accumulate;
+  p.act = d->activation;
   p.unit_floats = macow::unit_floats(d->C, d->hidden, d->k0, d->k1);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   return reverse ? launch<true>(d, p, g, s) : launch<false>(d, p, g, s);

@@ -30,7 +30,6 @@
 
 namespace macow {
 
-constexpr int kQC = 4;        // pixels along the line per phase-1 work item
 enum Act { ACT_RELU = 0, ACT_ELU = 1, ACT_LEAKY = 2 };
 
 struct UnitParams {
@@ -43,6 +42,7 @@ struct UnitParams {
   int stage_begin, stage_end;   // global stage range [begin, end) over n_units * 6, forward order
   int tile_lines;               // lines per forward tile (the inverse always steps one line)
   int accumulate;               // logdet += instead of =
+  int act;                      // Act
   long long unit_floats;
 };
 
@@ -53,15 +53,15 @@ __host__ __device__ inline long long unit_floats(int C, int Hd, int k0, int k1) 
   return 4 * flow_floats(C, Hd, k0, k1) + 4 * C;
 }
 
-template <int kAct>
-__device__ __forceinline__ float activate(float h) {
-  if (kAct == ACT_RELU) return fmaxf(h, 0.f);
-  if (kAct == ACT_ELU) return h > 0.f ? h : expm1f(h);
+__device__ __forceinline__ float activate(float h, int act) {
+  if (act == ACT_RELU) return fmaxf(h, 0.f);
+  if (act == ACT_ELU) return h > 0.f ? h : expm1f(h);
   return h > 0.f ? h : 0.1f * h;
 }
 
 // One masked-convolution flow over the image in shared memory, in place.
-template <int kAct, bool kReverse, int kK1>
+// kQC = pixels along the line per phase-1 work item (one thread: one hidden channel, kQC pixels, all taps).
+template <bool kReverse, int kK1, int kQC>
 __device__ __forceinline__ void mcf_stage(float* __restrict__ X, float* __restrict__ hid, const float* __restrict__ fw,
                                           const UnitParams& p, int flow, float& logdet_acc) {
   const int C = p.C, Hd = p.Hd, H = p.H, W = p.W, k0 = p.k0, HW = H * W;
@@ -115,7 +115,7 @@ __device__ __forceinline__ void mcf_stage(float* __restrict__ X, float* __restri
       }
 #pragma unroll
       for (int i = 0; i < kQC; ++i)
-        if (q0 + i < Q) hid[(long long)(t * Q + q0 + i) * Hd + j] = activate<kAct>(acc[i]);
+        if (q0 + i < Q) hid[(long long)(t * Q + q0 + i) * Hd + j] = activate(acc[i], p.act);
     }
     __syncthreads();
     // ---- phase 2: mu / log_scale per (channel, pixel) and the affine map, in place
@@ -170,7 +170,7 @@ __device__ __forceinline__ void actnorm_stage(float* __restrict__ X, const float
 
 // grid = B, dynamic smem = (C H W + hidden tile) floats.  Hd must be a multiple of 4 (float4 reads of hid);
 // kK1 = kernel_size[1], the centred taps along the line (odd; the reference's configs use 3).
-template <int kAct, bool kReverse, int kK1>
+template <bool kReverse, int kK1, int kQC>
 __global__ void __launch_bounds__(256) macow_unit_kernel(const UnitParams p) {
   extern __shared__ __align__(16) float smem[];
   const int n = p.C * p.H * p.W;
@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(256) macow_unit_kernel(const UnitParams p) {
       actnorm_stage<kReverse>(X, up + 4 * ff + (st == 5 ? 2 * p.C : 0), p, logdet_acc);
     } else {
       const int flow = st < 2 ? st : st - 1;
-      mcf_stage<kAct, kReverse, kK1>(X, hid, up + flow * ff, p, flow, logdet_acc);
+      mcf_stage<kReverse, kK1, kQC>(X, hid, up + flow * ff, p, flow, logdet_acc);
     }
   }
   float* dst = p.out + (long long)b * n;

@@ -28,13 +28,13 @@ namespace macow { alignas(16) float smem[1 << 20]; }
 
 #include "../../ipoke-main-opticalflow_b200/csrc/macow_kernel.cuh"
 
-template <int kAct, bool kRev>
+template <bool kRev, int kQC>
 static void run_k1(int k1, const macow::UnitParams& p) {
   for (unsigned b = 0; b < (unsigned)p.B; ++b) {
     blockIdx.x = b;
-    if (k1 == 1) macow::macow_unit_kernel<kAct, kRev, 1>(p);
-    else if (k1 == 3) macow::macow_unit_kernel<kAct, kRev, 3>(p);
-    else macow::macow_unit_kernel<kAct, kRev, 5>(p);
+    if (k1 == 1) macow::macow_unit_kernel<kRev, 1, kQC>(p);
+    else if (k1 == 3) macow::macow_unit_kernel<kRev, 3, kQC>(p);
+    else macow::macow_unit_kernel<kRev, 5, kQC>(p);
   }
 }
 
@@ -52,17 +52,18 @@ void emul_pack(const float* const* params, float* packed, int C, int Hd, int k0,
 
 void emul_run(const float* packed, int n_units, const float* in, float* out, float* logdet, int accumulate, int B,
               int C, int Hd, int H, int W, int k0, int k1, int act, float alpha, int s0, int s1, int tile_lines,
-              int reverse) {
+              int reverse, int qc) {
   macow::UnitParams p;
   p.packed = packed; p.in = in; p.out = out; p.logdet = logdet;
   p.B = B; p.C = C; p.Hd = Hd; p.H = H; p.W = W; p.k0 = k0; p.k1 = k1; p.alpha = alpha;
   p.stage_begin = s0; p.stage_end = s1; p.tile_lines = tile_lines; p.accumulate = accumulate;
   p.unit_floats = macow::unit_floats(C, Hd, k0, k1);
   blockDim.x = 1; gridDim.x = B; threadIdx.x = 0;
+  p.act = act;
   if (reverse) {
-    if (act == 0) run_k1<0, true>(k1, p); else if (act == 1) run_k1<1, true>(k1, p); else run_k1<2, true>(k1, p);
+    if (qc == 8) run_k1<true, 8>(k1, p); else run_k1<true, 4>(k1, p);
   } else {
-    if (act == 0) run_k1<0, false>(k1, p); else if (act == 1) run_k1<1, false>(k1, p); else run_k1<2, false>(k1, p);
+    if (qc == 8) run_k1<false, 8>(k1, p); else run_k1<false, 4>(k1, p);
   }
 }
 }

@@ -43,7 +43,7 @@ def pack(L, sd, C, Hd, k0, k1):
     return packed
 
 
-def run(L, packed, x, meta, s0, s1, reverse, tile=1, n_units=1, logdet0=None):
+def run(L, packed, x, meta, s0, s1, reverse, tile=1, n_units=1, logdet0=None, qc=4):
     C, Hd, k0, k1, act, alpha = meta
     x = np.ascontiguousarray(x, dtype=np.float32)
     B, _, H, W = x.shape
@@ -51,7 +51,7 @@ def run(L, packed, x, meta, s0, s1, reverse, tile=1, n_units=1, logdet0=None):
     ld = np.zeros(B, dtype=np.float32) if logdet0 is None else logdet0.astype(np.float32).copy()
     L.emul_run(packed.ctypes.data_as(ctypes.c_void_p), n_units, x.ctypes.data_as(ctypes.c_void_p),
                out.ctypes.data_as(ctypes.c_void_p), ld.ctypes.data_as(ctypes.c_void_p), int(logdet0 is not None), B,
-               C, Hd, H, W, k0, k1, ACT[act], ctypes.c_float(alpha), s0, s1, tile, int(reverse))
+               C, Hd, H, W, k0, k1, ACT[act], ctypes.c_float(alpha), s0, s1, tile, int(reverse), qc)
     return out, ld
 
 
@@ -68,11 +68,12 @@ def test_emulated_kernel_matches_reference_fixtures(emul, name):
     g, sd, meta = load(name)
     packed = pack(emul, sd, *meta[:4])
     for tile in (1, 2, 3, 64):                                   # forward tiling must not change the result
-        out, ld = run(emul, packed, g["x"], meta, 0, 6, False, tile=tile)
+        out, ld = run(emul, packed, g["x"], meta, 0, 6, False, tile=tile, qc=8 if tile == 2 else 4)
         np.testing.assert_allclose(out, g["out64"], rtol=2e-5, atol=2e-5)
         np.testing.assert_allclose(ld, g["logdet64"], rtol=2e-5, atol=3e-4)
-    x_smp, _ = run(emul, packed, g["z_in"], meta, 0, 6, True)
-    np.testing.assert_allclose(x_smp, g["x_smp"], rtol=1e-4, atol=1e-4)
+    for qc in (4, 8):
+        x_smp, _ = run(emul, packed, g["z_in"], meta, 0, 6, True, qc=qc)
+        np.testing.assert_allclose(x_smp, g["x_smp"], rtol=1e-4, atol=1e-4)
     x_rec, _ = run(emul, packed, g["out"], meta, 0, 6, True)
     np.testing.assert_allclose(x_rec, g["x"], rtol=1e-4, atol=1e-4)
 
@@ -122,7 +123,7 @@ def test_emulated_two_unit_chain_other_kernels(emul, C, k0, k1, H, W, act):
     x = rng.standard_normal((2, C, H, W)).astype(np.float32)
     m, ld0 = mo.unit_forward(sd0, x, act, 0.8)
     want, ld1 = mo.unit_forward(sd1, m, act, 0.8)
-    out, ld = run(emul, packed, x, meta, 0, 12, False, tile=3, n_units=2)
+    out, ld = run(emul, packed, x, meta, 0, 12, False, tile=3, n_units=2, qc=8)
     np.testing.assert_allclose(out, want, rtol=3e-5, atol=3e-5)
     np.testing.assert_allclose(ld, ld0 + ld1, rtol=3e-5, atol=3e-4)
     back, _ = run(emul, packed, out, meta, 0, 12, True, n_units=2)
