@@ -66,7 +66,8 @@ int ipoke_macow_forward(const ipoke_macow_desc* desc, const float* packed, int n
 int ipoke_macow_reverse(const ipoke_macow_desc* desc, const float* packed, int n_units, const float* z, float* out,
                         int B, int H, int W, int stage_begin, int stage_end, void* stream);
 
-/* Dynamic shared memory (bytes) and threads per CTA the two calls above would launch with, for reporting. */
+/* Dynamic shared memory (bytes) and threads per CTA the two calls above would launch with (for batches below 2048;
+ * the inverse uses half the threads from there on), for reporting. */
 int ipoke_macow_launch_info(const ipoke_macow_desc* desc, int H, int W, int reverse, int* smem_bytes, int* threads,
                             int* tile_lines);
 

@@ -25,9 +25,11 @@ int check_desc(const ipoke_macow_desc* d) {
   return IPOKE_INN_OK;
 }
 
-int geometry(const ipoke_macow_desc* d, int H, int W, bool reverse, Geometry* g) {
+int geometry(const ipoke_macow_desc* d, int B, int H, int W, bool reverse, Geometry* g) {
   if (H < 1 || W < 1) return IPOKE_INN_E_INVALID;
-  int threads = 128;
+  // measured on B200 (profiles/r02_macow_bench.txt): 256 threads per CTA win while a CTA's latency is what is timed;
+  // the inverse at thousands of samples prefers more, smaller CTAs per SM
+  int threads = (reverse && B >= 2048) ? 128 : 256;
   if (const char* e = std::getenv("IPOKE_MACOW_THREADS")) threads = std::atoi(e);
   threads = std::min(256, std::max(32, threads)) & ~31;
   int hid_kb = 48;                                                     // forward: hidden tile budget
@@ -87,7 +89,7 @@ int run(const ipoke_macow_desc* d, const float* packed, int n_units, const float
   if (s0 < 0 || s1 > n_units * IPOKE_MACOW_STAGES_PER_UNIT || s0 > s1) return IPOKE_INN_E_INVALID;
   if (B == 0) return IPOKE_INN_OK;
   Geometry g;
-  if (int e = geometry(d, H, W, reverse, &g)) return e;
+  if (int e = geometry(d, B, H, W, reverse, &g)) return e;
   macow::UnitParams p;
   p.packed = packed;
   p.in = in;
@@ -142,7 +144,7 @@ int ipoke_macow_launch_info(const ipoke_macow_desc* d, int H, int W, int reverse
                             int* tile_lines) {
   if (int e = check_desc(d)) return e;
   Geometry g;
-  if (int e = geometry(d, H, W, reverse != 0, &g)) return e;
+  if (int e = geometry(d, 1, H, W, reverse != 0, &g)) return e;
   if (smem_bytes) *smem_bytes = g.smem_bytes;
   if (threads) *threads = g.threads;
   if (tile_lines) *tile_lines = g.tile_lines;

@@ -68,9 +68,9 @@ def test_first_call_initialisation_matches_reference():
             assert int(v) == 1, k
         if k.endswith("weight_g"):
             assert not v.any(), k
-    # with zero gains every masked flow is the identity: the output is the two ActNorms of x, normalised per channel
-    flat = out.transpose(0, 1).reshape(C, -1)
-    assert flat.mean(1).abs().max().item() < 1e-5 and (flat.std(1) - 1).abs().max().item() < 1e-4
+    # with zero gains every masked flow is the identity and the output is the two ActNorms of x.  It is NOT exactly
+    # normalised: the reference takes its statistics of data * exp(log_scale) + bias with the constructor's random
+    # log_scale (macow2.py:531) and then overwrites log_scale -- the fixture comparison above pins that quirk.
     want = mo.unit_forward(new, g["x"], act, alpha)
     assert max_rel(out.cpu().numpy(), want[0]) <= TOL_FWD and max_rel(ld.cpu().numpy(), want[1]) <= TOL_LD
 
