@@ -28,14 +28,15 @@
 extern "C" {
 #endif
 
-#define IPOKE_INN_VERSION 110 /* major*100 + minor */
+#define IPOKE_INN_VERSION 111 /* major*100 + minor */
 
 enum {
   IPOKE_INN_OK = 0,
   IPOKE_INN_E_INVALID = -1,     /* bad argument (null pointer, B <= 0, bad block range ...) */
   IPOKE_INN_E_UNSUPPORTED = -2, /* shape outside what the kernels cover (odd C, E > 0 unconditional ...) */
   IPOKE_INN_E_NO_DEVICE = -3,   /* no sm_100 device / driver entry point missing */
-  IPOKE_INN_E_INTERNAL = -4
+  IPOKE_INN_E_INTERNAL = -4,
+  IPOKE_INN_E_TOO_LARGE = -5    /* ipoke_inn_flow_loss_static only: B * C beyond IPOKE_INN_FLOW_LOSS_STATIC_MAX_ELEMS */
 };
 
 enum { IPOKE_INN_PREC_FP32_SPLIT = 0, /* bf16 hi+lo operands, 3 MMAs per k-step: <= 1e-4 vs fp32 */
@@ -176,6 +177,23 @@ int ipoke_inn_flow_loss_ref(const float* z, const float* logdet, const float* re
 int ipoke_inn_flow_loss_scratch_bytes(void);
 int ipoke_inn_flow_loss_ws(const float* z, const float* logdet, const float* ref_sample, int B, int C, float nll_weight,
                            float logdet_weight, float* out4, float* dz, float* dlogdet, void* scratch, void* stream);
+
+/* The same loss for callers that must not allocate device memory (code under CUDA graph capture, serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Arguments as ipoke_inn_flow_loss_ws minus `scratch`: the fp64 partial sums live in a file-scope __device__ array
+ * inside the library (6400 bytes per GPU that loads the library, held until the process exits), so the call performs
+ * no cudaMalloc / cudaFree and calls no allocating routine; the caller still passes every input and output.
+ * Limit: B * C <= IPOKE_INN_FLOW_LOSS_STATIC_MAX_ELEMS (256 CTAs x 65536 elements); larger sizes return
+ * IPOKE_INN_E_TOO_LARGE and launch nothing.  The array is shared by every call on that GPU and keeps the last call's
+ * contents (the ticket word is cleared on `stream` before each launch): calls that overlap on one GPU -- two streams,
+ * two host threads -- race on it; serialise them.  The first call on each device resolves the array's device address
+ * (cudaGetSymbolAddress, with that device current): make it before starting a graph capture.
+ * Results agree with ipoke_inn_flow_loss_ws to fp64-summation-order accuracy (not bitwise: the CTA count differs). */
+#define IPOKE_INN_FLOW_LOSS_STATIC_MAX_BLOCKS 256
+#define IPOKE_INN_FLOW_LOSS_STATIC_MAX_ELEMS 16777216LL
+int ipoke_inn_flow_loss_static(const float* z, const float* logdet, const float* ref_sample, int B, int C,
+                               float nll_weight, float logdet_weight, float* out4, float* dz, float* dlogdet,
+                               void* stream);
 
 /* Fused Adam / AMSGrad step over all parameter tensors in one launch -- replaces the reference's
  * torch.optim.Adam(lr, betas, weight_decay, amsgrad=True).step() (models/second_stage_video_fc.py:685-687;

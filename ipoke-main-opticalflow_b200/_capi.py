@@ -21,7 +21,7 @@ SYMBOLS = [
     "ipoke_inn_adam_chunk_elems", "ipoke_inn_adam_step", "ipoke_inn_reverse_draws", "ipoke_inn_forward_draws",
     "ipoke_inn_param_layout", "ipoke_inn_pack_small", "ipoke_inn_adam_shard_step", "ipoke_inn_master_to_packed",
     "ipoke_inn_grad_to_bf16", "ipoke_inn_flow_loss_ref", "ipoke_inn_flow_loss_ws",
-    "ipoke_inn_flow_loss_scratch_bytes",
+    "ipoke_inn_flow_loss_scratch_bytes", "ipoke_inn_flow_loss_static",
 ]
 
 
@@ -109,6 +109,8 @@ def lib():
     L.ipoke_inn_flow_loss_ws.argtypes = [vp, vp, vp, i32, i32, f32, f32, vp, vp, vp, vp, vp]
     L.ipoke_inn_flow_loss_ref.restype = i32
     L.ipoke_inn_flow_loss_ref.argtypes = [vp, vp, vp, i32, i32, f32, f32, vp, vp, vp, vp]
+    L.ipoke_inn_flow_loss_static.restype = i32
+    L.ipoke_inn_flow_loss_static.argtypes = [vp, vp, vp, i32, i32, f32, f32, vp, vp, vp, vp]
     L.ipoke_inn_param_layout.restype = i32
     L.ipoke_inn_param_layout.argtypes = [vp, vp, i32]
     L.ipoke_inn_pack_small.restype = i32

@@ -7,7 +7,8 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libipoke_inn.so")
-SOURCES = [os.path.join(CSRC, "inn_capi.cu"), os.path.join(CSRC, "macow_capi.cu")]
+SOURCES = [os.path.join(CSRC, "inn_capi.cu"), os.path.join(CSRC, "macow_capi.cu"),
+           os.path.join(CSRC, "noalloc_capi.cu")]
 DEPS = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(ROOT, "include", h) for h in ("ipoke_inn.h", "ipoke_macow.h")]
 
 

@@ -1840,6 +1840,7 @@ const char* ipoke_inn_last_error_string(int code) {
     case IPOKE_INN_E_UNSUPPORTED: return "ipoke_inn: unsupported shape (C must be even and >= 2; H, depth, n_flows >= 1; E == 0 iff unconditional; 0 <= mlp_slope <= 1)";
     case IPOKE_INN_E_NO_DEVICE: return "ipoke_inn: no sm_100 CUDA device / driver entry point unavailable";
     case IPOKE_INN_E_INTERNAL: return "ipoke_inn: internal error (tensor map encode failed)";
+    case IPOKE_INN_E_TOO_LARGE: return "ipoke_inn: B * C exceeds IPOKE_INN_FLOW_LOSS_STATIC_MAX_ELEMS (16777216), the size the library's fixed scratch array covers; use ipoke_inn_flow_loss_ws with caller-provided scratch";
     default: break;
   }
   if (code > 0) return cudaGetErrorString(static_cast<cudaError_t>(code));

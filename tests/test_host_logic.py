@@ -45,7 +45,7 @@ def test_library_exports_every_declared_symbol():
     for sym in sorted(declared):
         assert hasattr(L, sym), f"{sym} declared in include/ipoke_inn.h but not exported"
     assert set(_capi.SYMBOLS) == declared
-    assert _capi.lib().ipoke_inn_version() == 110
+    assert _capi.lib().ipoke_inn_version() == 111
 
 
 def test_plan_layout_without_gpu():
