@@ -42,7 +42,7 @@ typedef struct ipoke_macow_desc {
 } ipoke_macow_desc;
 
 /* Floats of one packed unit (shift weights transposed to [C][k0][k1][hidden], weight-normed 1x1 weights
- * transposed to [hidden][2C], biases, ActNorm log-scales and biases). */
+ * transposed to [hidden][C][2] = (shift, log-scale) pairs, biases likewise, ActNorm log-scales and biases). */
 size_t ipoke_macow_unit_floats(const ipoke_macow_desc* desc);
 
 /* Pack one unit.  `params` is a HOST array of 20 device pointers in the reference's state_dict order of the

@@ -14,6 +14,9 @@ constexpr int kMaxSmem = 227 * 1024;
 struct Geometry {
   int threads, tile_lines, smem_bytes;
   int qc;         // pixels per phase-1 work item: 8 when a line has more than 4 pixels
+  int ksplit;     // inverse: thread groups sharing one line's input-channel loop
+  int hid_floats; // hidden-activation area
+  int wsmem;      // 1: one flow's weights are staged in shared memory
   int carveout;   // preferred shared-memory carve-out in percent, -1 = driver default
 };
 
@@ -27,24 +30,38 @@ int check_desc(const ipoke_macow_desc* d) {
 
 int geometry(const ipoke_macow_desc* d, int B, int H, int W, bool reverse, Geometry* g) {
   if (H < 1 || W < 1) return IPOKE_INN_E_INVALID;
-  // measured on B200 (profiles/r02_macow_bench.txt): 256 threads per CTA win while a CTA's latency is what is timed;
-  // the inverse at thousands of samples prefers more, smaller CTAs per SM
-  int threads = (reverse && B >= 2048) ? 128 : 256;
+  // measured on B200 (profiles/r02_macow_sweep.txt): one CTA per SM with the weights in shared memory; 512 threads up to
+  // 8 x 8 latents, 256 from 16 x 16 on (more work items per thread, fewer barrier stalls)
+  (void)B;
+  int threads = std::max(H, W) > 8 ? 256 : 512;
   if (const char* e = std::getenv("IPOKE_MACOW_THREADS")) threads = std::atoi(e);
-  threads = std::min(256, std::max(32, threads)) & ~31;
+  threads = std::min(512, std::max(32, threads)) & ~31;
   int hid_kb = 48;                                                     // forward: hidden tile budget
   if (const char* e = std::getenv("IPOKE_MACOW_HID_KB")) hid_kb = std::max(1, std::atoi(e));
-  const long long img = ((long long)d->C * H * W + 3) & ~3LL;
+  g->qc = std::max(H, W) > 4 ? 8 : 4;
+  if (const char* e = std::getenv("IPOKE_MACOW_QC")) g->qc = std::atoi(e) == 8 ? 8 : 4;
+  const long long img = 2 * (((long long)d->C * H * W + 3) & ~3LL);      // row-major and column-major copies
   const long long line = (long long)std::max(H, W) * d->hidden;         // hidden floats of one line
-  int tile = 1;
+  int tile = 1, ksplit = 1;
   if (!reverse) {
     tile = (int)std::max(1LL, std::min<long long>(std::max(H, W), (long long)hid_kb * 256 / line));
     while (tile > 1 && (img + tile * line) * 4 > kMaxSmem) --tile;
+  } else {
+    // one line offers hidden * ceil(Q / qc) work items: share the input-channel loop until every thread has one
+    const int items = (d->hidden / 2) * ((std::min(H, W) + g->qc - 1) / g->qc);
+    ksplit = std::max(1, std::min(std::min(4, d->C), threads / std::max(items, 1)));   // 8 groups measured slower than 4
+    if (const char* e = std::getenv("IPOKE_MACOW_KSPLIT")) ksplit = std::max(1, std::min(std::min(8, d->C), std::atoi(e)));
+    while (ksplit > 1 && (img + ksplit * line) * 4 > kMaxSmem) --ksplit;
   }
-  const long long smem = (img + tile * line) * 4;
-  if (smem > kMaxSmem) return IPOKE_INN_E_UNSUPPORTED;                   // image + one hidden line must fit one SM
-  g->qc = std::max(H, W) > 4 ? 8 : 4;
-  if (const char* e = std::getenv("IPOKE_MACOW_QC")) g->qc = std::atoi(e) == 8 ? 8 : 4;
+  const long long hid = ((long long)tile * ksplit * line + 3) & ~3LL;
+  long long smem = (img + hid) * 4;
+  if (smem > kMaxSmem) return IPOKE_INN_E_UNSUPPORTED;                   // two images + one hidden line must fit one SM
+  const long long wfl = (macow::flow_floats(d->C, d->hidden, d->k0, d->k1) + 3) & ~3LL;
+  g->wsmem = smem + wfl * 4 <= kMaxSmem;                                 // the flow's weights fit beside them
+  if (const char* e = std::getenv("IPOKE_MACOW_WSMEM")) g->wsmem = g->wsmem && std::atoi(e) != 0;
+  if (g->wsmem) smem += wfl * 4;
+  g->hid_floats = (int)hid;
+  g->ksplit = ksplit;
   g->carveout = -1;
   if (const char* e = std::getenv("IPOKE_MACOW_CARVEOUT")) g->carveout = std::min(100, std::max(-1, std::atoi(e)));
   g->threads = threads;
@@ -53,10 +70,10 @@ int geometry(const ipoke_macow_desc* d, int B, int H, int W, bool reverse, Geome
   return IPOKE_INN_OK;
 }
 
-template <bool kReverse, int kK1, int kQC>
-int launch_t(const macow::UnitParams& p, const Geometry& g, cudaStream_t s) {
-  auto kern = macow::macow_unit_kernel<kReverse, kK1, kQC>;
-  if (g.smem_bytes > 48 * 1024) {
+template <bool kReverse, int kK1, int kQC, bool kWS>
+int launch_w(const macow::UnitParams& p, const Geometry& g, cudaStream_t s) {
+  auto kern = macow::macow_unit_kernel<kReverse, kK1, kQC, kWS>;
+  if (g.smem_bytes > 32 * 1024) {   // the 48 KB default covers dynamic + static shared memory together
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, g.smem_bytes);
     if (e != cudaSuccess) return (int)e;
   }
@@ -66,6 +83,11 @@ int launch_t(const macow::UnitParams& p, const Geometry& g, cudaStream_t s) {
   }
   kern<<<p.B, g.threads, g.smem_bytes, s>>>(p);
   return (int)cudaGetLastError();
+}
+
+template <bool kReverse, int kK1, int kQC>
+int launch_t(const macow::UnitParams& p, const Geometry& g, cudaStream_t s) {
+  return g.wsmem ? launch_w<kReverse, kK1, kQC, true>(p, g, s) : launch_w<kReverse, kK1, kQC, false>(p, g, s);
 }
 
 template <bool kReverse, int kK1>
@@ -101,6 +123,8 @@ int run(const ipoke_macow_desc* d, const float* packed, int n_units, const float
   p.tile_lines = g.tile_lines;
   p.accumulate = accumulate;
   p.act = d->activation;
+  p.ksplit = g.ksplit;
+  p.hid_floats = g.hid_floats;
   p.unit_floats = macow::unit_floats(d->C, d->hidden, d->k0, d->k1);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   return reverse ? launch<true>(d, p, g, s) : launch<false>(d, p, g, s);

@@ -28,6 +28,12 @@
 #endif
 #include <stdint.h>
 
+#ifdef MACOW_HOST_EMULATION
+#define MACOW_FAST_EXP(v) expf(v)
+#else
+#define MACOW_FAST_EXP(v) __expf(v)
+#endif
+
 namespace macow {
 
 enum Act { ACT_RELU = 0, ACT_ELU = 1, ACT_LEAKY = 2 };
@@ -43,6 +49,8 @@ struct UnitParams {
   int tile_lines;               // lines per forward tile (the inverse always steps one line)
   int accumulate;               // logdet += instead of =
   int act;                      // Act
+  int hid_floats;               // floats of the hidden-activation area (tile x ksplit), 4-float aligned
+  int ksplit;                   // inverse: groups of threads sharing the input-channel loop of one line (>= 1)
   long long unit_floats;
 };
 
@@ -55,96 +63,209 @@ __host__ __device__ inline long long unit_floats(int C, int Hd, int k0, int k1) 
 
 __device__ __forceinline__ float activate(float h, int act) {
   if (act == ACT_RELU) return fmaxf(h, 0.f);
-  if (act == ACT_ELU) return h > 0.f ? h : expm1f(h);
+  // ELU: exp(h) - 1 with the fast exponential (absolute error < 5e-7 for h < 0, inside the stated 2e-5 tolerance);
+  // expm1f costs ~35 instructions per value, 7 % of the forward kernel
+  if (act == ACT_ELU) return h > 0.f ? h : MACOW_FAST_EXP(h) - 1.0f;
   return h > 0.f ? h : 0.1f * h;
 }
 
 // One masked-convolution flow over the image in shared memory, in place.
-// kQC = pixels along the line per phase-1 work item (one thread: one hidden channel, kQC pixels, all taps).
-template <bool kReverse, int kK1, int kQC>
-__device__ __forceinline__ void mcf_stage(float* __restrict__ X, float* __restrict__ hid, const float* __restrict__ fw,
+// The image is held twice, row-major (XA[c][y][x]) and column-major (XB[c][x][y]), so that every flow reads its lines
+// contiguously: Xl = the copy whose rows are this flow's lines ([c][l][q]), Xo = the other one ([c][q][l]).
+// kQC = pixels along the line per phase-1 work item (one thread: one hidden channel, kQC pixels, all taps of its
+// share of the input channels).  p.ksplit > 1 (inverse: a line offers only Hd * Q / kQC work items) splits the input
+// channels over ksplit groups of threads; their partial sums meet in shared memory before the activation.
+// kWS: the flow's packed weights (flow_floats() floats) are first copied into shared memory (wsm) and every line step
+// reads them from there; otherwise they stream from global memory through L1 (units too wide for one SM's shared memory).
+template <bool kWS>
+__device__ __forceinline__ float ldw(const float* ptr) {
+  if (kWS) return *ptr;
+  return __ldg(ptr);
+}
+
+template <bool kWS>
+__device__ __forceinline__ float2 ldw2(const float* ptr) {          // ptr is 8-byte aligned (even float index)
+  if (kWS) return *reinterpret_cast<const float2*>(ptr);
+  return __ldg(reinterpret_cast<const float2*>(ptr));
+}
+
+template <bool kReverse, int kK1, int kQC, bool kWS>
+__device__ __forceinline__ void mcf_stage(float* __restrict__ XA, float* __restrict__ XB, float* __restrict__ hid,
+                                          float* __restrict__ wsm, const float* __restrict__ fw_global,
                                           const UnitParams& p, int flow, float& logdet_acc) {
-  const int C = p.C, Hd = p.Hd, H = p.H, W = p.W, k0 = p.k0, HW = H * W;
+  const int C = p.C, Hd = p.Hd, k0 = p.k0, HW = p.H * p.W;
   constexpr int k1 = kK1;
+  constexpr int cq = (k1 - 1) >> 1;
+  constexpr int kJT = 2;                         // hidden channels per phase-1 item
+  constexpr int kPT = kReverse ? 1 : 4;          // pixels per phase-2 item (the inverse has one line's worth of items)
   const bool rows = flow < 2;                    // A, B: lines are rows; C, D: lines are columns
   const bool before = (flow & 1) == 0;           // A, C: the window lies before the line; B, D: after it
-  const int L = rows ? H : W, Q = rows ? W : H;
-  const int sl = rows ? W : 1, sq = rows ? 1 : W;
-  const int cq = (k1 - 1) >> 1;
+  const int L = rows ? p.H : p.W, Q = rows ? p.W : p.H;
+  float* __restrict__ Xl = rows ? XA : XB;
+  float* __restrict__ Xo = rows ? XB : XA;
+  const float* fw = fw_global;
+  if (kWS) {
+    const int nf = (int)flow_floats(C, Hd, k0, k1);
+    int done = 0;
+    if ((reinterpret_cast<uintptr_t>(fw_global) & 15) == 0) {          // 16-byte copies where the unit's offset allows
+      const float4* src4 = reinterpret_cast<const float4*>(fw_global);
+      float4* dst4 = reinterpret_cast<float4*>(wsm);
+      const int n4 = nf >> 2;
+#pragma unroll 8
+      for (int i = threadIdx.x; i < n4; i += blockDim.x) dst4[i] = __ldg(src4 + i);
+      done = n4 << 2;
+    }
+    for (int i = done + threadIdx.x; i < nf; i += blockDim.x) wsm[i] = __ldg(fw_global + i);
+    __syncthreads();
+    fw = wsm;
+  }
   const float* __restrict__ wT = fw;                                   // [C][k0][k1][Hd]
-  const float* __restrict__ w1T = fw + (long long)C * k0 * k1 * Hd;     // [Hd][2C]
-  const float* __restrict__ b1 = w1T + (long long)Hd * 2 * C;           // [2C]
+  const float* __restrict__ w1T = fw + (long long)C * k0 * k1 * Hd;     // [Hd][C][2]
+  const float* __restrict__ b1 = w1T + (long long)Hd * 2 * C;           // [C][2]
   const int T = kReverse ? 1 : p.tile_lines;
+  const int S = kReverse ? p.ksplit : 1;
+  const int cpk = (C + S - 1) / S;
   const int ntiles = (L + T - 1) / T;
   const bool ascending = kReverse ? before : !before;
   const int nqc = (Q + kQC - 1) / kQC;
+  const bool vec = (Q & 3) == 0;                 // float4 reads of a line: every line starts 16-byte aligned
+  const int part_stride = T * Q * Hd;            // floats between the partial-sum buffers of two channel groups
 
   for (int it = 0; it < ntiles; ++it) {
     const int ti = ascending ? it : ntiles - 1 - it;
     const int l0 = ti * T, tl = min(T, L - l0);
-    // ---- phase 1: hidden activations of the tile's pixels, hid[pixel][j]
-    const int items1 = Hd * tl * nqc;
+    // ---- phase 1: hidden activations of the tile's pixels, hid[pixel][j]; one item = kJT adjacent hidden channels
+    const int HJ = Hd / kJT;
+    const int items1 = HJ * tl * nqc * S;
     for (int item = threadIdx.x; item < items1; item += blockDim.x) {
-      const int j = item % Hd;
-      const int r = item / Hd;
-      const int qc = r % nqc, t = r / nqc;
+      const int j = (item % HJ) * kJT;
+      int r = item / HJ;
+      const int qc = r % nqc;
+      r /= nqc;
+      const int t = r % tl, ks = r / tl;
       const int l = l0 + t, q0 = qc * kQC;
-      float acc[kQC];
+      const int c0 = ks * cpk, c1 = min(C, c0 + cpk);
+      float acc[kJT][kQC];
 #pragma unroll
-      for (int i = 0; i < kQC; ++i) acc[i] = 0.f;
+      for (int i = 0; i < kQC; ++i) {
+#pragma unroll
+        for (int jt = 0; jt < kJT; ++jt) acc[jt][i] = 0.f;
+      }
       for (int dl = 0; dl < k0; ++dl) {
         const int ls = before ? l - k0 + dl : l + 1 + dl;
         if (ls < 0 || ls >= L) continue;                               // zero padding along the masked axis
-        const float* xrow = X + ls * sl;
+        const float* xline = Xl + ls * Q;
         const float* wrow = wT + (long long)dl * k1 * Hd + j;
-        for (int c = 0; c < C; ++c) {
+#pragma unroll(kWS ? 2 : 4)
+        for (int c = c0; c < c1; ++c) {
+          const float* xr = xline + c * HW;
           float xs[kQC + k1 - 1];
+          if (vec) {
 #pragma unroll
-          for (int i = 0; i < kQC + k1 - 1; ++i) {
-            const int q = q0 - cq + i;
-            xs[i] = (q >= 0 && q < Q) ? xrow[c * HW + q * sq] : 0.f;
+            for (int v = 0; v < kQC / 4; ++v) {
+              float4 x4 = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (q0 + 4 * v < Q) x4 = *reinterpret_cast<const float4*>(xr + q0 + 4 * v);
+              xs[cq + 4 * v + 0] = x4.x;
+              xs[cq + 4 * v + 1] = x4.y;
+              xs[cq + 4 * v + 2] = x4.z;
+              xs[cq + 4 * v + 3] = x4.w;
+            }
+#pragma unroll
+            for (int i = 0; i < cq; ++i) {
+              const int ql = q0 - cq + i, qr = q0 + kQC + i;
+              xs[i] = ql >= 0 ? xr[ql] : 0.f;
+              xs[cq + kQC + i] = qr < Q ? xr[qr] : 0.f;
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < kQC + k1 - 1; ++i) {
+              const int q = q0 - cq + i;
+              xs[i] = (q >= 0 && q < Q) ? xr[q] : 0.f;
+            }
           }
           const float* wc = wrow + (long long)c * k0 * k1 * Hd;
 #pragma unroll
           for (int dq = 0; dq < k1; ++dq) {
-            const float w = __ldg(wc + dq * Hd);
+            if (kJT == 2) {
+              const float2 w = ldw2<kWS>(wc + dq * Hd);
 #pragma unroll
-            for (int i = 0; i < kQC; ++i) acc[i] = fmaf(w, xs[i + dq], acc[i]);
+              for (int i = 0; i < kQC; ++i) {
+                acc[0][i] = fmaf(w.x, xs[i + dq], acc[0][i]);
+                acc[kJT - 1][i] = fmaf(w.y, xs[i + dq], acc[kJT - 1][i]);
+              }
+            } else {
+              const float w = ldw<kWS>(wc + dq * Hd);
+#pragma unroll
+              for (int i = 0; i < kQC; ++i) acc[0][i] = fmaf(w, xs[i + dq], acc[0][i]);
+            }
           }
         }
       }
+      float* dst = hid + ks * part_stride + (long long)(t * Q + q0) * Hd + j;
 #pragma unroll
-      for (int i = 0; i < kQC; ++i)
-        if (q0 + i < Q) hid[(long long)(t * Q + q0 + i) * Hd + j] = activate(acc[i], p.act);
+      for (int i = 0; i < kQC; ++i) {
+        if (q0 + i < Q) {
+#pragma unroll
+          for (int jt = 0; jt < kJT; ++jt) dst[i * Hd + jt] = S == 1 ? activate(acc[jt][i], p.act) : acc[jt][i];
+        }
+      }
     }
     __syncthreads();
-    // ---- phase 2: mu / log_scale per (channel, pixel) and the affine map, in place
-    const int items2 = C * tl * Q;
+    if (S > 1) {                                   // add the channel groups' partial sums in a fixed order, activate
+      const int nh = tl * Q * Hd;
+      for (int i = threadIdx.x; i < nh; i += blockDim.x) {
+        float s = hid[i];
+        for (int ks = 1; ks < S; ++ks) s += hid[ks * part_stride + i];
+        hid[i] = activate(s, p.act);
+      }
+      __syncthreads();
+    }
+    // ---- phase 2: mu / log_scale per (channel, group of kPT pixels) and the affine map, in place in both copies
+    const int npix = tl * Q, ngrp = (npix + kPT - 1) / kPT;
+    const int items2 = C * ngrp;
     for (int item = threadIdx.x; item < items2; item += blockDim.x) {
       const int c = item % C;
-      const int pix = item / C;
-      const int t = pix / Q, q = pix - t * Q;
-      const float* h = hid + (long long)pix * Hd;
-      float mu = __ldg(b1 + c), lsc = __ldg(b1 + C + c);
-      const float* wm = w1T + c;
-      for (int j = 0; j < Hd; j += 4) {
-        const float4 hv = *reinterpret_cast<const float4*>(h + j);
-        mu = fmaf(__ldg(wm + (j + 0) * 2 * C), hv.x, mu);
-        lsc = fmaf(__ldg(wm + (j + 0) * 2 * C + C), hv.x, lsc);
-        mu = fmaf(__ldg(wm + (j + 1) * 2 * C), hv.y, mu);
-        lsc = fmaf(__ldg(wm + (j + 1) * 2 * C + C), hv.y, lsc);
-        mu = fmaf(__ldg(wm + (j + 2) * 2 * C), hv.z, mu);
-        lsc = fmaf(__ldg(wm + (j + 2) * 2 * C + C), hv.z, lsc);
-        mu = fmaf(__ldg(wm + (j + 3) * 2 * C), hv.w, mu);
-        lsc = fmaf(__ldg(wm + (j + 3) * 2 * C + C), hv.w, lsc);
+      const int pix0 = (item / C) * kPT;
+      const float* hp[kPT];
+      float mu[kPT], lg[kPT];
+      const float2 bias = ldw2<kWS>(b1 + 2 * c);
+#pragma unroll
+      for (int k = 0; k < kPT; ++k) {
+        hp[k] = hid + (long long)min(pix0 + k, npix - 1) * Hd;          // tail groups re-read the last pixel, unused
+        mu[k] = bias.x;
+        lg[k] = bias.y;
       }
-      const float scale = tanhf(0.5f * lsc) * p.alpha + 1.0f;
-      float* xp = X + c * HW + (l0 + t) * sl + q * sq;
-      if (kReverse) {
-        *xp = (*xp - mu) / (scale + 1e-12f);
-      } else {
-        *xp = fmaf(scale, *xp, mu);
-        logdet_acc += logf(scale);
+      const float* wm = w1T + 2 * c;                                    // [Hd][C][2]: (mu, log-scale) weights of channel c
+#pragma unroll 2
+      for (int j = 0; j < Hd; j += 4) {
+        const float* w = wm + (long long)j * 2 * C;
+        const float2 w0 = ldw2<kWS>(w), w1 = ldw2<kWS>(w + 2 * C), w2 = ldw2<kWS>(w + 4 * C), w3 = ldw2<kWS>(w + 6 * C);
+#pragma unroll
+        for (int k = 0; k < kPT; ++k) {
+          const float4 h = *reinterpret_cast<const float4*>(hp[k] + j);
+          mu[k] = fmaf(w0.x, h.x, mu[k]); lg[k] = fmaf(w0.y, h.x, lg[k]);
+          mu[k] = fmaf(w1.x, h.y, mu[k]); lg[k] = fmaf(w1.y, h.y, lg[k]);
+          mu[k] = fmaf(w2.x, h.z, mu[k]); lg[k] = fmaf(w2.y, h.z, lg[k]);
+          mu[k] = fmaf(w3.x, h.w, mu[k]); lg[k] = fmaf(w3.y, h.w, lg[k]);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < kPT; ++k) {
+        const int pix = pix0 + k;
+        if (pix < npix) {
+          const int t = pix / Q, q = pix - t * Q, l = l0 + t;
+          const float scale = tanhf(0.5f * lg[k]) * p.alpha + 1.0f;
+          float* xl = Xl + c * HW + l * Q + q;
+          float v = *xl;
+          if (kReverse) {
+            v = (v - mu[k]) / (scale + 1e-12f);
+          } else {
+            v = fmaf(scale, v, mu[k]);
+            logdet_acc += logf(scale);
+          }
+          *xl = v;
+          Xo[c * HW + q * L + l] = v;
+        }
       }
     }
     __syncthreads();
@@ -152,13 +273,16 @@ __device__ __forceinline__ void mcf_stage(float* __restrict__ X, float* __restri
 }
 
 template <bool kReverse>
-__device__ __forceinline__ void actnorm_stage(float* __restrict__ X, const float* __restrict__ an, const UnitParams& p,
-                                              float& logdet_acc) {
-  const int HW = p.H * p.W, n = p.C * HW;
+__device__ __forceinline__ void actnorm_stage(float* __restrict__ XA, float* __restrict__ XB, const float* __restrict__ an,
+                                              const UnitParams& p, float& logdet_acc) {
+  const int H = p.H, W = p.W, HW = H * W, n = p.C * HW;
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    const int c = i / HW;
+    const int c = i / HW, rem = i - c * HW;
+    const int y = rem / W, x = rem - y * W;
     const float e = expf(__ldg(an + c)), b = __ldg(an + p.C + c);
-    X[i] = kReverse ? (X[i] - b) / (e + 1e-8f) : fmaf(X[i], e, b);
+    const float v = kReverse ? (XA[i] - b) / (e + 1e-8f) : fmaf(XA[i], e, b);
+    XA[i] = v;
+    XB[c * HW + x * H + y] = v;
   }
   if (!kReverse && threadIdx.x == 0) {
     float s = 0.f;
@@ -168,17 +292,26 @@ __device__ __forceinline__ void actnorm_stage(float* __restrict__ X, const float
   __syncthreads();
 }
 
-// grid = B, dynamic smem = (C H W + hidden tile) floats.  Hd must be a multiple of 4 (float4 reads of hid);
+// grid = B, dynamic smem = (2 images + hidden tile x ksplit [+ one flow's weights]) floats.  Hd must be a multiple of 4 (float4 reads of hid);
 // kK1 = kernel_size[1], the centred taps along the line (odd; the reference's configs use 3).
-template <bool kReverse, int kK1, int kQC>
-__global__ void __launch_bounds__(256) macow_unit_kernel(const UnitParams p) {
+template <bool kReverse, int kK1, int kQC, bool kWS>
+__global__ void __launch_bounds__(512, 1) macow_unit_kernel(const UnitParams p) {
   extern __shared__ __align__(16) float smem[];
-  const int n = p.C * p.H * p.W;
-  float* X = smem;
-  float* hid = smem + ((n + 3) & ~3);
+  const int H = p.H, W = p.W, HW = H * W, n = p.C * HW;
+  const int n4 = (n + 3) & ~3;
+  float* XA = smem;
+  float* XB = smem + n4;
+  float* hid = smem + 2 * n4;
+  float* wsm = hid + p.hid_floats;          // kWS only: one flow's weights
   const int b = blockIdx.x;
   const float* src = p.in + (long long)b * n;
-  for (int i = threadIdx.x; i < n; i += blockDim.x) X[i] = __ldg(src + i);
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int c = i / HW, rem = i - c * HW;
+    const int y = rem / W, x = rem - y * W;
+    const float v = __ldg(src + i);
+    XA[i] = v;
+    XB[c * HW + x * H + y] = v;
+  }
   __syncthreads();
   float logdet_acc = 0.f;
   const int ns = p.stage_end - p.stage_begin;
@@ -188,17 +321,17 @@ __global__ void __launch_bounds__(256) macow_unit_kernel(const UnitParams p) {
     const float* up = p.packed + unit * p.unit_floats;
     const long long ff = flow_floats(p.C, p.Hd, p.k0, p.k1);
     if (st == 2 || st == 5) {
-      actnorm_stage<kReverse>(X, up + 4 * ff + (st == 5 ? 2 * p.C : 0), p, logdet_acc);
+      actnorm_stage<kReverse>(XA, XB, up + 4 * ff + (st == 5 ? 2 * p.C : 0), p, logdet_acc);
     } else {
       const int flow = st < 2 ? st : st - 1;
-      mcf_stage<kReverse, kK1, kQC>(X, hid, up + flow * ff, p, flow, logdet_acc);
+      mcf_stage<kReverse, kK1, kQC, kWS>(XA, XB, hid, wsm, up + flow * ff, p, flow, logdet_acc);
     }
   }
   float* dst = p.out + (long long)b * n;
-  for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = X[i];
+  for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = XA[i];
   if (!kReverse && p.logdet != nullptr) {
     // deterministic block reduction (fixed item -> thread mapping, fixed tree)
-    __shared__ float red[8];
+    __shared__ float red[16];
     float v = logdet_acc;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -252,8 +385,9 @@ __global__ void macow_pack_kernel(const PackParams p) {
       float ss = 0.f;
       for (int j = 0; j < Hd; ++j) ss = fmaf(v[o * Hd + j], v[o * Hd + j], ss);
       const float mul = g[o] / sqrtf(ss);
-      for (int j = 0; j < Hd; ++j) w1T[(long long)j * 2 * C + o] = v[o * Hd + j] * mul;
-      b1[o] = bias[o];
+      const int slot = o < C ? 2 * o : 2 * (o - C) + 1;               // output o: mu of channel o, or log-scale of o - C
+      for (int j = 0; j < Hd; ++j) w1T[(long long)j * 2 * C + slot] = v[o * Hd + j] * mul;
+      b1[slot] = bias[o];
     }
   }
   float* an = p.packed + 4 * ff;

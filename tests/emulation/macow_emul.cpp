@@ -15,8 +15,10 @@
 #define __restrict__
 #define __shared__
 #define __align__(n)
-#define __launch_bounds__(n)
+#define __launch_bounds__(...)
 struct float4 { float x, y, z, w; };
+static inline float4 make_float4(float x, float y, float z, float w) { return float4{x, y, z, w}; }
+struct float2 { float x, y; };
 struct dim3e { unsigned x, y, z; };
 static dim3e threadIdx = {0, 0, 0}, blockDim = {1, 1, 1}, blockIdx = {0, 0, 0}, gridDim = {1, 1, 1};
 static inline void __syncthreads() {}
@@ -28,14 +30,19 @@ namespace macow { alignas(16) float smem[1 << 20]; }
 
 #include "../../ipoke-main-opticalflow_b200/csrc/macow_kernel.cuh"
 
-template <bool kRev, int kQC>
-static void run_k1(int k1, const macow::UnitParams& p) {
+template <bool kRev, int kQC, bool kWS>
+static void run_ws(int k1, const macow::UnitParams& p) {
   for (unsigned b = 0; b < (unsigned)p.B; ++b) {
     blockIdx.x = b;
-    if (k1 == 1) macow::macow_unit_kernel<kRev, 1, kQC>(p);
-    else if (k1 == 3) macow::macow_unit_kernel<kRev, 3, kQC>(p);
-    else macow::macow_unit_kernel<kRev, 5, kQC>(p);
+    if (k1 == 1) macow::macow_unit_kernel<kRev, 1, kQC, kWS>(p);
+    else if (k1 == 3) macow::macow_unit_kernel<kRev, 3, kQC, kWS>(p);
+    else macow::macow_unit_kernel<kRev, 5, kQC, kWS>(p);
   }
+}
+
+template <bool kRev, int kQC>
+static void run_k1(int k1, const macow::UnitParams& p, int ws) {
+  if (ws) run_ws<kRev, kQC, true>(k1, p); else run_ws<kRev, kQC, false>(k1, p);
 }
 
 extern "C" {
@@ -52,7 +59,7 @@ void emul_pack(const float* const* params, float* packed, int C, int Hd, int k0,
 
 void emul_run(const float* packed, int n_units, const float* in, float* out, float* logdet, int accumulate, int B,
               int C, int Hd, int H, int W, int k0, int k1, int act, float alpha, int s0, int s1, int tile_lines,
-              int reverse, int qc) {
+              int reverse, int qc, int ksplit, int ws) {
   macow::UnitParams p;
   p.packed = packed; p.in = in; p.out = out; p.logdet = logdet;
   p.B = B; p.C = C; p.Hd = Hd; p.H = H; p.W = W; p.k0 = k0; p.k1 = k1; p.alpha = alpha;
@@ -60,10 +67,12 @@ void emul_run(const float* packed, int n_units, const float* in, float* out, flo
   p.unit_floats = macow::unit_floats(C, Hd, k0, k1);
   blockDim.x = 1; gridDim.x = B; threadIdx.x = 0;
   p.act = act;
+  p.ksplit = ksplit;
+  p.hid_floats = ((reverse ? 1 : tile_lines) * ksplit * (H > W ? H : W) * Hd + 3) & ~3;
   if (reverse) {
-    if (qc == 8) run_k1<true, 8>(k1, p); else run_k1<true, 4>(k1, p);
+    if (qc == 8) run_k1<true, 8>(k1, p, ws); else run_k1<true, 4>(k1, p, ws);
   } else {
-    if (qc == 8) run_k1<false, 8>(k1, p); else run_k1<false, 4>(k1, p);
+    if (qc == 8) run_k1<false, 8>(k1, p, ws); else run_k1<false, 4>(k1, p, ws);
   }
 }
 }

@@ -43,7 +43,7 @@ def pack(L, sd, C, Hd, k0, k1):
     return packed
 
 
-def run(L, packed, x, meta, s0, s1, reverse, tile=1, n_units=1, logdet0=None, qc=4):
+def run(L, packed, x, meta, s0, s1, reverse, tile=1, n_units=1, logdet0=None, qc=4, ksplit=1, ws=0):
     C, Hd, k0, k1, act, alpha = meta
     x = np.ascontiguousarray(x, dtype=np.float32)
     B, _, H, W = x.shape
@@ -51,7 +51,7 @@ def run(L, packed, x, meta, s0, s1, reverse, tile=1, n_units=1, logdet0=None, qc
     ld = np.zeros(B, dtype=np.float32) if logdet0 is None else logdet0.astype(np.float32).copy()
     L.emul_run(packed.ctypes.data_as(ctypes.c_void_p), n_units, x.ctypes.data_as(ctypes.c_void_p),
                out.ctypes.data_as(ctypes.c_void_p), ld.ctypes.data_as(ctypes.c_void_p), int(logdet0 is not None), B,
-               C, Hd, H, W, k0, k1, ACT[act], ctypes.c_float(alpha), s0, s1, tile, int(reverse), qc)
+               C, Hd, H, W, k0, k1, ACT[act], ctypes.c_float(alpha), s0, s1, tile, int(reverse), qc, ksplit, ws)
     return out, ld
 
 
@@ -68,11 +68,11 @@ def test_emulated_kernel_matches_reference_fixtures(emul, name):
     g, sd, meta = load(name)
     packed = pack(emul, sd, *meta[:4])
     for tile in (1, 2, 3, 64):                                   # forward tiling must not change the result
-        out, ld = run(emul, packed, g["x"], meta, 0, 6, False, tile=tile, qc=8 if tile == 2 else 4)
+        out, ld = run(emul, packed, g["x"], meta, 0, 6, False, tile=tile, qc=8 if tile == 2 else 4, ws=tile & 1)
         np.testing.assert_allclose(out, g["out64"], rtol=2e-5, atol=2e-5)
         np.testing.assert_allclose(ld, g["logdet64"], rtol=2e-5, atol=3e-4)
-    for qc in (4, 8):
-        x_smp, _ = run(emul, packed, g["z_in"], meta, 0, 6, True, qc=qc)
+    for qc, ksplit in ((4, 1), (8, 2), (8, 3)):                  # 3 does not divide the channel counts: ragged last group
+        x_smp, _ = run(emul, packed, g["z_in"], meta, 0, 6, True, qc=qc, ksplit=ksplit, ws=ksplit & 1)
         np.testing.assert_allclose(x_smp, g["x_smp"], rtol=1e-4, atol=1e-4)
     x_rec, _ = run(emul, packed, g["out"], meta, 0, 6, True)
     np.testing.assert_allclose(x_rec, g["x"], rtol=1e-4, atol=1e-4)
@@ -114,7 +114,8 @@ def random_unit(rng, C, k0, k1, gain=0.3):
     return sd, Hd
 
 
-@pytest.mark.parametrize("C,k0,k1,H,W,act", [(8, 3, 5, 5, 7, "elu"), (32, 2, 3, 8, 8, "relu"), (3, 1, 1, 4, 9, "leaky_relu")])
+@pytest.mark.parametrize("C,k0,k1,H,W,act", [(8, 3, 5, 5, 7, "elu"), (32, 2, 3, 8, 8, "relu"), (3, 1, 1, 4, 9, "leaky_relu"),
+                                                (4, 2, 5, 8, 12, "elu")])      # float4 line reads with 5 centred taps
 def test_emulated_two_unit_chain_other_kernels(emul, C, k0, k1, H, W, act):
     rng = np.random.default_rng(C)
     (sd0, Hd), (sd1, _) = random_unit(rng, C, k0, k1), random_unit(rng, C, k0, k1)
@@ -130,5 +131,5 @@ def test_emulated_two_unit_chain_other_kernels(emul, C, k0, k1, H, W, act):
     np.testing.assert_allclose(back, x, rtol=2e-4, atol=2e-4)
     z = rng.standard_normal((2, C, H, W)).astype(np.float32)
     want_rev = mo.unit_reverse(sd0, mo.unit_reverse(sd1, z, act, 0.8), act, 0.8)
-    got, _ = run(emul, packed, z, meta, 0, 12, True, n_units=2)
+    got, _ = run(emul, packed, z, meta, 0, 12, True, n_units=2, ksplit=min(C, 4), ws=1)       # odd C: unaligned unit offsets
     np.testing.assert_allclose(got, want_rev, rtol=2e-4, atol=2e-4)

@@ -58,7 +58,9 @@ def test_unit_floats_and_launch_geometry_without_gpu():
     assert L.ipoke_macow_unit_floats(ctypes.byref(d)) == 4 * per_flow + 4 * 16
     smem, thr, tile = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
     assert L.ipoke_macow_launch_info(ctypes.byref(d), 8, 8, 1, ctypes.byref(smem), ctypes.byref(thr), ctypes.byref(tile)) == 0
-    assert tile.value == 1 and smem.value == (16 * 64 + 8 * 64) * 4 and thr.value % 32 == 0
+    # inverse: two image copies + one hidden line per channel group (512 threads / 32 work items, at most 4 groups)
+    # ... + one flow's packed weights staged in shared memory
+    assert tile.value == 1 and smem.value == (2 * 16 * 64 + 4 * 8 * 64 + per_flow) * 4 and thr.value % 32 == 0
     assert L.ipoke_macow_launch_info(ctypes.byref(d), 8, 8, 0, ctypes.byref(smem), ctypes.byref(thr), ctypes.byref(tile)) == 0
     assert tile.value == 8                                      # the whole 8 x 8 image's hidden tile fits the budget
     bad = macow.MacowDesc(16, 64, 2, 4, 1, 1.0)                 # even centred kernel: the reference asserts
