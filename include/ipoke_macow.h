@@ -71,6 +71,59 @@ int ipoke_macow_reverse(const ipoke_macow_desc* desc, const float* packed, int n
 int ipoke_macow_launch_info(const ipoke_macow_desc* desc, int H, int W, int reverse, int* smem_bytes, int* threads,
                             int* tile_lines);
 
+/* The two calls above with explicit sample strides (floats between consecutive samples of x / out, >= C * H * W):
+ * the multi-scale flow (MultiScaleInternal, macow2.py:872-918) runs every level in place on the first channels of
+ * one [B, C_total, H, W] buffer, so its split2d / unsplit2d (macow2.py:15-23) cost nothing. */
+int ipoke_macow_units_forward(const ipoke_macow_desc* desc, const float* packed, int n_units, const float* x,
+                              long long x_stride, float* out, long long out_stride, float* logdet, int accumulate,
+                              int B, int H, int W, int stage_begin, int stage_end, void* stream);
+int ipoke_macow_units_reverse(const ipoke_macow_desc* desc, const float* packed, int n_units, const float* z,
+                              long long z_stride, float* out, long long out_stride, int B, int H, int W,
+                              int stage_begin, int stage_end, void* stream);
+
+/* ---- NICE2d coupling with the convolutional net (macow2.py:291-437; NICEConvBlock macow_utils.py:253-338 without
+ * normalisation layers, attention or conditioning; Affine macow_utils.py:42-66).  The net reads image channels
+ * z_off + z_stride * i (i < c_in) and transforms channels p_off + p_stride * i (i < c_t) in place:
+ *   split 'continuous', order 'up'   (macow2.py:366-367, 410):  z_off 0,         z_stride 1, p_off C - C / factor, p_stride 1
+ *   split 'continuous', order 'down':                           z_off C / factor, z_stride 1, p_off 0,              p_stride 1
+ *   split 'skip' (even C), 'up'      (macow2.py:368-373):       z_off 0,         z_stride 2, p_off 1,              p_stride 2
+ *   split 'skip' (even C), 'down':                              z_off 1,         z_stride 2, p_off 0,              p_stride 2
+ * with c_t = C / factor, c_in = C - c_t. */
+typedef struct ipoke_macow_nice_desc {
+  int32_t c_in, z_off, z_stride;
+  int32_t c_t, p_off, p_stride;
+  int32_t hidden;     /* hidden_channels of the coupling net (flow_mid_channels)                macow2.py:312-313 */
+  int32_t activation; /* IPOKE_MACOW_ACT_*                                                                         */
+  float alpha;
+} ipoke_macow_nice_desc;
+
+/* Floats of one packed coupling net (the three convolutions transposed to [K][N] with N padded to 4, the last one
+ * weight-normed with (shift, log-scale) column pairs, and its bias). */
+size_t ipoke_macow_nice_floats(const ipoke_macow_nice_desc* desc);
+
+/* `params`: HOST array of 5 device pointers, float32 contiguous, in state_dict order:
+ *   net.conv1.weight [hidden, c_in, 3, 3], net.conv2.weight [hidden, hidden, 1, 1], net.conv3.conv.bias [2 c_t],
+ *   net.conv3.conv.weight_g [2 c_t], net.conv3.conv.weight_v [2 c_t, hidden, 3, 3]. */
+int ipoke_macow_pack_nice(const ipoke_macow_nice_desc* desc, const void* const* params, float* packed, void* stream);
+
+/* Preferred workspace (floats) for batch B: two pixel-major hidden-activation buffers and the per-row log-determinants
+ * of as many samples as keep a pass in L2.  Any size >= H * W * (2 * hidden + 1) works (fewer samples per pass). */
+size_t ipoke_macow_nice_workspace_floats(const ipoke_macow_nice_desc* desc, int B, int H, int W);
+
+/* Forward (reverse == 0: transformed channels <- scale * x + shift, logdet[b] += sum log scale; logdet nullable) or
+ * inverse (reverse != 0: (x - shift) / (scale + 1e-12)) of one coupling on x [B, *, H, W] with sample stride x_stride. */
+int ipoke_macow_nice(const ipoke_macow_nice_desc* desc, const float* packed, float* x, long long x_stride, float* logdet,
+                     int reverse, int B, int H, int W, float* ws, size_t ws_floats, void* stream);
+
+/* Per-channel glue of MaCowStep / MultiScalePrior / MultiScaleInternal, in place on the first channels of every sample:
+ * an optional ActNorm2dFlow (macow2.py:502-521; forward x * exp(log_scale) + bias with logdet[b] += H W sum(log_scale),
+ * inverse (x - bias) / (exp(log_scale) + 1e-8)) on channels [norm_c0, norm_c0 + norm_n), and an optional Shuffle
+ * (flow_blocks.py:322-326) out[c] = in[perm[c]] of the first n_perm channels (perm: the module's int64 buffer on the
+ * device); norm_first != 0 applies the ActNorm before the permutation, else after it. */
+int ipoke_macow_chanmap(float* x, long long x_stride, int B, int H, int W, const long long* perm, int n_perm,
+                        const float* log_scale, const float* bias, int norm_c0, int norm_n, int norm_inverse,
+                        int norm_first, float* logdet, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

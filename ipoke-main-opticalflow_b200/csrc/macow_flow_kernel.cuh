@@ -1,0 +1,291 @@
+// The rest of the MaCow flow around the units (macow_kernel.cuh), sm_100a, float32 like the reference:
+//   * NICE2d coupling with the convolutional net (macow2.py:291-437, macow_utils.py:253-338): 3x3 conv -> activation ->
+//     1x1 conv -> activation -> weight-normed 3x3 conv -> Affine (macow_utils.py:42-66), forward and inverse;
+//   * the per-channel glue of MaCowStep / MultiScalePrior / MultiScaleInternal (macow2.py:543-594, 821-918, 999-1117):
+//     ActNorm2dFlow (macow2.py:502-521) and the Shuffle permutation (flow_blocks.py:314-326), in place on a channel
+//     prefix of the image (the multi-scale split / unsplit is then no operation at all: a level works on the first
+//     channels of every sample and leaves the factored-out channels where the final concatenation wants them).
+//
+// Design.  The coupling net is three GEMMs over rows = (sample, pixel):  [M, 9 c_in] x [9 c_in, Hd],  [M, Hd] x [Hd, Hd],
+// [M, 9 Hd] x [9 Hd, 2 c_t], the 3x3 windows gathered while the A tile is loaded (implicit im2col: from the NCHW image for
+// the first layer, as row shifts of the pixel-major hidden activations for the last), activations fused into the
+// epilogues of the first two and the affine map + per-row log-determinant into the epilogue of the third.  Hidden
+// activations are pixel-major [M, Hd] so every layer reads contiguous K.  One tiled float32 kernel (128-row tiles,
+// 16-deep K slices in shared memory, 8 x 8 or 8 x 2 register tiles, 256 threads) serves all three.  The hidden width of
+// the reference's configuration (2048) makes the middle GEMM tensor-core work; this float32 version is the parity
+// path (DESIGN.md section 4b says what the tcgen05 version changes).
+#pragma once
+#include "macow_kernel.cuh"
+
+namespace macow {
+
+// Channel geometry of one NICE2d: the net reads image channels z_off + z_stride * i (i < c_in) and transforms
+// channels p_off + p_stride * i (i < c_t)  (continuous / skip split, order up / down: macow2.py:363-389, 410-414).
+struct NiceGeom {
+  int c_in, z_off, z_stride, c_t, p_off, p_stride;
+};
+
+__host__ __device__ inline int round4(int v) { return (v + 3) & ~3; }
+
+// Packed coupling net: Wt1 [9 c_in][ld] | Wt2 [Hd][ld] | Wt3 [9 Hd][ld3] | bias3 [ld3], ld = round4(Hd), ld3 = round4(2 c_t);
+// Wt3 / bias3 columns interleaved: 2 i = shift of transformed channel i, 2 i + 1 = its log-scale.
+__host__ __device__ inline long long nice_floats(int c_in, int c_t, int Hd) {
+  const long long ld = round4(Hd), ld3 = round4(2 * c_t);
+  return 9LL * c_in * ld + (long long)Hd * ld + 9LL * Hd * ld3 + ld3;
+}
+
+enum { SRC_IMAGE = 0, SRC_ROWS = 1, SRC_TAPS = 2 };
+enum { EPI_ACT = 0, EPI_AFFINE = 1 };
+
+struct GemmParams {
+  const float* A;      // SRC_ROWS / SRC_TAPS: activations [M][lda];  SRC_IMAGE: the image (first sample of the chunk)
+  const float* Wt;     // [K][ldw], ldw a multiple of 4, columns >= N zero
+  const float* bias;   // EPI_AFFINE: [round4(2 c_t)]
+  float* Y;            // EPI_ACT: [M][ldy]
+  float* x;            // EPI_AFFINE: the image (first sample of the chunk), transformed channels updated in place
+  float* rowld;        // EPI_AFFINE forward: sum over channels of log(scale) per row [M]; nullable
+  int M, N, K, lda, ldw, ldy;
+  int H, W, Hd;
+  long long sample_stride;
+  NiceGeom g;
+  int act, reverse;
+  float alpha;
+};
+
+constexpr int kGemmBK = 16;
+constexpr int kGemmThreads = 256;
+
+template <int kSrc>
+__device__ __forceinline__ float gemm_fetch_a(const GemmParams& p, int m, int k, int py, int px) {
+  if (m >= p.M || k >= p.K) return 0.f;
+  if (kSrc == SRC_ROWS) return __ldg(p.A + (long long)m * p.lda + k);
+  const int HW = p.H * p.W;
+  if (kSrc == SRC_TAPS) {                                   // k = tap * Hd + j: hidden channel j of the pixel's tap-th neighbour
+    const int tap = k / p.Hd, j = k - tap * p.Hd;
+    const int dy = tap / 3 - 1, dx = tap - (tap / 3) * 3 - 1;
+    const int yy = py + dy, xx = px + dx;
+    if (yy < 0 || yy >= p.H || xx < 0 || xx >= p.W) return 0.f;          // zero padding of the 3x3 convolution
+    return __ldg(p.A + (long long)(m + dy * p.W + dx) * p.lda + j);
+  }
+  const int c = k / 9, tap = k - c * 9;                      // SRC_IMAGE: k = c * 9 + tap
+  const int dy = tap / 3 - 1, dx = tap - (tap / 3) * 3 - 1;
+  const int yy = py + dy, xx = px + dx;
+  if (yy < 0 || yy >= p.H || xx < 0 || xx >= p.W) return 0.f;
+  const int b = m / HW;
+  return __ldg(p.A + b * p.sample_stride + (long long)(p.g.z_off + p.g.z_stride * c) * HW + yy * p.W + xx);
+}
+
+// grid.x = row tiles; grid.y = column tiles (EPI_ACT) or 1 (EPI_AFFINE walks its column tiles itself so that a row's
+// log-determinant is summed by one thread in a fixed order).
+template <int kSrc, int kEpi, int BM, int BN, int TM, int TN>
+__global__ void __launch_bounds__(kGemmThreads) nice_gemm_kernel(const GemmParams p) {
+  static_assert((BM / TM) * (BN / TN) == kGemmThreads, "one register tile per thread");
+  static_assert(BM % 16 == 0 && BN % 4 == 0 && TM % 4 == 0, "tile shapes");
+  constexpr int BK = kGemmBK;
+  constexpr int LDA_S = BM + 4;                              // As[k][row], rows 16-byte aligned
+  MACOW_SHARED __align__(16) float As[BK * LDA_S];
+  MACOW_SHARED __align__(16) float Bs[BK * BN];
+  MACOW_SHARED float red[kEpi == EPI_AFFINE ? BM * (BN / TN + 1) : 1];
+  const int tid = threadIdx.x;
+  const int tx = tid % (BN / TN), ty = tid / (BN / TN);
+  const int m0 = blockIdx.x * BM;
+  const int HW = p.H * p.W;
+  // A-tile loader: thread -> (kk = tid % 16, rows r0 + 16 i)
+  constexpr int RPT = BM / 16;
+  const int a_kk = tid & 15, a_r0 = tid >> 4;
+  int a_py[RPT], a_px[RPT];
+#pragma unroll
+  for (int i = 0; i < RPT; ++i) {
+    const int pix = (m0 + a_r0 + 16 * i) % HW;
+    a_py[i] = pix / p.W;
+    a_px[i] = pix - a_py[i] * p.W;
+  }
+  float rowacc = 0.f;
+  const int n_begin = kEpi == EPI_AFFINE ? 0 : blockIdx.y * BN;
+  const int n_end = kEpi == EPI_AFFINE ? p.N : min(p.N, n_begin + BN);
+  for (int n0 = n_begin; n0 < n_end; n0 += BN) {
+    float acc[TM][TN];
+#pragma unroll
+    for (int i = 0; i < TM; ++i) {
+#pragma unroll
+      for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+    }
+    for (int k0 = 0; k0 < p.K; k0 += BK) {
+#pragma unroll
+      for (int i = 0; i < RPT; ++i) {
+        const int r = a_r0 + 16 * i;
+        As[a_kk * LDA_S + r] = gemm_fetch_a<kSrc>(p, m0 + r, k0 + a_kk, a_py[i], a_px[i]);
+      }
+      for (int v = tid; v < BK * (BN / 4); v += kGemmThreads) {
+        const int kk = v / (BN / 4), n4 = (v - kk * (BN / 4)) * 4;
+        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (k0 + kk < p.K && n0 + n4 < p.ldw) w = __ldg(reinterpret_cast<const float4*>(p.Wt + (long long)(k0 + kk) * p.ldw + n0 + n4));
+        *reinterpret_cast<float4*>(Bs + kk * BN + n4) = w;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int kk = 0; kk < BK; ++kk) {
+        float a[TM], b[TN];
+#pragma unroll
+        for (int i = 0; i < TM; i += 4) {
+          const float4 v = *reinterpret_cast<const float4*>(As + kk * LDA_S + ty * TM + i);
+          a[i] = v.x; a[i + 1] = v.y; a[i + 2] = v.z; a[i + 3] = v.w;
+        }
+#pragma unroll
+        for (int j = 0; j < TN; ++j) b[j] = Bs[kk * BN + tx * TN + j];
+#pragma unroll
+        for (int i = 0; i < TM; ++i) {
+#pragma unroll
+          for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        }
+      }
+      __syncthreads();
+    }
+    if (kEpi == EPI_ACT) {
+#pragma unroll
+      for (int i = 0; i < TM; ++i) {
+        const int m = m0 + ty * TM + i;
+        if (m >= p.M) continue;
+        float* y = p.Y + (long long)m * p.ldy + n0 + tx * TN;
+#pragma unroll
+        for (int j = 0; j < TN; ++j) {
+          if (n0 + tx * TN + j < p.N) y[j] = activate(acc[i][j], p.act);
+        }
+      }
+    } else {
+      // TN == 2: the thread holds (shift, log-scale) of transformed channel ch for TM consecutive pixels
+      const int ch = (n0 >> 1) + tx;
+      const float b_mu = ch < p.g.c_t ? __ldg(p.bias + 2 * ch) : 0.f;
+      const float b_ls = ch < p.g.c_t ? __ldg(p.bias + 2 * ch + 1) : 0.f;
+#pragma unroll
+      for (int i = 0; i < TM; ++i) {
+        const int r = ty * TM + i, m = m0 + r;
+        float lg = 0.f;
+        if (m < p.M && ch < p.g.c_t) {
+          const float mu = acc[i][0] + b_mu;
+          const float scale = tanhf(0.5f * (acc[i][TN - 1] + b_ls)) * p.alpha + 1.0f;
+          const int b = m / HW, pix = m - b * HW;
+          float* xp = p.x + b * p.sample_stride + (long long)(p.g.p_off + p.g.p_stride * ch) * HW + pix;
+          if (p.reverse) {
+            *xp = (*xp - mu) / (scale + 1e-12f);
+          } else {
+            *xp = fmaf(scale, *xp, mu);
+            lg = logf(scale);
+          }
+        }
+        red[r * (BN / TN + 1) + tx] = lg;
+      }
+      __syncthreads();
+      if (tid < BM) {
+        float s = 0.f;
+        for (int t = 0; t < BN / TN; ++t) s += red[tid * (BN / TN + 1) + t];
+        rowacc += s;
+      }
+      __syncthreads();
+    }
+  }
+  if (kEpi == EPI_AFFINE && !p.reverse && p.rowld != nullptr && tid < BM && m0 + tid < p.M) p.rowld[m0 + tid] = rowacc;
+}
+
+// logdet[b] += sum of the HW row values of sample b, fixed order.  One thread per sample.
+__global__ void macow_rowsum_kernel(const float* __restrict__ rowld, float* __restrict__ logdet, int B, int HW) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  float s = 0.f;
+  for (int i = 0; i < HW; ++i) s += rowld[(long long)b * HW + i];
+  logdet[b] += s;
+}
+
+// Per-channel glue, in place, one CTA per sample with the touched channel prefix staged in shared memory:
+//   optional ActNorm2dFlow (forward x * exp(ls) + b, inverse (x - b) / (exp(ls) + 1e-8)) on channels [norm_c0, norm_c0 + norm_n),
+//   optional permutation out[c] = in[perm[c]] of the first n_perm channels, in either order (norm_first).
+struct ChanMapParams {
+  float* x;
+  long long sample_stride;
+  int HW, n_stage;                 // channels staged = max(n_perm, norm_c0 + norm_n)
+  const long long* perm;           // int64 [n_perm] (the module's buffer) or null
+  int n_perm;
+  const float* log_scale;          // [norm_n] or null
+  const float* bias;
+  int norm_c0, norm_n, norm_inverse, norm_first;
+  float* logdet;                   // forward ActNorm: += HW * sum(log_scale); nullable
+};
+
+__device__ __forceinline__ float chanmap_norm(const ChanMapParams& p, float v, int c) {
+  const float e = expf(__ldg(p.log_scale + c)), b = __ldg(p.bias + c);
+  return p.norm_inverse ? (v - b) / (e + 1e-8f) : fmaf(v, e, b);
+}
+
+__global__ void macow_chanmap_kernel(const ChanMapParams p) {
+  extern __shared__ __align__(16) float smem[];
+  const int HW = p.HW, n = p.n_stage * HW;
+  float* img = p.x + blockIdx.x * p.sample_stride;
+  const bool has_norm = p.log_scale != nullptr && p.norm_n > 0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    float v = img[i];
+    const int c = i / HW;
+    if (has_norm && p.norm_first && c >= p.norm_c0 && c < p.norm_c0 + p.norm_n) v = chanmap_norm(p, v, c - p.norm_c0);
+    smem[i] = v;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int c = i / HW, pix = i - c * HW;
+    const int src = (p.perm != nullptr && c < p.n_perm) ? (int)p.perm[c] : c;
+    float v = smem[src * HW + pix];
+    if (has_norm && !p.norm_first && c >= p.norm_c0 && c < p.norm_c0 + p.norm_n) v = chanmap_norm(p, v, c - p.norm_c0);
+    img[i] = v;
+  }
+  if (has_norm && !p.norm_inverse && p.logdet != nullptr && threadIdx.x == 0) {
+    float s = 0.f;
+    for (int c = 0; c < p.norm_n; ++c) s += __ldg(p.log_scale + c);
+    p.logdet[blockIdx.x] += s * (float)HW;
+  }
+}
+
+// Pack one coupling net.  params: conv1.weight [Hd, c_in, 3, 3], conv2.weight [Hd, Hd, 1, 1], conv3.conv.bias [2 c_t],
+// conv3.conv.weight_g [2 c_t], conv3.conv.weight_v [2 c_t, Hd, 3, 3]  (macow_utils.py:270-283, 211-233).
+struct PackNiceParams {
+  const float* params[5];
+  float* packed;
+  int c_in, c_t, Hd;
+};
+
+__global__ void macow_pack_nice_kernel(const PackNiceParams p) {
+  const int c_in = p.c_in, c_t = p.c_t, Hd = p.Hd;
+  const int ld = round4(Hd), ld3 = round4(2 * c_t);
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (long long)gridDim.x * blockDim.x;
+  float* w1 = p.packed;
+  float* w2 = w1 + 9LL * c_in * ld;
+  float* w3 = w2 + (long long)Hd * ld;
+  for (long long i = tid; i < 9LL * c_in * ld; i += nthreads) {           // Wt1[(c * 9 + tap)][j] = conv1.weight[j][c][tap]
+    const int j = (int)(i % ld), k = (int)(i / ld);
+    w1[i] = j < Hd ? p.params[0][(long long)j * c_in * 9 + k] : 0.f;
+  }
+  for (long long i = tid; i < (long long)Hd * ld; i += nthreads) {        // Wt2[jin][jout] = conv2.weight[jout][jin]
+    const int jo = (int)(i % ld), ji = (int)(i / ld);
+    w2[i] = jo < Hd ? p.params[1][(long long)jo * Hd + ji] : 0.f;
+  }
+  for (long long i = tid; i < 9LL * Hd * ld3 + ld3; i += nthreads) w3[i] = 0.f;   // padded columns of Wt3 / b3
+}
+
+// Second launch of the pack (same stream, after the zero fill above): the weight-normed last convolution
+// (torch _weight_norm, dim 0: row o of v scaled by g[o] / ||v[o]||), one thread per output row, and its bias.
+__global__ void macow_pack_nice_rows_kernel(const PackNiceParams p) {
+  const int c_t = p.c_t, Hd = p.Hd;
+  const int ld = round4(Hd), ld3 = round4(2 * c_t);
+  float* w3 = p.packed + 9LL * p.c_in * ld + (long long)Hd * ld;
+  float* b3 = w3 + 9LL * Hd * ld3;
+  const int o = blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= 2 * c_t) return;
+  const float* v = p.params[4] + (long long)o * Hd * 9;
+  float ss = 0.f;
+  for (int i = 0; i < Hd * 9; ++i) ss = fmaf(v[i], v[i], ss);
+  const float mul = p.params[3][o] / sqrtf(ss);
+  const int slot = o < c_t ? 2 * o : 2 * (o - c_t) + 1;
+  for (int j = 0; j < Hd; ++j) {
+    for (int tap = 0; tap < 9; ++tap) w3[(long long)(tap * Hd + j) * ld3 + slot] = v[j * 9 + tap] * mul;
+  }
+  b3[slot] = p.params[2][o];
+}
+
+}  // namespace macow

@@ -30,8 +30,10 @@
 
 #ifdef MACOW_HOST_EMULATION
 #define MACOW_FAST_EXP(v) expf(v)
+#define MACOW_SHARED static               // function-scope shared arrays: one copy for all emulated threads
 #else
 #define MACOW_FAST_EXP(v) __expf(v)
+#define MACOW_SHARED __shared__
 #endif
 
 namespace macow {
@@ -52,6 +54,7 @@ struct UnitParams {
   int hid_floats;               // floats of the hidden-activation area (tile x ksplit), 4-float aligned
   int ksplit;                   // inverse: groups of threads sharing the input-channel loop of one line (>= 1)
   long long unit_floats;
+  long long in_stride, out_stride;  // floats between consecutive samples of in / out (C * H * W when dense)
 };
 
 __host__ __device__ inline long long flow_floats(int C, int Hd, int k0, int k1) {
@@ -304,7 +307,7 @@ __global__ void __launch_bounds__(512, 1) macow_unit_kernel(const UnitParams p) 
   float* hid = smem + 2 * n4;
   float* wsm = hid + p.hid_floats;          // kWS only: one flow's weights
   const int b = blockIdx.x;
-  const float* src = p.in + (long long)b * n;
+  const float* src = p.in + (long long)b * p.in_stride;
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
     const int c = i / HW, rem = i - c * HW;
     const int y = rem / W, x = rem - y * W;
@@ -327,11 +330,11 @@ __global__ void __launch_bounds__(512, 1) macow_unit_kernel(const UnitParams p) 
       mcf_stage<kReverse, kK1, kQC, kWS>(XA, XB, hid, wsm, up + flow * ff, p, flow, logdet_acc);
     }
   }
-  float* dst = p.out + (long long)b * n;
+  float* dst = p.out + (long long)b * p.out_stride;
   for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = XA[i];
   if (!kReverse && p.logdet != nullptr) {
     // deterministic block reduction (fixed item -> thread mapping, fixed tree)
-    __shared__ float red[16];
+    MACOW_SHARED float red[16];
     float v = logdet_acc;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -23,6 +23,44 @@ class MacowDesc(ctypes.Structure):
                 ("activation", ctypes.c_int32), ("alpha", ctypes.c_float)]
 
 
+class NiceDesc(ctypes.Structure):
+    _fields_ = [("c_in", ctypes.c_int32), ("z_off", ctypes.c_int32), ("z_stride", ctypes.c_int32),
+                ("c_t", ctypes.c_int32), ("p_off", ctypes.c_int32), ("p_stride", ctypes.c_int32),
+                ("hidden", ctypes.c_int32), ("activation", ctypes.c_int32), ("alpha", ctypes.c_float)]
+
+
+def _bind(L):
+    """Argument types of the entry points of include/ipoke_macow.h on a loaded library."""
+    vp, i32, i64, sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_size_t
+    dp, ndp = ctypes.POINTER(MacowDesc), ctypes.POINTER(NiceDesc)
+    L.ipoke_macow_unit_floats.restype = sz
+    L.ipoke_macow_unit_floats.argtypes = [dp]
+    L.ipoke_macow_pack_unit.restype = i32
+    L.ipoke_macow_pack_unit.argtypes = [dp, ctypes.POINTER(vp), vp, vp]
+    L.ipoke_macow_forward.restype = i32
+    L.ipoke_macow_forward.argtypes = [dp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
+    L.ipoke_macow_reverse.restype = i32
+    L.ipoke_macow_reverse.argtypes = [dp, vp, i32, vp, vp, i32, i32, i32, i32, i32, vp]
+    L.ipoke_macow_units_forward.restype = i32
+    L.ipoke_macow_units_forward.argtypes = [dp, vp, i32, vp, i64, vp, i64, vp, i32, i32, i32, i32, i32, i32, vp]
+    L.ipoke_macow_units_reverse.restype = i32
+    L.ipoke_macow_units_reverse.argtypes = [dp, vp, i32, vp, i64, vp, i64, i32, i32, i32, i32, i32, vp]
+    L.ipoke_macow_launch_info.restype = i32
+    L.ipoke_macow_launch_info.argtypes = [dp, i32, i32, i32, ctypes.POINTER(i32), ctypes.POINTER(i32),
+                                          ctypes.POINTER(i32)]
+    L.ipoke_macow_nice_floats.restype = sz
+    L.ipoke_macow_nice_floats.argtypes = [ndp]
+    L.ipoke_macow_pack_nice.restype = i32
+    L.ipoke_macow_pack_nice.argtypes = [ndp, ctypes.POINTER(vp), vp, vp]
+    L.ipoke_macow_nice_workspace_floats.restype = sz
+    L.ipoke_macow_nice_workspace_floats.argtypes = [ndp, i32, i32, i32]
+    L.ipoke_macow_nice.restype = i32
+    L.ipoke_macow_nice.argtypes = [ndp, vp, vp, i64, vp, i32, i32, i32, i32, vp, sz, vp]
+    L.ipoke_macow_chanmap.restype = i32
+    L.ipoke_macow_chanmap.argtypes = [vp, i64, i32, i32, i32, vp, i32, vp, vp, i32, i32, i32, i32, vp, vp]
+    return L
+
+
 _bound = False
 
 
@@ -30,19 +68,7 @@ def _lib():
     global _bound
     L = _capi.lib()
     if not _bound:
-        vp, i32 = ctypes.c_void_p, ctypes.c_int
-        dp = ctypes.POINTER(MacowDesc)
-        L.ipoke_macow_unit_floats.restype = ctypes.c_size_t
-        L.ipoke_macow_unit_floats.argtypes = [dp]
-        L.ipoke_macow_pack_unit.restype = i32
-        L.ipoke_macow_pack_unit.argtypes = [dp, ctypes.POINTER(vp), vp, vp]
-        L.ipoke_macow_forward.restype = i32
-        L.ipoke_macow_forward.argtypes = [dp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
-        L.ipoke_macow_reverse.restype = i32
-        L.ipoke_macow_reverse.argtypes = [dp, vp, i32, vp, vp, i32, i32, i32, i32, i32, vp]
-        L.ipoke_macow_launch_info.restype = i32
-        L.ipoke_macow_launch_info.argtypes = [dp, i32, i32, i32, ctypes.POINTER(i32), ctypes.POINTER(i32),
-                                              ctypes.POINTER(i32)]
+        _bind(L)
         _bound = True
     return L
 

@@ -65,6 +65,7 @@ void emul_run(const float* packed, int n_units, const float* in, float* out, flo
   p.B = B; p.C = C; p.Hd = Hd; p.H = H; p.W = W; p.k0 = k0; p.k1 = k1; p.alpha = alpha;
   p.stage_begin = s0; p.stage_end = s1; p.tile_lines = tile_lines; p.accumulate = accumulate;
   p.unit_floats = macow::unit_floats(C, Hd, k0, k1);
+  p.in_stride = p.out_stride = (long long)C * H * W;
   blockDim.x = 1; gridDim.x = B; threadIdx.x = 0;
   p.act = act;
   p.ksplit = ksplit;
