@@ -166,4 +166,15 @@ int ipoke_macow_chanmap(float* x, long long x_stride, int B, int H, int W, const
                             norm_first, logdet);
 }
 
+int ipoke_macow_launch_info(const ipoke_macow_desc* d, int H, int W, int reverse, int* smem_bytes, int* threads,
+                            int* tile_lines) {
+  if (int e = macow::check_desc(d)) return e;
+  Geometry g;
+  if (int e = macow::geometry(d, 1, H, W, reverse != 0, &g)) return e;
+  if (smem_bytes) *smem_bytes = g.smem_bytes;
+  if (threads) *threads = g.threads;
+  if (tile_lines) *tile_lines = g.tile_lines;
+  return IPOKE_INN_OK;
+}
+
 }  // extern "C"

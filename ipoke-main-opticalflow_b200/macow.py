@@ -106,11 +106,11 @@ class _WeightNormedConv(nn.Module):
     """``nn.utils.weight_norm(nn.Conv2d(hidden, out, 1))`` as plain parameters bias / weight_g / weight_v in the
     reference's registration order, drawing the same random numbers (macow_utils.py:216-233)."""
 
-    def __init__(self, in_channels, out_channels):
+    def __init__(self, in_channels, out_channels, kernel_size=1):
         super().__init__()
-        w = torch.empty(out_channels, in_channels, 1, 1)
+        w = torch.empty(out_channels, in_channels, kernel_size, kernel_size)
         nn.init.kaiming_uniform_(w, a=math.sqrt(5))                    # nn.Conv2d.reset_parameters: weight ...
-        bound = 1 / math.sqrt(in_channels)
+        bound = 1 / math.sqrt(in_channels * kernel_size * kernel_size)
         self.bias = nn.Parameter(torch.empty(out_channels))
         nn.init.uniform_(self.bias, -bound, bound)                     # ... and bias
         nn.init.normal_(w, mean=0.0, std=0.05)                         # macow_utils.py:227
@@ -120,11 +120,12 @@ class _WeightNormedConv(nn.Module):
 
 
 class Conv2dWeightNorm(nn.Module):
-    """macow_utils.py:211-251 for the 1x1 / zero_init case MCFBlock uses."""
+    """macow_utils.py:211-251 for the zero_init cases: the 1x1 convolution of MCFBlock and the 3x3 one (padding 1) that
+    ends NICEConvBlock (macow_utils.py:283)."""
 
-    def __init__(self, in_channels, out_channels, zero_init=True):
+    def __init__(self, in_channels, out_channels, zero_init=True, kernel_size=1):
         super().__init__()
-        self.conv = _WeightNormedConv(in_channels, out_channels)
+        self.conv = _WeightNormedConv(in_channels, out_channels, kernel_size)
         self.register_buffer("initialized", torch.tensor(0, dtype=torch.uint8))
         self.zero_init = zero_init
 
@@ -132,7 +133,7 @@ class Conv2dWeightNorm(nn.Module):
         """Conv2dWeightNorm.init with init_scale = 0 (macow_utils.py:235-251, zero_init): the gain becomes
         0 / (std + 1e-6) = 0 and the bias -mean * 0 = 0 whatever the (finite) activations are."""
         if not self.zero_init:
-            raise NotImplementedError("only the zero_init 1x1 convolution of MCFBlock is built")
+            raise NotImplementedError("only the zero_init convolutions of MCFBlock / NICEConvBlock are built")
         with torch.no_grad():
             self.conv.weight_g.zero_()
             self.conv.bias.zero_()

@@ -1,0 +1,168 @@
+"""The full MaCow flow on the CPU: the Python host code of ipoke-main-opticalflow_b200/macow_flow.py driving a g++ build
+of the DEVICE code (csrc/macow_kernel.cuh, csrc/macow_flow_kernel.cuh) and of the launch logic (csrc/macow_flow_host.h)
+through tests/emulation/macow_flow_emul.cpp: every CUDA thread is a fiber, __syncthreads() a scheduler round, CTAs run
+with the real thread counts / grids / shared-memory carving, in ascending and in descending thread order (a missing
+barrier gives a wrong result in one of the two).  Checked against the fixtures of the live reference
+(tests/golden/macow_stack_*.npz) and the float64 oracle.  The emulation library is handed to the host code by
+monkeypatching; the package itself never loads it (CPU tensors raise in the product path -- asserted below)."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+import torch
+
+import ipoke_inn_b200 as P
+from ipoke_inn_b200 import macow
+from oracle import macow_stack_oracle as so
+from conftest import max_rel
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+SRC = os.path.join(HERE, "emulation", "macow_flow_emul.cpp")
+OUT = os.path.join(HERE, "emulation", "_build", "libmacow_flow_emul.so")
+DEPS = [SRC, os.path.join(HERE, "emulation", "cuda_emul.h")] + [
+    os.path.join(ROOT, "ipoke-main-opticalflow_b200", "csrc", f)
+    for f in ("macow_kernel.cuh", "macow_flow_kernel.cuh", "macow_flow_host.h")] + [
+    os.path.join(ROOT, "include", "ipoke_macow.h")]
+
+
+@pytest.fixture(scope="module")
+def emul_lib():
+    os.makedirs(os.path.dirname(OUT), exist_ok=True)
+    if not os.path.exists(OUT) or os.path.getmtime(OUT) < max(os.path.getmtime(f) for f in DEPS):
+        subprocess.run(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes",
+                        "-I", os.path.join(ROOT, "include"), "-o", OUT, SRC], check=True)
+    return macow._bind(ctypes.CDLL(OUT))
+
+
+@pytest.fixture()
+def emulated(emul_lib, monkeypatch):
+    """The host code's three touch points with CUDA, redirected: library, stream, the CUDA-only input check."""
+    def check(x, channels):
+        assert x.dim() == 4 and x.shape[1] == channels and x.dtype == torch.float32
+        return x.contiguous()
+    monkeypatch.setattr(macow, "_lib", lambda: emul_lib)
+    monkeypatch.setattr(macow, "_stream", lambda dev: None)
+    monkeypatch.setattr(macow, "_check_input", check)
+    emul_lib.emul_set_descending(0)
+    return emul_lib
+
+
+def load(name):
+    g = np.load(os.path.join(HERE, "golden", name + ".npz"))
+    sd = {k[4:]: torch.from_numpy(g[k]) for k in g.files if k.startswith("sd::")}
+    C, mid, factor, k0, k1 = (int(v) for v in g["meta"])
+    cfg = dict(num_steps=[int(v) for v in g["num_steps"]], flow_in_channels=C, flow_mid_channels=mid, factor=factor,
+               transform="affine", prior_transform="affine", kernel_size=[k0, k1], coupling_type="conv",
+               activation=str(g["activation"]))
+    return g, sd, cfg
+
+
+def test_product_path_refuses_cpu_tensors():
+    g, sd, cfg = load("macow_stack_a")
+    net = P.UnsupervisedMaCowTransformer3(cfg)
+    with torch.no_grad(), pytest.raises(RuntimeError, match="CUDA"):
+        net(torch.from_numpy(g["x"]))
+
+
+def test_construction_matches_the_reference_draw_for_draw():
+    """Same seed -> the reference's constructor-time weights and permutations, same keys / shapes / dtypes."""
+    for name in ("macow_stack_a", "macow_stack_b"):
+        g, sd, cfg = load(name)
+        torch.manual_seed(42)
+        fresh = P.UnsupervisedMaCowTransformer3(cfg).state_dict()
+        assert list(fresh.keys()) == list(sd.keys())
+        for k, v in sd.items():
+            assert fresh[k].shape == v.shape and fresh[k].dtype == v.dtype, k
+            if k.endswith(("shuffle_idx", "weight_v", "conv1.weight", "conv2.weight", "shift_conv.weight")):
+                assert torch.equal(fresh[k], v), k                     # untouched by the data-dependent initialisation
+
+
+def test_first_call_initialisation(emulated):
+    g, sd, cfg = load("macow_stack_b")
+    torch.manual_seed(42)
+    net = P.UnsupervisedMaCowTransformer3(cfg).eval()
+    with torch.no_grad():
+        out, ld = net(torch.from_numpy(g["x"]))
+    assert max_rel(out.numpy(), g["init_out"]) <= 2e-5 and max_rel(ld.numpy(), g["init_logdet"]) <= 2e-5
+    new = net.state_dict()
+    for k in g.files:
+        if k.startswith("init::"):
+            np.testing.assert_allclose(new[k[6:]].numpy(), g[k], rtol=1e-4, atol=2e-5, err_msg=k)
+    assert all(int(v) == 1 for k, v in new.items() if k.endswith("initialized"))
+    with torch.no_grad():                                              # second call takes the plain program
+        out2, ld2 = net(torch.from_numpy(g["x"]))
+    assert max_rel(out2.numpy(), out.numpy()) <= 1e-6 and max_rel(ld2.numpy(), ld.numpy()) <= 1e-6
+
+
+@pytest.mark.parametrize("name,descending", [("macow_stack_a", 0), ("macow_stack_b", 1)])
+def test_flow_matches_reference_fixtures(emulated, name, descending):
+    g, sd, cfg = load(name)
+    net = P.UnsupervisedMaCowTransformer3(cfg).eval()
+    net.load_state_dict(sd)
+    emulated.emul_set_descending(descending)
+    x = torch.from_numpy(g["x"])
+    with torch.no_grad():
+        out, ld = net(x)
+        smp = net(torch.from_numpy(g["z_in"]), reverse=True)
+    assert torch.equal(x, torch.from_numpy(g["x"]))                    # the caller's tensor is not modified
+    assert max_rel(out.numpy(), g["out64"]) <= 2e-5 and max_rel(ld.numpy(), g["logdet64"]) <= 2e-5
+    assert max_rel(out.numpy(), g["out"]) <= 2e-5
+    assert max_rel(smp.numpy(), g["x_smp64"]) <= 2e-4 and max_rel(smp.numpy(), g["x_smp"]) <= 2e-4
+
+
+def test_components_called_like_the_reference_calls_them(emulated):
+    """One NICE2d per split type / order, one step, one prior."""
+    g, sd, cfg = load("macow_stack_a")
+    net = P.UnsupervisedMaCowTransformer3(cfg).eval()
+    net.load_state_dict(sd)
+    emulated.emul_set_descending(1)
+    x, z = torch.from_numpy(g["x"]), torch.from_numpy(g["z_in"])
+    step = net.flow.layers[0][0]
+    with torch.no_grad():
+        for cn in ("coupling1_up", "coupling1_dn", "coupling2_up", "coupling2_dn"):
+            o, l = getattr(step, cn)(x)
+            assert max_rel(o.numpy(), g[cn + "_out"]) <= 2e-5 and max_rel(l.numpy(), g[cn + "_logdet"]) <= 2e-5, cn
+            assert max_rel(getattr(step, cn)(z, reverse=True).numpy(), g[cn + "_rev"]) <= 2e-5, cn
+        o, l = step(x)
+        assert max_rel(o.numpy(), g["step_out"]) <= 2e-5 and max_rel(l.numpy(), g["step_logdet"]) <= 2e-5
+        assert max_rel(step(z, reverse=True).numpy(), g["step_rev"]) <= 2e-4
+        o, l = net.flow.priors[0](x)
+        assert max_rel(o.numpy(), g["prior_out"]) <= 2e-5 and max_rel(l.numpy(), g["prior_logdet"]) <= 2e-5
+        assert max_rel(net.flow.priors[0](z, reverse=True).numpy(), g["prior_rev"]) <= 2e-5
+
+
+def test_coupling_rows_beyond_one_tile_and_workspace_passes(emulated):
+    """A coupling on 3 x 7 x 9 pixels = 189 rows (two 128-row tiles, the second ragged) with hidden width 40 (not a
+    multiple of the 16-deep K slice, one ragged 128-column tile) and a workspace of 2 samples (passes of 2 + 1)."""
+    rng = np.random.default_rng(5)
+    C, Hd, B, H, W = 6, 40, 3, 7, 9
+    nice = P.NICE2d(C, hidden_channels=Hd, split_type="continuous", order="down", factor=3, activation="leaky_relu",
+                    alpha=0.8).eval()
+    with torch.no_grad():
+        nice.net.conv3.conv.weight_g.copy_(torch.from_numpy(0.2 + 0.3 * rng.random((4, 1, 1, 1)).astype(np.float32)))
+        nice.net.conv3.conv.bias.copy_(torch.from_numpy(0.1 * rng.standard_normal(4).astype(np.float32)))
+        nice.net.conv3.initialized.fill_(1)
+    sd = {k: v.numpy() for k, v in nice.state_dict().items()}
+    x = rng.standard_normal((B, C, H, W)).astype(np.float32)
+    want, want_ld = so.nice_apply(sd, x, False, "continuous", 3, "leaky_relu", 0.8)
+    d = nice._desc
+    n = emulated.ipoke_macow_nice_floats(ctypes.byref(d))
+    packed = np.zeros(n, dtype=np.float32)
+    arrs = [p.detach().numpy() for p in nice.params()]
+    ptrs = (ctypes.c_void_p * 5)(*[a.ctypes.data for a in arrs])
+    assert emulated.ipoke_macow_pack_nice(ctypes.byref(d), ptrs, packed.ctypes.data, None) == 0
+    ws = np.zeros(2 * H * W * (2 * Hd + 1), dtype=np.float32)
+    got, ld = x.copy(), np.full(B, 1.5, dtype=np.float32)
+    assert emulated.ipoke_macow_nice(ctypes.byref(d), packed.ctypes.data, got.ctypes.data, C * H * W, ld.ctypes.data, 0,
+                                     B, H, W, ws.ctypes.data, ws.size, None) == 0
+    assert max_rel(got, want) <= 1e-5 and max_rel(ld - 1.5, want_ld) <= 1e-5
+    back = got.copy()
+    assert emulated.ipoke_macow_nice(ctypes.byref(d), packed.ctypes.data, back.ctypes.data, C * H * W, None, 1, B, H, W,
+                                     ws.ctypes.data, ws.size, None) == 0
+    assert max_rel(back, x) <= 1e-5
+    # a workspace smaller than one sample is refused
+    assert emulated.ipoke_macow_nice(ctypes.byref(d), packed.ctypes.data, back.ctypes.data, C * H * W, None, 1, B, H, W,
+                                     ws.ctypes.data, H * W * (2 * Hd + 1) - 1, None) != 0

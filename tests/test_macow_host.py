@@ -44,8 +44,10 @@ def test_state_dict_keys_shapes_and_rng_order(name):
 def test_header_symbols_are_exported():
     hdr = open(os.path.join(ROOT, "include", "ipoke_macow.h")).read()
     names = sorted(set(re.findall(r"\b(ipoke_macow_[a-z_]+)\s*\(", hdr)))
-    assert names == ["ipoke_macow_forward", "ipoke_macow_launch_info", "ipoke_macow_pack_unit", "ipoke_macow_reverse",
-                     "ipoke_macow_unit_floats"]
+    assert names == ["ipoke_macow_chanmap", "ipoke_macow_forward", "ipoke_macow_launch_info", "ipoke_macow_nice",
+                     "ipoke_macow_nice_floats", "ipoke_macow_nice_workspace_floats", "ipoke_macow_pack_nice",
+                     "ipoke_macow_pack_unit", "ipoke_macow_reverse", "ipoke_macow_unit_floats",
+                     "ipoke_macow_units_forward", "ipoke_macow_units_reverse"]
     L = _capi.lib()
     for n in names:
         assert hasattr(L, n), n
@@ -82,3 +84,27 @@ def test_unbuilt_variants_and_cpu_tensors_fail_loudly():
     with torch.no_grad(), pytest.raises(RuntimeError, match="CUDA"):
         unit(torch.randn(2, 4, 6, 6))
     assert "MaCowUnit" in P.__all__
+
+
+def test_flow_sizes_argument_errors_and_unbuilt_variants_without_gpu():
+    L = macow._lib()
+    d = macow.NiceDesc(16, 0, 1, 16, 16, 1, 2048, 1, 1.0)        # continuous / up coupling of a 32-channel step
+    assert L.ipoke_macow_nice_floats(ctypes.byref(d)) == 9 * 16 * 2048 + 2048 * 2048 + 9 * 2048 * 32 + 32
+    # preferred workspace: as many samples as keep two hidden-activation buffers within 48 MB (8 x 8 latents: 47)
+    per_sample = 64 * (2 * 2048 + 1)
+    assert L.ipoke_macow_nice_workspace_floats(ctypes.byref(d), 4096, 8, 8) == (48 * 2 ** 20 // 4 // per_sample) * per_sample
+    assert L.ipoke_macow_nice_workspace_floats(ctypes.byref(d), 3, 8, 8) == 3 * per_sample
+    assert L.ipoke_macow_nice_floats(ctypes.byref(macow.NiceDesc(0, 0, 1, 16, 16, 1, 64, 1, 1.0))) == 0
+    assert L.ipoke_macow_nice(ctypes.byref(d), None, None, 0, None, 0, 1, 8, 8, None, 0, None) == -1     # NULL pointers
+    assert L.ipoke_macow_chanmap(None, 0, 1, 8, 8, None, 0, None, None, 0, 0, 0, 0, None, None) == -1
+    cfg = dict(num_steps=[1], flow_in_channels=8, flow_mid_channels=16, factor=4, transform="affine",
+               prior_transform="affine", kernel_size=[2, 3], coupling_type="conv", activation="elu")
+    net = P.UnsupervisedMaCowTransformer3(cfg)
+    assert net.flow.z_channels == 6 and net.flow._program is None
+    assert [op[0] for op in net.flow.ops()] == ["glue", "units", "nice", "nice", "glue", "units", "nice", "nice",
+                                                 "glue", "nice", "glue"]
+    for bad in (dict(cfg, transform="nlsq"), dict(cfg, use1x1=True), dict(cfg, prior_transform="additive")):
+        with pytest.raises(NotImplementedError):
+            P.UnsupervisedMaCowTransformer3(bad)
+    with pytest.raises(NotImplementedError):
+        P.NICE2d(8, h_channels=4)

@@ -1,0 +1,148 @@
+"""GPU parity of the full MaCow flow (row N3): ``UnsupervisedMaCowTransformer3`` and its parts through the CUDA kernels
+behind include/ipoke_macow.h, against the fixtures of the live reference (tests/golden/macow_stack_*.npz) and the float64
+oracle (oracle/macow_stack_oracle.py) on seeded inputs.
+
+Tolerance: the reference computes this path in float32; the kernels are float32 with a different summation order:
+max |a - b| / max |b| <= 2e-5 forward and log-determinant, 2e-4 through the inverse (the units' sequential line loops).
+Collected late (file name) so that a failure here cannot hide the tests of the flat-INN path under ``pytest -x``."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import ipoke_inn_b200 as P
+from oracle import macow_stack_oracle as so
+from conftest import max_rel
+from test_macow_flow_emulation import load
+
+pytestmark = pytest.mark.gpu
+TOL_FWD, TOL_REV = 2e-5, 2e-4
+
+
+def make(cfg, sd, dev):
+    net = P.UnsupervisedMaCowTransformer3(cfg)
+    net.load_state_dict(sd)
+    return net.to(dev).eval()
+
+
+@pytest.mark.parametrize("name", ["macow_stack_a", "macow_stack_b"])
+def test_reference_fixtures(name):
+    dev = torch.device("cuda:0")
+    g, sd, cfg = load(name)
+    net = make(cfg, sd, dev)
+    x = torch.from_numpy(g["x"]).to(dev)
+    with torch.no_grad():
+        out, ld = net(x)
+        smp = net(torch.from_numpy(g["z_in"]).to(dev), reverse=True)
+        back = net(out, reverse=True)
+        out2, ld2 = net(x)
+    assert torch.equal(x.cpu(), torch.from_numpy(g["x"]))
+    assert max_rel(out.cpu().numpy(), g["out64"]) <= TOL_FWD and max_rel(out.cpu().numpy(), g["out"]) <= TOL_FWD
+    assert max_rel(ld.cpu().numpy(), g["logdet64"]) <= TOL_FWD
+    assert max_rel(smp.cpu().numpy(), g["x_smp64"]) <= TOL_REV and max_rel(smp.cpu().numpy(), g["x_smp"]) <= TOL_REV
+    assert max_rel(back.cpu().numpy(), g["x"]) <= TOL_REV
+    assert torch.equal(out, out2) and torch.equal(ld, ld2)             # deterministic: fixed summation orders
+
+
+def test_components_called_like_the_reference_calls_them():
+    dev = torch.device("cuda:0")
+    g, sd, cfg = load("macow_stack_a")
+    net = make(cfg, sd, dev)
+    x, z = torch.from_numpy(g["x"]).to(dev), torch.from_numpy(g["z_in"]).to(dev)
+    step = net.flow.layers[0][0]
+    with torch.no_grad():
+        for cn in ("coupling1_up", "coupling1_dn", "coupling2_up", "coupling2_dn"):
+            o, l = getattr(step, cn)(x)
+            assert max_rel(o.cpu().numpy(), g[cn + "_out"]) <= TOL_FWD, cn
+            assert max_rel(l.cpu().numpy(), g[cn + "_logdet"]) <= TOL_FWD, cn
+            assert max_rel(getattr(step, cn)(z, reverse=True).cpu().numpy(), g[cn + "_rev"]) <= TOL_FWD, cn
+        o, l = step(x)
+        assert max_rel(o.cpu().numpy(), g["step_out"]) <= TOL_FWD and max_rel(l.cpu().numpy(), g["step_logdet"]) <= TOL_FWD
+        assert max_rel(step(z, reverse=True).cpu().numpy(), g["step_rev"]) <= TOL_REV
+        o, l = net.flow.priors[0](x)
+        assert max_rel(o.cpu().numpy(), g["prior_out"]) <= TOL_FWD and max_rel(l.cpu().numpy(), g["prior_logdet"]) <= TOL_FWD
+        assert max_rel(net.flow.priors[0](z, reverse=True).cpu().numpy(), g["prior_rev"]) <= TOL_FWD
+
+
+def test_first_call_initialisation_matches_reference():
+    dev = torch.device("cuda:0")
+    g, sd, cfg = load("macow_stack_b")
+    torch.manual_seed(42)
+    net = P.UnsupervisedMaCowTransformer3(cfg).to(dev).eval()
+    with torch.no_grad():
+        out, ld = net(torch.from_numpy(g["x"]).to(dev))
+    assert max_rel(out.cpu().numpy(), g["init_out"]) <= TOL_FWD and max_rel(ld.cpu().numpy(), g["init_logdet"]) <= TOL_FWD
+    new = {k: v.cpu().numpy() for k, v in net.state_dict().items()}
+    for k in g.files:
+        if k.startswith("init::"):
+            np.testing.assert_allclose(new[k[6:]], g[k], rtol=1e-4, atol=2e-5, err_msg=k)
+    assert all(int(v) == 1 for k, v in new.items() if k.endswith("initialized"))
+
+
+def randomise(net, seed):
+    """Non-trivial gains / biases for every zero-initialised convolution and ActNorm (a fresh flow is the identity)."""
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for k, p in net.state_dict().items():
+            if k.endswith("weight_g"):
+                p.copy_(0.1 + 0.3 * torch.rand(p.shape, generator=g))
+            elif k.endswith("conv.bias") or k.endswith("actnorm.bias") or k.endswith("actnorm1.bias") or k.endswith("actnorm2.bias"):
+                p.copy_(0.1 * torch.randn(p.shape, generator=g))
+            elif k.endswith("log_scale"):
+                p.copy_(0.1 * torch.randn(p.shape, generator=g))
+            elif k.endswith("initialized"):
+                p.fill_(1)
+    return net
+
+
+SHAPES = [  # channels, hidden of the couplings, factor, num_steps, H, W, batch, activation, coupling-pass budget (MB)
+    (32, 96, 16, [1, 1], 8, 8, 37, "elu", None),         # z_dim-32 latents at 8 x 8 (config/second_stage.yaml), 19 row tiles
+    (16, 136, 4, [1, 1, 1], 16, 16, 5, "elu", "1"),      # 16 x 16 latents; 1 MB budget: 3 samples per coupling pass (2 passes)
+    (12, 20, 4, [2], 5, 7, 3, "leaky_relu", None),       # non-square, odd level widths
+]
+
+
+@pytest.mark.parametrize("C,mid,factor,steps,H,W,B,act,mb", SHAPES)
+def test_against_float64_oracle(C, mid, factor, steps, H, W, B, act, mb, monkeypatch):
+    dev = torch.device("cuda:0")
+    if mb is not None:
+        monkeypatch.setenv("IPOKE_MACOW_NICE_MB", mb)
+    cfg = dict(num_steps=steps, flow_in_channels=C, flow_mid_channels=mid, factor=factor, transform="affine",
+               prior_transform="affine", kernel_size=[2, 3], coupling_type="conv", activation=act)
+    torch.manual_seed(C)
+    net = randomise(P.UnsupervisedMaCowTransformer3(cfg), 100 + C).to(dev).eval()
+    sd = so.sub({k: v.cpu().numpy() for k, v in net.state_dict().items()}, "flow.")
+    rng = np.random.default_rng(C)
+    x = rng.standard_normal((B, C, H, W)).astype(np.float32)
+    z = rng.standard_normal((B, C, H, W)).astype(np.float32)
+    want, want_ld = so.flow_forward(sd, x, steps, factor, act)
+    want_rev = so.flow_reverse(sd, z, steps, factor, act)
+    with torch.no_grad():
+        out, ld = net(torch.from_numpy(x).to(dev))
+        got = net(torch.from_numpy(z).to(dev), reverse=True)
+        back = net(out, reverse=True)
+    assert max_rel(out.cpu().numpy(), want) <= TOL_FWD and max_rel(ld.cpu().numpy(), want_ld) <= TOL_FWD
+    assert max_rel(got.cpu().numpy(), want_rev) <= TOL_REV
+    assert max_rel(back.cpu().numpy(), x) <= TOL_REV
+
+
+def test_large_batch_round_trip_and_sample():
+    dev = torch.device("cuda:0")
+    cfg = dict(num_steps=[1, 1], flow_in_channels=8, flow_mid_channels=64, factor=4, transform="affine",
+               prior_transform="affine", kernel_size=[2, 3], coupling_type="conv", activation="elu")
+    torch.manual_seed(3)
+    net = randomise(P.UnsupervisedMaCowTransformer3(cfg), 7).to(dev).eval()
+    x = torch.randn(2048, 8, 8, 8, device=dev)
+    with torch.no_grad():
+        z, ld = net(x)
+        back = net(z, reverse=True)
+        smp = net.sample((4, 8, 8, 8), device=dev)
+    assert torch.isfinite(ld).all() and torch.isfinite(smp).all() and smp.shape == (4, 8, 8, 8)
+    assert max_rel(back.cpu().numpy(), x.cpu().numpy()) <= TOL_REV
+    # rows of a batch are independent: the first 16 samples alone give the same result
+    with torch.no_grad():
+        z16, ld16 = net(x[:16])
+    assert max_rel(z16.cpu().numpy(), z[:16].cpu().numpy()) <= 1e-6 and max_rel(ld16.cpu().numpy(), ld[:16].cpu().numpy()) <= 1e-6
+    with pytest.raises(NotImplementedError):
+        net(x.requires_grad_())
