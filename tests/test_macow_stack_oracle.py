@@ -66,3 +66,17 @@ def test_level_bookkeeping_matches_the_state_dict():
         assert sd[f"flow.priors.{i}.coupling.net.conv1.weight"].shape[:2] == (m["mid"], c_in)
         assert sd[f"flow.priors.{i}.coupling.net.conv3.conv.weight_v"].shape[0] == 2 * c_t
         assert f"flow.layers.{i}.{n - 1}.actnorm1.bias" in sd and f"flow.layers.{i}.{n}.actnorm1.bias" not in sd
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_torch_restatement_matches_the_reference(name):
+    """oracle/macow_stack_oracle_torch.py (the op sequence the bench times as the reference's stock path)."""
+    import torch
+    from oracle.macow_stack_oracle_torch import TorchFlow
+    g, sd, m = load(name)
+    flow = TorchFlow(so.sub(sd, "flow."), m["C"], m["num_steps"], m["factor"], m["act"])
+    with torch.no_grad():
+        out, ld = flow.forward(torch.from_numpy(g["x"]))
+        smp = flow.reverse(torch.from_numpy(g["z_in"]))
+    assert max_rel(out.numpy(), g["out"]) <= 2e-6 and max_rel(ld.numpy(), g["logdet"]) <= 2e-6
+    assert max_rel(smp.numpy(), g["x_smp"]) <= 1e-5
