@@ -98,7 +98,7 @@ typedef struct ipoke_macow_nice_desc {
 } ipoke_macow_nice_desc;
 
 /* Floats of one packed coupling net (the three convolutions transposed to [K][N] with N padded to 4, the last one
- * weight-normed with (shift, log-scale) column pairs, and its bias). */
+ * weight-normed, its nine taps side by side with (shift, log-scale) column pairs, and its bias). */
 size_t ipoke_macow_nice_floats(const ipoke_macow_nice_desc* desc);
 
 /* `params`: HOST array of 5 device pointers, float32 contiguous, in state_dict order:
@@ -106,8 +106,9 @@ size_t ipoke_macow_nice_floats(const ipoke_macow_nice_desc* desc);
  *   net.conv3.conv.weight_g [2 c_t], net.conv3.conv.weight_v [2 c_t, hidden, 3, 3]. */
 int ipoke_macow_pack_nice(const ipoke_macow_nice_desc* desc, const void* const* params, float* packed, void* stream);
 
-/* Preferred workspace (floats) for batch B: two pixel-major hidden-activation buffers and the per-row log-determinants
- * of as many samples as keep a pass in L2.  Any size >= H * W * (2 * hidden + 1) works (fewer samples per pass). */
+/* Preferred workspace (floats) for batch B: two pixel-major hidden-activation buffers and the nine tap outputs of the
+ * last convolution for as many samples as keep a pass in L2.  Any size >= H * W * (2 * hidden + 9 * round4(2 * c_t))
+ * works (fewer samples per pass). */
 size_t ipoke_macow_nice_workspace_floats(const ipoke_macow_nice_desc* desc, int B, int H, int W);
 
 /* Forward (reverse == 0: transformed channels <- scale * x + shift, logdet[b] += sum log scale; logdet nullable) or

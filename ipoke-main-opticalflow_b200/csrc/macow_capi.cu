@@ -21,8 +21,8 @@ struct CudaLauncher {
     macow::nice_gemm_kernel<kSrc, kEpi, BM, BN, TM, TN><<<dim3(gx, gy), macow::kGemmThreads, 0, s>>>(p);
     return (int)cudaGetLastError();
   }
-  int rowsum(int blocks, int threads, const float* rowld, float* logdet, int nb, int HW) {
-    macow::macow_rowsum_kernel<<<blocks, threads, 0, s>>>(rowld, logdet, nb, HW);
+  int affine(int blocks, int threads, const macow::AffineParams& p) {
+    macow::nice_affine_kernel<<<blocks, threads, 0, s>>>(p);
     return (int)cudaGetLastError();
   }
   int chanmap(int B, int threads, size_t smem, const macow::ChanMapParams& p) {
@@ -149,7 +149,7 @@ int ipoke_macow_pack_nice(const ipoke_macow_nice_desc* d, const void* const* par
 
 size_t ipoke_macow_nice_workspace_floats(const ipoke_macow_nice_desc* d, int B, int H, int W) {
   if (macow::check_nice(d) || B < 1 || H < 1 || W < 1) return 0;
-  return (size_t)macow::nice_chunk_samples(d, B, H, W, ~(size_t)0) * H * W * (2 * (size_t)d->hidden + 1);
+  return (size_t)macow::nice_chunk_samples(d, B, H, W, ~(size_t)0) * (size_t)macow::nice_sample_floats(d, H, W);
 }
 
 int ipoke_macow_nice(const ipoke_macow_nice_desc* d, const float* packed, float* x, long long x_stride, float* logdet,

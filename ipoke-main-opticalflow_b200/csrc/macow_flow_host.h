@@ -111,12 +111,18 @@ inline int check_nice(const ipoke_macow_nice_desc* d) {
   return IPOKE_INN_OK;
 }
 
-// Samples per pass of the coupling net: the two hidden-activation buffers of a pass should stay in L2 (48 MB budget,
-// IPOKE_MACOW_NICE_MB overrides), bounded by the workspace the caller brought.
+// Workspace floats of one sample of a coupling pass: two pixel-major hidden-activation buffers [HW][Hd] and the nine
+// tap outputs of the last convolution [HW][9 * round4(2 c_t)].
+inline long long nice_sample_floats(const ipoke_macow_nice_desc* d, int H, int W) {
+  return (long long)H * W * (2LL * d->hidden + 9LL * round4(2 * d->c_t));
+}
+
+// Samples per pass of the coupling net: the buffers of a pass should stay in L2 (48 MB budget, IPOKE_MACOW_NICE_MB
+// overrides), bounded by the workspace the caller brought.
 inline int nice_chunk_samples(const ipoke_macow_nice_desc* d, int B, int H, int W, size_t ws_floats) {
   long long mb = 48;
   if (const char* e = std::getenv("IPOKE_MACOW_NICE_MB")) mb = std::max(1, std::atoi(e));
-  const long long per_sample = (long long)H * W * (2LL * d->hidden + 1);
+  const long long per_sample = nice_sample_floats(d, H, W);
   long long chunk = std::max(1LL, mb * 1024 * 1024 / 4 / per_sample);
   chunk = std::min<long long>(chunk, (long long)(ws_floats / (size_t)per_sample));
   return (int)std::max(1LL, std::min<long long>(chunk, B));
@@ -144,39 +150,41 @@ int nice_run(Launcher& L, const ipoke_macow_nice_desc* d, const float* packed, f
   const int HW = H * W, Hd = d->hidden;
   const int c_hi = std::max(d->z_off + d->z_stride * (d->c_in - 1), d->p_off + d->p_stride * (d->c_t - 1)) + 1;
   if (x_stride < (long long)c_hi * HW) return IPOKE_INN_E_INVALID;
-  if (ws_floats < (size_t)HW * (2 * (size_t)Hd + 1)) return IPOKE_INN_E_INVALID;       // at least one sample per pass
+  if (ws_floats < (size_t)nice_sample_floats(d, H, W)) return IPOKE_INN_E_INVALID;      // at least one sample per pass
   if (B == 0) return IPOKE_INN_OK;
   const int chunk = nice_chunk_samples(d, B, H, W, ws_floats);
-  const int ld = round4(Hd), ld3 = round4(2 * d->c_t);
+  const int ld = round4(Hd), ld3 = round4(2 * d->c_t), ldt = 9 * ld3;
   const float* w1 = packed;
   const float* w2 = w1 + 9LL * d->c_in * ld;
   const float* w3 = w2 + (long long)Hd * ld;
   const float* b3 = w3 + 9LL * Hd * ld3;
   float* a1 = ws;
   float* a2 = a1 + (size_t)chunk * HW * Hd;
-  float* rowld = a2 + (size_t)chunk * HW * Hd;
+  float* taps = a2 + (size_t)chunk * HW * Hd;
   for (int b0 = 0; b0 < B; b0 += chunk) {
     const int nb = std::min(chunk, B - b0), M = nb * HW;
+    float* img = x + (long long)b0 * x_stride;
     GemmParams p{};
-    p.M = M; p.H = H; p.W = W; p.Hd = Hd;
+    p.M = M; p.H = H; p.W = W;
     p.sample_stride = x_stride;
     p.g = NiceGeom{d->c_in, d->z_off, d->z_stride, d->c_t, d->p_off, d->p_stride};
-    p.act = d->activation; p.alpha = d->alpha; p.reverse = reverse != 0;
-    p.x = x + (long long)b0 * x_stride;
-    const int gx = (M + 127) / 128, gy = (Hd + 127) / 128;
+    p.act = d->activation;
+    const int gx = (M + 127) / 128;
     // conv1: 3x3 over the net's input channels of the image -> activation -> a1 [M, Hd]
-    p.A = p.x; p.Wt = w1; p.ldw = ld; p.K = 9 * d->c_in; p.N = Hd; p.Y = a1; p.ldy = Hd; p.lda = 0;
-    if (int e = L.template gemm<SRC_IMAGE, EPI_ACT, 128, 128, 8, 8>(gx, gy, p)) return e;
+    p.A = img; p.lda = 0; p.Wt = w1; p.ldw = ld; p.K = 9 * d->c_in; p.N = Hd; p.Y = a1; p.ldy = Hd;
+    if (int e = L.template gemm<SRC_IMAGE, EPI_ACT, 128, 128, 8, 8>(gx, (Hd + 127) / 128, p)) return e;
     // conv2: 1x1 -> activation -> a2
     p.A = a1; p.lda = Hd; p.Wt = w2; p.K = Hd; p.Y = a2;
-    if (int e = L.template gemm<SRC_ROWS, EPI_ACT, 128, 128, 8, 8>(gx, gy, p)) return e;
-    // conv3: weight-normed 3x3 over a2 -> (shift, log-scale) -> affine map of the transformed channels in place
-    p.A = a2; p.Wt = w3; p.ldw = ld3; p.K = 9 * Hd; p.N = 2 * d->c_t; p.bias = b3; p.Y = nullptr;
-    p.rowld = (!reverse && logdet) ? rowld : nullptr;
-    if (int e = L.template gemm<SRC_TAPS, EPI_AFFINE, 128, 32, 8, 2>(gx, 1, p)) return e;
-    if (p.rowld) {
-      if (int e = L.rowsum((nb + 127) / 128, 128, rowld, logdet + b0, nb, HW)) return e;
-    }
+    if (int e = L.template gemm<SRC_ROWS, EPI_ACT, 128, 128, 8, 8>(gx, (Hd + 127) / 128, p)) return e;
+    // conv3 (weight-normed 3x3) as nine 1x1 tap products side by side: taps [M, 9 ld3]
+    p.A = a2; p.Wt = w3; p.ldw = ldt; p.N = ldt; p.Y = taps; p.ldy = ldt;
+    if (int e = L.template gemm<SRC_ROWS, EPI_STORE, 128, 64, 8, 4>(gx, (ldt + 63) / 64, p)) return e;
+    // shift-add of the taps + bias -> (shift, scale) -> affine map of the transformed channels in place, log-det
+    AffineParams q;
+    q.T = taps; q.bias = b3; q.x = img; q.logdet = (!reverse && logdet) ? logdet + b0 : nullptr;
+    q.H = H; q.W = W; q.ldt = ldt; q.ld3 = ld3; q.sample_stride = x_stride; q.g = p.g; q.alpha = d->alpha;
+    q.reverse = reverse != 0;
+    if (int e = L.affine(nb, 256, q)) return e;
   }
   return IPOKE_INN_OK;
 }

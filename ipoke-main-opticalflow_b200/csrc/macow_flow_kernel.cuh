@@ -6,14 +6,16 @@
 //     prefix of the image (the multi-scale split / unsplit is then no operation at all: a level works on the first
 //     channels of every sample and leaves the factored-out channels where the final concatenation wants them).
 //
-// Design.  The coupling net is three GEMMs over rows = (sample, pixel):  [M, 9 c_in] x [9 c_in, Hd],  [M, Hd] x [Hd, Hd],
-// [M, 9 Hd] x [9 Hd, 2 c_t], the 3x3 windows gathered while the A tile is loaded (implicit im2col: from the NCHW image for
-// the first layer, as row shifts of the pixel-major hidden activations for the last), activations fused into the
-// epilogues of the first two and the affine map + per-row log-determinant into the epilogue of the third.  Hidden
-// activations are pixel-major [M, Hd] so every layer reads contiguous K.  One tiled float32 kernel (128-row tiles,
-// 16-deep K slices in shared memory, 8 x 8 or 8 x 2 register tiles, 256 threads) serves all three.  The hidden width of
-// the reference's configuration (2048) makes the middle GEMM tensor-core work; this float32 version is the parity
-// path (DESIGN.md section 4b says what the tcgen05 version changes).
+// Design.  The coupling net is three GEMMs over rows = (sample, pixel):  [M, 9 c_in] x [9 c_in, Hd] with the 3x3 window
+// gathered from the NCHW image while the A tile is loaded (implicit im2col),  [M, Hd] x [Hd, Hd],  and the last 3x3
+// convolution as nine 1x1 "tap" GEMMs in one  [M, Hd] x [Hd, 9 * 2 c_t]  product whose taps a small per-sample kernel
+// shift-adds (K stays Hd and N grows ninefold: full tiles and enough CTAs, where the im2col formulation had 9 Hd deep
+// K loops on a handful of CTAs -- measured: 68 % of the flow's time).  Activations are fused into the epilogues of the
+// first two, bias + affine map + log-determinant into the tap kernel.  Hidden activations are pixel-major [M, Hd] so
+// every layer reads contiguous K.  One tiled float32 kernel (128-row tiles, 16-deep K slices in shared memory, 8 x 8 or
+// 8 x 4 register tiles, 256 threads) serves all three.  The hidden width of the reference's configurations
+// (1536 - 2048) makes the middle GEMM tensor-core work; this float32 version is the parity path (DESIGN.md section 4b
+// says what the tcgen05 version changes).
 #pragma once
 #include "macow_kernel.cuh"
 
@@ -27,29 +29,26 @@ struct NiceGeom {
 
 __host__ __device__ inline int round4(int v) { return (v + 3) & ~3; }
 
-// Packed coupling net: Wt1 [9 c_in][ld] | Wt2 [Hd][ld] | Wt3 [9 Hd][ld3] | bias3 [ld3], ld = round4(Hd), ld3 = round4(2 c_t);
-// Wt3 / bias3 columns interleaved: 2 i = shift of transformed channel i, 2 i + 1 = its log-scale.
+// Packed coupling net: Wt1 [9 c_in][ld] | Wt2 [Hd][ld] | Wt3 [Hd][9 ld3] | bias3 [ld3], ld = round4(Hd), ld3 = round4(2 c_t);
+// Wt3 holds the nine taps of the last convolution side by side (column tap * ld3 + slot), slots interleaved like bias3:
+// 2 i = shift of transformed channel i, 2 i + 1 = its log-scale.
 __host__ __device__ inline long long nice_floats(int c_in, int c_t, int Hd) {
   const long long ld = round4(Hd), ld3 = round4(2 * c_t);
   return 9LL * c_in * ld + (long long)Hd * ld + 9LL * Hd * ld3 + ld3;
 }
 
-enum { SRC_IMAGE = 0, SRC_ROWS = 1, SRC_TAPS = 2 };
-enum { EPI_ACT = 0, EPI_AFFINE = 1 };
+enum { SRC_IMAGE = 0, SRC_ROWS = 1 };
+enum { EPI_ACT = 0, EPI_STORE = 1 };
 
 struct GemmParams {
-  const float* A;      // SRC_ROWS / SRC_TAPS: activations [M][lda];  SRC_IMAGE: the image (first sample of the chunk)
+  const float* A;      // SRC_ROWS: activations [M][lda];  SRC_IMAGE: the image (first sample of the pass)
   const float* Wt;     // [K][ldw], ldw a multiple of 4, columns >= N zero
-  const float* bias;   // EPI_AFFINE: [round4(2 c_t)]
-  float* Y;            // EPI_ACT: [M][ldy]
-  float* x;            // EPI_AFFINE: the image (first sample of the chunk), transformed channels updated in place
-  float* rowld;        // EPI_AFFINE forward: sum over channels of log(scale) per row [M]; nullable
+  float* Y;            // [M][ldy]
   int M, N, K, lda, ldw, ldy;
-  int H, W, Hd;
+  int H, W;
   long long sample_stride;
   NiceGeom g;
-  int act, reverse;
-  float alpha;
+  int act;
 };
 
 constexpr int kGemmBK = 16;
@@ -60,14 +59,7 @@ __device__ __forceinline__ float gemm_fetch_a(const GemmParams& p, int m, int k,
   if (m >= p.M || k >= p.K) return 0.f;
   if (kSrc == SRC_ROWS) return __ldg(p.A + (long long)m * p.lda + k);
   const int HW = p.H * p.W;
-  if (kSrc == SRC_TAPS) {                                   // k = tap * Hd + j: hidden channel j of the pixel's tap-th neighbour
-    const int tap = k / p.Hd, j = k - tap * p.Hd;
-    const int dy = tap / 3 - 1, dx = tap - (tap / 3) * 3 - 1;
-    const int yy = py + dy, xx = px + dx;
-    if (yy < 0 || yy >= p.H || xx < 0 || xx >= p.W) return 0.f;          // zero padding of the 3x3 convolution
-    return __ldg(p.A + (long long)(m + dy * p.W + dx) * p.lda + j);
-  }
-  const int c = k / 9, tap = k - c * 9;                      // SRC_IMAGE: k = c * 9 + tap
+  const int c = k / 9, tap = k - c * 9;                      // SRC_IMAGE: k = c * 9 + tap, 3x3 window with zero padding
   const int dy = tap / 3 - 1, dx = tap - (tap / 3) * 3 - 1;
   const int yy = py + dy, xx = px + dx;
   if (yy < 0 || yy >= p.H || xx < 0 || xx >= p.W) return 0.f;
@@ -75,20 +67,22 @@ __device__ __forceinline__ float gemm_fetch_a(const GemmParams& p, int m, int k,
   return __ldg(p.A + b * p.sample_stride + (long long)(p.g.z_off + p.g.z_stride * c) * HW + yy * p.W + xx);
 }
 
-// grid.x = row tiles; grid.y = column tiles (EPI_ACT) or 1 (EPI_AFFINE walks its column tiles itself so that a row's
-// log-determinant is summed by one thread in a fixed order).
+// Y[m][n] = epi(sum_k A(m, k) Wt[k][n]); grid = (row tiles, column tiles).  A thread owns TM consecutive rows and TN
+// columns in groups of 4: group g covers columns g * (BN / (TN / 4)) + tx * 4 .. + 3, so that the lanes of a warp read
+// consecutive 16-byte words of a Bs row (no bank conflicts) and store 16-byte pieces of consecutive columns.
 template <int kSrc, int kEpi, int BM, int BN, int TM, int TN>
 __global__ void __launch_bounds__(kGemmThreads) nice_gemm_kernel(const GemmParams p) {
   static_assert((BM / TM) * (BN / TN) == kGemmThreads, "one register tile per thread");
-  static_assert(BM % 16 == 0 && BN % 4 == 0 && TM % 4 == 0, "tile shapes");
+  static_assert(BM % 16 == 0 && TN % 4 == 0 && TM % 4 == 0, "tile shapes");
   constexpr int BK = kGemmBK;
   constexpr int LDA_S = BM + 4;                              // As[k][row], rows 16-byte aligned
+  constexpr int NG = TN / 4;                                 // column groups per thread
+  constexpr int GW = BN / NG;                                // columns of one group across the CTA
   MACOW_SHARED __align__(16) float As[BK * LDA_S];
   MACOW_SHARED __align__(16) float Bs[BK * BN];
-  MACOW_SHARED float red[kEpi == EPI_AFFINE ? BM * (BN / TN + 1) : 1];
   const int tid = threadIdx.x;
   const int tx = tid % (BN / TN), ty = tid / (BN / TN);
-  const int m0 = blockIdx.x * BM;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
   const int HW = p.H * p.W;
   // A-tile loader: thread -> (kk = tid % 16, rows r0 + 16 i)
   constexpr int RPT = BM / 16;
@@ -100,100 +94,130 @@ __global__ void __launch_bounds__(kGemmThreads) nice_gemm_kernel(const GemmParam
     a_py[i] = pix / p.W;
     a_px[i] = pix - a_py[i] * p.W;
   }
-  float rowacc = 0.f;
-  const int n_begin = kEpi == EPI_AFFINE ? 0 : blockIdx.y * BN;
-  const int n_end = kEpi == EPI_AFFINE ? p.N : min(p.N, n_begin + BN);
-  for (int n0 = n_begin; n0 < n_end; n0 += BN) {
-    float acc[TM][TN];
+  float acc[TM][TN];
 #pragma unroll
-    for (int i = 0; i < TM; ++i) {
+  for (int i = 0; i < TM; ++i) {
 #pragma unroll
-      for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+    for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+  }
+  for (int k0 = 0; k0 < p.K; k0 += BK) {
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) {
+      const int r = a_r0 + 16 * i;
+      As[a_kk * LDA_S + r] = gemm_fetch_a<kSrc>(p, m0 + r, k0 + a_kk, a_py[i], a_px[i]);
     }
-    for (int k0 = 0; k0 < p.K; k0 += BK) {
-#pragma unroll
-      for (int i = 0; i < RPT; ++i) {
-        const int r = a_r0 + 16 * i;
-        As[a_kk * LDA_S + r] = gemm_fetch_a<kSrc>(p, m0 + r, k0 + a_kk, a_py[i], a_px[i]);
-      }
-      for (int v = tid; v < BK * (BN / 4); v += kGemmThreads) {
-        const int kk = v / (BN / 4), n4 = (v - kk * (BN / 4)) * 4;
-        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (k0 + kk < p.K && n0 + n4 < p.ldw) w = __ldg(reinterpret_cast<const float4*>(p.Wt + (long long)(k0 + kk) * p.ldw + n0 + n4));
-        *reinterpret_cast<float4*>(Bs + kk * BN + n4) = w;
-      }
-      __syncthreads();
-#pragma unroll
-      for (int kk = 0; kk < BK; ++kk) {
-        float a[TM], b[TN];
-#pragma unroll
-        for (int i = 0; i < TM; i += 4) {
-          const float4 v = *reinterpret_cast<const float4*>(As + kk * LDA_S + ty * TM + i);
-          a[i] = v.x; a[i + 1] = v.y; a[i + 2] = v.z; a[i + 3] = v.w;
-        }
-#pragma unroll
-        for (int j = 0; j < TN; ++j) b[j] = Bs[kk * BN + tx * TN + j];
-#pragma unroll
-        for (int i = 0; i < TM; ++i) {
-#pragma unroll
-          for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
-        }
-      }
-      __syncthreads();
+    for (int v = tid; v < BK * (BN / 4); v += kGemmThreads) {
+      const int kk = v / (BN / 4), n4 = (v - kk * (BN / 4)) * 4;
+      float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (k0 + kk < p.K && n0 + n4 < p.ldw) w = __ldg(reinterpret_cast<const float4*>(p.Wt + (long long)(k0 + kk) * p.ldw + n0 + n4));
+      *reinterpret_cast<float4*>(Bs + kk * BN + n4) = w;
     }
-    if (kEpi == EPI_ACT) {
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < BK; ++kk) {
+      float a[TM], b[TN];
+#pragma unroll
+      for (int i = 0; i < TM; i += 4) {
+        const float4 v = *reinterpret_cast<const float4*>(As + kk * LDA_S + ty * TM + i);
+        a[i] = v.x; a[i + 1] = v.y; a[i + 2] = v.z; a[i + 3] = v.w;
+      }
+#pragma unroll
+      for (int g = 0; g < NG; ++g) {
+        const float4 v = *reinterpret_cast<const float4*>(Bs + kk * BN + g * GW + tx * 4);
+        b[4 * g] = v.x; b[4 * g + 1] = v.y; b[4 * g + 2] = v.z; b[4 * g + 3] = v.w;
+      }
 #pragma unroll
       for (int i = 0; i < TM; ++i) {
-        const int m = m0 + ty * TM + i;
-        if (m >= p.M) continue;
-        float* y = p.Y + (long long)m * p.ldy + n0 + tx * TN;
 #pragma unroll
-        for (int j = 0; j < TN; ++j) {
-          if (n0 + tx * TN + j < p.N) y[j] = activate(acc[i][j], p.act);
+        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+      }
+    }
+    __syncthreads();
+  }
+  const bool vec_ok = (p.ldy & 3) == 0 && (reinterpret_cast<uintptr_t>(p.Y) & 15) == 0;
+#pragma unroll
+  for (int i = 0; i < TM; ++i) {
+    const int m = m0 + ty * TM + i;
+    if (m >= p.M) continue;
+#pragma unroll
+    for (int g = 0; g < NG; ++g) {
+      const int n = n0 + g * GW + tx * 4;
+      float v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = kEpi == EPI_ACT ? activate(acc[i][4 * g + j], p.act) : acc[i][4 * g + j];
+      float* y = p.Y + (long long)m * p.ldy + n;
+      if (vec_ok && n + 3 < p.N) {
+        *reinterpret_cast<float4*>(y) = make_float4(v[0], v[1], v[2], v[3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (n + j < p.N) y[j] = v[j];
         }
       }
-    } else {
-      // TN == 2: the thread holds (shift, log-scale) of transformed channel ch for TM consecutive pixels
-      const int ch = (n0 >> 1) + tx;
-      const float b_mu = ch < p.g.c_t ? __ldg(p.bias + 2 * ch) : 0.f;
-      const float b_ls = ch < p.g.c_t ? __ldg(p.bias + 2 * ch + 1) : 0.f;
-#pragma unroll
-      for (int i = 0; i < TM; ++i) {
-        const int r = ty * TM + i, m = m0 + r;
-        float lg = 0.f;
-        if (m < p.M && ch < p.g.c_t) {
-          const float mu = acc[i][0] + b_mu;
-          const float scale = tanhf(0.5f * (acc[i][TN - 1] + b_ls)) * p.alpha + 1.0f;
-          const int b = m / HW, pix = m - b * HW;
-          float* xp = p.x + b * p.sample_stride + (long long)(p.g.p_off + p.g.p_stride * ch) * HW + pix;
-          if (p.reverse) {
-            *xp = (*xp - mu) / (scale + 1e-12f);
-          } else {
-            *xp = fmaf(scale, *xp, mu);
-            lg = logf(scale);
-          }
-        }
-        red[r * (BN / TN + 1) + tx] = lg;
-      }
-      __syncthreads();
-      if (tid < BM) {
-        float s = 0.f;
-        for (int t = 0; t < BN / TN; ++t) s += red[tid * (BN / TN + 1) + t];
-        rowacc += s;
-      }
-      __syncthreads();
     }
   }
-  if (kEpi == EPI_AFFINE && !p.reverse && p.rowld != nullptr && tid < BM && m0 + tid < p.M) p.rowld[m0 + tid] = rowacc;
 }
 
-// logdet[b] += sum of the HW row values of sample b, fixed order.  One thread per sample.
-__global__ void macow_rowsum_kernel(const float* __restrict__ rowld, float* __restrict__ logdet, int B, int HW) {
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= B) return;
-  float s = 0.f;
-  for (int i = 0; i < HW; ++i) s += rowld[(long long)b * HW + i];
-  logdet[b] += s;
+// Last step of a coupling.  The weight-normed 3x3 convolution was computed as nine 1x1 "tap" GEMMs,
+// T[m][tap * ld3 + 2 i (+ 1)] = a2[m] . w3[tap][:, shift (log-scale) of transformed channel i]; here every output pixel
+// adds the taps of its in-image neighbours (zero padding) and the bias, turns the log-scale into
+// scale = tanh(ls / 2) * alpha + 1 (macow_utils.py:49-52) and maps the transformed channels in place: forward
+// scale * x + shift with logdet[b] += sum log(scale), inverse (x - shift) / (scale + 1e-12) (macow_utils.py:54-66).
+// One CTA per sample; the log-determinant is reduced in a fixed order (thread-strided partial sums, shuffle tree,
+// warp sums added by thread 0).
+struct AffineParams {
+  const float* T;      // [M][ldt] of the pass
+  const float* bias;   // [ld3]: (shift, log-scale) pairs
+  float* x;            // image, first sample of the pass
+  float* logdet;       // [samples of the pass] or null
+  int H, W, ldt, ld3;
+  long long sample_stride;
+  NiceGeom g;
+  float alpha;
+  int reverse;
+};
+
+__global__ void __launch_bounds__(256) nice_affine_kernel(const AffineParams p) {
+  const int HW = p.H * p.W, c_t = p.g.c_t, n = HW * c_t;
+  const int b = blockIdx.x;
+  float* img = p.x + b * p.sample_stride;
+  const float* Tb = p.T + (long long)b * HW * p.ldt;
+  float lsum = 0.f;
+  for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
+    const int pix = idx / c_t, ch = idx - pix * c_t;
+    const int py = pix / p.W, px = pix - py * p.W;
+    float mu = __ldg(p.bias + 2 * ch), ls = __ldg(p.bias + 2 * ch + 1);
+#pragma unroll
+    for (int tap = 0; tap < 9; ++tap) {
+      const int dy = tap / 3 - 1, dx = tap % 3 - 1;
+      const int yy = py + dy, xx = px + dx;
+      if (yy < 0 || yy >= p.H || xx < 0 || xx >= p.W) continue;
+      const float* t = Tb + (long long)(yy * p.W + xx) * p.ldt + tap * p.ld3 + 2 * ch;
+      mu += t[0];
+      ls += t[1];
+    }
+    const float scale = tanhf(0.5f * ls) * p.alpha + 1.0f;
+    float* xp = img + (long long)(p.g.p_off + p.g.p_stride * ch) * HW + pix;
+    if (p.reverse) {
+      *xp = (*xp - mu) / (scale + 1e-12f);
+    } else {
+      *xp = fmaf(scale, *xp, mu);
+      lsum += logf(scale);
+    }
+  }
+  if (!p.reverse && p.logdet != nullptr) {
+    MACOW_SHARED float red[8];
+    float v = lsum;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float s = 0.f;
+      for (int w = 0; w < (int)((blockDim.x + 31) >> 5); ++w) s += red[w];
+      p.logdet[b] += s;
+    }
+  }
 }
 
 // Per-channel glue, in place, one CTA per sample with the touched channel prefix staged in shared memory:
@@ -283,7 +307,7 @@ __global__ void macow_pack_nice_rows_kernel(const PackNiceParams p) {
   const float mul = p.params[3][o] / sqrtf(ss);
   const int slot = o < c_t ? 2 * o : 2 * (o - c_t) + 1;
   for (int j = 0; j < Hd; ++j) {
-    for (int tap = 0; tap < 9; ++tap) w3[(long long)(tap * Hd + j) * ld3 + slot] = v[j * 9 + tap] * mul;
+    for (int tap = 0; tap < 9; ++tap) w3[((long long)j * 9 + tap) * ld3 + slot] = v[j * 9 + tap] * mul;
   }
   b3[slot] = p.params[2][o];
 }

@@ -13,7 +13,7 @@ How a call runs: the image lives in ONE [B, C, H, W] buffer for the whole flow. 
 channels of each sample, so ``split2d`` / ``unsplit2d`` (macow2.py:15-23, 886-896) move no data: the channels a level
 factors out already sit where the final concatenation wants them.  The module tree is flattened once into a program of
 three kinds of kernel calls -- per-channel glue (ActNorm2dFlow and / or Shuffle, one launch), a chain of MaCow units
-(one launch per pair), a NICE coupling (three GEMM launches + the log-determinant reduction) -- and the inverse walks
+(one launch per pair), a NICE coupling (three GEMM launches + the tap / affine kernel) -- and the inverse walks
 the same program backwards.
 """
 import ctypes
@@ -435,7 +435,8 @@ class Program:
 
     @property
     def launches(self):
-        """Kernel launches of one forward call at a batch that needs one pass per coupling."""
+        """Kernel launches of one call (either direction) at a batch that needs one pass per coupling: a coupling is
+        three GEMMs and the tap / affine kernel."""
         return sum({"glue": 1, "units": 1, "nice": 4}[op[0]] for op in self.ops)
 
 

@@ -154,7 +154,8 @@ def test_coupling_rows_beyond_one_tile_and_workspace_passes(emulated):
     arrs = [p.detach().numpy() for p in nice.params()]
     ptrs = (ctypes.c_void_p * 5)(*[a.ctypes.data for a in arrs])
     assert emulated.ipoke_macow_pack_nice(ctypes.byref(d), ptrs, packed.ctypes.data, None) == 0
-    ws = np.zeros(2 * H * W * (2 * Hd + 1), dtype=np.float32)
+    per_sample = H * W * (2 * Hd + 9 * 4)                                # round4(2 c_t) = 4
+    ws = np.zeros(2 * per_sample, dtype=np.float32)
     got, ld = x.copy(), np.full(B, 1.5, dtype=np.float32)
     assert emulated.ipoke_macow_nice(ctypes.byref(d), packed.ctypes.data, got.ctypes.data, C * H * W, ld.ctypes.data, 0,
                                      B, H, W, ws.ctypes.data, ws.size, None) == 0
@@ -165,4 +166,4 @@ def test_coupling_rows_beyond_one_tile_and_workspace_passes(emulated):
     assert max_rel(back, x) <= 1e-5
     # a workspace smaller than one sample is refused
     assert emulated.ipoke_macow_nice(ctypes.byref(d), packed.ctypes.data, back.ctypes.data, C * H * W, None, 1, B, H, W,
-                                     ws.ctypes.data, H * W * (2 * Hd + 1) - 1, None) != 0
+                                     ws.ctypes.data, per_sample - 1, None) != 0

@@ -90,8 +90,8 @@ def test_flow_sizes_argument_errors_and_unbuilt_variants_without_gpu():
     L = macow._lib()
     d = macow.NiceDesc(16, 0, 1, 16, 16, 1, 2048, 1, 1.0)        # continuous / up coupling of a 32-channel step
     assert L.ipoke_macow_nice_floats(ctypes.byref(d)) == 9 * 16 * 2048 + 2048 * 2048 + 9 * 2048 * 32 + 32
-    # preferred workspace: as many samples as keep two hidden-activation buffers within 48 MB (8 x 8 latents: 47)
-    per_sample = 64 * (2 * 2048 + 1)
+    # preferred workspace: as many samples as keep a pass (two hidden-activation buffers + tap outputs) within 48 MB
+    per_sample = 64 * (2 * 2048 + 9 * 32)
     assert L.ipoke_macow_nice_workspace_floats(ctypes.byref(d), 4096, 8, 8) == (48 * 2 ** 20 // 4 // per_sample) * per_sample
     assert L.ipoke_macow_nice_workspace_floats(ctypes.byref(d), 3, 8, 8) == 3 * per_sample
     assert L.ipoke_macow_nice_floats(ctypes.byref(macow.NiceDesc(0, 0, 1, 16, 16, 1, 64, 1, 1.0))) == 0

@@ -90,7 +90,6 @@ def main():
     net = net.to(dev).eval()
     B, C, H, W = args.batch, w["flow_in_channels"], w["H"], w["W"]
     x = torch.randn(B, C, H, W, device=dev)
-    z = torch.randn(B, C, H, W, device=dev)
     flush = torch.zeros(64 * 1024 * 1024, device=dev)
     sms = torch.cuda.get_device_properties(dev).multi_processor_count
     flops = 2.0 * nice_macs_per_sample(w) * B
@@ -98,8 +97,8 @@ def main():
             "H": H, "W": W, "batch": B, "dtype": "f32", "coupling_flops_per_call": flops, "steps": args.steps,
             "warmup": args.warmup, "l2": "packed weights exceed L2; 256 MB written between timed iterations"}
     with torch.no_grad():
-        net(x)                                                # pack + first call
-        net(z, reverse=True)
+        z = net(x)[0]                                         # pack + first call; the inverse is timed on the flow's own
+        net(z, reverse=True)                                  # outputs (a deep random flow inverts N(0, 1) noise to inf)
         clk = ClockSampler(0)
         t0 = time.time()
         f_ms, f_min = timed(lambda: net(x), args.steps, args.warmup, flush)
@@ -110,7 +109,7 @@ def main():
     launches = net.flow._program.launches
     for tag, ms, mn in (("forward", f_ms, f_min), ("reverse", r_ms, r_min)):
         line[tag] = {"ms": round(ms, 3), "ms_min": round(mn, 3), "samples_per_s": round(B / ms * 1e3, 1),
-                     "gpu_launches": launches if tag == "forward" else launches - sum(op[0] == "nice" for op in net.flow._program.ops),
+                     "gpu_launches": launches,
                      "roofline": {"bound": "fp32 fma", "achieved": round(flops / ms / 1e9, 2), "peak": round(peak, 1),
                                   "unit": "TFLOP/s", "frac": round(flops / ms / 1e9 / peak, 4)}}
     line["clocks"] = clocks
@@ -123,8 +122,9 @@ def main():
             err_f = float((a - b).abs().max() / a.abs().max())
             a, b = ref.reverse(z), net(z, reverse=True)
             err_r = float((a - b).abs().max() / a.abs().max())
+            round_trip = float((b - x).abs().max() / x.abs().max())
         line["eager_gpu"] = {"forward_ms": round(ef, 2), "reverse_ms": round(er, 2), "speedup_forward": round(ef / f_ms, 2),
-                             "speedup_reverse": round(er / r_ms, 2), "max_rel_forward": err_f, "max_rel_reverse": err_r,
+                             "speedup_reverse": round(er / r_ms, 2), "max_rel_forward": err_f, "max_rel_reverse": err_r, "round_trip_max_rel": round_trip,
                              "tf32": {"cudnn": torch.backends.cudnn.allow_tf32, "matmul": torch.backends.cuda.matmul.allow_tf32},
                              "what": "reference op sequence (oracle/macow_stack_oracle_torch.py), torch eager defaults, same GPU"}
         nb = max(1, min(B, args.cpu_samples))
