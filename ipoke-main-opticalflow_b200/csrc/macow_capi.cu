@@ -17,8 +17,9 @@ using macow::Geometry;
 struct CudaLauncher {
   cudaStream_t s;
   template <int kSrc, int kEpi, int BM, int BN, int TM, int TN>
-  int gemm(int gx, int gy, const macow::GemmParams& p) {
-    macow::nice_gemm_kernel<kSrc, kEpi, BM, BN, TM, TN><<<dim3(gx, gy), macow::kGemmThreads, 0, s>>>(p);
+  int gemm(bool async, int gx, int gy, int gz, const macow::GemmParams& p) {
+    if (async) macow::nice_gemm_kernel<kSrc, kEpi, BM, BN, TM, TN, true><<<dim3(gx, gy, gz), macow::kGemmThreads, 0, s>>>(p);
+    else macow::nice_gemm_kernel<kSrc, kEpi, BM, BN, TM, TN, false><<<dim3(gx, gy, gz), macow::kGemmThreads, 0, s>>>(p);
     return (int)cudaGetLastError();
   }
   int affine(int blocks, int threads, const macow::AffineParams& p) {

@@ -128,6 +128,16 @@ inline int nice_chunk_samples(const ipoke_macow_nice_desc* d, int B, int H, int 
   return (int)std::max(1LL, std::min<long long>(chunk, B));
 }
 
+// K slices of the tap GEMM: enough CTAs for two per SM when the batch is small, at most 8, and only as many as fit the
+// dead first activation buffer (slices * ldt <= Hd).  IPOKE_MACOW_TAP_SPLITS overrides the CTA-count rule.
+inline int nice_tap_splits(int ctas, int Hd, int ldt) {
+  int s = ctas >= 148 ? 1 : std::min(8, (296 + ctas - 1) / ctas);
+  if (const char* e = std::getenv("IPOKE_MACOW_TAP_SPLITS")) s = std::max(1, std::atoi(e));
+  s = std::min(s, Hd / ldt);
+  s = std::min(s, (Hd + kGemmBK - 1) / kGemmBK);
+  return std::max(s, 1);
+}
+
 template <class Launcher>
 int pack_nice_run(Launcher& L, const ipoke_macow_nice_desc* d, const void* const* params, float* packed) {
   if (int e = check_nice(d)) return e;
@@ -153,6 +163,8 @@ int nice_run(Launcher& L, const ipoke_macow_nice_desc* d, const float* packed, f
   if (ws_floats < (size_t)nice_sample_floats(d, H, W)) return IPOKE_INN_E_INVALID;      // at least one sample per pass
   if (B == 0) return IPOKE_INN_OK;
   const int chunk = nice_chunk_samples(d, B, H, W, ws_floats);
+  bool async = true;                                         // double-buffered cp.async K slices (IPOKE_MACOW_GEMM_ASYNC=0:
+  if (const char* e = std::getenv("IPOKE_MACOW_GEMM_ASYNC")) async = std::atoi(e) != 0;   // single buffer through registers)
   const int ld = round4(Hd), ld3 = round4(2 * d->c_t), ldt = 9 * ld3;
   const float* w1 = packed;
   const float* w2 = w1 + 9LL * d->c_in * ld;
@@ -169,19 +181,29 @@ int nice_run(Launcher& L, const ipoke_macow_nice_desc* d, const float* packed, f
     p.sample_stride = x_stride;
     p.g = NiceGeom{d->c_in, d->z_off, d->z_stride, d->c_t, d->p_off, d->p_stride};
     p.act = d->activation;
+    p.k_split = 1 << 30; p.y_split_stride = 0;
     const int gx = (M + 127) / 128;
     // conv1: 3x3 over the net's input channels of the image -> activation -> a1 [M, Hd]
     p.A = img; p.lda = 0; p.Wt = w1; p.ldw = ld; p.K = 9 * d->c_in; p.N = Hd; p.Y = a1; p.ldy = Hd;
-    if (int e = L.template gemm<SRC_IMAGE, EPI_ACT, 128, 128, 8, 8>(gx, (Hd + 127) / 128, p)) return e;
+    if (int e = L.template gemm<SRC_IMAGE, EPI_ACT, 128, 128, 8, 8>(async, gx, (Hd + 127) / 128, 1, p)) return e;
     // conv2: 1x1 -> activation -> a2
     p.A = a1; p.lda = Hd; p.Wt = w2; p.K = Hd; p.Y = a2;
-    if (int e = L.template gemm<SRC_ROWS, EPI_ACT, 128, 128, 8, 8>(gx, (Hd + 127) / 128, p)) return e;
-    // conv3 (weight-normed 3x3) as nine 1x1 tap products side by side: taps [M, 9 ld3]
-    p.A = a2; p.Wt = w3; p.ldw = ldt; p.N = ldt; p.Y = taps; p.ldy = ldt;
-    if (int e = L.template gemm<SRC_ROWS, EPI_STORE, 128, 64, 8, 4>(gx, (ldt + 63) / 64, p)) return e;
+    if (int e = L.template gemm<SRC_ROWS, EPI_ACT, 128, 128, 8, 8>(async, gx, (Hd + 127) / 128, 1, p)) return e;
+    // conv3 (weight-normed 3x3) as nine 1x1 tap products side by side: taps [M, 9 ld3].  A small batch gives this
+    // narrow product only a handful of CTAs: K is then split across grid.z and the partial products (parked in a1, which
+    // is dead by now) are added in slice order by the tap kernel.
+    const int splits = nice_tap_splits(gx * ((ldt + 63) / 64), Hd, ldt);
+    p.A = a2; p.Wt = w3; p.ldw = ldt; p.N = ldt; p.ldy = ldt;
+    p.Y = splits > 1 ? a1 : taps;
+    if (splits > 1) {
+      p.k_split = ((Hd + splits - 1) / splits + kGemmBK - 1) / kGemmBK * kGemmBK;
+      p.y_split_stride = (long long)M * ldt;
+    }
+    const int gz = splits > 1 ? (Hd + p.k_split - 1) / p.k_split : 1;
+    if (int e = L.template gemm<SRC_ROWS, EPI_STORE, 128, 64, 8, 4>(async, gx, (ldt + 63) / 64, gz, p)) return e;
     // shift-add of the taps + bias -> (shift, scale) -> affine map of the transformed channels in place, log-det
     AffineParams q;
-    q.T = taps; q.bias = b3; q.x = img; q.logdet = (!reverse && logdet) ? logdet + b0 : nullptr;
+    q.T = p.Y; q.splits = gz; q.split_stride = p.y_split_stride; q.bias = b3; q.x = img; q.logdet = (!reverse && logdet) ? logdet + b0 : nullptr;
     q.H = H; q.W = W; q.ldt = ldt; q.ld3 = ld3; q.sample_stride = x_stride; q.g = p.g; q.alpha = d->alpha;
     q.reverse = reverse != 0;
     if (int e = L.affine(nb, 256, q)) return e;

@@ -49,28 +49,58 @@ struct GemmParams {
   long long sample_stride;
   NiceGeom g;
   int act;
+  int k_split;               // K elements per grid.z slice (a multiple of 16); slice z writes Y + z * y_split_stride
+  long long y_split_stride;  // (split-K partial products, added in a fixed order by the consumer)
 };
 
 constexpr int kGemmBK = 16;
 constexpr int kGemmThreads = 256;
 
+// Address of A(m, k), or null where the operand is zero (outside the matrix / the image: zero padding of the 3x3 window).
 template <int kSrc>
-__device__ __forceinline__ float gemm_fetch_a(const GemmParams& p, int m, int k, int py, int px) {
-  if (m >= p.M || k >= p.K) return 0.f;
-  if (kSrc == SRC_ROWS) return __ldg(p.A + (long long)m * p.lda + k);
+__device__ __forceinline__ const float* gemm_addr_a(const GemmParams& p, int m, int k, int py, int px) {
+  if (m >= p.M || k >= p.K) return nullptr;
+  if (kSrc == SRC_ROWS) return p.A + (long long)m * p.lda + k;
   const int HW = p.H * p.W;
-  const int c = k / 9, tap = k - c * 9;                      // SRC_IMAGE: k = c * 9 + tap, 3x3 window with zero padding
+  const int c = k / 9, tap = k - c * 9;                      // SRC_IMAGE: k = c * 9 + tap
   const int dy = tap / 3 - 1, dx = tap - (tap / 3) * 3 - 1;
   const int yy = py + dy, xx = px + dx;
-  if (yy < 0 || yy >= p.H || xx < 0 || xx >= p.W) return 0.f;
+  if (yy < 0 || yy >= p.H || xx < 0 || xx >= p.W) return nullptr;
   const int b = m / HW;
-  return __ldg(p.A + b * p.sample_stride + (long long)(p.g.z_off + p.g.z_stride * c) * HW + yy * p.W + xx);
+  return p.A + b * p.sample_stride + (long long)(p.g.z_off + p.g.z_stride * c) * HW + yy * p.W + xx;
 }
 
-// Y[m][n] = epi(sum_k A(m, k) Wt[k][n]); grid = (row tiles, column tiles).  A thread owns TM consecutive rows and TN
-// columns in groups of 4: group g covers columns g * (BN / (TN / 4)) + tx * 4 .. + 3, so that the lanes of a warp read
-// consecutive 16-byte words of a Bs row (no bank conflicts) and store 16-byte pieces of consecutive columns.
-template <int kSrc, int kEpi, int BM, int BN, int TM, int TN>
+// Asynchronous global -> shared copies (LDGSTS): 4 bytes for the transposed A tile, 16 bytes for the B tile; a null
+// source zero-fills (src-size 0).  The emulation copies at once.
+#ifdef MACOW_HOST_EMULATION
+inline void cp_async4(float* dst, const float* src, const float*) { *dst = src ? *src : 0.f; }
+inline void cp_async16(float* dst, const float* src, const float*) {
+  for (int i = 0; i < 4; ++i) dst[i] = src ? src[i] : 0.f;
+}
+inline void cp_async_commit() {}
+template <int N> inline void cp_async_wait() {}
+#else
+__device__ __forceinline__ void cp_async4(float* dst, const float* src, const float* valid_base) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+  const int bytes = src ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(d), "l"(src ? src : valid_base), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async16(float* dst, const float* src, const float* valid_base) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+  const int bytes = src ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(src ? src : valid_base), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+#endif
+
+// Y[m][n] = epi(sum_k A(m, k) Wt[k][n]); grid = (row tiles, column tiles, K slices).  A thread owns TM consecutive rows
+// and TN columns in groups of 4: group g covers columns g * (BN / (TN / 4)) + tx * 4 .. + 3, so that the lanes of a warp
+// read consecutive 16-byte words of a Bs row (no bank conflicts) and store 16-byte pieces of consecutive columns.
+// kAsync: the K slices are double-buffered in shared memory, slice t + 1 in flight (cp.async) while slice t is
+// multiplied; otherwise one buffer, loads through registers (the first version, kept for A/B and as the fallback).
+template <int kSrc, int kEpi, int BM, int BN, int TM, int TN, bool kAsync>
 __global__ void __launch_bounds__(kGemmThreads) nice_gemm_kernel(const GemmParams p) {
   static_assert((BM / TM) * (BN / TN) == kGemmThreads, "one register tile per thread");
   static_assert(BM % 16 == 0 && TN % 4 == 0 && TM % 4 == 0, "tile shapes");
@@ -78,8 +108,9 @@ __global__ void __launch_bounds__(kGemmThreads) nice_gemm_kernel(const GemmParam
   constexpr int LDA_S = BM + 4;                              // As[k][row], rows 16-byte aligned
   constexpr int NG = TN / 4;                                 // column groups per thread
   constexpr int GW = BN / NG;                                // columns of one group across the CTA
-  MACOW_SHARED __align__(16) float As[BK * LDA_S];
-  MACOW_SHARED __align__(16) float Bs[BK * BN];
+  constexpr int NBUF = kAsync ? 2 : 1;
+  MACOW_SHARED __align__(16) float As[NBUF * BK * LDA_S];
+  MACOW_SHARED __align__(16) float Bs[NBUF * BK * BN];
   const int tid = threadIdx.x;
   const int tx = tid % (BN / TN), ty = tid / (BN / TN);
   const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
@@ -100,30 +131,45 @@ __global__ void __launch_bounds__(kGemmThreads) nice_gemm_kernel(const GemmParam
 #pragma unroll
     for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
   }
-  for (int k0 = 0; k0 < p.K; k0 += BK) {
+  const int k_begin = blockIdx.z * p.k_split, k_end = min(p.K, k_begin + p.k_split);
+
+  auto load_tile = [&](int k0, int buf) {
+    float* as = As + buf * BK * LDA_S;
+    float* bs = Bs + buf * BK * BN;
 #pragma unroll
     for (int i = 0; i < RPT; ++i) {
       const int r = a_r0 + 16 * i;
-      As[a_kk * LDA_S + r] = gemm_fetch_a<kSrc>(p, m0 + r, k0 + a_kk, a_py[i], a_px[i]);
+      const float* src = gemm_addr_a<kSrc>(p, m0 + r, k0 + a_kk, a_py[i], a_px[i]);
+      if (kAsync) cp_async4(as + a_kk * LDA_S + r, src, p.A);
+      else as[a_kk * LDA_S + r] = src ? __ldg(src) : 0.f;
     }
     for (int v = tid; v < BK * (BN / 4); v += kGemmThreads) {
       const int kk = v / (BN / 4), n4 = (v - kk * (BN / 4)) * 4;
-      float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (k0 + kk < p.K && n0 + n4 < p.ldw) w = __ldg(reinterpret_cast<const float4*>(p.Wt + (long long)(k0 + kk) * p.ldw + n0 + n4));
-      *reinterpret_cast<float4*>(Bs + kk * BN + n4) = w;
+      const bool ok = k0 + kk < p.K && n0 + n4 < p.ldw;
+      const float* src = ok ? p.Wt + (long long)(k0 + kk) * p.ldw + n0 + n4 : nullptr;
+      if (kAsync) {
+        cp_async16(bs + kk * BN + n4, src, p.Wt);
+      } else {
+        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ok) w = __ldg(reinterpret_cast<const float4*>(src));
+        *reinterpret_cast<float4*>(bs + kk * BN + n4) = w;
+      }
     }
-    __syncthreads();
+  };
+  auto multiply_tile = [&](int buf) {
+    const float* as = As + buf * BK * LDA_S;
+    const float* bs = Bs + buf * BK * BN;
 #pragma unroll
     for (int kk = 0; kk < BK; ++kk) {
       float a[TM], b[TN];
 #pragma unroll
       for (int i = 0; i < TM; i += 4) {
-        const float4 v = *reinterpret_cast<const float4*>(As + kk * LDA_S + ty * TM + i);
+        const float4 v = *reinterpret_cast<const float4*>(as + kk * LDA_S + ty * TM + i);
         a[i] = v.x; a[i + 1] = v.y; a[i + 2] = v.z; a[i + 3] = v.w;
       }
 #pragma unroll
       for (int g = 0; g < NG; ++g) {
-        const float4 v = *reinterpret_cast<const float4*>(Bs + kk * BN + g * GW + tx * 4);
+        const float4 v = *reinterpret_cast<const float4*>(bs + kk * BN + g * GW + tx * 4);
         b[4 * g] = v.x; b[4 * g + 1] = v.y; b[4 * g + 2] = v.z; b[4 * g + 3] = v.w;
       }
 #pragma unroll
@@ -132,9 +178,35 @@ __global__ void __launch_bounds__(kGemmThreads) nice_gemm_kernel(const GemmParam
         for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
       }
     }
-    __syncthreads();
+  };
+
+  if (kAsync) {
+    if (k_begin < k_end) {
+      load_tile(k_begin, 0);
+      cp_async_commit();
+    }
+    int buf = 0;
+    for (int k0 = k_begin; k0 < k_end; k0 += BK, buf ^= 1) {
+      if (k0 + BK < k_end) {                                 // next slice into the other buffer (free since the barrier
+        load_tile(k0 + BK, buf ^ 1);                         // that ended the previous iteration)
+        cp_async_commit();
+        cp_async_wait<1>();                                  // this thread's copies of the current slice have landed
+      } else {
+        cp_async_wait<0>();
+      }
+      __syncthreads();                                       // ... and everybody else's
+      multiply_tile(buf);
+      __syncthreads();                                       // all reads of this buffer done before it is refilled
+    }
+  } else {
+    for (int k0 = k_begin; k0 < k_end; k0 += BK) {
+      load_tile(k0, 0);
+      __syncthreads();
+      multiply_tile(0);
+      __syncthreads();
+    }
   }
-  const bool vec_ok = (p.ldy & 3) == 0 && (reinterpret_cast<uintptr_t>(p.Y) & 15) == 0;
+  const bool vec_ok = (p.ldy & 3) == 0 && (p.y_split_stride & 3) == 0 && (reinterpret_cast<uintptr_t>(p.Y) & 15) == 0;
 #pragma unroll
   for (int i = 0; i < TM; ++i) {
     const int m = m0 + ty * TM + i;
@@ -145,7 +217,7 @@ __global__ void __launch_bounds__(kGemmThreads) nice_gemm_kernel(const GemmParam
       float v[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) v[j] = kEpi == EPI_ACT ? activate(acc[i][4 * g + j], p.act) : acc[i][4 * g + j];
-      float* y = p.Y + (long long)m * p.ldy + n;
+      float* y = p.Y + blockIdx.z * p.y_split_stride + (long long)m * p.ldy + n;
       if (vec_ok && n + 3 < p.N) {
         *reinterpret_cast<float4*>(y) = make_float4(v[0], v[1], v[2], v[3]);
       } else {
@@ -166,7 +238,9 @@ __global__ void __launch_bounds__(kGemmThreads) nice_gemm_kernel(const GemmParam
 // One CTA per sample; the log-determinant is reduced in a fixed order (thread-strided partial sums, shuffle tree,
 // warp sums added by thread 0).
 struct AffineParams {
-  const float* T;      // [M][ldt] of the pass
+  const float* T;      // [splits][M][ldt] of the pass (split-K partial products of the tap GEMM)
+  int splits;
+  long long split_stride;
   const float* bias;   // [ld3]: (shift, log-scale) pairs
   float* x;            // image, first sample of the pass
   float* logdet;       // [samples of the pass] or null
@@ -187,14 +261,17 @@ __global__ void __launch_bounds__(256) nice_affine_kernel(const AffineParams p) 
     const int pix = idx / c_t, ch = idx - pix * c_t;
     const int py = pix / p.W, px = pix - py * p.W;
     float mu = __ldg(p.bias + 2 * ch), ls = __ldg(p.bias + 2 * ch + 1);
+    for (int sp = 0; sp < p.splits; ++sp) {
+      const float* Ts = Tb + sp * p.split_stride;
 #pragma unroll
-    for (int tap = 0; tap < 9; ++tap) {
-      const int dy = tap / 3 - 1, dx = tap % 3 - 1;
-      const int yy = py + dy, xx = px + dx;
-      if (yy < 0 || yy >= p.H || xx < 0 || xx >= p.W) continue;
-      const float* t = Tb + (long long)(yy * p.W + xx) * p.ldt + tap * p.ld3 + 2 * ch;
-      mu += t[0];
-      ls += t[1];
+      for (int tap = 0; tap < 9; ++tap) {
+        const int dy = tap / 3 - 1, dx = tap % 3 - 1;
+        const int yy = py + dy, xx = px + dx;
+        if (yy < 0 || yy >= p.H || xx < 0 || xx >= p.W) continue;
+        const float* t = Ts + (long long)(yy * p.W + xx) * p.ldt + tap * p.ld3 + 2 * ch;
+        mu += t[0];
+        ls += t[1];
+      }
     }
     const float scale = tanhf(0.5f * ls) * p.alpha + 1.0f;
     float* xp = img + (long long)(p.g.p_off + p.g.p_stride * ch) * HW + pix;

@@ -38,6 +38,7 @@ namespace emul {
 
 constexpr size_t kStackBytes = 256 * 1024;
 static bool descending = false;
+static int grid_z = 0;                    // blockIdx.z of the CTAs a launch() call runs (set by the caller)
 
 struct Runner {
   std::vector<ucontext_t> ctx;
@@ -97,7 +98,7 @@ static void launch(int gx, int gy, int nthreads, const std::function<void()>& ca
   gridDim = {(unsigned)gx, (unsigned)gy, 1};
   for (int by = 0; by < gy; ++by) {
     for (int bx = 0; bx < gx; ++bx) {
-      blockIdx = {(unsigned)bx, (unsigned)by, 0};
+      blockIdx = {(unsigned)bx, (unsigned)by, (unsigned)grid_z};
       run_block(nthreads, call);
     }
   }

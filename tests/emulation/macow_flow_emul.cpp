@@ -14,8 +14,13 @@ namespace {
 
 struct EmulLauncher {
   template <int kSrc, int kEpi, int BM, int BN, int TM, int TN>
-  int gemm(int gx, int gy, const macow::GemmParams& p) {
-    emul::launch(gx, gy, macow::kGemmThreads, [&] { macow::nice_gemm_kernel<kSrc, kEpi, BM, BN, TM, TN>(p); });
+  int gemm(bool async, int gx, int gy, int gz, const macow::GemmParams& p) {
+    for (int z = 0; z < gz; ++z) {
+      emul::grid_z = z;
+      if (async) emul::launch(gx, gy, macow::kGemmThreads, [&] { macow::nice_gemm_kernel<kSrc, kEpi, BM, BN, TM, TN, true>(p); });
+      else emul::launch(gx, gy, macow::kGemmThreads, [&] { macow::nice_gemm_kernel<kSrc, kEpi, BM, BN, TM, TN, false>(p); });
+    }
+    emul::grid_z = 0;
     return 0;
   }
   int affine(int blocks, int threads, const macow::AffineParams& p) {

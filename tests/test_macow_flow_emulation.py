@@ -134,11 +134,14 @@ def test_components_called_like_the_reference_calls_them(emulated):
         assert max_rel(net.flow.priors[0](z, reverse=True).numpy(), g["prior_rev"]) <= 2e-5
 
 
-def test_coupling_rows_beyond_one_tile_and_workspace_passes(emulated):
+@pytest.mark.parametrize("Hd", [40, 100])
+def test_coupling_rows_beyond_one_tile_and_workspace_passes(emulated, Hd):
     """A coupling on 3 x 7 x 9 pixels = 189 rows (two 128-row tiles, the second ragged) with hidden width 40 (not a
-    multiple of the 16-deep K slice, one ragged 128-column tile) and a workspace of 2 samples (passes of 2 + 1)."""
+    multiple of the 16-deep K slice, one ragged 128-column tile) and a workspace of 2 samples (passes of 2 + 1); at
+    hidden width 100 the tap product of the last convolution runs as two K slices (64 + 36) parked in the first
+    activation buffer."""
     rng = np.random.default_rng(5)
-    C, Hd, B, H, W = 6, 40, 3, 7, 9
+    C, B, H, W = 6, 3, 7, 9
     nice = P.NICE2d(C, hidden_channels=Hd, split_type="continuous", order="down", factor=3, activation="leaky_relu",
                     alpha=0.8).eval()
     with torch.no_grad():
