@@ -82,12 +82,21 @@ def shifted_conv(x, w, order, rows=None, cols=None):
     return out
 
 
-def mcf_params(sd, name, x, act, alpha, dtype, rows=None, cols=None):
-    """MCFBlock.forward (macow_utils.py:429-436: shifted conv -> activation -> weight-normed 1x1 conv; dropout
-    p = 0) followed by Affine.calc_params (macow_utils.py:49-52): mu, scale = tanh(log_scale / 2) * alpha + 1."""
+def mcf_params(sd, name, x, act, alpha, dtype, rows=None, cols=None, h=None):
+    """MCFBlock.forward (macow_utils.py:429-436: shifted conv -> [concatenate the conditioning h on the channel axis]
+    -> activation -> weight-normed 1x1 conv; dropout p = 0) followed by Affine.calc_params (macow_utils.py:49-52):
+    mu, scale = tanh(log_scale / 2) * alpha + 1.  ``h`` [B, h_channels, H, W] is cut to the same output pixels."""
     prefix = name + ".net"
     w = sd[prefix + ".shift_conv.weight"].astype(dtype)
-    hid = activation(shifted_conv(x, w, ORDERS[name], rows, cols), act)
+    hid = shifted_conv(x, w, ORDERS[name], rows, cols)
+    if h is not None:
+        hh = np.asarray(h, dtype=dtype)
+        if rows is not None:
+            hh = hh[:, :, rows[0]:rows[0] + rows[1], :]
+        if cols is not None:
+            hh = hh[:, :, :, cols[0]:cols[0] + cols[1]]
+        hid = np.concatenate([hid, hh], axis=1)
+    hid = activation(hid, act)
     w1, b1 = weight_norm_1x1(sd, prefix, dtype)
     p = np.einsum("oj,bjhw->bohw", w1, hid) + b1.reshape(1, -1, 1, 1)
     C = x.shape[1]
@@ -95,14 +104,14 @@ def mcf_params(sd, name, x, act, alpha, dtype, rows=None, cols=None):
     return mu, np.tanh(log_scale * dtype(0.5)) * dtype(alpha) + dtype(1.0)
 
 
-def mcf_forward(sd, name, x, act="elu", alpha=1.0, dtype=np.float64):
+def mcf_forward(sd, name, x, act="elu", alpha=1.0, dtype=np.float64, h=None):
     """MaskedConvFlow.forward(reverse=False) (macow2.py:116-119) with Affine.fwd (macow_utils.py:54-59)."""
     x = np.asarray(x, dtype=dtype)
-    mu, scale = mcf_params(sd, name, x, act, alpha, dtype)
+    mu, scale = mcf_params(sd, name, x, act, alpha, dtype, h=h)
     return scale * x + mu, np.log(scale).reshape(x.shape[0], -1).sum(1)
 
 
-def mcf_reverse(sd, name, z, act="elu", alpha=1.0, dtype=np.float64):
+def mcf_reverse(sd, name, z, act="elu", alpha=1.0, dtype=np.float64, h=None):
     """MaskedConvFlow.backward_analytic (macow2.py:139-151): one line at a time, rows top-down (A), bottom-up
     (B), columns left-right (C), right-left (D) (backward_height macow2.py:222-246, backward_width :271-289);
     each line is Affine.bwd (macow_utils.py:61-66) of the input line with parameters computed from the lines
@@ -115,10 +124,10 @@ def mcf_reverse(sd, name, z, act="elu", alpha=1.0, dtype=np.float64):
     lines = range(n) if order in "AC" else range(n - 1, -1, -1)
     for l in lines:                                                   # causal: line l sees finished lines only
         if order in "AB":
-            mu, scale = mcf_params(sd, name, out, act, alpha, dtype, rows=(l, 1))
+            mu, scale = mcf_params(sd, name, out, act, alpha, dtype, rows=(l, 1), h=h)
             out[:, :, l:l + 1, :] = (z[:, :, l:l + 1, :] - mu) / (scale + dtype(AFFINE_BWD_EPS))
         else:
-            mu, scale = mcf_params(sd, name, out, act, alpha, dtype, cols=(l, 1))
+            mu, scale = mcf_params(sd, name, out, act, alpha, dtype, cols=(l, 1), h=h)
             out[:, :, :, l:l + 1] = (z[:, :, :, l:l + 1] - mu) / (scale + dtype(AFFINE_BWD_EPS))
     return out
 
@@ -151,25 +160,25 @@ def actnorm2d_init(x, dtype=np.float64):
 STAGES = ("conv1", "conv2", "actnorm1", "conv3", "conv4", "actnorm2")     # macow2.py:965-982
 
 
-def unit_forward(sd, x, act="elu", alpha=1.0, dtype=np.float64, stages=STAGES):
-    """MaCowUnit.forward(reverse=False) (macow2.py:963-982)."""
+def unit_forward(sd, x, act="elu", alpha=1.0, dtype=np.float64, stages=STAGES, h=None):
+    """MaCowUnit.forward(reverse=False) (macow2.py:963-982); ``h``: the conditioning every masked flow receives."""
     out = np.asarray(x, dtype=dtype)
     logdet = np.zeros(out.shape[0], dtype=dtype)
     for s in stages:
         if s.startswith("conv"):
-            out, ld = mcf_forward(sd, s, out, act, alpha, dtype)
+            out, ld = mcf_forward(sd, s, out, act, alpha, dtype, h=h)
         else:
             out, ld = actnorm2d_forward(sd, s, out, dtype)
         logdet = logdet + ld
     return out, logdet
 
 
-def unit_reverse(sd, z, act="elu", alpha=1.0, dtype=np.float64, stages=STAGES):
+def unit_reverse(sd, z, act="elu", alpha=1.0, dtype=np.float64, stages=STAGES, h=None):
     """MaCowUnit.forward(reverse=True) (macow2.py:983-996): the stages in the opposite order, each inverted."""
     out = np.asarray(z, dtype=dtype)
     for s in reversed(stages):
         if s.startswith("conv"):
-            out = mcf_reverse(sd, s, out, act, alpha, dtype)
+            out = mcf_reverse(sd, s, out, act, alpha, dtype, h=h)
         else:
             out = actnorm2d_reverse(sd, s, out, dtype)
     return out

@@ -114,7 +114,7 @@ STEP_COUPLINGS = (("coupling1_up", True, "continuous"), ("coupling1_dn", False, 
                   ("coupling2_up", True, "skip"), ("coupling2_dn", False, "skip"))        # macow2.py:1025-1057
 
 
-def step_forward(sd, x, act="elu", alpha=1.0, dtype=np.float64):
+def step_forward(sd, x, act="elu", alpha=1.0, dtype=np.float64, h=None):
     """MaCowStep.forward (macow2.py:1063-1091): actnorm1, Shuffle, 2 units, NICE up / down (continuous split),
     actnorm2, 2 units, NICE up / down (skip split)."""
     out, logdet = mo.actnorm2d_forward(sd, "actnorm1", x, dtype)
@@ -124,7 +124,7 @@ def step_forward(sd, x, act="elu", alpha=1.0, dtype=np.float64):
             out, ld = mo.actnorm2d_forward(sd, an, out, dtype)
             logdet = logdet + ld
         for u in range(2):
-            out, ld = mo.unit_forward(sub(sd, f"units{part}.{u}."), out, act, alpha, dtype)
+            out, ld = mo.unit_forward(sub(sd, f"units{part}.{u}."), out, act, alpha, dtype, h=h)
             logdet = logdet + ld
         for name, up, st in STEP_COUPLINGS[2 * (part - 1):2 * part]:
             out, ld = nice_apply(sub(sd, name + "."), out, up, st, 2, act, alpha, dtype)
@@ -132,14 +132,14 @@ def step_forward(sd, x, act="elu", alpha=1.0, dtype=np.float64):
     return out, logdet
 
 
-def step_reverse(sd, z, act="elu", alpha=1.0, dtype=np.float64):
+def step_reverse(sd, z, act="elu", alpha=1.0, dtype=np.float64, h=None):
     """MaCowStep.forward(reverse=True) (macow2.py:1092-1117)."""
     out = np.asarray(z, dtype=dtype)
     for part, an in ((2, "actnorm2"), (1, None)):
         for name, up, st in reversed(STEP_COUPLINGS[2 * (part - 1):2 * part]):
             out = nice_apply(sub(sd, name + "."), out, up, st, 2, act, alpha, dtype, reverse=True)
         for u in (1, 0):
-            out = mo.unit_reverse(sub(sd, f"units{part}.{u}."), out, act, alpha, dtype)
+            out = mo.unit_reverse(sub(sd, f"units{part}.{u}."), out, act, alpha, dtype, h=h)
         if an:
             out = mo.actnorm2d_reverse(sd, an, out, dtype)
     out = shuffle(sub(sd, "conv1x1."), out, reverse=True)
@@ -175,14 +175,16 @@ def levels(C, num_steps, factor):
     return out
 
 
-def flow_forward(sd, x, num_steps, factor, act="elu", alpha=1.0, dtype=np.float64):
-    """MultiScaleInternal.forward (macow2.py:872-897) below the prefix of its ``layers / priors / shuffle_layers``."""
+def flow_forward(sd, x, num_steps, factor, act="elu", alpha=1.0, dtype=np.float64, h=None):
+    """MultiScaleInternal.forward (macow2.py:872-897) below the prefix of its ``layers / priors / shuffle_layers``.
+    ``h``: the conditioning of SupervisedMacowTransformer (INN.py:447-482) with ``condition_nice`` false: it reaches the
+    masked flows of the units only (the couplings ignore it, macow_utils.py:330)."""
     out = np.asarray(x, dtype=dtype)
     logdet = np.zeros(out.shape[0], dtype=dtype)
     outputs = []
     for i, (C, f, n) in enumerate(levels(out.shape[1], num_steps, factor)):
         for s in range(n):
-            out, ld = step_forward(sub(sd, f"layers.{i}.{s}."), out, act, alpha, dtype)
+            out, ld = step_forward(sub(sd, f"layers.{i}.{s}."), out, act, alpha, dtype, h=h)
             logdet = logdet + ld
         out, ld = prior_forward(sub(sd, f"priors.{i}."), out, f, act, alpha, dtype)
         logdet = logdet + ld
@@ -195,7 +197,7 @@ def flow_forward(sd, x, num_steps, factor, act="elu", alpha=1.0, dtype=np.float6
     return np.concatenate(outputs, axis=1), logdet
 
 
-def flow_reverse(sd, z, num_steps, factor, act="elu", alpha=1.0, dtype=np.float64):
+def flow_reverse(sd, z, num_steps, factor, act="elu", alpha=1.0, dtype=np.float64, h=None):
     """MultiScaleInternal.forward(reverse=True) (macow2.py:898-918)."""
     out = np.asarray(z, dtype=dtype)
     lv = levels(out.shape[1], num_steps, factor)
@@ -210,5 +212,5 @@ def flow_reverse(sd, z, num_steps, factor, act="elu", alpha=1.0, dtype=np.float6
         out = shuffle(sub(sd, f"shuffle_layers.{i}."), out, reverse=True)
         out = prior_reverse(sub(sd, f"priors.{i}."), out, f, act, alpha, dtype)
         for s in range(n - 1, -1, -1):
-            out = step_reverse(sub(sd, f"layers.{i}.{s}."), out, act, alpha, dtype)
+            out = step_reverse(sub(sd, f"layers.{i}.{s}."), out, act, alpha, dtype, h=h)
     return out

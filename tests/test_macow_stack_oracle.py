@@ -12,7 +12,7 @@ from oracle import macow_stack_oracle as so
 from conftest import max_rel
 
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
-CASES = ["macow_stack_a", "macow_stack_b"]
+CASES = ["macow_stack_a", "macow_stack_b", "macow_stack_c"]           # c: conditional (SupervisedMacowTransformer)
 
 
 def load(name):
@@ -20,20 +20,20 @@ def load(name):
     sd = {k[4:]: g[k] for k in g.files if k.startswith("sd::")}
     C, mid, factor, k0, k1 = (int(v) for v in g["meta"])
     return g, sd, dict(C=C, mid=mid, factor=factor, ks=[k0, k1], act=str(g["activation"]),
-                       num_steps=[int(v) for v in g["num_steps"]])
+                       num_steps=[int(v) for v in g["num_steps"]], h=g["h"] if "h" in g.files else None)
 
 
 @pytest.mark.parametrize("name", CASES)
 def test_full_flow_forward_and_inverse(name):
     g, sd, m = load(name)
     fsd = so.sub(sd, "flow.")
-    out, ld = so.flow_forward(fsd, g["x"], m["num_steps"], m["factor"], m["act"])
+    out, ld = so.flow_forward(fsd, g["x"], m["num_steps"], m["factor"], m["act"], h=m["h"])
     assert max_rel(out, g["out64"]) <= 1e-12 and max_rel(ld, g["logdet64"]) <= 1e-12
     assert max_rel(g["out"], out) <= 2e-5 and max_rel(g["logdet"], ld) <= 2e-5
-    smp = so.flow_reverse(fsd, g["z_in"], m["num_steps"], m["factor"], m["act"])
+    smp = so.flow_reverse(fsd, g["z_in"], m["num_steps"], m["factor"], m["act"], h=m["h"])
     assert max_rel(smp, g["x_smp64"]) <= 1e-10
     assert max_rel(g["x_smp"], smp) <= 5e-4
-    back = so.flow_reverse(fsd, out, m["num_steps"], m["factor"], m["act"])
+    back = so.flow_reverse(fsd, out, m["num_steps"], m["factor"], m["act"], h=m["h"])
     # not exact even in float64: every ActNorm2dFlow inverse divides by exp(log_scale) + 1e-8 (macow2.py:520)
     assert max_rel(back, g["x"].astype(np.float64)) <= 5e-6
 
@@ -48,9 +48,15 @@ def test_components(name):
         o, l = so.nice_apply(csd, x, up, st, 2, m["act"])
         assert max_rel(g[cn + "_out"], o) <= 2e-5 and max_rel(g[cn + "_logdet"], l) <= 2e-5, cn
         assert max_rel(g[cn + "_rev"], so.nice_apply(csd, z, up, st, 2, m["act"], reverse=True)) <= 2e-5, cn
-    o, l = so.step_forward(step, x, m["act"])
+    o, l = so.step_forward(step, x, m["act"], h=m["h"])
     assert max_rel(g["step_out"], o) <= 2e-5 and max_rel(g["step_logdet"], l) <= 2e-5
-    assert max_rel(g["step_rev"], so.step_reverse(step, z, m["act"])) <= 5e-4
+    assert max_rel(g["step_rev"], so.step_reverse(step, z, m["act"], h=m["h"])) <= 5e-4
+    if m["h"] is not None:                                            # one conditional MaCow unit on its own
+        from oracle import macow_oracle as mo
+        usd = so.sub(step, "units1.0.")
+        o, l = mo.unit_forward(usd, x, m["act"], h=m["h"])
+        assert max_rel(g["unit_out"], o) <= 2e-5 and max_rel(g["unit_logdet"], l) <= 2e-5
+        assert max_rel(g["unit_rev"], mo.unit_reverse(usd, z, m["act"], h=m["h"])) <= 5e-4
     prior = so.sub(sd, "flow.priors.0.")
     o, l = so.prior_forward(prior, x, m["factor"], m["act"])
     assert max_rel(g["prior_out"], o) <= 2e-5 and max_rel(g["prior_logdet"], l) <= 2e-5
@@ -68,7 +74,7 @@ def test_level_bookkeeping_matches_the_state_dict():
         assert f"flow.layers.{i}.{n - 1}.actnorm1.bias" in sd and f"flow.layers.{i}.{n}.actnorm1.bias" not in sd
 
 
-@pytest.mark.parametrize("name", CASES)
+@pytest.mark.parametrize("name", CASES[:2])
 def test_torch_restatement_matches_the_reference(name):
     """oracle/macow_stack_oracle_torch.py (the op sequence the bench times as the reference's stock path)."""
     import torch
