@@ -39,6 +39,8 @@ typedef struct ipoke_macow_desc {
   int32_t k1;         /* kernel_size[1]: centred taps along the line, odd (1, 3 or 5)   macow_utils.py:454 */
   int32_t activation; /* IPOKE_MACOW_ACT_*                                                                  */
   float alpha;        /* Affine alpha: scale = tanh(log_scale / 2) * alpha + 1           macow_utils.py:51 */
+  int32_t h_channels; /* conditioning channels concatenated to the hidden activations of every masked flow
+                         (MCFBlock, macow_utils.py:409-412, 431-432); 0 = unconditional                        */
 } ipoke_macow_desc;
 
 /* Floats of one packed unit (shift weights transposed to [C][k0][k1][hidden], weight-normed 1x1 weights
@@ -80,6 +82,29 @@ int ipoke_macow_units_forward(const ipoke_macow_desc* desc, const float* packed,
 int ipoke_macow_units_reverse(const ipoke_macow_desc* desc, const float* packed, int n_units, const float* z,
                               long long z_stride, float* out, long long out_stride, int B, int H, int W,
                               int stage_begin, int stage_end, void* stream);
+
+/* ---- Conditional units (h_channels > 0: SupervisedMacowTransformer, INN.py:447-482, as models/second_stage_video.py:122
+ * builds it).  The conditioning h [B, h_channels, H, W] is concatenated to the hidden activations of every masked flow
+ * before the activation and the weight-normed 1x1 convolution (macow_utils.py:429-436), so its contribution to
+ * (shift, log-scale) does not depend on the image: for a chain of n_units units it is ONE product
+ *   hb [B H W, n_units * 4 * 2C] = act(h) [B H W, h_channels] x Wh [h_channels, n_units * 4 * 2C]
+ * computed once per call and added by the unit kernel in both directions. */
+/* Floats of Wh for a chain of n_units units: h_channels rows of round4(n_units * 8 C) columns. */
+size_t ipoke_macow_cond_floats(const ipoke_macow_desc* desc, int n_units);
+/* ipoke_macow_pack_unit for a conditional unit (weight_v is [2C, hidden + h_channels]); also writes the unit's columns
+ * of Wh (`wh`: the chain's matrix, `unit_index` < n_units). */
+int ipoke_macow_pack_unit_cond(const ipoke_macow_desc* desc, const void* const* params, float* packed, float* wh,
+                               int n_units, int unit_index, void* stream);
+/* hb [B * H * W][round4(n_units * 8 C)] from h (sample stride h_stride >= h_channels * H * W). */
+int ipoke_macow_cond_bias(const ipoke_macow_desc* desc, const float* wh, int n_units, const float* h, long long h_stride,
+                          float* hb, int B, int H, int W, void* stream);
+/* ipoke_macow_units_forward / _reverse with the conditioning product `hb` of the chain. */
+int ipoke_macow_units_forward_cond(const ipoke_macow_desc* desc, const float* packed, int n_units, const float* hb,
+                                   const float* x, long long x_stride, float* out, long long out_stride, float* logdet,
+                                   int accumulate, int B, int H, int W, int stage_begin, int stage_end, void* stream);
+int ipoke_macow_units_reverse_cond(const ipoke_macow_desc* desc, const float* packed, int n_units, const float* hb,
+                                   const float* z, long long z_stride, float* out, long long out_stride, int B, int H,
+                                   int W, int stage_begin, int stage_end, void* stream);
 
 /* ---- NICE2d coupling with the convolutional net (macow2.py:291-437; NICEConvBlock macow_utils.py:253-338 without
  * normalisation layers, attention or conditioning; Affine macow_utils.py:42-66).  The net reads image channels

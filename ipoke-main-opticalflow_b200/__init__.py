@@ -17,14 +17,14 @@ from .optim import FusedAdam, linear_var
 from .optim_sharded import ShardedAdam, plan_pieces
 from .parallel import GradSync, broadcast_parameters, shard_batch, shard_bounds
 from .macow import MaCowUnit, MaskedConvFlow, ActNorm2dFlow
-from .macow_flow import (UnsupervisedMaCowTransformer3, MultiScaleInternal, MultiScalePrior, MaCowStep, NICE2d,
+from .macow_flow import (UnsupervisedMaCowTransformer3, SupervisedMacowTransformer, MultiScaleInternal, MultiScalePrior, MaCowStep, NICE2d,
                          NICEConvBlock)
 from .modules import ActNorm, BasicFullyConnectedNet, IgnoreLeakyRelu, InvLeakyRelu, Shuffle
 
 __all__ = ["SupervisedTransformer", "UnsupervisedTransformer3", "ConditionalFlow", "UnconditionalFlow2",
            "FlowLoss", "ActNorm", "BasicFullyConnectedNet", "Shuffle", "InvLeakyRelu", "IgnoreLeakyRelu",
            "FusedAdam", "linear_var", "install_as_reference", "SecondStageLatentInterface",
-           "FlowAELatentInterface", "ThirdStageLatentInterface", "MaCowUnit", "MaskedConvFlow", "ActNorm2dFlow", "UnsupervisedMaCowTransformer3", "MultiScaleInternal", "MultiScalePrior", "MaCowStep", "NICE2d", "NICEConvBlock", "GradSync", "ShardedAdam", "broadcast_parameters", "shard_batch", "shard_bounds"]
+           "FlowAELatentInterface", "ThirdStageLatentInterface", "MaCowUnit", "MaskedConvFlow", "ActNorm2dFlow", "UnsupervisedMaCowTransformer3", "SupervisedMacowTransformer", "MultiScaleInternal", "MultiScalePrior", "MaCowStep", "NICE2d", "NICEConvBlock", "GradSync", "ShardedAdam", "broadcast_parameters", "shard_batch", "shard_bounds"]
 
 
 def install_as_reference():

@@ -18,8 +18,13 @@ struct CudaLauncher {
   cudaStream_t s;
   template <int kSrc, int kEpi, int BM, int BN, int TM, int TN>
   int gemm(bool async, int gx, int gy, int gz, const macow::GemmParams& p) {
-    if (async) macow::nice_gemm_kernel<kSrc, kEpi, BM, BN, TM, TN, true><<<dim3(gx, gy, gz), macow::kGemmThreads, 0, s>>>(p);
-    else macow::nice_gemm_kernel<kSrc, kEpi, BM, BN, TM, TN, false><<<dim3(gx, gy, gz), macow::kGemmThreads, 0, s>>>(p);
+    if constexpr (kSrc != macow::SRC_NCHW_ACT) {
+      if (async) {
+        macow::nice_gemm_kernel<kSrc, kEpi, BM, BN, TM, TN, true><<<dim3(gx, gy, gz), macow::kGemmThreads, 0, s>>>(p);
+        return (int)cudaGetLastError();
+      }
+    }
+    macow::nice_gemm_kernel<kSrc, kEpi, BM, BN, TM, TN, false><<<dim3(gx, gy, gz), macow::kGemmThreads, 0, s>>>(p);
     return (int)cudaGetLastError();
   }
   int affine(int blocks, int threads, const macow::AffineParams& p) {
@@ -35,6 +40,10 @@ struct CudaLauncher {
     return (int)cudaGetLastError();
   }
   int units(bool reverse, int k1, const macow::UnitParams& p, const Geometry& g);
+  int pack_unit(const macow::PackParams& p) {
+    macow::macow_pack_kernel<<<32, 256, 0, s>>>(p);
+    return (int)cudaGetLastError();
+  }
   int pack_nice(const macow::PackNiceParams& p, int row_blocks, int row_threads) {
     macow::macow_pack_nice_kernel<<<148, 256, 0, s>>>(p);
     macow::macow_pack_nice_rows_kernel<<<row_blocks, row_threads, 0, s>>>(p);
@@ -80,11 +89,11 @@ int CudaLauncher::units(bool reverse, int k1, const macow::UnitParams& p, const 
   return reverse ? launch<true>(k1, p, g, s) : launch<false>(k1, p, g, s);
 }
 
-int run(const ipoke_macow_desc* d, const float* packed, int n_units, const float* in, long long in_stride, float* out,
-        long long out_stride, float* logdet, int accumulate, int B, int H, int W, int s0, int s1, bool reverse,
+int run(const ipoke_macow_desc* d, const float* packed, int n_units, const float* hb, const float* in, long long in_stride,
+        float* out, long long out_stride, float* logdet, int accumulate, int B, int H, int W, int s0, int s1, bool reverse,
         void* stream) {
   CudaLauncher L{static_cast<cudaStream_t>(stream)};
-  return macow::units_run(L, d, packed, n_units, in, in_stride, out, out_stride, logdet, accumulate, B, H, W, s0, s1,
+  return macow::units_run(L, d, packed, n_units, hb, in, in_stride, out, out_stride, logdet, accumulate, B, H, W, s0, s1,
                           reverse);
 }
 
@@ -98,43 +107,65 @@ size_t ipoke_macow_unit_floats(const ipoke_macow_desc* d) {
 }
 
 int ipoke_macow_pack_unit(const ipoke_macow_desc* d, const void* const* params, float* packed, void* stream) {
-  if (int e = macow::check_desc(d)) return e;
-  if (!params || !packed) return IPOKE_INN_E_INVALID;
-  macow::PackParams p;
-  for (int i = 0; i < 20; ++i) {
-    if (!params[i]) return IPOKE_INN_E_INVALID;
-    p.params[i] = static_cast<const float*>(params[i]);
-  }
-  p.packed = packed;
-  p.C = d->C; p.Hd = d->hidden; p.k0 = d->k0; p.k1 = d->k1;
-  macow::macow_pack_kernel<<<32, 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
-  return (int)cudaGetLastError();
+  CudaLauncher L{static_cast<cudaStream_t>(stream)};
+  return macow::pack_unit_run(L, d, params, packed, nullptr, 0, 0);
+}
+
+size_t ipoke_macow_cond_floats(const ipoke_macow_desc* d, int n_units) {
+  if (macow::check_desc(d) || d->h_channels < 1 || n_units < 1) return 0;
+  return (size_t)d->h_channels * macow::cond_ld(d, n_units);
+}
+
+int ipoke_macow_pack_unit_cond(const ipoke_macow_desc* d, const void* const* params, float* packed, float* wh, int n_units,
+                               int unit_index, void* stream) {
+  CudaLauncher L{static_cast<cudaStream_t>(stream)};
+  return macow::pack_unit_run(L, d, params, packed, wh, n_units, unit_index);
+}
+
+int ipoke_macow_cond_bias(const ipoke_macow_desc* d, const float* wh, int n_units, const float* h, long long h_stride,
+                          float* hb, int B, int H, int W, void* stream) {
+  CudaLauncher L{static_cast<cudaStream_t>(stream)};
+  return macow::cond_bias_run(L, d, wh, n_units, h, h_stride, hb, B, H, W);
+}
+
+int ipoke_macow_units_forward_cond(const ipoke_macow_desc* d, const float* packed, int n_units, const float* hb,
+                                   const float* x, long long x_stride, float* out, long long out_stride, float* logdet,
+                                   int accumulate, int B, int H, int W, int stage_begin, int stage_end, void* stream) {
+  return run(d, packed, n_units, hb, x, x_stride, out, out_stride, logdet, accumulate, B, H, W, stage_begin, stage_end,
+             false, stream);
+}
+
+int ipoke_macow_units_reverse_cond(const ipoke_macow_desc* d, const float* packed, int n_units, const float* hb,
+                                   const float* z, long long z_stride, float* out, long long out_stride, int B, int H,
+                                   int W, int stage_begin, int stage_end, void* stream) {
+  return run(d, packed, n_units, hb, z, z_stride, out, out_stride, nullptr, 0, B, H, W, stage_begin, stage_end, true,
+             stream);
 }
 
 int ipoke_macow_forward(const ipoke_macow_desc* d, const float* packed, int n_units, const float* x, float* out,
                         float* logdet, int accumulate, int B, int H, int W, int stage_begin, int stage_end,
                         void* stream) {
   const long long n = d ? (long long)d->C * H * W : 0;
-  return run(d, packed, n_units, x, n, out, n, logdet, accumulate, B, H, W, stage_begin, stage_end, false, stream);
+  return run(d, packed, n_units, nullptr, x, n, out, n, logdet, accumulate, B, H, W, stage_begin, stage_end, false, stream);
 }
 
 int ipoke_macow_reverse(const ipoke_macow_desc* d, const float* packed, int n_units, const float* z, float* out,
                         int B, int H, int W, int stage_begin, int stage_end, void* stream) {
   const long long n = d ? (long long)d->C * H * W : 0;
-  return run(d, packed, n_units, z, n, out, n, nullptr, 0, B, H, W, stage_begin, stage_end, true, stream);
+  return run(d, packed, n_units, nullptr, z, n, out, n, nullptr, 0, B, H, W, stage_begin, stage_end, true, stream);
 }
 
 int ipoke_macow_units_forward(const ipoke_macow_desc* d, const float* packed, int n_units, const float* x,
                               long long x_stride, float* out, long long out_stride, float* logdet, int accumulate,
                               int B, int H, int W, int stage_begin, int stage_end, void* stream) {
-  return run(d, packed, n_units, x, x_stride, out, out_stride, logdet, accumulate, B, H, W, stage_begin, stage_end,
-             false, stream);
+  return run(d, packed, n_units, nullptr, x, x_stride, out, out_stride, logdet, accumulate, B, H, W, stage_begin,
+             stage_end, false, stream);
 }
 
 int ipoke_macow_units_reverse(const ipoke_macow_desc* d, const float* packed, int n_units, const float* z,
                               long long z_stride, float* out, long long out_stride, int B, int H, int W,
                               int stage_begin, int stage_end, void* stream) {
-  return run(d, packed, n_units, z, z_stride, out, out_stride, nullptr, 0, B, H, W, stage_begin, stage_end, true,
+  return run(d, packed, n_units, nullptr, z, z_stride, out, out_stride, nullptr, 0, B, H, W, stage_begin, stage_end, true,
              stream);
 }
 

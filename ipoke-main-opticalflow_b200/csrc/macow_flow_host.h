@@ -26,9 +26,11 @@ inline int check_desc(const ipoke_macow_desc* d) {
   if (!d) return IPOKE_INN_E_INVALID;
   if (d->C < 1 || d->hidden < 4 || (d->hidden & 3) || d->k0 < 1) return IPOKE_INN_E_UNSUPPORTED;
   if (d->k1 != 1 && d->k1 != 3 && d->k1 != 5) return IPOKE_INN_E_UNSUPPORTED;     // ShiftedConv2d asserts odd (macow_utils.py:454)
-  if (d->activation < 0 || d->activation > 2) return IPOKE_INN_E_INVALID;
+  if (d->activation < 0 || d->activation > 2 || d->h_channels < 0) return IPOKE_INN_E_INVALID;
   return IPOKE_INN_OK;
 }
+
+inline int cond_ld(const ipoke_macow_desc* d, int n_units) { return round4(n_units * 8 * d->C); }
 
 inline int geometry(const ipoke_macow_desc* d, int B, int H, int W, bool reverse, Geometry* g) {
   if (H < 1 || W < 1) return IPOKE_INN_E_INVALID;
@@ -73,11 +75,12 @@ inline int geometry(const ipoke_macow_desc* d, int B, int H, int W, bool reverse
 }
 
 template <class Launcher>
-int units_run(Launcher& L, const ipoke_macow_desc* d, const float* packed, int n_units, const float* in,
+int units_run(Launcher& L, const ipoke_macow_desc* d, const float* packed, int n_units, const float* hb, const float* in,
               long long in_stride, float* out, long long out_stride, float* logdet, int accumulate, int B, int H, int W,
               int s0, int s1, bool reverse) {
   if (int e = check_desc(d)) return e;
   if (!packed || !in || !out || n_units < 1 || B < 0) return IPOKE_INN_E_INVALID;
+  if ((d->h_channels > 0) != (hb != nullptr)) return IPOKE_INN_E_INVALID;      // conditional units need their hb, others none
   if (in_stride < (long long)d->C * H * W || out_stride < (long long)d->C * H * W) return IPOKE_INN_E_INVALID;
   if (s0 < 0 || s1 > n_units * IPOKE_MACOW_STAGES_PER_UNIT || s0 > s1) return IPOKE_INN_E_INVALID;
   if (B == 0) return IPOKE_INN_OK;
@@ -99,7 +102,51 @@ int units_run(Launcher& L, const ipoke_macow_desc* d, const float* packed, int n
   p.unit_floats = unit_floats(d->C, d->hidden, d->k0, d->k1);
   p.in_stride = in_stride;
   p.out_stride = out_stride;
+  p.hbias = hb;
+  p.hb_ld = hb ? cond_ld(d, n_units) : 0;
   return L.units(reverse, d->k1, p, g);
+}
+
+template <class Launcher>
+int pack_unit_run(Launcher& L, const ipoke_macow_desc* d, const void* const* params, float* packed, float* wh, int n_units,
+                  int unit_index) {
+  if (int e = check_desc(d)) return e;
+  if (!params || !packed) return IPOKE_INN_E_INVALID;
+  if ((d->h_channels > 0) != (wh != nullptr)) return IPOKE_INN_E_INVALID;
+  if (wh && (n_units < 1 || unit_index < 0 || unit_index >= n_units)) return IPOKE_INN_E_INVALID;
+  PackParams p;
+  for (int i = 0; i < 20; ++i) {
+    if (!params[i]) return IPOKE_INN_E_INVALID;
+    p.params[i] = static_cast<const float*>(params[i]);
+  }
+  p.packed = packed;
+  p.C = d->C; p.Hd = d->hidden; p.k0 = d->k0; p.k1 = d->k1;
+  p.hc = d->h_channels; p.wh = wh;
+  p.wh_ld = wh ? cond_ld(d, n_units) : 0;
+  p.wh_col0 = unit_index * 8 * d->C;
+  return L.pack_unit(p);
+}
+
+// hb = act(h) x Wh for a chain of conditional units (one GEMM over rows = (sample, pixel); the activation is applied
+// while the NCHW conditioning is gathered into the A tile).
+template <class Launcher>
+int cond_bias_run(Launcher& L, const ipoke_macow_desc* d, const float* wh, int n_units, const float* h, long long h_stride,
+                  float* hb, int B, int H, int W) {
+  if (int e = check_desc(d)) return e;
+  if (d->h_channels < 1 || !wh || !h || !hb || n_units < 1 || B < 0 || H < 1 || W < 1) return IPOKE_INN_E_INVALID;
+  if (h_stride < (long long)d->h_channels * H * W) return IPOKE_INN_E_INVALID;
+  if (B == 0) return IPOKE_INN_OK;
+  const int ldn = cond_ld(d, n_units);
+  GemmParams p{};
+  p.A = h; p.sample_stride = h_stride; p.lda = 0;
+  p.Wt = wh; p.ldw = ldn;
+  p.Y = hb; p.ldy = ldn;
+  p.M = B * H * W; p.N = ldn; p.K = d->h_channels;
+  p.H = H; p.W = W;
+  p.g = NiceGeom{0, 0, 1, 0, 0, 1};
+  p.act = d->activation;
+  p.k_split = 1 << 30; p.y_split_stride = 0;
+  return L.template gemm<SRC_NCHW_ACT, EPI_STORE, 128, 64, 8, 4>(false, (p.M + 127) / 128, (ldn + 63) / 64, 1, p);
 }
 
 // ---- coupling nets and per-channel glue (macow_flow_kernel.cuh)

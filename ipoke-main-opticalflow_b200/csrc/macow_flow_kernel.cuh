@@ -37,7 +37,7 @@ __host__ __device__ inline long long nice_floats(int c_in, int c_t, int Hd) {
   return 9LL * c_in * ld + (long long)Hd * ld + 9LL * Hd * ld3 + ld3;
 }
 
-enum { SRC_IMAGE = 0, SRC_ROWS = 1 };
+enum { SRC_IMAGE = 0, SRC_ROWS = 1, SRC_NCHW_ACT = 2 };   // NCHW_ACT: A(m, k) = act(h[b][k][pixel]) (register path only)
 enum { EPI_ACT = 0, EPI_STORE = 1 };
 
 struct GemmParams {
@@ -62,6 +62,7 @@ __device__ __forceinline__ const float* gemm_addr_a(const GemmParams& p, int m, 
   if (m >= p.M || k >= p.K) return nullptr;
   if (kSrc == SRC_ROWS) return p.A + (long long)m * p.lda + k;
   const int HW = p.H * p.W;
+  if (kSrc == SRC_NCHW_ACT) return p.A + (m / HW) * p.sample_stride + (long long)k * HW + py * p.W + px;
   const int c = k / 9, tap = k - c * 9;                      // SRC_IMAGE: k = c * 9 + tap
   const int dy = tap / 3 - 1, dx = tap - (tap / 3) * 3 - 1;
   const int yy = py + dy, xx = px + dx;
@@ -103,6 +104,7 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 template <int kSrc, int kEpi, int BM, int BN, int TM, int TN, bool kAsync>
 __global__ void __launch_bounds__(kGemmThreads) nice_gemm_kernel(const GemmParams p) {
   static_assert((BM / TM) * (BN / TN) == kGemmThreads, "one register tile per thread");
+  static_assert(!(kAsync && kSrc == SRC_NCHW_ACT), "the activation on load needs the register path");
   static_assert(BM % 16 == 0 && TN % 4 == 0 && TM % 4 == 0, "tile shapes");
   constexpr int BK = kGemmBK;
   constexpr int LDA_S = BM + 4;                              // As[k][row], rows 16-byte aligned
@@ -140,8 +142,13 @@ __global__ void __launch_bounds__(kGemmThreads) nice_gemm_kernel(const GemmParam
     for (int i = 0; i < RPT; ++i) {
       const int r = a_r0 + 16 * i;
       const float* src = gemm_addr_a<kSrc>(p, m0 + r, k0 + a_kk, a_py[i], a_px[i]);
-      if (kAsync) cp_async4(as + a_kk * LDA_S + r, src, p.A);
-      else as[a_kk * LDA_S + r] = src ? __ldg(src) : 0.f;
+      if (kAsync) {
+        cp_async4(as + a_kk * LDA_S + r, src, p.A);
+      } else {
+        float v = src ? __ldg(src) : 0.f;
+        if (kSrc == SRC_NCHW_ACT) v = activate(v, p.act);    // act(0) = 0 for relu / elu / leaky_relu: padding stays zero
+        as[a_kk * LDA_S + r] = v;
+      }
     }
     for (int v = tid; v < BK * (BN / 4); v += kGemmThreads) {
       const int kk = v / (BN / 4), n4 = (v - kk * (BN / 4)) * 4;

@@ -55,6 +55,8 @@ struct UnitParams {
   int ksplit;                   // inverse: groups of threads sharing the input-channel loop of one line (>= 1)
   long long unit_floats;
   long long in_stride, out_stride;  // floats between consecutive samples of in / out (C * H * W when dense)
+  const float* hbias;               // conditional units: [B * H * W][hb_ld], column (unit * 4 + flow) * 2C + 2c = the
+  int hb_ld;                        // conditioning's contribution to (shift, log-scale) of channel c; null = unconditional
 };
 
 __host__ __device__ inline long long flow_floats(int C, int Hd, int k0, int k1) {
@@ -95,7 +97,8 @@ __device__ __forceinline__ float2 ldw2(const float* ptr) {          // ptr is 8-
 template <bool kReverse, int kK1, int kQC, bool kWS>
 __device__ __forceinline__ void mcf_stage(float* __restrict__ XA, float* __restrict__ XB, float* __restrict__ hid,
                                           float* __restrict__ wsm, const float* __restrict__ fw_global,
-                                          const UnitParams& p, int flow, float& logdet_acc) {
+                                          const UnitParams& p, int flow, const float* __restrict__ hb,
+                                          float& logdet_acc) {
   const int C = p.C, Hd = p.Hd, k0 = p.k0, HW = p.H * p.W;
   constexpr int k1 = kK1;
   constexpr int cq = (k1 - 1) >> 1;
@@ -257,6 +260,11 @@ __device__ __forceinline__ void mcf_stage(float* __restrict__ XA, float* __restr
         const int pix = pix0 + k;
         if (pix < npix) {
           const int t = pix / Q, q = pix - t * Q, l = l0 + t;
+          if (hb != nullptr) {                                          // conditioning term of this image pixel
+            const float2 hv = __ldg(reinterpret_cast<const float2*>(hb + (long long)(rows ? l * Q + q : q * L + l) * p.hb_ld + 2 * c));
+            mu[k] += hv.x;
+            lg[k] += hv.y;
+          }
           const float scale = tanhf(0.5f * lg[k]) * p.alpha + 1.0f;
           float* xl = Xl + c * HW + l * Q + q;
           float v = *xl;
@@ -327,7 +335,9 @@ __global__ void __launch_bounds__(512, 1) macow_unit_kernel(const UnitParams p) 
       actnorm_stage<kReverse>(XA, XB, up + 4 * ff + (st == 5 ? 2 * p.C : 0), p, logdet_acc);
     } else {
       const int flow = st < 2 ? st : st - 1;
-      mcf_stage<kReverse, kK1, kQC, kWS>(XA, XB, hid, wsm, up + flow * ff, p, flow, logdet_acc);
+      const float* hb = p.hbias == nullptr ? nullptr
+                                           : p.hbias + (long long)b * HW * p.hb_ld + (unit * 4 + flow) * 2 * p.C;
+      mcf_stage<kReverse, kK1, kQC, kWS>(XA, XB, hid, wsm, up + flow * ff, p, flow, hb, logdet_acc);
     }
   }
   float* dst = p.out + (long long)b * p.out_stride;
@@ -355,6 +365,9 @@ struct PackParams {
   const float* params[20];
   float* packed;
   int C, Hd, k0, k1;
+  int hc;            // conditioning channels: weight_v rows are [Hd + hc] wide, the last hc columns go to wh
+  float* wh;         // [hc][wh_ld]: the chain's conditioning matrix (null when hc == 0)
+  int wh_ld, wh_col0;  // this unit's first column = unit_index * 8 C
 };
 
 __global__ void macow_pack_kernel(const PackParams p) {
@@ -384,12 +397,14 @@ __global__ void macow_pack_kernel(const PackParams p) {
     const float* v = p.params[f * 4 + 3];
     float* w1T = dst + nshift;
     float* b1 = w1T + (long long)Hd * 2 * C;
+    const int vw = Hd + p.hc;                                         // row width of weight_v
     for (int o = tid; o < 2 * C; o += nthreads) {
       float ss = 0.f;
-      for (int j = 0; j < Hd; ++j) ss = fmaf(v[o * Hd + j], v[o * Hd + j], ss);
+      for (int j = 0; j < vw; ++j) ss = fmaf(v[o * vw + j], v[o * vw + j], ss);
       const float mul = g[o] / sqrtf(ss);
       const int slot = o < C ? 2 * o : 2 * (o - C) + 1;               // output o: mu of channel o, or log-scale of o - C
-      for (int j = 0; j < Hd; ++j) w1T[(long long)j * 2 * C + slot] = v[o * Hd + j] * mul;
+      for (int j = 0; j < Hd; ++j) w1T[(long long)j * 2 * C + slot] = v[o * vw + j] * mul;
+      for (int k = 0; k < p.hc; ++k) p.wh[(long long)k * p.wh_ld + p.wh_col0 + f * 2 * C + slot] = v[o * vw + Hd + k] * mul;
       b1[slot] = bias[o];
     }
   }

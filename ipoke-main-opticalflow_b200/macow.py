@@ -20,7 +20,7 @@ STAGES = ("conv1", "conv2", "actnorm1", "conv3", "conv4", "actnorm2")
 
 class MacowDesc(ctypes.Structure):
     _fields_ = [("C", ctypes.c_int32), ("hidden", ctypes.c_int32), ("k0", ctypes.c_int32), ("k1", ctypes.c_int32),
-                ("activation", ctypes.c_int32), ("alpha", ctypes.c_float)]
+                ("activation", ctypes.c_int32), ("alpha", ctypes.c_float), ("h_channels", ctypes.c_int32)]
 
 
 class NiceDesc(ctypes.Structure):
@@ -45,6 +45,16 @@ def _bind(L):
     L.ipoke_macow_units_forward.argtypes = [dp, vp, i32, vp, i64, vp, i64, vp, i32, i32, i32, i32, i32, i32, vp]
     L.ipoke_macow_units_reverse.restype = i32
     L.ipoke_macow_units_reverse.argtypes = [dp, vp, i32, vp, i64, vp, i64, i32, i32, i32, i32, i32, vp]
+    L.ipoke_macow_cond_floats.restype = sz
+    L.ipoke_macow_cond_floats.argtypes = [dp, i32]
+    L.ipoke_macow_pack_unit_cond.restype = i32
+    L.ipoke_macow_pack_unit_cond.argtypes = [dp, ctypes.POINTER(vp), vp, vp, i32, i32, vp]
+    L.ipoke_macow_cond_bias.restype = i32
+    L.ipoke_macow_cond_bias.argtypes = [dp, vp, i32, vp, i64, vp, i32, i32, i32, vp]
+    L.ipoke_macow_units_forward_cond.restype = i32
+    L.ipoke_macow_units_forward_cond.argtypes = [dp, vp, i32, vp, vp, i64, vp, i64, vp, i32, i32, i32, i32, i32, i32, vp]
+    L.ipoke_macow_units_reverse_cond.restype = i32
+    L.ipoke_macow_units_reverse_cond.argtypes = [dp, vp, i32, vp, vp, i64, vp, i64, i32, i32, i32, i32, i32, vp]
     L.ipoke_macow_launch_info.restype = i32
     L.ipoke_macow_launch_info.argtypes = [dp, i32, i32, i32, ctypes.POINTER(i32), ctypes.POINTER(i32),
                                           ctypes.POINTER(i32)]
@@ -146,13 +156,12 @@ class MCFBlock(nn.Module):
     def __init__(self, in_channels, out_channels, kernel_size, hidden_channels, order, activation, h_channels=None,
                  p_dropout=0.):
         super().__init__()
-        if h_channels is not None:
-            raise NotImplementedError("conditional MCF blocks (h_channels > 0) are not built")
         if p_dropout != 0.:
             raise NotImplementedError("dropout inside the MCF block is not built")
         assert activation in ACTIVATIONS
         self.shift_conv = ShiftedConv2d(in_channels, hidden_channels, kernel_size, order=order)
-        self.conv1x1 = Conv2dWeightNorm(hidden_channels, out_channels, zero_init=True)
+        # the conditioning is concatenated to the hidden activations in front of the 1x1 convolution (macow_utils.py:409-412)
+        self.conv1x1 = Conv2dWeightNorm(hidden_channels + (h_channels or 0), out_channels, zero_init=True)
 
 
 class ActNorm2dFlow(nn.Module):
@@ -187,8 +196,6 @@ class MaskedConvFlow(nn.Module):
         super().__init__()
         self.in_channels = in_channels
         self.cond = h_channels is not None and h_channels > 0
-        if self.cond:
-            raise NotImplementedError("conditional masked-convolution flows (h_channels > 0) are not built")
         if transform != "affine":
             raise NotImplementedError(f"transform {transform!r}: only 'affine' is built")
         if hidden_channels is None:
@@ -199,19 +206,21 @@ class MaskedConvFlow(nn.Module):
         self.order = order
         self.analytic_bwd = True
         self.net = MCFBlock(in_channels, in_channels * 2, kernel_size, hidden_channels, order, activation,
-                            h_channels=None, p_dropout=p_dropout)
+                            h_channels=h_channels if self.cond else None, p_dropout=p_dropout)
 
 
 class MaCowUnit(nn.Module):
     """Drop-in for macow2.py:925-996: ``forward(input, h=None, reverse=False)`` returns ``(out, logdet)`` or,
-    with ``reverse=True``, the inverse image.  One kernel launch per call (one CTA per sample)."""
+    with ``reverse=True``, the inverse image.  One kernel launch per call (one CTA per sample); a conditional unit
+    (``h_channels > 0``, conditioning ``h`` [B, h_channels, H, W]) adds the launch of its conditioning product."""
 
     def __init__(self, in_channels, kernel_size, h_channels=0, transform="affine", alpha=1.0, h_type=None,
                  activation="relu", cond_conv=False, cond_conv_hidden_channels=None, p_dropout=0.):
         super().__init__()
-        if h_channels:
-            raise NotImplementedError("conditional MaCow units (h_channels > 0) are not built")
+        if cond_conv and h_channels:
+            raise NotImplementedError("the gated convolution on the conditioning (cond_conv) is not built")
         self.cond_conv = False
+        self.h_channels = int(h_channels or 0)
         k0, k1 = kernel_size[0], kernel_size[1]
         kw = dict(h_channels=h_channels, transform=transform, alpha=alpha, h_type=h_type, activation=activation,
                   p_dropout=p_dropout)
@@ -222,7 +231,9 @@ class MaCowUnit(nn.Module):
         self.conv4 = MaskedConvFlow(in_channels, (k1, k0), order="D", **kw)
         self.actnorm2 = ActNorm2dFlow(in_channels)
         self.in_channels = in_channels
-        self._desc = MacowDesc(in_channels, self.conv1.hidden_channels, k0, k1, ACTIVATIONS[activation], alpha)
+        self._desc = MacowDesc(in_channels, self.conv1.hidden_channels, k0, k1, ACTIVATIONS[activation], alpha,
+                               self.h_channels)
+        self._program = None
         self._packed = None
         self._packed_key = None
         self._init_checked = False
@@ -312,8 +323,13 @@ class MaCowUnit(nn.Module):
         return out, logdet
 
     def forward(self, input, h=None, reverse=False):
+        if self.h_channels:                       # conditional: through a one-call program (macow_flow.Program)
+            if self._program is None:
+                from .macow_flow import Program
+                self._program = Program([("units", [self])], self.in_channels, [self])
+            return self._program.run(input, reverse, h)
         if h is not None:
-            raise NotImplementedError("conditional MaCow units are not built")
+            raise ValueError("this unit was built without conditioning channels (h_channels = 0)")
         if torch.is_grad_enabled() and (input.requires_grad or any(p.requires_grad for p in self.parameters())):
             raise NotImplementedError("the MaCow path is inference only: call it under torch.no_grad()")
         x = _check_input(input, self.in_channels)

@@ -1,12 +1,14 @@
 """The multi-scale MaCow flow on B200: drop-ins for the reference's ``NICE2d`` / ``NICEConvBlock``
 (models/modules/INN/macow2.py:291-437, macow_utils.py:253-338), ``MaCowStep`` (macow2.py:999-1117),
 ``MultiScalePrior`` (macow2.py:543-594), ``MultiScaleInternal`` (macow2.py:821-918) and the wrapper
-``UnsupervisedMaCowTransformer3`` (INN.py:365-390) with the same constructors, attribute names, state_dict keys and RNG
-draw order, computing through the CUDA kernels behind ``include/ipoke_macow.h``.  Row N3 of SURVEY.md section 8(f).
+wrappers ``UnsupervisedMaCowTransformer3`` (INN.py:365-390) and ``SupervisedMacowTransformer`` (INN.py:447-482) with the
+same constructors, attribute names, state_dict keys and RNG draw order, computing through the CUDA kernels behind
+``include/ipoke_macow.h``.  Row N3 of SURVEY.md section 8(f).
 
-Built: what ``config/second_stage.yaml:53-80`` selects -- unconditional (``h_channels = 0``), 'affine' transforms,
-'conv' couplings, Shuffle permutations (``use1x1`` false), no normalisation layers / attention / conditioning
-convolutions, dropout 0.  Anything else raises NotImplementedError.  Inference only (forward with logdet and the inverse
+Built: what ``config/second_stage.yaml:53-80`` selects -- 'affine' transforms, 'conv' couplings, Shuffle permutations
+(``use1x1`` false), no normalisation layers / attention, ``cond_conv`` and ``condition_nice`` false, dropout 0;
+unconditional, or conditional on ``h`` [B, h_channels, H, W] (which then reaches the masked flows of the units, as in
+the reference with ``condition_nice`` false).  Anything else raises NotImplementedError.  Inference only (forward with logdet and the inverse
 used for sampling); there is no CPU or eager fallback.
 
 How a call runs: the image lives in ONE [B, C, H, W] buffer for the whole flow.  Every level works in place on the first
@@ -98,8 +100,7 @@ class NICE2d(nn.Module):
         return [n.conv1.weight, n.conv2.weight, n.conv3.conv.bias, n.conv3.conv.weight_g, n.conv3.conv.weight_v]
 
     def forward(self, input, h=None, reverse=False):
-        if h is not None:
-            raise NotImplementedError("conditional NICE couplings are not built")
+        # built with h_channels = 0: like the reference's NICEConvBlock (macow_utils.py:330) it ignores a conditioning
         if self._program is None:
             self._program = Program([("nice", self)], self.in_channels, [self])
         return self._program.run(input, reverse)
@@ -111,14 +112,16 @@ class MaCowStep(nn.Module):
     def __init__(self, in_channels, kernel_size, hidden_channels, h_channels, transform="affine", alpha=1.0,
                  coupling_type="conv", h_type=None, activation="relu", normalize=None, num_groups=None, **kwargs):
         super().__init__()
-        _unsupported(h_channels=(h_channels, (0, None)))
+        _unsupported(condition_nice=(bool(kwargs.get("condition_nice", False)), (False,)),
+                     cond_conv=(bool(kwargs.get("cond_conv", False)) and bool(h_channels), (False,)))
+        self.h_channels = int(h_channels or 0)
         attention = bool(kwargs.get("attention", False))
         heads = kwargs.get("heads", 4)
         ssize = kwargs.get("spatial_size", 8)
         cond_conv = kwargs.get("cond_conv", False)
         cchc = kwargs.get("cond_conv_hidden_channels", None)
         p_dropout = kwargs.get("p_dropout", 0.)
-        unit_kw = dict(h_channels=0, transform=transform, alpha=alpha, h_type=h_type, activation=activation,
+        unit_kw = dict(h_channels=self.h_channels, transform=transform, alpha=alpha, h_type=h_type, activation=activation,
                        cond_conv=cond_conv, cond_conv_hidden_channels=cchc, p_dropout=p_dropout)
         nice_kw = dict(hidden_channels=hidden_channels, h_channels=0, transform=transform, alpha=alpha,
                        type=coupling_type, h_type=h_type, activation=activation, normalize=normalize,
@@ -145,11 +148,9 @@ class MaCowStep(nn.Module):
                 ("units", list(self.units2)), ("nice", self.coupling2_up), ("nice", self.coupling2_dn)]
 
     def forward(self, input, h=None, reverse=False):
-        if h is not None:
-            raise NotImplementedError("conditional MaCow steps are not built")
         if self._program is None:
             self._program = Program(self.ops(), self.in_channels, [self])
-        return self._program.run(input, reverse)
+        return self._program.run(input, reverse, h)
 
 
 class MultiScalePrior(nn.Module):
@@ -159,7 +160,7 @@ class MultiScalePrior(nn.Module):
                  activation, normalize, num_groups, use_1x1=False, condition_nice=False, attention=False, heads=4,
                  spatial_size=8, cond_conv=False, cond_conv_hidden_channels=None, p_dropout=0.):
         super().__init__()
-        _unsupported(use_1x1=(bool(use_1x1), (False,)), h_channels=(h_channels, (0, None)))
+        _unsupported(use_1x1=(bool(use_1x1), (False,)), condition_nice=(bool(condition_nice), (False,)))
         self.in_channels = in_channels
         self.conv1x1 = Shuffle(in_channels)
         self.coupling = NICE2d(in_channels, hidden_channels=hidden_channels, h_channels=0, transform=transform,
@@ -182,8 +183,8 @@ class MultiScalePrior(nn.Module):
                  C - self.z1_channels)]
 
     def forward(self, input, h=None, reverse=False):
-        if h is not None:
-            raise NotImplementedError("conditional priors are not built")
+        # with condition_nice false the prior's coupling is built without conditioning channels and ignores h
+        # (macow2.py:556, macow_utils.py:330)
         if self._program is None:
             self._program = Program(self.ops(), self.in_channels, [self])
         return self._program.run(input, reverse)
@@ -198,7 +199,9 @@ class MultiScaleInternal(nn.Module):
                  attention=False, heads=4, spatial_size=8, cond_conv=False, cond_conv_hidden_channels=None,
                  p_dropout=0.):
         super().__init__()
-        _unsupported(use_1x1=(bool(use_1x1), (False,)), h_channels=(h_channels, (0, None)))
+        _unsupported(use_1x1=(bool(use_1x1), (False,)), condition_nice=(bool(condition_nice), (False,)),
+                     cond_conv=(bool(cond_conv) and bool(h_channels), (False,)))
+        self.h_channels = int(h_channels or 0)
         self.reshape = "none"
         num_layers = len(num_steps)
         assert num_layers < factor
@@ -239,11 +242,9 @@ class MultiScaleInternal(nn.Module):
         return ops
 
     def forward(self, input, h=None, reverse=False):
-        if h is not None:
-            raise NotImplementedError("conditional MaCow flows are not built")
         if self._program is None:
             self._program = Program(self.ops(), self.in_channels, [self])
-        return self._program.run(input, reverse)
+        return self._program.run(input, reverse, h)
 
     def invalidate(self):
         """Force a repack and a re-read of the ``initialized`` flags (after writing parameters through ``.data``)."""
@@ -262,6 +263,8 @@ class Program:
         self.packed = [None] * len(ops)           # per op: (tensor, key)
         self.init_done = False
         self.ws = None
+        self.hb = None
+        self.h_channels = max([op[1][0].h_channels for op in ops if op[0] == "units"] + [0])
         for r in roots:
             r.register_load_state_dict_post_hook(lambda module, incompatible, self=self: self.invalidate())
 
@@ -280,7 +283,7 @@ class Program:
         key = tuple((p.data_ptr(), p._version) for p in ps)
         cur = self.packed[i]
         if cur is not None and cur[1] == key and cur[0].device == dev:
-            return cur[0]
+            return cur[0] if op[0] != "units" else (cur[0], cur[2])
         L = _m._lib()
         if any(p.dtype != torch.float32 for p in ps):
             raise TypeError("MaCow parameters must be float32")
@@ -291,10 +294,20 @@ class Program:
             if n == 0:
                 raise RuntimeError("ipoke_macow: unsupported unit shape (hidden % 4, kernel_size[1] in {1, 3, 5})")
             buf = torch.empty(n * len(units), dtype=torch.float32, device=dev)
+            wh = None
+            if d.h_channels:                       # conditional chain: the conditioning matrix of all its flows
+                wh = torch.empty(L.ipoke_macow_cond_floats(ctypes.byref(d), len(units)), dtype=torch.float32, device=dev)
             for u in range(len(units)):
                 ptrs = (ctypes.c_void_p * 20)(*[t.data_ptr() for t in tensors[20 * u:20 * u + 20]])
-                _capi.check(L.ipoke_macow_pack_unit(ctypes.byref(d), ptrs, buf.data_ptr() + 4 * n * u, _m._stream(dev)),
-                            "ipoke_macow_pack_unit")
+                if wh is None:
+                    _capi.check(L.ipoke_macow_pack_unit(ctypes.byref(d), ptrs, buf.data_ptr() + 4 * n * u,
+                                                        _m._stream(dev)), "ipoke_macow_pack_unit")
+                else:
+                    _capi.check(L.ipoke_macow_pack_unit_cond(ctypes.byref(d), ptrs, buf.data_ptr() + 4 * n * u,
+                                                             wh.data_ptr(), len(units), u, _m._stream(dev)),
+                                "ipoke_macow_pack_unit_cond")
+            self.packed[i] = (buf, key, wh)
+            return buf, wh
         else:
             d = op[1]._desc
             n = L.ipoke_macow_nice_floats(ctypes.byref(d))
@@ -329,13 +342,32 @@ class Program:
             int(reverse), int(not reverse), logdet.data_ptr() if (logdet is not None and not reverse) else None,
             _m._stream(buf.device)), "ipoke_macow_chanmap")
 
-    def _units(self, i, buf, stride, B, H, W, logdet, reverse, s0=None, s1=None):
+    def _units(self, i, buf, stride, B, H, W, logdet, reverse, h=None, s0=None, s1=None):
         units = self.ops[i][1]
-        packed = self._segment(i, buf.device)
+        packed, wh = self._segment(i, buf.device)
         d = units[0]._desc
         s0 = 0 if s0 is None else s0
         s1 = 6 * len(units) if s1 is None else s1
         L = _m._lib()
+        if wh is not None:
+            # the conditioning's contribution to every (shift, log-scale) of the chain: hb = act(h) x Wh, one launch
+            need = B * H * W * (wh.numel() // d.h_channels)
+            if self.hb is None or self.hb.numel() < need or self.hb.device != buf.device:
+                self.hb = torch.empty(need, dtype=torch.float32, device=buf.device)
+            st = _m._stream(buf.device)
+            _capi.check(L.ipoke_macow_cond_bias(ctypes.byref(d), wh.data_ptr(), len(units), h.data_ptr(),
+                                                d.h_channels * H * W, self.hb.data_ptr(), B, H, W, st),
+                        "ipoke_macow_cond_bias")
+            if reverse:
+                _capi.check(L.ipoke_macow_units_reverse_cond(ctypes.byref(d), packed.data_ptr(), len(units),
+                                                             self.hb.data_ptr(), buf.data_ptr(), stride, buf.data_ptr(),
+                                                             stride, B, H, W, s0, s1, st), "ipoke_macow_units_reverse_cond")
+            else:
+                _capi.check(L.ipoke_macow_units_forward_cond(ctypes.byref(d), packed.data_ptr(), len(units),
+                                                             self.hb.data_ptr(), buf.data_ptr(), stride, buf.data_ptr(),
+                                                             stride, logdet.data_ptr(), 1, B, H, W, s0, s1, st),
+                            "ipoke_macow_units_forward_cond")
+            return
         if reverse:
             _capi.check(L.ipoke_macow_units_reverse(ctypes.byref(d), packed.data_ptr(), len(units), buf.data_ptr(), stride,
                                                     buf.data_ptr(), stride, B, H, W, s0, s1, _m._stream(buf.device)),
@@ -372,7 +404,7 @@ class Program:
         self.init_done = True
         return False
 
-    def _forward_with_init(self, buf, stride, B, H, W, logdet):
+    def _forward_with_init(self, buf, stride, B, H, W, logdet, h=None):
         """ActNorm2dFlow.init on the data that reaches it (macow2.py:503-505, 526-541); the zero_init weight-normed
         convolutions get gain 0 and bias 0 (macow_utils.py:235-251 with init_scale = 0)."""
         for i, op in enumerate(self.ops):
@@ -398,14 +430,25 @@ class Program:
                         elif int(mod.initialized.item()) == 0:
                             mod.init(buf[:, :C])
                             mod.initialized.fill_(1)
-                        self._units(i, buf, stride, B, H, W, logdet, False, 6 * u + s, 6 * u + s + 1)
+                        self._units(i, buf, stride, B, H, W, logdet, False, h, 6 * u + s, 6 * u + s + 1)
 
-    def run(self, input, reverse=False):
+    def _check_h(self, h, x):
+        if not self.h_channels:
+            return None                                          # no conditional unit in this program: h is ignored
+        if h is None:
+            raise ValueError(f"this flow is conditional: pass the conditioning h [batch, {self.h_channels}, H, W]")
+        want = (x.shape[0], self.h_channels, x.shape[2], x.shape[3])
+        if tuple(h.shape) != want or h.dtype != torch.float32 or h.device != x.device:
+            raise ValueError(f"conditioning: expected float32 {want} on {x.device}, got {h.dtype} {tuple(h.shape)} on {h.device}")
+        return h.contiguous()
+
+    def run(self, input, reverse=False, h=None):
         if torch.is_grad_enabled() and (input.requires_grad or any(p.requires_grad for r in self.roots
                                                                    for p in r.parameters())):
             raise NotImplementedError("the MaCow path is inference only: call it under torch.no_grad()")
         x = _m._check_input(input, self.channels)
         B, C, H, W = x.shape
+        h = self._check_h(h, x)
         buf = x.clone() if x.data_ptr() == input.data_ptr() else x
         stride = C * H * W
         if B == 0:
@@ -416,19 +459,19 @@ class Program:
                 if op[0] == "glue":
                     self._glue(op, buf, stride, B, H, W, None, True)
                 elif op[0] == "units":
-                    self._units(i, buf, stride, B, H, W, None, True)
+                    self._units(i, buf, stride, B, H, W, None, True, h)
                 else:
                     self._nice(i, buf, stride, B, H, W, None, True)
             return buf
         logdet = torch.zeros(B, dtype=torch.float32, device=buf.device)
         if self._needs_init():
-            self._forward_with_init(buf, stride, B, H, W, logdet)
+            self._forward_with_init(buf, stride, B, H, W, logdet, h)
             return buf, logdet
         for i, op in enumerate(self.ops):
             if op[0] == "glue":
                 self._glue(op, buf, stride, B, H, W, logdet, False)
             elif op[0] == "units":
-                self._units(i, buf, stride, B, H, W, logdet, False)
+                self._units(i, buf, stride, B, H, W, logdet, False, h)
             else:
                 self._nice(i, buf, stride, B, H, W, logdet, False)
         return buf, logdet
@@ -437,7 +480,7 @@ class Program:
     def launches(self):
         """Kernel launches of one call (either direction) at a batch that needs one pass per coupling: a coupling is
         three GEMMs and the tap / affine kernel."""
-        return sum({"glue": 1, "units": 1, "nice": 4}[op[0]] for op in self.ops)
+        return sum({"glue": 1, "units": 2 if self.h_channels else 1, "nice": 4}[op[0]] for op in self.ops)
 
 
 class UnsupervisedMaCowTransformer3(nn.Module):
@@ -467,4 +510,45 @@ class UnsupervisedMaCowTransformer3(nn.Module):
     def sample(self, shape, device="cpu"):
         z_tilde = torch.randn(shape).to(device)
         sample = self.reverse(z_tilde)
+        return sample
+
+
+class SupervisedMacowTransformer(nn.Module):
+    """INN.py:447-482: the conditional flow of the conv second stage (models/second_stage_video.py:122).  Reads the same
+    config keys as the reference (``flow_attn_heads`` and ``cond_conv_hidden_channels`` are required there too)."""
+
+    def __init__(self, config):
+        super().__init__()
+        self.config = config
+        condition_nice = "condition_nice" in self.config and self.config["condition_nice"]
+        attention = "attention" in self.config and self.config["attention"]
+        heads = self.config["flow_attn_heads"]
+        ssize = "ssize" in self.config and self.config["ssize"]
+        cond_conv = "cond_conv" in config and config["cond_conv"]
+        cond_conv_hidden_channels = config["cond_conv_hidden_channels"]
+        p_drop = config["p_dropout"] if "p_dropout" in config else 0.
+        self.flow = MultiScaleInternal(MaCowStep, num_steps=self.config["num_steps"],
+                                       in_channels=self.config["flow_in_channels"],
+                                       hidden_channels=self.config["flow_mid_channels"],
+                                       h_channels=self.config["h_channels"], factor=self.config["factor"],
+                                       transform=self.config["transform"], prior_transform=self.config["prior_transform"],
+                                       kernel_size=self.config["kernel_size"], coupling_type=self.config["coupling_type"],
+                                       activation=self.config["activation"],
+                                       use_1x1=self.config["use1x1"] if "use1x1" in self.config else False,
+                                       condition_nice=condition_nice, attention=attention, heads=heads, spatial_size=ssize,
+                                       cond_conv=cond_conv, cond_conv_hidden_channels=cond_conv_hidden_channels,
+                                       p_dropout=p_drop)
+
+    def forward(self, input, cond, reverse=False):
+        if reverse:
+            return self.reverse(input, cond)
+        out, logdet = self.flow(input, cond)
+        return out, logdet
+
+    def reverse(self, out, cond):
+        return self.flow(out, cond, reverse=True)
+
+    def sample(self, shape, cond, device="cpu"):
+        z_tilde = torch.randn(shape).to(device)
+        sample = self.reverse(z_tilde, cond)
         return sample

@@ -53,6 +53,7 @@ void emul_pack(const float* const* params, float* packed, int C, int Hd, int k0,
   macow::PackParams p;
   for (int i = 0; i < 20; ++i) p.params[i] = params[i];
   p.packed = packed; p.C = C; p.Hd = Hd; p.k0 = k0; p.k1 = k1;
+  p.hc = 0; p.wh = nullptr; p.wh_ld = 0; p.wh_col0 = 0;
   blockDim.x = 1; gridDim.x = 1; blockIdx.x = 0; threadIdx.x = 0;
   macow::macow_pack_kernel(p);
 }
@@ -66,6 +67,7 @@ void emul_run(const float* packed, int n_units, const float* in, float* out, flo
   p.stage_begin = s0; p.stage_end = s1; p.tile_lines = tile_lines; p.accumulate = accumulate;
   p.unit_floats = macow::unit_floats(C, Hd, k0, k1);
   p.in_stride = p.out_stride = (long long)C * H * W;
+  p.hbias = nullptr; p.hb_ld = 0;
   blockDim.x = 1; gridDim.x = B; threadIdx.x = 0;
   p.act = act;
   p.ksplit = ksplit;

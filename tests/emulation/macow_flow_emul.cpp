@@ -17,8 +17,14 @@ struct EmulLauncher {
   int gemm(bool async, int gx, int gy, int gz, const macow::GemmParams& p) {
     for (int z = 0; z < gz; ++z) {
       emul::grid_z = z;
-      if (async) emul::launch(gx, gy, macow::kGemmThreads, [&] { macow::nice_gemm_kernel<kSrc, kEpi, BM, BN, TM, TN, true>(p); });
-      else emul::launch(gx, gy, macow::kGemmThreads, [&] { macow::nice_gemm_kernel<kSrc, kEpi, BM, BN, TM, TN, false>(p); });
+      bool done = false;
+      if constexpr (kSrc != macow::SRC_NCHW_ACT) {
+        if (async) {
+          emul::launch(gx, gy, macow::kGemmThreads, [&] { macow::nice_gemm_kernel<kSrc, kEpi, BM, BN, TM, TN, true>(p); });
+          done = true;
+        }
+      }
+      if (!done) emul::launch(gx, gy, macow::kGemmThreads, [&] { macow::nice_gemm_kernel<kSrc, kEpi, BM, BN, TM, TN, false>(p); });
     }
     emul::grid_z = 0;
     return 0;
@@ -30,6 +36,10 @@ struct EmulLauncher {
   int chanmap(int B, int threads, size_t smem, const macow::ChanMapParams& p) {
     if (smem > sizeof(macow::smem)) return IPOKE_INN_E_UNSUPPORTED;
     emul::launch(B, 1, threads, [&] { macow::macow_chanmap_kernel(p); });
+    return 0;
+  }
+  int pack_unit(const macow::PackParams& p) {
+    emul::launch(2, 1, 64, [&] { macow::macow_pack_kernel(p); });
     return 0;
   }
   int pack_nice(const macow::PackNiceParams& p, int row_blocks, int row_threads) {
@@ -69,27 +79,53 @@ size_t ipoke_macow_unit_floats(const ipoke_macow_desc* d) {
 }
 
 int ipoke_macow_pack_unit(const ipoke_macow_desc* d, const void* const* params, float* packed, void*) {
-  if (int e = macow::check_desc(d)) return e;
-  macow::PackParams p;
-  for (int i = 0; i < 20; ++i) p.params[i] = static_cast<const float*>(params[i]);
-  p.packed = packed;
-  p.C = d->C; p.Hd = d->hidden; p.k0 = d->k0; p.k1 = d->k1;
-  emul::launch(2, 1, 64, [&] { macow::macow_pack_kernel(p); });
-  return 0;
+  EmulLauncher L;
+  return macow::pack_unit_run(L, d, params, packed, nullptr, 0, 0);
+}
+
+size_t ipoke_macow_cond_floats(const ipoke_macow_desc* d, int n_units) {
+  if (macow::check_desc(d) || d->h_channels < 1 || n_units < 1) return 0;
+  return (size_t)d->h_channels * macow::cond_ld(d, n_units);
+}
+
+int ipoke_macow_pack_unit_cond(const ipoke_macow_desc* d, const void* const* params, float* packed, float* wh, int n_units,
+                               int unit_index, void*) {
+  EmulLauncher L;
+  return macow::pack_unit_run(L, d, params, packed, wh, n_units, unit_index);
+}
+
+int ipoke_macow_cond_bias(const ipoke_macow_desc* d, const float* wh, int n_units, const float* h, long long h_stride,
+                          float* hb, int B, int H, int W, void*) {
+  EmulLauncher L;
+  return macow::cond_bias_run(L, d, wh, n_units, h, h_stride, hb, B, H, W);
+}
+
+int ipoke_macow_units_forward_cond(const ipoke_macow_desc* d, const float* packed, int n_units, const float* hb,
+                                   const float* x, long long x_stride, float* out, long long out_stride, float* logdet,
+                                   int accumulate, int B, int H, int W, int s0, int s1, void*) {
+  EmulLauncher L;
+  return macow::units_run(L, d, packed, n_units, hb, x, x_stride, out, out_stride, logdet, accumulate, B, H, W, s0, s1, false);
+}
+
+int ipoke_macow_units_reverse_cond(const ipoke_macow_desc* d, const float* packed, int n_units, const float* hb,
+                                   const float* z, long long z_stride, float* out, long long out_stride, int B, int H,
+                                   int W, int s0, int s1, void*) {
+  EmulLauncher L;
+  return macow::units_run(L, d, packed, n_units, hb, z, z_stride, out, out_stride, nullptr, 0, B, H, W, s0, s1, true);
 }
 
 int ipoke_macow_units_forward(const ipoke_macow_desc* d, const float* packed, int n_units, const float* x,
                               long long x_stride, float* out, long long out_stride, float* logdet, int accumulate,
                               int B, int H, int W, int s0, int s1, void*) {
   EmulLauncher L;
-  return macow::units_run(L, d, packed, n_units, x, x_stride, out, out_stride, logdet, accumulate, B, H, W, s0, s1, false);
+  return macow::units_run(L, d, packed, n_units, nullptr, x, x_stride, out, out_stride, logdet, accumulate, B, H, W, s0, s1, false);
 }
 
 int ipoke_macow_units_reverse(const ipoke_macow_desc* d, const float* packed, int n_units, const float* z,
                               long long z_stride, float* out, long long out_stride, int B, int H, int W, int s0, int s1,
                               void*) {
   EmulLauncher L;
-  return macow::units_run(L, d, packed, n_units, z, z_stride, out, out_stride, nullptr, 0, B, H, W, s0, s1, true);
+  return macow::units_run(L, d, packed, n_units, nullptr, z, z_stride, out, out_stride, nullptr, 0, B, H, W, s0, s1, true);
 }
 
 int ipoke_macow_forward(const ipoke_macow_desc* d, const float* packed, int n_units, const float* x, float* out,

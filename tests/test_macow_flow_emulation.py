@@ -57,6 +57,8 @@ def load(name):
     cfg = dict(num_steps=[int(v) for v in g["num_steps"]], flow_in_channels=C, flow_mid_channels=mid, factor=factor,
                transform="affine", prior_transform="affine", kernel_size=[k0, k1], coupling_type="conv",
                activation=str(g["activation"]))
+    if "h_channels" in g.files and int(g["h_channels"]) > 0:      # SupervisedMacowTransformer reads these keys too
+        cfg.update(h_channels=int(g["h_channels"]), flow_attn_heads=4, cond_conv_hidden_channels=16)
     return g, sd, cfg
 
 
@@ -111,6 +113,47 @@ def test_flow_matches_reference_fixtures(emulated, name, descending):
     assert max_rel(out.numpy(), g["out64"]) <= 2e-5 and max_rel(ld.numpy(), g["logdet64"]) <= 2e-5
     assert max_rel(out.numpy(), g["out"]) <= 2e-5
     assert max_rel(smp.numpy(), g["x_smp64"]) <= 2e-4 and max_rel(smp.numpy(), g["x_smp"]) <= 2e-4
+
+
+def test_conditional_flow(emulated):
+    """SupervisedMacowTransformer (INN.py:447-482): same-seed construction, first-call initialisation, forward / inverse
+    with the conditioning, one conditional unit and one step on their own -- against the live-reference fixture."""
+    g, sd, cfg = load("macow_stack_c")
+    x, z, h = torch.from_numpy(g["x"]), torch.from_numpy(g["z_in"]), torch.from_numpy(g["h"])
+    torch.manual_seed(42)
+    net = P.SupervisedMacowTransformer(cfg).eval()
+    fresh = net.state_dict()
+    assert list(fresh.keys()) == list(sd.keys())
+    for k, v in sd.items():
+        assert fresh[k].shape == v.shape and fresh[k].dtype == v.dtype, k
+        if k.endswith(("shuffle_idx", "weight_v", "conv1.weight", "conv2.weight", "shift_conv.weight")):
+            assert torch.equal(fresh[k], v), k
+    with torch.no_grad():
+        out, ld = net(x, h)
+    assert max_rel(out.numpy(), g["init_out"]) <= 2e-5 and max_rel(ld.numpy(), g["init_logdet"]) <= 2e-5
+    for k in g.files:
+        if k.startswith("init::"):
+            np.testing.assert_allclose(net.state_dict()[k[6:]].numpy(), g[k], rtol=1e-4, atol=2e-5, err_msg=k)
+    net.load_state_dict(sd)
+    emulated.emul_set_descending(1)
+    with torch.no_grad():
+        out, ld = net(x, h)
+        smp = net(z, h, reverse=True)
+        assert max_rel(out.numpy(), g["out64"]) <= 2e-5 and max_rel(ld.numpy(), g["logdet64"]) <= 2e-5
+        assert max_rel(smp.numpy(), g["x_smp64"]) <= 2e-4
+        step = net.flow.layers[0][0]
+        o, l = step.units1[0](x, h=h)
+        assert max_rel(o.numpy(), g["unit_out"]) <= 2e-5 and max_rel(l.numpy(), g["unit_logdet"]) <= 2e-5
+        assert max_rel(step.units1[0](z, h=h, reverse=True).numpy(), g["unit_rev"]) <= 2e-4
+        o, l = step(x, h=h)
+        assert max_rel(o.numpy(), g["step_out"]) <= 2e-5 and max_rel(l.numpy(), g["step_logdet"]) <= 2e-5
+        assert max_rel(step(z, h=h, reverse=True).numpy(), g["step_rev"]) <= 2e-4
+        # a different conditioning gives a different result; a missing or mis-shaped one is refused
+        assert not torch.equal(net(x, h + 0.5)[0], out)
+        with pytest.raises(ValueError):
+            net.flow(x)
+        with pytest.raises(ValueError):
+            net(x, h[:, :3])
 
 
 def test_components_called_like_the_reference_calls_them(emulated):

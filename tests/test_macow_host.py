@@ -44,10 +44,12 @@ def test_state_dict_keys_shapes_and_rng_order(name):
 def test_header_symbols_are_exported():
     hdr = open(os.path.join(ROOT, "include", "ipoke_macow.h")).read()
     names = sorted(set(re.findall(r"\b(ipoke_macow_[a-z_]+)\s*\(", hdr)))
-    assert names == ["ipoke_macow_chanmap", "ipoke_macow_forward", "ipoke_macow_launch_info", "ipoke_macow_nice",
-                     "ipoke_macow_nice_floats", "ipoke_macow_nice_workspace_floats", "ipoke_macow_pack_nice",
-                     "ipoke_macow_pack_unit", "ipoke_macow_reverse", "ipoke_macow_unit_floats",
-                     "ipoke_macow_units_forward", "ipoke_macow_units_reverse"]
+    assert names == ["ipoke_macow_chanmap", "ipoke_macow_cond_bias", "ipoke_macow_cond_floats", "ipoke_macow_forward",
+                     "ipoke_macow_launch_info", "ipoke_macow_nice", "ipoke_macow_nice_floats",
+                     "ipoke_macow_nice_workspace_floats", "ipoke_macow_pack_nice", "ipoke_macow_pack_unit",
+                     "ipoke_macow_pack_unit_cond", "ipoke_macow_reverse", "ipoke_macow_unit_floats",
+                     "ipoke_macow_units_forward", "ipoke_macow_units_forward_cond", "ipoke_macow_units_reverse",
+                     "ipoke_macow_units_reverse_cond"]
     L = _capi.lib()
     for n in names:
         assert hasattr(L, n), n
@@ -73,7 +75,14 @@ def test_unit_floats_and_launch_geometry_without_gpu():
 
 def test_unbuilt_variants_and_cpu_tensors_fail_loudly():
     with pytest.raises(NotImplementedError):
-        macow.MaCowUnit(4, [2, 3], h_channels=8)
+        macow.MaCowUnit(4, [2, 3], h_channels=8, cond_conv=True, cond_conv_hidden_channels=16)
+    cond = macow.MaCowUnit(4, [2, 3], h_channels=8)                # conditional unit: 1x1 convolutions 16 + 8 wide
+    assert cond.conv1.net.conv1x1.conv.weight_v.shape == (8, 24, 1, 1) and cond._desc.h_channels == 8
+    L = macow._lib()
+    assert L.ipoke_macow_cond_floats(ctypes.byref(cond._desc), 2) == 8 * 2 * 8 * 4          # h_channels x (units * 8 C)
+    assert L.ipoke_macow_cond_floats(ctypes.byref(macow.MacowDesc(4, 16, 2, 3, 1, 1.0)), 2) == 0
+    # conditional descriptor without its conditioning product (and the other way round) is refused before any launch
+    assert L.ipoke_macow_units_forward(ctypes.byref(cond._desc), 1, 1, 1, 64, 1, 64, None, 0, 1, 4, 4, 0, 6, None) == -1
     with pytest.raises(NotImplementedError):
         macow.MaCowUnit(4, [2, 3], transform="nlsq")
     with pytest.raises(NotImplementedError):
@@ -108,3 +117,12 @@ def test_flow_sizes_argument_errors_and_unbuilt_variants_without_gpu():
             P.UnsupervisedMaCowTransformer3(bad)
     with pytest.raises(NotImplementedError):
         P.NICE2d(8, h_channels=4)
+    ccfg = dict(cfg, h_channels=6, flow_attn_heads=4, cond_conv_hidden_channels=16)
+    cnet = P.SupervisedMacowTransformer(ccfg)
+    assert cnet.flow.h_channels == 6 and cnet.flow.layers[0][0].units1[0].h_channels == 6
+    assert cnet.flow.layers[0][0].coupling1_up.net.conv1.weight.shape[1] == 4           # couplings: no conditioning
+    for bad in (dict(ccfg, condition_nice=True), dict(ccfg, cond_conv=True)):
+        with pytest.raises(NotImplementedError):
+            P.SupervisedMacowTransformer(bad)
+    with pytest.raises(KeyError):
+        P.SupervisedMacowTransformer(dict(cfg, h_channels=6, flow_attn_heads=4))      # the reference requires the key too

@@ -80,6 +80,65 @@ def test_first_call_initialisation_matches_reference():
     assert all(int(v) == 1 for k, v in new.items() if k.endswith("initialized"))
 
 
+def test_conditional_flow_reference_fixture():
+    """SupervisedMacowTransformer (INN.py:447-482, condition_nice false): forward / inverse with the conditioning, a
+    conditional unit and a step on their own, the first-call initialisation."""
+    dev = torch.device("cuda:0")
+    g, sd, cfg = load("macow_stack_c")
+    x, z, h = (torch.from_numpy(g[k]).to(dev) for k in ("x", "z_in", "h"))
+    torch.manual_seed(42)
+    net = P.SupervisedMacowTransformer(cfg).to(dev).eval()
+    with torch.no_grad():
+        out, ld = net(x, h)
+    assert max_rel(out.cpu().numpy(), g["init_out"]) <= TOL_FWD and max_rel(ld.cpu().numpy(), g["init_logdet"]) <= TOL_FWD
+    for k in g.files:
+        if k.startswith("init::"):
+            np.testing.assert_allclose(net.state_dict()[k[6:]].cpu().numpy(), g[k], rtol=1e-4, atol=2e-5, err_msg=k)
+    net.load_state_dict(sd)
+    with torch.no_grad():
+        out, ld = net(x, h)
+        smp = net(z, h, reverse=True)
+        back = net(out, h, reverse=True)
+        assert max_rel(out.cpu().numpy(), g["out64"]) <= TOL_FWD and max_rel(ld.cpu().numpy(), g["logdet64"]) <= TOL_FWD
+        assert max_rel(smp.cpu().numpy(), g["x_smp64"]) <= TOL_REV and max_rel(back.cpu().numpy(), g["x"]) <= TOL_REV
+        step = net.flow.layers[0][0]
+        o, l = step.units1[0](x, h=h)
+        assert max_rel(o.cpu().numpy(), g["unit_out"]) <= TOL_FWD and max_rel(l.cpu().numpy(), g["unit_logdet"]) <= TOL_FWD
+        assert max_rel(step.units1[0](z, h=h, reverse=True).cpu().numpy(), g["unit_rev"]) <= TOL_REV
+        o, l = step(x, h=h)
+        assert max_rel(o.cpu().numpy(), g["step_out"]) <= TOL_FWD and max_rel(l.cpu().numpy(), g["step_logdet"]) <= TOL_FWD
+        assert max_rel(step(z, h=h, reverse=True).cpu().numpy(), g["step_rev"]) <= TOL_REV
+        assert not torch.equal(net(x, h + 0.5)[0], out)
+        smp2 = net.sample(tuple(x.shape), h, device=dev)
+        assert smp2.shape == x.shape
+    with pytest.raises(ValueError):
+        net.flow(x)
+
+
+def test_conditional_flow_against_float64_oracle():
+    """z_dim-32 latents at 8 x 8 with 128 conditioning channels (conditioner + poke embedding), batch 20 (the reference's
+    test batch): two conditional unit chains per step, 1024-column conditioning product."""
+    dev = torch.device("cuda:0")
+    C, hc, B, H, W = 32, 128, 20, 8, 8
+    cfg = dict(num_steps=[1], flow_in_channels=C, flow_mid_channels=64, factor=16, transform="affine",
+               prior_transform="affine", kernel_size=[2, 3], coupling_type="conv", activation="elu", h_channels=hc,
+               flow_attn_heads=4, cond_conv_hidden_channels=16)
+    torch.manual_seed(5)
+    net = randomise(P.SupervisedMacowTransformer(cfg), 55).to(dev).eval()
+    sd = so.sub({k: v.cpu().numpy() for k, v in net.state_dict().items()}, "flow.")
+    rng = np.random.default_rng(9)
+    x = rng.standard_normal((B, C, H, W)).astype(np.float32)
+    z = rng.standard_normal((B, C, H, W)).astype(np.float32)
+    h = rng.standard_normal((B, hc, H, W)).astype(np.float32)
+    want, want_ld = so.flow_forward(sd, x, [1], 16, "elu", h=h)
+    want_rev = so.flow_reverse(sd, z, [1], 16, "elu", h=h)
+    with torch.no_grad():
+        out, ld = net(torch.from_numpy(x).to(dev), torch.from_numpy(h).to(dev))
+        got = net(torch.from_numpy(z).to(dev), torch.from_numpy(h).to(dev), reverse=True)
+    assert max_rel(out.cpu().numpy(), want) <= TOL_FWD and max_rel(ld.cpu().numpy(), want_ld) <= TOL_FWD
+    assert max_rel(got.cpu().numpy(), want_rev) <= TOL_REV
+
+
 def randomise(net, seed):
     """Non-trivial gains / biases for every zero-initialised convolution and ActNorm (a fresh flow is the identity).
     The gains are kept small: with alpha = 1 the affine scale tanh(log_scale / 2) + 1 reaches 0 when a random net
