@@ -111,8 +111,8 @@ def test_conditional_flow_reference_fixture():
         assert not torch.equal(net(x, h + 0.5)[0], out)
         smp2 = net.sample(tuple(x.shape), h, device=dev)
         assert smp2.shape == x.shape
-    with pytest.raises(ValueError):
-        net.flow(x)
+        with pytest.raises(ValueError):
+            net.flow(x)                                                # a conditional flow needs its conditioning
 
 
 def test_conditional_flow_against_float64_oracle():
