@@ -1,20 +1,23 @@
-/* ipoke_macow.h -- C ABI of the MaCow unit (masked-convolution autoregressive flow), sm_100a.
+/* ipoke_macow.h -- C ABI of the MaCow conv flow (masked-convolution autoregressive flow), sm_100a.
  *
- * Row N3 of SURVEY.md section 8(f), first slice: the reference's `MaCowUnit`
- * (models/modules/INN/macow2.py:925-996) = MaskedConvFlow A, B (macow2.py:25-289) -> ActNorm2dFlow
- * (macow2.py:476-541) -> MaskedConvFlow C, D -> ActNorm2dFlow, unconditional (h_channels = 0), affine
- * transform (macow_utils.py:42-66), dropout 0 -- the configuration `config/second_stage.yaml:53-80` selects.
- * Forward returns (out, logdet); the inverse is the reference's sequential line-by-line loop
- * (macow2.py:222-289) run inside one kernel launch, one CTA per sample.
+ * Row N3 of SURVEY.md section 8(f): everything `UnsupervisedMaCowTransformer3` / `SupervisedMacowTransformer`
+ * (models/modules/INN/INN.py:365-390, 447-482) compute --
+ *   * `MaCowUnit` (macow2.py:925-996) = MaskedConvFlow A, B (macow2.py:25-289) -> ActNorm2dFlow (macow2.py:476-541) ->
+ *     MaskedConvFlow C, D -> ActNorm2dFlow, unconditional or conditional (h_channels > 0), forward (out, logdet) and the
+ *     reference's sequential line-by-line inverse (macow2.py:222-289) inside one kernel launch, one CTA per sample;
+ *   * `NICE2d` couplings with the convolutional net (macow2.py:291-437, macow_utils.py:253-338);
+ *   * the ActNorm2dFlow / Shuffle glue of `MaCowStep`, `MultiScalePrior`, `MultiScaleInternal` (macow2.py:543-594,
+ *     821-918, 999-1117), in place on one [B, C, H, W] buffer
+ * for the affine transform (macow_utils.py:42-66), dropout 0 -- the configuration `config/second_stage.yaml:53-80` selects.
  *
  * Everything is float32 on the device (the reference computes this path in fp32).  All pointers are device
  * pointers unless stated otherwise; `stream` is a cudaStream_t passed as void*.  Error codes are those of
  * ipoke_inn.h (IPOKE_INN_OK, IPOKE_INN_E_*; positive values are cudaError_t) and
  * ipoke_inn_last_error_string() decodes them.  The calls are stateless and thread safe.
  *
- * The ctypes binding a maintainer of the reference would add is in INTEGRATION.md; the Python mirror of the
- * reference modules (same constructor, state_dict keys and RNG draw order) is
- * ipoke-main-opticalflow_b200/macow.py.
+ * The ctypes binding a maintainer of the reference would add is in INTEGRATION.md section 7; the Python mirrors of the
+ * reference modules (same constructors, state_dict keys and RNG draw order) are
+ * ipoke-main-opticalflow_b200/macow.py and macow_flow.py.
  */
 #ifndef IPOKE_MACOW_H_
 #define IPOKE_MACOW_H_

@@ -1,10 +1,10 @@
 """MaCow unit on B200: the reference's ``MaCowUnit`` / ``MaskedConvFlow`` / ``ActNorm2dFlow`` modules
 (models/modules/INN/macow2.py:25-289, 476-541, 925-996; macow_utils.py:42-66, 211-252, 407-497) with the same
 constructors, state_dict keys and RNG draw order, computing through the CUDA kernels behind
-``include/ipoke_macow.h``.  Row N3 of SURVEY.md section 8(f), first slice: unconditional (``h_channels = 0``),
-affine transform, dropout 0 -- what ``config/second_stage.yaml:53-80`` selects.  Inference only (forward with
-logdet, and the sequential inverse used for sampling); anything else raises NotImplementedError.  There is no
-CPU or eager fallback: CPU tensors raise.
+``include/ipoke_macow.h``.  Row N3 of SURVEY.md section 8(f); the couplings, steps and the multi-scale flow built from
+these units are in ``macow_flow.py``.  Affine transform, dropout 0, unconditional or conditional (``h_channels > 0``)
+-- what ``config/second_stage.yaml:53-80`` selects.  Inference only (forward with logdet, and the sequential inverse
+used for sampling); anything else raises NotImplementedError.  There is no CPU or eager fallback: CPU tensors raise.
 """
 import ctypes
 import math
