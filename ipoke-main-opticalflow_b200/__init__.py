@@ -30,10 +30,12 @@ __all__ = ["SupervisedTransformer", "UnsupervisedTransformer3", "ConditionalFlow
 def install_as_reference():
     """Shadow the reference's import paths so its LightningModules pick up these classes unchanged:
     ``from models.modules.INN.INN import SupervisedTransformer`` (models/second_stage_video_fc.py:16) etc.
-    Only the two wrappers and FlowLoss are replaced; other names of those modules keep resolving to the
-    reference (if it is importable)."""
-    from . import INN as _inn, loss as _loss
+    The flat-INN wrappers, the MaCow wrappers (``UnsupervisedMaCowTransformer3`` for INN_test.py / opticalFlowINN.py /
+    models/flow_motion.py, ``SupervisedMacowTransformer`` for models/second_stage_video.py:122) and FlowLoss are replaced;
+    other names of those modules keep resolving to the reference (if it is importable)."""
+    from . import INN as _inn, loss as _loss, macow_flow as _mf
     for name, ours, attrs in (("models.modules.INN.INN", _inn, ("SupervisedTransformer", "UnsupervisedTransformer3")),
+                              ("models.modules.INN.INN", _mf, ("UnsupervisedMaCowTransformer3", "SupervisedMacowTransformer")),
                               ("models.modules.INN.loss", _loss, ("FlowLoss",))):
         mod = sys.modules.get(name)
         if mod is None:

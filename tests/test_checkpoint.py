@@ -57,3 +57,23 @@ def test_select_checkpoint_like_the_reference(tmp_path):
     os.remove(a); os.remove(b)
     with pytest.raises(ValueError, match="No valid files"):
         C.select_checkpoint(str(d))
+
+
+@pytest.mark.parametrize("name", ["macow_stack_a", "macow_stack_c"])
+def test_macow_lightning_checkpoint_round_trip(tmp_path, name):
+    """The conv second stage / FlowMotion save their MaCow flow under 'flow.' (models/second_stage_video.py:142,
+    models/flow_motion.py): the live-reference state_dict of the fixtures loads strictly into the drop-in wrappers."""
+    import ipoke_inn_b200 as P
+    from test_macow_flow_emulation import load
+    g, sd_ref, cfg = load(name)
+    ckpt = {"state_dict": {**{"flow." + k: v for k, v in sd_ref.items()}, "first_stage_model.enc.weight": torch.zeros(2, 2)}}
+    path = tmp_path / "macow.ckpt"
+    torch.save(ckpt, path)
+    torch.manual_seed(3)
+    net = (P.SupervisedMacowTransformer if "h_channels" in cfg else P.UnsupervisedMaCowTransformer3)(cfg)
+    res = C.load_flow_from_lightning(net, str(path), prefix="flow.")
+    assert not res.missing_keys and not res.unexpected_keys
+    for k, v in net.state_dict().items():
+        assert torch.equal(v, sd_ref[k]), k
+    out = C.export_flow_to_lightning(net, ckpt, prefix="flow.")
+    assert set(out["state_dict"]) == set(ckpt["state_dict"])

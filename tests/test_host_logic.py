@@ -159,6 +159,9 @@ def test_install_as_reference_shadows_import_paths():
     from models.modules.INN.loss import FlowLoss
     assert SupervisedTransformer is P.SupervisedTransformer and UnsupervisedTransformer3 is P.UnsupervisedTransformer3
     assert FlowLoss is P.FlowLoss
+    from models.modules.INN.INN import SupervisedMacowTransformer, UnsupervisedMaCowTransformer3
+    assert UnsupervisedMaCowTransformer3 is P.UnsupervisedMaCowTransformer3
+    assert SupervisedMacowTransformer is P.SupervisedMacowTransformer
     for k in [k for k in sys.modules if k.startswith("models")]:
         del sys.modules[k]
 
