@@ -58,12 +58,14 @@ def flow_entries(state_dict, prefix):
 
 def load_flow_from_lightning(module, ckpt, prefix="flow.", strict=True):
     """Load the INN part of a LightningModule checkpoint (path, checkpoint dict or state_dict) into ``module``
-    (SupervisedTransformer / UnsupervisedTransformer3).  The engine repacks at the next call."""
+    (SupervisedTransformer / UnsupervisedTransformer3, or the MaCow wrappers UnsupervisedMaCowTransformer3 /
+    SupervisedMacowTransformer).  The packed parameters are rebuilt at the next call."""
     sd = flow_entries(_state_dict_of(ckpt), prefix)
     if not sd:
         raise KeyError(f"no entries under prefix '{prefix}' in the checkpoint")
     out = module.load_state_dict(sd, strict=strict)
-    module.flow.engine.invalidate()
+    flow = module.flow
+    (flow.engine if hasattr(flow, "engine") else flow).invalidate()       # flat INN: the engine; MaCow: the flow's program
     return out
 
 
