@@ -161,6 +161,36 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------- CPU arm (oracle port)
+def macow_flow_line(timeout_s=240):
+    """The MaCow conv flow at the config/INN_test.yaml stack, batch 40: the line of
+    tools/macow_flow_bench.py (its own process, after this bench's timed regions; CUDA events, 3 warm-ups, the flow's
+    1.7 GB of packed weights exceed L2) reduced to the figures DESIGN.md section 4b quotes.  Informational: any failure
+    becomes an "error" entry, the headline line is never lost."""
+    import subprocess
+    try:
+        cmd = [sys.executable, os.path.join(ROOT, "tools", "macow_flow_bench.py"), "--workload", "inn_test", "--batch", "40",
+               "--steps", "3"]
+        res = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout_s)
+        lines = [ln for ln in res.stdout.splitlines() if ln.startswith("{")]
+        if res.returncode != 0 or not lines:
+            return {"error": ("rc %d: " % res.returncode) + (res.stderr or res.stdout)[-200:]}
+        m = json.loads(lines[-1])
+        out = {"workload": "UnsupervisedMaCowTransformer3, config/INN_test.yaml stack, batch %d, %dx%d latents" % (m["batch"], m["H"], m["W"]),
+               "dtype": m["dtype"], "coupling_flops_per_call": m["coupling_flops_per_call"]}
+        for tag in ("forward", "reverse"):
+            out[tag] = {k: m[tag][k] for k in ("ms", "samples_per_s", "gpu_launches")}
+            out[tag]["fp32_fma_frac"] = m[tag]["roofline"]["frac"]
+            out[tag]["tflops"] = m[tag]["roofline"]["achieved"]
+        out["fp32_fma_peak_tflops"] = m["forward"]["roofline"]["peak"]
+        if "eager_gpu" in m:
+            out["eager_reference_ops_same_gpu"] = {k: m["eager_gpu"][k] for k in ("forward_ms", "reverse_ms", "max_rel_forward", "round_trip_max_rel")}
+        if "cpu" in m:
+            out["cpu"] = m["cpu"]
+        return out
+    except Exception as e:      # noqa: BLE001
+        return {"error": str(e)[:200]}
+
+
 def cpu_port_run(cfg_name, B, steps, warmup, budget_s=20.0):
     """Times the CPU restatement of the reference path on the host cores.  One step = forward + reverse on a sample
     of the workload; the sample batch is bounded so a run stays short.  The timed code is oracle/inn_oracle_torch.py:
@@ -650,6 +680,9 @@ def gpu_run(args):
         train = [train_workload(ctx, "cfgA", 64, "bf16"), train_workload(ctx, "cfgA", 4096, "bf16")]
         if rank == 0:
             out["roofline"]["train_step"] = train
+    # ---- MaCow conv flow (row N3): its own tool in its own process, rank 0 at N = 1
+    if rank == 0 and world == 1 and not args.no_macow:
+        out["roofline"]["macow_flow"] = macow_flow_line()
     # ---- CPU baseline: the oracle port on the host cores, rank 0 at N = 1 only (contract); at N > 1 torchrun pins
     # OMP_NUM_THREADS=1 and the other ranks would spin in a barrier, so the figure is not taken there
     if rank == 0:
@@ -677,6 +710,7 @@ def main():
                     help="fp32 = parity mode (bf16 hi+lo split operands, <= 1e-4 of the fp32 reference); bf16 = one pass")
     ap.add_argument("--no-regimes", action="store_true")
     ap.add_argument("--no-train", action="store_true")
+    ap.add_argument("--no-macow", action="store_true", help="skip the MaCow conv-flow section (roofline.macow_flow)")
     ap.add_argument("--no-sweep", action="store_true", help="same as --no-regimes --no-train")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

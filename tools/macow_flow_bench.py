@@ -28,8 +28,16 @@ sys.path.insert(0, ROOT)
 
 import ipoke_inn_b200 as P  # noqa: E402
 from bench import ClockSampler  # noqa: E402
-from oracle.macow_stack_oracle import levels, sub  # noqa: E402  (baseline legs only)
-from oracle.macow_stack_oracle_torch import TorchFlow  # noqa: E402
+
+
+def levels(C, num_steps, factor):
+    """Channels, prior factor and steps per level (MultiScaleInternal.__init__, macow2.py:841-868)."""
+    step, out = C // factor, []
+    for n in num_steps:
+        out.append((C, factor, n))
+        C, factor = C - step, factor - 1
+    return out
+
 
 WORKLOADS = {
     "inn_test": dict(num_steps=[20, 8, 5, 5, 3, 3, 1], flow_in_channels=8, flow_mid_channels=1536, factor=8, H=8, W=8),
@@ -86,6 +94,9 @@ def main():
                 v.copy_(0.02 + 0.06 * torch.rand_like(v))          # small gains: a well-conditioned inverse (tests/test_zy_gpu_macow_flow.py::randomise)
             elif k.endswith("bias") or k.endswith("log_scale"):
                 v.copy_(0.05 * torch.randn_like(v))
+    if not args.no_baselines:          # the baseline legs are the only users of oracle/ here
+        from oracle.macow_stack_oracle import sub
+        from oracle.macow_stack_oracle_torch import TorchFlow
     sd = None if args.no_baselines else sub({k: v.clone().numpy() for k, v in net.state_dict().items()}, "flow.")
     net = net.to(dev).eval()
     B, C, H, W = args.batch, w["flow_in_channels"], w["H"], w["W"]
