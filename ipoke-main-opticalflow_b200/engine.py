@@ -6,6 +6,7 @@ import ctypes
 import torch
 
 from . import _capi
+from ._nvtx import annotate
 
 
 def _ptr_array(tensors):
@@ -290,6 +291,7 @@ class FlowEngine:
                                         self._stream()), "forward")
         self.launches = L.ipoke_inn_last_launch_count(self._plan)
 
+    @annotate("inn.forward")
     def forward(self, x, cond, want_blocks=False):
         """-> z [B,C], logdet [B] (+ block_outs [n,B,C], block_logdets [n,B])"""
         B, x2, c2 = self._prep(x, cond)
@@ -305,6 +307,7 @@ class FlowEngine:
         self._forward_raw(x2, c2, z, ld, outs, lds, 0, self.n_flows)
         return z, ld, outs, lds
 
+    @annotate("inn.reverse")
     def reverse(self, z, cond):
         B, z2, c2 = self._prep(z, cond)
         L = self._ensure(z2.device)
@@ -346,6 +349,7 @@ class FlowEngine:
             x3, c2 = xp, cp
         return n_draws, B, Bp, x3.contiguous(), c2.contiguous()
 
+    @annotate("inn.reverse_draws")
     def reverse_draws(self, z, cond, n_draws):
         """n_draws latents per conditioning row in one call: z [n_draws, B, C], cond [B, E] -> x [n_draws, B, C].
         The cond-only subnetworks of the 'cond' couplings run once per conditioning row (include/ipoke_inn.h)."""
@@ -359,6 +363,7 @@ class FlowEngine:
         self.launches = L.ipoke_inn_last_launch_count(self._plan)
         return x[:, :B]
 
+    @annotate("inn.forward_draws")
     def forward_draws(self, x, cond, n_draws):
         """-> z [n_draws, B, C], logdet [n_draws, B] for n_draws inputs per conditioning row."""
         n, B, Bp, x3, c2 = self._prep_draws(x, cond, n_draws)
@@ -375,6 +380,7 @@ class FlowEngine:
         return z[:, :B], ld[:, :B]
 
     # ------------------------------------------------------------------ training (forward with saved state, backward)
+    @annotate("inn.forward_train")
     def forward_train(self, x, cond):
         """Forward that keeps what the fused backward needs.  -> z, logdet, block_outs [n,B,C], block_logdets [n,B], saved"""
         B, x2, c2 = self._prep(x, cond)
@@ -521,6 +527,7 @@ class FlowEngine:
             views = [fv[j] for j in self._grad_perm]
         return flat, views, arrays
 
+    @annotate("inn.backward")
     def backward(self, x2, c2, outs, saved, dz, dld, grad_ptrs, want_dx=True, want_dcond=True, block_begin=0,
                  block_end=None, dcond=None):
         """Fused backward over blocks [block_begin, block_end).  -> dx [B,C] or None, dcond [B,E] or None."""
@@ -548,6 +555,7 @@ class FlowEngine:
                                "and does the ActNorm data init), then use the *_host entry points")
         self.pack()
 
+    @annotate("inn.forward_host")
     def forward_host(self, x_host, cond_host, z_host, logdet_host):
         L = _capi.lib()
         self._ready_for_host_call()
@@ -559,6 +567,7 @@ class FlowEngine:
                                              self._stream()), "forward_host")
         self.launches = L.ipoke_inn_last_launch_count(self._plan)
 
+    @annotate("inn.reverse_host")
     def reverse_host(self, z_host, cond_host, x_host):
         L = _capi.lib()
         self._ready_for_host_call()

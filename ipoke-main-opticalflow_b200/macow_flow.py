@@ -25,6 +25,7 @@ import torch.nn as nn
 
 from . import _capi
 from . import macow as _m
+from ._nvtx import annotate
 from .macow import ACTIVATIONS, ActNorm2dFlow, Conv2dWeightNorm, MaCowUnit, NiceDesc
 from .modules import Shuffle
 
@@ -327,6 +328,7 @@ class Program:
         return self.ws
 
     # ---- kernel calls
+    @annotate("macow.glue")
     def _glue(self, op, buf, stride, B, H, W, logdet, reverse):
         _, shuffle, n_perm, actnorm, c0, n = op
         perm = None
@@ -342,6 +344,7 @@ class Program:
             int(reverse), int(not reverse), logdet.data_ptr() if (logdet is not None and not reverse) else None,
             _m._stream(buf.device)), "ipoke_macow_chanmap")
 
+    @annotate("macow.units")
     def _units(self, i, buf, stride, B, H, W, logdet, reverse, h=None, s0=None, s1=None):
         units = self.ops[i][1]
         packed, wh = self._segment(i, buf.device)
@@ -377,6 +380,7 @@ class Program:
                                                     buf.data_ptr(), stride, logdet.data_ptr(), 1, B, H, W, s0, s1,
                                                     _m._stream(buf.device)), "ipoke_macow_units_forward")
 
+    @annotate("macow.nice")
     def _nice(self, i, buf, stride, B, H, W, logdet, reverse):
         nice = self.ops[i][1]
         packed = self._segment(i, buf.device)
@@ -442,6 +446,7 @@ class Program:
             raise ValueError(f"conditioning: expected float32 {want} on {x.device}, got {h.dtype} {tuple(h.shape)} on {h.device}")
         return h.contiguous()
 
+    @annotate("macow.flow")
     def run(self, input, reverse=False, h=None):
         if torch.is_grad_enabled() and (input.requires_grad or any(p.requires_grad for r in self.roots
                                                                    for p in r.parameters())):

@@ -13,6 +13,8 @@ import ctypes
 
 import torch
 
+from ._nvtx import annotate
+
 from . import _capi
 
 
@@ -121,6 +123,7 @@ class FusedAdam(torch.optim.Optimizer):
         return plan[1]
 
     @torch.no_grad()
+    @annotate("optim.step")
     def step(self, closure=None):
         loss = None
         if closure is not None:

@@ -26,6 +26,8 @@ The fp32 master of the spans a rank does not own goes stale between checkpoints:
 automatically by the module's ``state_dict()``) all-gathers it.
 """
 import torch
+
+from ._nvtx import annotate
 import torch.distributed as dist
 
 from . import _capi
@@ -146,6 +148,7 @@ class ShardedAdam(torch.optim.Optimizer):
 
     # ------------------------------------------------------------------ the step
     @torch.no_grad()
+    @annotate("optim.step")
     def step(self, closure=None):
         loss = None
         if closure is not None:

@@ -222,3 +222,18 @@ def test_direct_param_grads_host_logic_with_a_stub_engine():
         assert torch.equal(params[1].grad, it * torch.arange(6, 11, dtype=torch.float32))
     assert torch.allclose(x.grad, torch.full((4, 6), 4.0))           # 2 backward passes x dz * 2
     assert eng.last_flat_grad is not None
+
+
+def test_nvtx_ranges_are_opt_in():
+    """IPOKE_NVTX=1 wraps the host entry points in torch.cuda.nvtx ranges; by default they are the plain functions."""
+    import subprocess
+    import sys
+    from ipoke_inn_b200 import engine
+    assert not hasattr(engine.FlowEngine.forward, "__wrapped__")
+    code = ("import ipoke_inn_b200 as P; from ipoke_inn_b200 import engine, macow_flow, optim; "
+            "assert hasattr(engine.FlowEngine.forward, '__wrapped__') and hasattr(engine.FlowEngine.backward, '__wrapped__'); "
+            "assert hasattr(macow_flow.Program.run, '__wrapped__') and hasattr(optim.FusedAdam.step, '__wrapped__'); print('ok')")
+    env = dict(os.environ, IPOKE_NVTX="1")
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env,
+                         cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert res.returncode == 0 and res.stdout.strip().endswith("ok"), res.stderr[-500:]
