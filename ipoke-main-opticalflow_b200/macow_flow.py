@@ -262,8 +262,10 @@ class Program:
         self.channels = channels
         self.roots = roots
         self.packed = [None] * len(ops)           # per op: (tensor, key)
+        self.params = [None] * len(ops)           # per op: its parameter tensors (walked once)
         self.init_done = False
         self.ws = None
+        self.ws_need = {}                         # (B, H, W) -> workspace floats of the widest coupling
         self.hb = None
         self.h_channels = max([op[1][0].h_channels for op in ops if op[0] == "units"] + [0])
         for r in roots:
@@ -271,16 +273,17 @@ class Program:
 
     def invalidate(self):
         self.packed = [None] * len(self.ops)
+        self.params = [None] * len(self.ops)
         self.init_done = False
 
     # ---- packed parameters
     def _segment(self, i, dev):
         op = self.ops[i]
-        if op[0] == "units":
-            units = op[1]
-            ps = [p for u in units for p in u._param_list()]
-        else:
-            ps = op[1].params()
+        units = op[1] if op[0] == "units" else None
+        ps = self.params[i]
+        if ps is None:                            # load_state_dict keeps the Parameter objects; invalidate() drops this
+            ps = [p for u in units for p in u._param_list()] if units is not None else op[1].params()
+            self.params[i] = ps
         key = tuple((p.data_ptr(), p._version) for p in ps)
         cur = self.packed[i]
         if cur is not None and cur[1] == key and cur[0].device == dev:
@@ -320,9 +323,12 @@ class Program:
         return buf
 
     def _workspace(self, B, H, W, dev):
-        L = _m._lib()
-        need = max([L.ipoke_macow_nice_workspace_floats(ctypes.byref(op[1]._desc), B, H, W)
-                    for op in self.ops if op[0] == "nice"] + [0])
+        need = self.ws_need.get((B, H, W))
+        if need is None:
+            L = _m._lib()
+            need = max([L.ipoke_macow_nice_workspace_floats(ctypes.byref(op[1]._desc), B, H, W)
+                        for op in self.ops if op[0] == "nice"] + [0])
+            self.ws_need[(B, H, W)] = need
         if self.ws is None or self.ws.numel() < need or self.ws.device != dev:
             self.ws = torch.empty(max(need, 1), dtype=torch.float32, device=dev)
         return self.ws
