@@ -1,4 +1,5 @@
-// C ABI of the MaCow unit (include/ipoke_macow.h): argument checks, launch geometry, kernel dispatch.
+// C ABI of the MaCow conv flow (include/ipoke_macow.h): the CUDA launcher behind the argument checks, pass sizing and
+// launch sequences of macow_flow_host.h (shared with the CPU emulation of the tests), and the extern "C" entry points.
 #include <cuda_runtime.h>
 
 #include <algorithm>

@@ -255,7 +255,9 @@ class MultiScaleInternal(nn.Module):
 
 class Program:
     """A flattened list of forward kernel calls over one in-place [B, C, H, W] buffer, its packed parameters (one segment
-    per call, repacked when a tensor of the segment changed) and the reference's first-call initialisations."""
+    per call, repacked when a tensor of the segment changed) and the reference's first-call initialisations.  A program
+    owns its workspaces: calls on one module are for one host thread and one stream at a time (like the reference's
+    modules, whose first call mutates parameters)."""
 
     def __init__(self, ops, channels, roots):
         self.ops = ops
