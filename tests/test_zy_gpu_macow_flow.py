@@ -189,6 +189,44 @@ def test_against_float64_oracle(C, mid, factor, steps, H, W, B, act, mb, monkeyp
     assert max_rel(back.cpu().numpy(), x) <= TOL_REV
 
 
+def test_inn_test_stack_against_float64_restatement():
+    """The benchmark shape itself (tools/macow_flow_bench.py --workload inn_test: config/INN_test.yaml, 45 steps over 7
+    levels, couplings 1536 wide, 467 M parameters): 4 samples against the float64 run of the torch restatement of the
+    reference's op sequence (oracle/macow_stack_oracle_torch.py, pinned to the live-reference fixtures) on the same GPU,
+    the round trip, and rows of a larger batch against the same rows alone.
+    Bounds: 1e-4 forward / log-determinant over the 277 stacked layers (the reference's own float32 arithmetic is 2e-6
+    from float64 here, measured on the CPU), 2e-4 for the round trip (float64 itself: 1e-5, every ActNorm2dFlow inverse
+    divides by exp(log_scale) + 1e-8)."""
+    from oracle.macow_stack_oracle_torch import TorchFlow
+    dev = torch.device("cuda:0")
+    cfg = dict(num_steps=[20, 8, 5, 5, 3, 3, 1], flow_in_channels=8, flow_mid_channels=1536, factor=8, transform="affine",
+               prior_transform="affine", kernel_size=[2, 3], coupling_type="conv", activation="elu")
+    torch.manual_seed(1)
+    net = P.UnsupervisedMaCowTransformer3(cfg).eval()
+    g = torch.Generator().manual_seed(17)
+    with torch.no_grad():                                    # the bench tool's "trained-looking" parameters
+        for k, v in net.state_dict().items():
+            if k.endswith("initialized"):
+                v.fill_(1)
+            elif k.endswith("weight_g"):
+                v.copy_(0.02 + 0.06 * torch.rand(v.shape, generator=g))
+            elif k.endswith("bias") or k.endswith("log_scale"):
+                v.copy_(0.05 * torch.randn(v.shape, generator=g))
+    sd = so.sub({k: v.numpy() for k, v in net.state_dict().items()}, "flow.")
+    ref = TorchFlow(sd, 8, cfg["num_steps"], 8, "elu", 1.0, device=dev, dtype=torch.float64)
+    net = net.to(dev)
+    x = torch.randn(24, 8, 8, 8, generator=torch.Generator().manual_seed(3)).to(dev)
+    with torch.no_grad():
+        want, want_ld = ref.forward(x[:4].double())
+        out, ld = net(x)
+        back = net(out, reverse=True)
+        out4, ld4 = net(x[:4])
+    assert max_rel(out[:4].cpu().numpy(), want.cpu().numpy()) <= 1e-4
+    assert max_rel(ld[:4].cpu().numpy(), want_ld.cpu().numpy()) <= 1e-4
+    assert max_rel(back.cpu().numpy(), x.cpu().numpy()) <= TOL_REV
+    assert max_rel(out4.cpu().numpy(), out[:4].cpu().numpy()) <= 1e-6 and max_rel(ld4.cpu().numpy(), ld[:4].cpu().numpy()) <= 1e-6
+
+
 def test_large_batch_round_trip_and_sample():
     dev = torch.device("cuda:0")
     cfg = dict(num_steps=[1, 1], flow_in_channels=8, flow_mid_channels=64, factor=4, transform="affine",
