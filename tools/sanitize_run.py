@@ -1,7 +1,9 @@
 #!/usr/bin/env python
 """Small workload for compute-sanitizer (tools/sanitize.sh): every kernel family once at tiny sizes -- forward /
 reverse (folded and unfolded programs, tail clusters), training forward + fused backward (dgrad, wgrad, EPI_DU, ActNorm
-gradients), FlowLoss, fused Adam, multi-draw sampling, host-buffer entry points, the sharded-optimizer kernels."""
+gradients), FlowLoss, fused Adam, multi-draw sampling, host-buffer entry points, the sharded-optimizer kernels, and the
+MaCow conv flow (unit chains both directions, coupling GEMMs in both variants with split-K taps, glue kernels, the
+conditional product)."""
 import os
 import sys
 
@@ -15,7 +17,7 @@ from test_host_logic import build  # noqa: E402
 
 dev = torch.device("cuda:0")
 os.environ.setdefault("IPOKE_INN_GRAPH", "0")           # plain launches: the sanitizer attributes errors per kernel
-which = sys.argv[1:] or ["infer", "train", "draws", "host", "sharded"]
+which = sys.argv[1:] or ["infer", "train", "draws", "host", "sharded", "macow"]
 g = torch.Generator().manual_seed(1)
 
 for prec in ("fp32", "bf16"):
@@ -80,3 +82,24 @@ for prec in ("fp32", "bf16"):
             opt.step()
 torch.cuda.synchronize()
 print("sanitize_run: done", which)
+
+if "macow" in which:
+    base = dict(num_steps=[1, 1], flow_in_channels=8, flow_mid_channels=160, factor=4, transform="affine",
+                prior_transform="affine", kernel_size=[2, 3], coupling_type="conv", activation="elu")
+    for async_gemm in ("1", "0"):
+        os.environ["IPOKE_MACOW_GEMM_ASYNC"] = async_gemm
+        for cfg, cls in ((base, P.UnsupervisedMaCowTransformer3),
+                         (dict(base, h_channels=12, flow_attn_heads=4, cond_conv_hidden_channels=16),
+                          P.SupervisedMacowTransformer)):
+            torch.manual_seed(2)
+            net = cls(cfg).to(dev).eval()
+            x = torch.randn(5, 8, 6, 7, generator=g).to(dev)                    # ragged tiles, non-square image
+            h = (torch.randn(5, 12, 6, 7, generator=g).to(dev),) if "h_channels" in cfg else ()
+            with torch.no_grad():
+                z, ld = net(x, *h)                                                  # first call: data-dependent inits
+                for k, v in net.state_dict().items():
+                    if k.endswith("weight_g"):
+                        v.fill_(0.05)
+                z, ld = net(x, *h)
+                back = net(z, *h, reverse=True)
+            assert float((back - x).abs().max()) < 1e-3
