@@ -40,44 +40,114 @@ constexpr size_t kStackBytes = 256 * 1024;
 static bool descending = false;
 static int grid_z = 0;                    // blockIdx.z of the CTAs a launch() call runs (set by the caller)
 
+// Context switch between fibers.  glibc's swapcontext saves / restores the signal mask with two system calls per
+// switch, which dominated the tests' run time; on x86-64 a fiber switch only needs the callee-saved registers and the
+// stack pointer (System V ABI), so a dozen instructions replace it there.  Other hosts keep ucontext.
+#if defined(__x86_64__) && !defined(EMUL_FORCE_UCONTEXT)
+#define EMUL_FAST_SWITCH 1
+extern "C" void emul_switch_stack(void** save_sp, void* load_sp);
+asm(R"(
+    .text
+    .p2align 4
+    .globl emul_switch_stack
+    .type emul_switch_stack, @function
+emul_switch_stack:
+    pushq %rbp
+    pushq %rbx
+    pushq %r12
+    pushq %r13
+    pushq %r14
+    pushq %r15
+    movq %rsp, (%rdi)
+    movq %rsi, %rsp
+    popq %r15
+    popq %r14
+    popq %r13
+    popq %r12
+    popq %rbx
+    popq %rbp
+    ret
+    .size emul_switch_stack, .-emul_switch_stack
+)");
+#else
+#define EMUL_FAST_SWITCH 0
+#endif
+
 struct Runner {
+#if EMUL_FAST_SWITCH
+  std::vector<void*> sp;          // saved stack pointer of every fiber
+  void* main_sp = nullptr;
+#else
   std::vector<ucontext_t> ctx;
-  std::vector<char> stacks;
-  std::vector<char> done;
   ucontext_t main;
+#endif
+  char* stacks = nullptr;          // nthreads * kStackBytes, from a pool that lives as long as the library
+  std::vector<char> done;
   int cur = 0;
   const std::function<void()>* body = nullptr;
 };
 static Runner* g_runner = nullptr;
 
+// Fiber stacks: one allocation reused by every CTA (a fresh 64 - 128 MB vector per CTA spent the time in page faults).
+static char* stack_pool(size_t bytes) {
+  static char* pool = nullptr;
+  static size_t size = 0;
+  if (bytes > size) {
+    std::free(pool);
+    pool = static_cast<char*>(std::malloc(bytes));
+    size = bytes;
+  }
+  return pool;
+}
+
+static inline void to_scheduler(Runner* r) {
+#if EMUL_FAST_SWITCH
+  emul_switch_stack(&r->sp[r->cur], r->main_sp);
+#else
+  swapcontext(&r->ctx[r->cur], &r->main);
+#endif
+}
+
 static void trampoline() {
   Runner* r = g_runner;
   (*r->body)();
   r->done[r->cur] = 1;
-  swapcontext(&r->ctx[r->cur], &r->main);
+  to_scheduler(r);                 // never resumed
+  abort();
 }
 
-static inline void barrier() {
-  Runner* r = g_runner;
-  swapcontext(&r->ctx[r->cur], &r->main);
-}
+static inline void barrier() { to_scheduler(g_runner); }
 
 // One CTA of `nthreads` threads running `body` (the kernel call) to completion.
 static void run_block(int nthreads, const std::function<void()>& body) {
   Runner r;
-  r.ctx.resize(nthreads);
-  r.stacks.resize((size_t)nthreads * kStackBytes);
+  r.stacks = stack_pool((size_t)nthreads * kStackBytes + 64);
   r.done.assign(nthreads, 0);
   r.body = &body;
   g_runner = &r;
   blockDim = {(unsigned)nthreads, 1, 1};
+#if EMUL_FAST_SWITCH
+  r.sp.resize(nthreads);
+  for (int t = 0; t < nthreads; ++t) {
+    // initial frame, low to high: r15 r14 r13 r12 rbx rbp | return address = trampoline | a null caller; the top is
+    // 16-byte aligned, so the trampoline starts with rsp = top - 8 like any function entered by a call
+    uintptr_t top = reinterpret_cast<uintptr_t>(r.stacks + (size_t)(t + 1) * kStackBytes) & ~(uintptr_t)15;
+    void** frame = reinterpret_cast<void**>(top) - 8;
+    for (int i = 0; i < 6; ++i) frame[i] = nullptr;
+    frame[6] = reinterpret_cast<void*>(&trampoline);
+    frame[7] = nullptr;
+    r.sp[t] = frame;
+  }
+#else
+  r.ctx.resize(nthreads);
   for (int t = 0; t < nthreads; ++t) {
     getcontext(&r.ctx[t]);
-    r.ctx[t].uc_stack.ss_sp = r.stacks.data() + (size_t)t * kStackBytes;
+    r.ctx[t].uc_stack.ss_sp = r.stacks + (size_t)t * kStackBytes;
     r.ctx[t].uc_stack.ss_size = kStackBytes;
     r.ctx[t].uc_link = &r.main;
     makecontext(&r.ctx[t], trampoline, 0);
   }
+#endif
   bool alive = true;
   while (alive) {
     alive = false;
@@ -86,7 +156,11 @@ static void run_block(int nthreads, const std::function<void()>& body) {
       if (r.done[t]) continue;
       r.cur = t;
       threadIdx = {(unsigned)t, 0, 0};
+#if EMUL_FAST_SWITCH
+      emul_switch_stack(&r.main_sp, r.sp[t]);
+#else
       swapcontext(&r.main, &r.ctx[t]);
+#endif
       if (!r.done[t]) alive = true;
     }
   }

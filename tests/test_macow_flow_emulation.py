@@ -213,3 +213,15 @@ def test_coupling_rows_beyond_one_tile_and_workspace_passes(emulated, Hd):
     # a workspace smaller than one sample is refused
     assert emulated.ipoke_macow_nice(ctypes.byref(d), packed.ctypes.data, back.ctypes.data, C * H * W, None, 1, B, H, W,
                                      ws.ctypes.data, per_sample - 1, None) != 0
+
+
+def test_gpu_test_functions_run_through_the_emulation(emulated, monkeypatch):
+    """The GPU parity tests themselves (tests/test_zy_gpu_macow_flow.py), device swapped for the CPU emulation: what the
+    B200 run asserts is asserted here first (their larger shapes take minutes in the numpy oracle and stay GPU-only)."""
+    import test_zy_gpu_macow_flow as G
+    monkeypatch.setattr(G, "DEV", torch.device("cpu"))
+    emulated.emul_set_descending(1)
+    G.test_conditional_flow_reference_fixture()
+    G.test_components_called_like_the_reference_calls_them()
+    G.test_first_call_initialisation_matches_reference()
+    G.test_against_float64_oracle(12, 20, 4, [2], 5, 7, 3, "leaky_relu", None, monkeypatch)

@@ -18,6 +18,7 @@ from test_macow_flow_emulation import load
 
 pytestmark = pytest.mark.gpu
 TOL_FWD, TOL_REV = 2e-5, 2e-4
+DEV = torch.device("cuda:0")       # tests/test_macow_flow_emulation.py re-runs some of these functions on its CPU emulation
 
 
 def make(cfg, sd, dev):
@@ -28,7 +29,7 @@ def make(cfg, sd, dev):
 
 @pytest.mark.parametrize("name", ["macow_stack_a", "macow_stack_b"])
 def test_reference_fixtures(name):
-    dev = torch.device("cuda:0")
+    dev = DEV
     g, sd, cfg = load(name)
     net = make(cfg, sd, dev)
     x = torch.from_numpy(g["x"]).to(dev)
@@ -46,7 +47,7 @@ def test_reference_fixtures(name):
 
 
 def test_components_called_like_the_reference_calls_them():
-    dev = torch.device("cuda:0")
+    dev = DEV
     g, sd, cfg = load("macow_stack_a")
     net = make(cfg, sd, dev)
     x, z = torch.from_numpy(g["x"]).to(dev), torch.from_numpy(g["z_in"]).to(dev)
@@ -66,7 +67,7 @@ def test_components_called_like_the_reference_calls_them():
 
 
 def test_first_call_initialisation_matches_reference():
-    dev = torch.device("cuda:0")
+    dev = DEV
     g, sd, cfg = load("macow_stack_b")
     torch.manual_seed(42)
     net = P.UnsupervisedMaCowTransformer3(cfg).to(dev).eval()
@@ -83,7 +84,7 @@ def test_first_call_initialisation_matches_reference():
 def test_conditional_flow_reference_fixture():
     """SupervisedMacowTransformer (INN.py:447-482, condition_nice false): forward / inverse with the conditioning, a
     conditional unit and a step on their own, the first-call initialisation."""
-    dev = torch.device("cuda:0")
+    dev = DEV
     g, sd, cfg = load("macow_stack_c")
     x, z, h = (torch.from_numpy(g[k]).to(dev) for k in ("x", "z_in", "h"))
     torch.manual_seed(42)
@@ -118,7 +119,7 @@ def test_conditional_flow_reference_fixture():
 def test_conditional_flow_against_float64_oracle():
     """z_dim-32 latents at 8 x 8 with 128 conditioning channels (conditioner + poke embedding), batch 20 (the reference's
     test batch): two conditional unit chains per step, 1024-column conditioning product."""
-    dev = torch.device("cuda:0")
+    dev = DEV
     C, hc, B, H, W = 32, 128, 20, 8, 8
     cfg = dict(num_steps=[1], flow_in_channels=C, flow_mid_channels=64, factor=16, transform="affine",
                prior_transform="affine", kernel_size=[2, 3], coupling_type="conv", activation="elu", h_channels=hc,
@@ -167,7 +168,7 @@ SHAPES = [  # channels, hidden of the couplings, factor, num_steps, H, W, batch,
 
 @pytest.mark.parametrize("C,mid,factor,steps,H,W,B,act,mb", SHAPES)
 def test_against_float64_oracle(C, mid, factor, steps, H, W, B, act, mb, monkeypatch):
-    dev = torch.device("cuda:0")
+    dev = DEV
     if mb is not None:
         monkeypatch.setenv("IPOKE_MACOW_NICE_MB", mb)
     cfg = dict(num_steps=steps, flow_in_channels=C, flow_mid_channels=mid, factor=factor, transform="affine",
@@ -198,7 +199,7 @@ def test_inn_test_stack_against_float64_restatement():
     from float64 here, measured on the CPU), 2e-4 for the round trip (float64 itself: 1e-5, every ActNorm2dFlow inverse
     divides by exp(log_scale) + 1e-8)."""
     from oracle.macow_stack_oracle_torch import TorchFlow
-    dev = torch.device("cuda:0")
+    dev = DEV
     cfg = dict(num_steps=[20, 8, 5, 5, 3, 3, 1], flow_in_channels=8, flow_mid_channels=1536, factor=8, transform="affine",
                prior_transform="affine", kernel_size=[2, 3], coupling_type="conv", activation="elu")
     torch.manual_seed(1)
@@ -228,7 +229,7 @@ def test_inn_test_stack_against_float64_restatement():
 
 
 def test_large_batch_round_trip_and_sample():
-    dev = torch.device("cuda:0")
+    dev = DEV
     cfg = dict(num_steps=[1, 1], flow_in_channels=8, flow_mid_channels=64, factor=4, transform="affine",
                prior_transform="affine", kernel_size=[2, 3], coupling_type="conv", activation="elu")
     torch.manual_seed(3)
