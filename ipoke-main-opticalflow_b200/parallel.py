@@ -41,6 +41,8 @@ def broadcast_parameters(module, src=0, group=None):
     eng = getattr(flow, "engine", None)
     if eng is not None:
         eng.invalidate()
+    elif hasattr(flow, "invalidate"):          # MaCow flows: writes through .data do not bump the version counters
+        flow.invalidate()                      # their packed segments are keyed on
 
 
 class GradSync:

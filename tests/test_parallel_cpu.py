@@ -155,3 +155,47 @@ def test_sharded_oracle_equals_single_process():
     key = "flow.sub_layers.5.coupling.t.1.main.2.weight"
     assert np.allclose(outs[0][2], d["grad::" + key], rtol=1e-4, atol=1e-7)
     assert np.allclose(outs[0][2], outs[1][2])
+
+
+def _macow_sharded(rank, world):
+    """MaCow flow, batch-sharded over 2 ranks through the CPU emulation of its C ABI: rank 0 runs the data-dependent
+    first call, its parameters are broadcast, every rank transforms its shard -- no collective on the data path."""
+    import ctypes
+    import ipoke_inn_b200 as P
+    from ipoke_inn_b200 import macow
+    from ipoke_inn_b200.parallel import broadcast_parameters, shard_batch
+    import test_macow_flow_emulation as E
+    L = macow._bind(ctypes.CDLL(E.OUT))
+    macow._lib, macow._stream = (lambda: L), (lambda dev: None)
+    macow._check_input = lambda x, channels: x.contiguous()
+    g, sd, cfg = E.load("macow_stack_a")
+    torch.manual_seed(100 + rank)                                  # ranks start with different parameters
+    net = P.UnsupervisedMaCowTransformer3(cfg).eval()
+    x = torch.from_numpy(np.concatenate([g["x"], g["z_in"]]))      # the same 6-sample batch on every rank
+    with torch.no_grad():
+        net(x if rank == 0 else x + 1.0)                           # first call: every rank initialises on ITS data and
+        if rank == 0:                                              # packs its own parameters ...
+            for k, p in net.state_dict().items():                  # (rank 0: non-trivial couplings)
+                if k.endswith("weight_g"):
+                    p.fill_(0.2)
+        broadcast_parameters(net)                                  # ... which rank 0's state replaces, incl. the
+                                                                   # `initialized` flags and permutations; stale packs dropped
+        mine = shard_batch(x, rank=rank, world=world)
+        z, ld = net(mine)
+        whole = net(x) if rank == 0 else None
+    return (z.numpy(), ld.numpy(), None if whole is None else (whole[0].numpy(), whole[1].numpy()),
+            {k: v.numpy() for k, v in net.state_dict().items() if k.endswith(("log_scale", "shuffle_idx"))})
+
+
+def test_macow_flow_shards_without_a_collective():
+    import test_macow_flow_emulation as E
+    import subprocess
+    os.makedirs(os.path.dirname(E.OUT), exist_ok=True)
+    if not os.path.exists(E.OUT) or os.path.getmtime(E.OUT) < max(os.path.getmtime(f) for f in E.DEPS):
+        subprocess.run(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-Wno-attributes",
+                        "-I", os.path.join(ROOT, "include"), "-o", E.OUT, E.SRC], check=True)
+    (z0, l0, whole, s0), (z1, l1, _, s1) = _run(_macow_sharded)
+    for k in s0:
+        assert np.array_equal(s0[k], s1[k]), k                     # rank 1 took rank 0's initialisation and permutations
+    np.testing.assert_allclose(np.concatenate([z0, z1]), whole[0], rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(np.concatenate([l0, l1]), whole[1], rtol=1e-6, atol=1e-5)
