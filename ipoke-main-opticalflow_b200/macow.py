@@ -97,6 +97,28 @@ def _check_input(x, channels):
     return x.contiguous()
 
 
+def _invalidate_after_load(module, incompatible):
+    """load_state_dict post hook (a module-level function, so that modules stay picklable)."""
+    module.invalidate()
+
+
+class ProgramOwner:
+    """Mixin of the modules that run through a lazily built ``macow_flow.Program``: the program (packed parameters,
+    workspaces) is not part of a copy or a pickle -- ``copy.deepcopy`` / ``torch.save(module)`` carry the parameters and
+    buffers, the copy rebuilds its program at its first call."""
+
+    def __getstate__(self):
+        state = self.__dict__.copy()
+        state["_program"] = None
+        return state
+
+    def invalidate(self):
+        """Force a repack and a re-read of the ``initialized`` flags (needed after writing parameters through ``.data``,
+        which the version counters used to detect changes do not see)."""
+        if getattr(self, "_program", None) is not None:
+            self._program.invalidate()
+
+
 class ShiftedConv2d(nn.Module):
     """Parameter holder of macow_utils.py:439-497 (``weight`` [hidden, C, kH, kW], no bias in MCFBlock)."""
 
@@ -209,7 +231,7 @@ class MaskedConvFlow(nn.Module):
                             h_channels=h_channels if self.cond else None, p_dropout=p_dropout)
 
 
-class MaCowUnit(nn.Module):
+class MaCowUnit(ProgramOwner, nn.Module):
     """Drop-in for macow2.py:925-996: ``forward(input, h=None, reverse=False)`` returns ``(out, logdet)`` or,
     with ``reverse=True``, the inverse image.  One kernel launch per call (one CTA per sample); a conditional unit
     (``h_channels > 0``, conditioning ``h`` [B, h_channels, H, W]) adds the launch of its conditioning product."""
@@ -237,13 +259,14 @@ class MaCowUnit(nn.Module):
         self._packed = None
         self._packed_key = None
         self._init_checked = False
-        self.register_load_state_dict_post_hook(lambda module, incompatible: module.invalidate())
+        self.register_load_state_dict_post_hook(_invalidate_after_load)
 
     def invalidate(self):
         """Force a repack and a re-read of the ``initialized`` flags on the next call.  Needed only after writing
         parameters through ``.data`` (which the version counters used to detect changes do not see)."""
         self._packed_key = None
         self._init_checked = False
+        ProgramOwner.invalidate(self)
 
     # ---- parameters -> packed kernel layout
     def _param_list(self):

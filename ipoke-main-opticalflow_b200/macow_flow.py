@@ -26,7 +26,8 @@ import torch.nn as nn
 from . import _capi
 from . import macow as _m
 from ._nvtx import annotate
-from .macow import ACTIVATIONS, ActNorm2dFlow, Conv2dWeightNorm, MaCowUnit, NiceDesc
+from .macow import (ACTIVATIONS, ActNorm2dFlow, Conv2dWeightNorm, MaCowUnit, NiceDesc, ProgramOwner,
+                    _invalidate_after_load)
 from .modules import Shuffle
 
 
@@ -58,7 +59,7 @@ class NICEConvBlock(nn.Module):
         raise RuntimeError("NICEConvBlock is a parameter container here: the coupling runs fused through NICE2d")
 
 
-class NICE2d(nn.Module):
+class NICE2d(ProgramOwner, nn.Module):
     """macow2.py:291-437 with the 'affine' transform.  ``forward(input, h=None, reverse=False)`` returns
     ``(out, logdet)`` or the inverse image, like the reference; inside a flow it is called through the flow's program."""
 
@@ -95,6 +96,7 @@ class NICE2d(nn.Module):
             geo = (c_in, 0, 2, c_t, 1, 2) if self.up else (c_in, 1, 2, c_t, 0, 2)
         self._desc = NiceDesc(*geo, hidden_channels, ACTIVATIONS[activation], alpha)
         self._program = None
+        self.register_load_state_dict_post_hook(_invalidate_after_load)
 
     def params(self):
         n = self.net
@@ -107,7 +109,7 @@ class NICE2d(nn.Module):
         return self._program.run(input, reverse)
 
 
-class MaCowStep(nn.Module):
+class MaCowStep(ProgramOwner, nn.Module):
     """macow2.py:999-1117."""
 
     def __init__(self, in_channels, kernel_size, hidden_channels, h_channels, transform="affine", alpha=1.0,
@@ -139,6 +141,7 @@ class MaCowStep(nn.Module):
         self.coupling2_up = NICE2d(in_channels, split_type="skip", order="up", **nice_kw)
         self.coupling2_dn = NICE2d(in_channels, split_type="skip", order="down", **nice_kw)
         self._program = None
+        self.register_load_state_dict_post_hook(_invalidate_after_load)
 
     def ops(self):
         """The step as forward kernel calls (macow2.py:1063-1091)."""
@@ -154,7 +157,7 @@ class MaCowStep(nn.Module):
         return self._program.run(input, reverse, h)
 
 
-class MultiScalePrior(nn.Module):
+class MultiScalePrior(ProgramOwner, nn.Module):
     """macow2.py:543-594."""
 
     def __init__(self, in_channels, hidden_channels, h_channels, factor, transform, alpha, coupling_type, h_type,
@@ -174,6 +177,7 @@ class MultiScalePrior(nn.Module):
         assert out_channels + self.z1_channels == in_channels
         self.actnorm = ActNorm2dFlow(out_channels)
         self._program = None
+        self.register_load_state_dict_post_hook(_invalidate_after_load)
 
     def ops(self, level_shuffle=None):
         """Forward calls (macow2.py:571-582); ``level_shuffle`` folds the permutation that follows the prior in
@@ -191,7 +195,7 @@ class MultiScalePrior(nn.Module):
         return self._program.run(input, reverse)
 
 
-class MultiScaleInternal(nn.Module):
+class MultiScaleInternal(ProgramOwner, nn.Module):
     """macow2.py:821-918."""
 
     def __init__(self, flow_step, num_steps, in_channels, hidden_channels, h_channels, factor=2, transform="affine",
@@ -233,6 +237,7 @@ class MultiScaleInternal(nn.Module):
             factor = factor - 1
         self.z_channels = in_channels
         self._program = None
+        self.register_load_state_dict_post_hook(_invalidate_after_load)
 
     def ops(self):
         ops = []
@@ -246,11 +251,6 @@ class MultiScaleInternal(nn.Module):
         if self._program is None:
             self._program = Program(self.ops(), self.in_channels, [self])
         return self._program.run(input, reverse, h)
-
-    def invalidate(self):
-        """Force a repack and a re-read of the ``initialized`` flags (after writing parameters through ``.data``)."""
-        if self._program is not None:
-            self._program.invalidate()
 
 
 class Program:
@@ -270,8 +270,6 @@ class Program:
         self.ws_need = {}                         # (B, H, W) -> workspace floats of the widest coupling
         self.hb = None
         self.h_channels = max([op[1][0].h_channels for op in ops if op[0] == "units"] + [0])
-        for r in roots:
-            r.register_load_state_dict_post_hook(lambda module, incompatible, self=self: self.invalidate())
 
     def invalidate(self):
         self.packed = [None] * len(self.ops)

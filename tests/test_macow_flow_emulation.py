@@ -225,3 +225,34 @@ def test_gpu_test_functions_run_through_the_emulation(emulated, monkeypatch):
     G.test_components_called_like_the_reference_calls_them()
     G.test_first_call_initialisation_matches_reference()
     G.test_against_float64_oracle(12, 20, 4, [2], 5, 7, 3, "leaky_relu", None, monkeypatch)
+
+
+def test_copy_and_pickle_rebuild_the_program(emulated):
+    """copy.deepcopy / torch.save(module) of a flow that has already run: the copy carries parameters and buffers, not the
+    packed program, and computes the same result; broadcast-style writes through .data need invalidate()."""
+    import copy
+    import io
+    g, sd, cfg = load("macow_stack_c")
+    net = P.SupervisedMacowTransformer(cfg).eval()
+    net.load_state_dict(sd)
+    x, h = torch.from_numpy(g["x"]), torch.from_numpy(g["h"])
+    with torch.no_grad():
+        want, want_ld = net(x, h)
+        assert net.flow._program is not None
+        twin = copy.deepcopy(net)
+        assert twin.flow._program is None and net.flow._program is not None
+        buf = io.BytesIO()
+        torch.save(net, buf)
+        buf.seek(0)
+        loaded = torch.load(buf, weights_only=False)
+        for other in (twin, loaded):
+            out, ld = other(x, h)
+            assert torch.equal(out, want) and torch.equal(ld, want_ld)
+        # a write through .data is invisible to the version keys until invalidate()
+        unit = net.flow.layers[0][0].units1[0]
+        unit.conv1.net.conv1x1.conv.bias.data.add_(0.5)
+        stale, _ = net(x, h)
+        assert torch.equal(stale, want)
+        net.flow.invalidate()
+        fresh, _ = net(x, h)
+        assert not torch.equal(fresh, want)
