@@ -459,6 +459,9 @@ class Program:
             raise NotImplementedError("the MaCow path is inference only: call it under torch.no_grad()")
         x = _m._check_input(input, self.channels)
         B, C, H, W = x.shape
+        where = next(self.roots[0].parameters()).device
+        if where != x.device:                                  # the kernels would dereference the other device's pointers
+            raise RuntimeError(f"module parameters are on {where}, the input is on {x.device}")
         h = self._check_h(h, x)
         buf = x.clone() if x.data_ptr() == input.data_ptr() else x
         stride = C * H * W
